@@ -1,0 +1,180 @@
+/*
+ * qec_b200.h -- C ABI of libqecb200.so: B200-native (sm_100a) Pauli-frame fault analysis.
+ *
+ * This is the drop-in boundary for the hot path of qiskit-qec's `analysis` package:
+ * what the reference's pybind11 module `qiskit_qec.analysis._c_analysis`
+ * (reference src/qiskit_qec/analysis/bindings/analysis_bindings.cpp:12-54) binds as
+ * C++ classes is exposed here as opaque handles + plain pointers and sizes.
+ * No torch / pybind / STL types appear in any signature.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative qec_status; the message is
+ *     available from qec_last_error() (thread local).  The messages for conditions the
+ *     reference also checks are the reference's own strings (see each function).
+ *   - "host" pointers are ordinary (ideally pinned) host memory; "_dev" entry points
+ *     take device pointers on the handle's device and a cudaStream_t passed as void*
+ *     (NULL = the legacy default stream) and are asynchronous.
+ *   - the library never retains a caller pointer past the call.
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry
+ *     point fails with QEC_ERR_CUDA.
+ *
+ * Packed outcome layout ("bit-sliced"): uint32 out[nc][n_words], n_words = ceil(n/32);
+ *   bit b of out[c*n_words + w] is outcome bit c (clbit c flipped?) of path/shot
+ *   lo + 32*w + b.  Bits past the end of the range are 0.
+ * Tally layout: uint64 tally[QEC_TALLY_LEN(nc)]:
+ *   [0..nc)        number of paths whose outcome bit c is 1 (per-clbit marginals)
+ *   [nc]           number of paths with any outcome bit set
+ *   [nc+1]         number of paths processed
+ *   [nc+2..nc+66)  histogram of faults per shot (sampler only; last bin = ">=63")
+ * Pauli code (4 bits) for a fault on an op with qubits (a, b):
+ *   bit0: X on a, bit1: Z on a, bit2: X on b, bit3: Z on b  (b only for cx: a=control,
+ *   b=target; reference errorpropagator.cpp:179-206).  'y' = X|Z, 'i'/anything else = 0.
+ */
+#ifndef QEC_B200_H
+#define QEC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QEC_TALLY_HIST_BINS 64
+#define QEC_TALLY_LEN(nc) ((size_t)(nc) + 2 + QEC_TALLY_HIST_BINS)
+#define QEC_MAX_ORDER 8
+#define QEC_MAX_QUBITS 16384
+#define QEC_MAX_CLBITS 16384
+
+typedef enum qec_status {
+  QEC_OK = 0,
+  QEC_ERR_LOGIC = -1,    /* reference std::logic_error   -> Python RuntimeError */
+  QEC_ERR_INVALID = -2,  /* reference std::invalid_argument -> Python ValueError */
+  QEC_ERR_CUDA = -3,     /* CUDA failure / no device / extension unusable -> RuntimeError */
+  QEC_ERR_LIMIT = -4,    /* size beyond what this library encodes -> RuntimeError */
+  QEC_ERR_OVERFLOW = -5  /* internal: sampler event buffer overflow (retried internally) */
+} qec_status;
+
+typedef struct qec_circuit qec_circuit;       /* compiled circuit IR, resident on one GPU */
+typedef struct qec_enumerator qec_enumerator; /* FaultEnumerator state on one GPU */
+typedef struct qec_sampler qec_sampler;       /* FaultSampler state on one GPU */
+
+/* ---- library ------------------------------------------------------------------------- */
+const char *qec_last_error(void);
+const char *qec_version(void);
+/* number of visible CUDA devices (0 if none / driver missing; never fails) */
+int qec_device_count(void);
+/* Dependent-free INT32 logic-op (LOP3) throughput of `device` in lane-ops/s: the
+ * integer-pipe roofline denominator of SURVEY.md 8(d).  Runs ~`ms` milliseconds. */
+int qec_measure_int_peak(int device, double ms, double *lane_ops_per_s, double *sm_clock_mhz);
+
+/* ---- circuit IR: replaces ErrorPropagator::load_circuit ------------------------------
+ * (reference src/qiskit_qec/analysis/intern/errorpropagator.cpp:103-149)
+ * rows are the reference's `encoded_circ` in CSR form: row i = row_data[row_off[i]..row_off[i+1]).
+ * Validation and messages as the reference: "bad 1-qubit instruction", "bad measure
+ * instruction", "bad cx instruction", "bad barrier instruction", "bad opcode",
+ * "qubit index out of range", "bit index out of range" (all QEC_ERR_LOGIC).
+ * The IR is lowered to a flat packed gate table and uploaded to `device` once. */
+int qec_circuit_create(int device, int nq, int nc, int n_ops, const int32_t *row_off,
+                       const int32_t *row_data, qec_circuit **out);
+void qec_circuit_destroy(qec_circuit *c);
+int qec_circuit_sizes(const qec_circuit *c, int *nq, int *nc, int *n_ops);
+/* W_bit of SURVEY.md 8(d) for this circuit (2 n_cx + 2 n_h + n_s + 2 n_reset + n_measure) */
+int64_t qec_circuit_bit_ops(const qec_circuit *c);
+
+/* ---- K1: batched ErrorPropagator::propagate -------------------------------------------
+ * (reference errorpropagator.cpp:259-313)  path p injects faults
+ * (fault_op[j], fault_pauli[j]) for j in [path_off[p], path_off[p+1]).  Duplicate op
+ * indices inside one path: the LAST one wins, as in the reference (:265-267).
+ * fault_op out of [0, n_ops) is rejected (the reference leaves it undefined).
+ * out_bits: host uint32[nc][ceil(n_paths/32)]; out_frame (may be NULL): host
+ * uint32[2*nq][ceil(n_paths/32)], final X frame rows then Z frame rows. */
+int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_t *path_off,
+                        const int32_t *fault_op, const uint8_t *fault_pauli,
+                        uint32_t *out_bits, uint32_t *out_frame);
+
+/* ---- K2: FaultEnumerator ---------------------------------------------------------------
+ * (reference src/qiskit_qec/analysis/intern/faultenumerator.cpp:6-24,71-111)
+ * L fault locations; location l sits on op loc_op[l] and offers the Pauli codes
+ * pauli_codes[pauli_off[l]..pauli_off[l+1]) in product-digit order.
+ * Path order = the reference's: k-subsets of locations in lexicographic order, inside a
+ * subset the mixed-radix product with the LAST location fastest
+ * (combinations.cpp:18-32, productiterator.cpp:17-32); path index = rank in that order.
+ * Errors as the reference's Combinations/ProductIterator constructors:
+ * "n must be positive", "0 <= k <= n", "each element must be positive" (QEC_ERR_INVALID). */
+int qec_enumerator_create(qec_circuit *c, int order, int L, const int32_t *loc_op,
+                          const int32_t *pauli_off, const uint8_t *pauli_codes,
+                          qec_enumerator **out);
+void qec_enumerator_destroy(qec_enumerator *e);
+/* total number of fault paths (fails with QEC_ERR_LIMIT if >= 2^62) */
+int qec_enumerator_num_paths(const qec_enumerator *e, int64_t *n);
+/* rank -> (locations[order], digits[order]); host-side closed form of what the kernel does */
+int qec_enumerator_unrank(const qec_enumerator *e, int64_t index, int32_t *locs, int32_t *digits);
+/* first path index of the subset `locs` and its number of paths */
+int qec_enumerator_subset_rank(const qec_enumerator *e, const int32_t *locs, int64_t *first,
+                               int64_t *count);
+/* propagate paths [lo, hi): out_bits host uint32[nc][ceil((hi-lo)/32)] (may be NULL),
+ * tally host uint64[QEC_TALLY_LEN(nc)] (may be NULL; overwritten, not accumulated) */
+int qec_enumerator_range(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *out_bits,
+                         uint64_t *tally);
+/* same with device pointers, asynchronous on `stream`; d_tally is ACCUMULATED into
+ * (zero it first) so it can be the send buffer of a following all-reduce */
+int qec_enumerator_range_dev(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_out_bits,
+                             uint64_t *d_tally, void *stream);
+
+/* ---- K3: FaultSampler ------------------------------------------------------------------
+ * (reference src/qiskit_qec/analysis/intern/faultsampler.cpp:6-32,49-77)
+ * Location l belongs to class (label) loc_class[l] in [0, n_classes); class k fails with
+ * probability class_p[k] per shot and then draws digit d with probability proportional to
+ * class_weight[class_off[k] + d]; digit d injects class_codes[class_off[k] + d].
+ * RNG: Philox4x32-10 keyed by `seed`, counter = (global 32-shot word index, draw index);
+ * results depend only on (seed, global shot id), never on grid shape or GPU count.
+ * Every probability is realised to within 2^-31 absolute (32-bit fixed point tables). */
+int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op, const int32_t *loc_class,
+                       int n_classes, const double *class_p, const int32_t *class_off,
+                       const uint8_t *class_codes, const double *class_weight, uint64_t seed,
+                       qec_sampler **out);
+void qec_sampler_destroy(qec_sampler *s);
+/* shots [shot_lo, shot_lo + n_shots); shot_lo must be a multiple of 32.
+ * out_bits host uint32[nc][ceil(n/32)] (may be NULL); tally host (may be NULL; overwritten);
+ * fault export (all three NULL or all non-NULL): fault_cnt host uint32[ceil(n/32)] = events
+ * of each 32-shot word, fault_ev host uint32[ceil(n/32)][fault_cap], event =
+ * location << 14 | shot_bit << 9 | digit, sorted by op order; *fault_cap_needed receives the
+ * largest count seen (if > fault_cap the lists are truncated and QEC_ERR_LIMIT is returned). */
+int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint32_t *out_bits,
+                       uint64_t *tally, uint32_t *fault_cnt, uint32_t *fault_ev, int fault_cap,
+                       int *fault_cap_needed);
+int qec_sampler_sample_dev(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                           uint32_t *d_out_bits, uint64_t *d_tally, void *stream);
+/* asynchronous sample_dev calls cannot report an event-buffer overflow (probability < 1e-20
+ * per word with the default sizing); this checks for one: QEC_ERR_OVERFLOW means the last
+ * batch of sample_dev results is invalid and must be re-run (the buffer has been grown). */
+int qec_sampler_check(qec_sampler *s);
+/* the fixed-point tables the sampler realises (for an independent CPU restatement to
+ * consume): writes up to `cap` uint32 and returns the count in *n.  Layout documented in
+ * DESIGN.md "sampler tables". */
+int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, int *n);
+
+/* ---- K4: full-outcome histogram over a packed outcome buffer --------------------------
+ * Counts distinct outcomes of n paths held bit-sliced on the device of `c`.
+ * Open-addressed table of `table_cap` (power of two) 64-bit outcome hashes + counts. */
+int qec_outcome_histogram_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                              uint64_t *d_keys, uint64_t *d_counts, int64_t table_cap,
+                              void *stream);
+
+/* ---- device memory helpers (so a ctypes/cgo caller needs no CUDA binding) ------------- */
+int qec_dev_alloc(int device, size_t bytes, void **out);
+int qec_dev_free(int device, void *p);
+int qec_dev_memset(int device, void *p, int value, size_t bytes, void *stream);
+int qec_dev_to_host(int device, void *host, const void *dev, size_t bytes, void *stream);
+int qec_host_to_dev(int device, void *dev, const void *host, size_t bytes, void *stream);
+int qec_host_alloc_pinned(size_t bytes, void **out);
+int qec_host_free_pinned(void *p);
+int qec_stream_sync(int device, void *stream);
+/* elapsed device time (ms) of the last *_dev / host call on handle, via CUDA events */
+int qec_last_kernel_ms(int device, float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QEC_B200_H */

@@ -1,0 +1,289 @@
+"""ctypes binding of ``libqecb200.so`` -- the C ABI declared in ``include/qec_b200.h``.
+
+Thin by design: numpy arrays in, numpy arrays out, one Python method per C entry point.
+There is no fallback: if the shared library is missing or no CUDA device is usable the
+calls raise.  Status codes map to the exception types pybind11 gives the reference's C++
+exceptions (``std::logic_error`` -> RuntimeError, ``std::invalid_argument`` -> ValueError;
+SURVEY.md 8(b) "Error conventions").
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libqecb200.so")
+
+QEC_ERR_LOGIC, QEC_ERR_INVALID, QEC_ERR_CUDA, QEC_ERR_LIMIT, QEC_ERR_OVERFLOW = -1, -2, -3, -4, -5
+TALLY_HIST_BINS = 64
+
+# every symbol include/qec_b200.h declares (checked by tests/test_capi_symbols.py)
+SYMBOLS = [
+    "qec_last_error", "qec_version", "qec_device_count", "qec_measure_int_peak",
+    "qec_circuit_create", "qec_circuit_destroy", "qec_circuit_sizes", "qec_circuit_bit_ops",
+    "qec_propagate_batch",
+    "qec_enumerator_create", "qec_enumerator_destroy", "qec_enumerator_num_paths",
+    "qec_enumerator_unrank", "qec_enumerator_subset_rank", "qec_enumerator_range",
+    "qec_enumerator_range_dev",
+    "qec_sampler_create", "qec_sampler_destroy", "qec_sampler_sample", "qec_sampler_sample_dev",
+    "qec_sampler_check", "qec_sampler_tables",
+    "qec_outcome_histogram_dev",
+    "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
+    "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
+]
+
+_lib = None
+
+
+def tally_len(nc: int) -> int:
+    return nc + 2 + TALLY_HIST_BINS
+
+
+def lib() -> C.CDLL:
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.qec_last_error.restype = C.c_char_p
+        L.qec_version.restype = C.c_char_p
+        L.qec_circuit_bit_ops.restype = C.c_int64
+        L.qec_circuit_bit_ops.argtypes = [C.c_void_p]
+        L.qec_circuit_destroy.restype = None
+        L.qec_circuit_destroy.argtypes = [C.c_void_p]
+        L.qec_enumerator_destroy.restype = None
+        L.qec_enumerator_destroy.argtypes = [C.c_void_p]
+        L.qec_sampler_destroy.restype = None
+        L.qec_sampler_destroy.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc == 0:
+        return
+    msg = lib().qec_last_error().decode()
+    if rc == QEC_ERR_INVALID:
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def _p(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _i32(x) -> np.ndarray:
+    return np.ascontiguousarray(x, dtype=np.int32)
+
+
+def device_count() -> int:
+    return int(lib().qec_device_count())
+
+
+def measure_int_peak(device: int = 0, ms: float = 50.0) -> Tuple[float, float]:
+    """(INT32 logic lane-ops/s, nominal SM clock MHz) of ``device``."""
+    ops, mhz = C.c_double(), C.c_double()
+    _check(lib().qec_measure_int_peak(C.c_int(device), C.c_double(ms), C.byref(ops), C.byref(mhz)))
+    return ops.value, mhz.value
+
+
+def last_kernel_ms(device: int = 0) -> float:
+    ms = C.c_float()
+    _check(lib().qec_last_kernel_ms(C.c_int(device), C.byref(ms)))
+    return ms.value
+
+
+def rows_to_csr(encoded_circ: Sequence[Sequence[int]]) -> Tuple[np.ndarray, np.ndarray]:
+    off = np.zeros(len(encoded_circ) + 1, dtype=np.int32)
+    for i, row in enumerate(encoded_circ):
+        off[i + 1] = off[i] + len(row)
+    data = np.fromiter((v for row in encoded_circ for v in row), dtype=np.int32, count=int(off[-1]))
+    return off, data
+
+
+_PAULI_BITS = {"x": 1, "y": 3, "z": 2}
+
+
+def pauli_code(pauli: str) -> int:
+    """4-bit code of a Pauli string: char 0 -> operand a, char 1 -> operand b
+    (reference errorpropagator.cpp:179-206; unknown characters and 'i' are identity)."""
+    code = 0
+    if len(pauli) > 0:
+        code |= _PAULI_BITS.get(pauli[0], 0)
+    if len(pauli) > 1:
+        code |= _PAULI_BITS.get(pauli[1], 0) << 2
+    return code
+
+
+class Circuit:
+    """``qec_circuit``: the compiled circuit IR resident on one GPU."""
+
+    def __init__(self, nq: int, nc: int, encoded_circ: Sequence[Sequence[int]], device: int = 0):
+        self.nq, self.nc, self.n_ops, self.device = int(nq), int(nc), len(encoded_circ), int(device)
+        off, data = rows_to_csr(encoded_circ)
+        h = C.c_void_p()
+        _check(lib().qec_circuit_create(C.c_int(device), C.c_int(nq), C.c_int(nc),
+                                        C.c_int(self.n_ops), _p(off), _p(data), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().qec_circuit_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def bit_ops(self) -> int:
+        return int(lib().qec_circuit_bit_ops(self._h))
+
+    def propagate_batch(self, path_off, fault_op, fault_pauli, want_frame: bool = False):
+        """K1.  Returns packed outcomes uint32[nc][n_words] (and the final frame if asked)."""
+        path_off = np.ascontiguousarray(path_off, dtype=np.int64)
+        fault_op = _i32(fault_op)
+        fault_pauli = np.ascontiguousarray(fault_pauli, dtype=np.uint8)
+        n = len(path_off) - 1
+        nw = (n + 31) // 32
+        out = np.zeros((self.nc, nw), dtype=np.uint32)
+        frame = np.zeros((2 * self.nq, nw), dtype=np.uint32) if want_frame else None
+        _check(lib().qec_propagate_batch(self._h, C.c_int64(n), _p(path_off), _p(fault_op),
+                                         _p(fault_pauli), _p(out), _p(frame)))
+        return (out, frame) if want_frame else out
+
+
+class Enumerator:
+    """``qec_enumerator``."""
+
+    def __init__(self, circuit: Circuit, order: int, loc_op, pauli_codes_per_loc):
+        self.circuit, self.order = circuit, int(order)
+        loc_op = _i32(loc_op)
+        off = np.zeros(len(loc_op) + 1, dtype=np.int32)
+        for i, codes in enumerate(pauli_codes_per_loc):
+            off[i + 1] = off[i] + len(codes)
+        flat = np.fromiter((c for codes in pauli_codes_per_loc for c in codes), dtype=np.uint8,
+                           count=int(off[-1]))
+        h = C.c_void_p()
+        _check(lib().qec_enumerator_create(circuit._h, C.c_int(order), C.c_int(len(loc_op)),
+                                           _p(loc_op), _p(off), _p(flat), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().qec_enumerator_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def num_paths(self) -> int:
+        n = C.c_int64()
+        _check(lib().qec_enumerator_num_paths(self._h, C.byref(n)))
+        return n.value
+
+    def unrank(self, index: int):
+        locs = np.zeros(self.order, dtype=np.int32)
+        digs = np.zeros(self.order, dtype=np.int32)
+        _check(lib().qec_enumerator_unrank(self._h, C.c_int64(index), _p(locs), _p(digs)))
+        return locs, digs
+
+    def subset_rank(self, locs) -> Tuple[int, int]:
+        locs = _i32(locs)
+        first, count = C.c_int64(), C.c_int64()
+        _check(lib().qec_enumerator_subset_rank(self._h, _p(locs), C.byref(first), C.byref(count)))
+        return first.value, count.value
+
+    def range(self, lo: int, hi: int, want_bits: bool = True, want_tally: bool = False):
+        nw = (max(hi - lo, 0) + 31) // 32
+        out = np.zeros((self.circuit.nc, nw), dtype=np.uint32) if want_bits else None
+        tally = np.zeros(tally_len(self.circuit.nc), dtype=np.uint64) if want_tally else None
+        _check(lib().qec_enumerator_range(self._h, C.c_int64(lo), C.c_int64(hi), _p(out), _p(tally)))
+        return out, tally
+
+    def range_dev(self, lo: int, hi: int, d_bits: int, d_tally: int, stream: int = 0):
+        _check(lib().qec_enumerator_range_dev(self._h, C.c_int64(lo), C.c_int64(hi),
+                                              C.c_void_p(d_bits or None), C.c_void_p(d_tally or None),
+                                              C.c_void_p(stream or None)))
+
+
+class Sampler:
+    """``qec_sampler``."""
+
+    def __init__(self, circuit: Circuit, loc_op, loc_class, class_p, class_codes, class_weights,
+                 seed: int):
+        self.circuit = circuit
+        loc_op, loc_class = _i32(loc_op), _i32(loc_class)
+        ncls = len(class_p)
+        off = np.zeros(ncls + 1, dtype=np.int32)
+        for i, codes in enumerate(class_codes):
+            off[i + 1] = off[i] + len(codes)
+        codes = np.fromiter((c for cs in class_codes for c in cs), dtype=np.uint8, count=int(off[-1]))
+        w = np.fromiter((x for ws in class_weights for x in ws), dtype=np.float64, count=int(off[-1]))
+        p = np.ascontiguousarray(class_p, dtype=np.float64)
+        h = C.c_void_p()
+        _check(lib().qec_sampler_create(circuit._h, C.c_int(len(loc_op)), _p(loc_op), _p(loc_class),
+                                        C.c_int(ncls), _p(p), _p(off), _p(codes), _p(w),
+                                        C.c_uint64(seed & (2**64 - 1)), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().qec_sampler_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def tables(self) -> np.ndarray:
+        n = C.c_int()
+        _check(lib().qec_sampler_tables(self._h, None, C.c_int(0), C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.uint32)
+        _check(lib().qec_sampler_tables(self._h, _p(buf), C.c_int(n.value), C.byref(n)))
+        return buf
+
+    def sample(self, shot_lo: int, n_shots: int, want_bits: bool = True, want_tally: bool = False,
+               fault_cap: int = 0):
+        """Returns (bits, tally, fault_cnt, fault_ev); absent outputs are None."""
+        nc = self.circuit.nc
+        nw = (max(n_shots, 0) + 31) // 32
+        out = np.zeros((nc, nw), dtype=np.uint32) if want_bits else None
+        tally = np.zeros(tally_len(nc), dtype=np.uint64) if want_tally else None
+        while True:
+            cnt = np.zeros(nw, dtype=np.uint32) if fault_cap else None
+            ev = np.zeros((nw, fault_cap), dtype=np.uint32) if fault_cap else None
+            need = C.c_int()
+            rc = lib().qec_sampler_sample(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(out),
+                                          _p(tally), _p(cnt), _p(ev), C.c_int(fault_cap),
+                                          C.byref(need))
+            if rc == QEC_ERR_LIMIT and fault_cap and need.value > fault_cap:
+                fault_cap = need.value + 8  # deterministic RNG: re-run with room for every event
+                continue
+            _check(rc)
+            return out, tally, cnt, ev
+
+    def sample_dev(self, shot_lo: int, n_shots: int, d_bits: int, d_tally: int, stream: int = 0):
+        _check(lib().qec_sampler_sample_dev(self._h, C.c_int64(shot_lo), C.c_int64(n_shots),
+                                            C.c_void_p(d_bits or None), C.c_void_p(d_tally or None),
+                                            C.c_void_p(stream or None)))
+
+    def check(self):
+        _check(lib().qec_sampler_check(self._h))
+
+
+def outcome_histogram_dev(circuit: Circuit, d_bits: int, n_paths: int, d_keys: int, d_counts: int,
+                          table_cap: int, stream: int = 0):
+    _check(lib().qec_outcome_histogram_dev(circuit._h, C.c_void_p(d_bits), C.c_int64(n_paths),
+                                           C.c_void_p(d_keys), C.c_void_p(d_counts),
+                                           C.c_int64(table_cap), C.c_void_p(stream or None)))
+
+
+def unpack_bits(packed: np.ndarray, n: int) -> np.ndarray:
+    """bit-sliced uint32[nc][n_words] -> uint8[n][nc] (one row per path, as the reference's
+    per-path outcome lists)."""
+    nc, nw = packed.shape
+    b = np.unpackbits(packed.view(np.uint8).reshape(nc, nw, 4), axis=2, bitorder="little")
+    return np.ascontiguousarray(b.reshape(nc, nw * 32)[:, :n].T)

@@ -1,0 +1,903 @@
+// qec_capi.cu -- host side of libqecb200.so: the C ABI of include/qec_b200.h.
+//
+// Lowers the reference's `encoded_circ` rows to the packed gate table, builds the
+// enumerator / sampler tables, owns device memory and launches the kernels of
+// qec_kernels.cu.  There is no CPU propagation path in this file: every outcome bit a
+// caller receives was produced by a kernel.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/qec_b200.h"
+#include "qec_kernels.cuh"
+
+// ---- error plumbing --------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(QEC_ERR_CUDA, "CUDA error %s at %s:%d (%s)", cudaGetErrorString(e__),   \
+                  __FILE__, __LINE__, #call);                                             \
+  } while (0)
+
+extern "C" const char *qec_last_error(void) { return g_err.c_str(); }
+extern "C" const char *qec_version(void) { return "qec_b200 0.1.0 (sm_100a)"; }
+
+extern "C" int qec_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+// ---- per-device state --------------------------------------------------------------------------
+struct DevInfo {
+  bool ok = false;
+  int sms = 0;
+  size_t smem_optin = 0, smem_sm = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+};
+static DevInfo g_dev[64];
+
+static int dev_info(int device, DevInfo **out) {
+  if (device < 0 || device >= 64) return fail(QEC_ERR_CUDA, "bad device index %d", device);
+  int n = qec_device_count();
+  if (n <= 0)
+    return fail(QEC_ERR_CUDA, "no CUDA device available: libqecb200 has no CPU fallback");
+  if (device >= n) return fail(QEC_ERR_CUDA, "device %d not present (%d visible)", device, n);
+  DevInfo &d = g_dev[device];
+  if (!d.ok) {
+    CU(cudaSetDevice(device));
+    cudaDeviceProp p;
+    CU(cudaGetDeviceProperties(&p, device));
+    d.sms = p.multiProcessorCount;
+    d.smem_optin = p.sharedMemPerBlockOptin;
+    d.smem_sm = p.sharedMemPerMultiprocessor;
+    CU(cudaEventCreate(&d.ev0));
+    CU(cudaEventCreate(&d.ev1));
+    d.ok = true;
+  }
+  *out = &d;
+  return 0;
+}
+
+struct DevBuf {  // growable device buffer
+  void *p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    CU(cudaMalloc(&p, bytes));
+    cap = bytes;
+    return 0;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+template <class T>
+static int upload(const std::vector<T> &v, T **out) {
+  *out = nullptr;
+  const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+  CU(cudaMalloc((void **)out, bytes));
+  if (!v.empty()) CU(cudaMemcpy(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+// ---- circuit IR --------------------------------------------------------------------------------
+// reference opcodes (errorpropagator.h:9-42)
+enum { R_H = 0, R_S, R_X, R_Y, R_Z, R_CX, R_ID, R_RESET, R_MEASURE, R_BARRIER };
+
+struct qec_circuit {
+  int device = 0, nq = 0, nc = 0, n_ops = 0;
+  std::vector<uint8_t> rop;       // reference opcode per op
+  std::vector<uint32_t> packed;   // padded gate table
+  int64_t bit_ops = 0;
+  QecCircuitDev dev{};
+  uint32_t *d_ops = nullptr;
+  DevBuf out_bits, out_frame, tally, ev_off, ev;  // staging for the host-pointer entry points
+  DevInfo *info = nullptr;
+};
+
+extern "C" int qec_circuit_create(int device, int nq, int nc, int n_ops, const int32_t *row_off,
+                                  const int32_t *row_data, qec_circuit **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  if (nq < 0 || nc < 0 || n_ops < 0) return fail(QEC_ERR_INVALID, "negative size");
+  if (nq > QEC_MAX_QUBITS || nc > QEC_MAX_CLBITS)
+    return fail(QEC_ERR_LIMIT, "at most %d qubits and %d clbits are supported", QEC_MAX_QUBITS,
+                QEC_MAX_CLBITS);
+  if (n_ops >= (1 << 22)) return fail(QEC_ERR_LIMIT, "at most 2^22 operations are supported");
+  std::vector<uint8_t> rop(n_ops);
+  std::vector<uint32_t> packed;
+  packed.reserve(n_ops + nc + 4);
+  std::vector<int> last_write(nc, -1);
+  int64_t bit_ops = 0;
+  // validation: same checks, order and messages as errorpropagator.cpp:112-148
+  for (int i = 0; i < n_ops; ++i) {
+    const int32_t *row = row_data + row_off[i];
+    const int len = row_off[i + 1] - row_off[i];
+    if (len < 1) return fail(QEC_ERR_LOGIC, "bad opcode");
+    const int op = row[0];
+    auto qchk = [&](int q) { return q >= 0 && q < nq; };
+    switch (op) {
+      case R_H: case R_S: case R_X: case R_Y: case R_Z: case R_ID: case R_RESET:
+        if (len != 2) return fail(QEC_ERR_LOGIC, "bad 1-qubit instruction");
+        if (!qchk(row[1])) return fail(QEC_ERR_LOGIC, "qubit index out of range");
+        break;
+      case R_MEASURE:
+        if (len != 3) return fail(QEC_ERR_LOGIC, "bad measure instruction");
+        if (!qchk(row[1])) return fail(QEC_ERR_LOGIC, "qubit index out of range");
+        if (row[2] < 0 || row[2] >= nc) return fail(QEC_ERR_LOGIC, "bit index out of range");
+        break;
+      case R_CX:
+        if (len != 3) return fail(QEC_ERR_LOGIC, "bad cx instruction");
+        if (!qchk(row[1]) || !qchk(row[2])) return fail(QEC_ERR_LOGIC, "qubit index out of range");
+        // control == target is accepted by the reference (it zeroes the qubit); it is not a
+        // CNOT and is refused here rather than given a meaning.
+        if (row[1] == row[2]) return fail(QEC_ERR_LOGIC, "bad cx instruction");
+        break;
+      case R_BARRIER:
+        if (len != 1) return fail(QEC_ERR_LOGIC, "bad barrier instruction");
+        break;
+      default:
+        return fail(QEC_ERR_LOGIC, "bad opcode");
+    }
+    rop[i] = (uint8_t)op;
+    switch (op) {
+      case R_H: packed.push_back(qec_pack_op(QOP_H, row[1], 0)); bit_ops += 2; break;
+      case R_S: packed.push_back(qec_pack_op(QOP_S, row[1], 0)); bit_ops += 1; break;
+      case R_CX: packed.push_back(qec_pack_op(QOP_CX, row[1], row[2])); bit_ops += 2; break;
+      case R_RESET: packed.push_back(qec_pack_op(QOP_RESET, row[1], 0)); bit_ops += 2; break;
+      case R_MEASURE:
+        packed.push_back(qec_pack_op(QOP_MEAS, row[1], row[2]));
+        last_write[row[2]] = i;
+        bit_ops += 1;
+        break;
+      case R_BARRIER: packed.push_back(qec_pack_op(QOP_NOP, 0, 1)); break;  // b=1: faults ignored
+      default: packed.push_back(qec_pack_op(QOP_NOP, row[1], 0)); break;     // x y z id
+    }
+  }
+  for (int c = 0; c < nc; ++c) {
+    if (last_write[c] >= 0)
+      packed[last_write[c]] = (packed[last_write[c]] & ~15u) | QOP_MEASF;
+    else
+      packed.push_back(qec_pack_op(QOP_ZEROC, c, 0));
+  }
+  while (packed.size() % 4 || packed.empty()) packed.push_back(qec_pack_op(QOP_NOP, 0, 1));
+
+  DevInfo *info;
+  int rc = dev_info(device, &info);
+  if (rc) return rc;
+  CU(cudaSetDevice(device));
+  qec_circuit *c = new qec_circuit;
+  c->device = device; c->nq = nq; c->nc = nc; c->n_ops = n_ops;
+  c->rop.swap(rop);
+  c->packed.swap(packed);
+  c->bit_ops = bit_ops;
+  c->info = info;
+  rc = upload(c->packed, &c->d_ops);
+  if (rc) { delete c; return rc; }
+  c->dev.nq = nq; c->dev.nc = nc; c->dev.n_ops = n_ops;
+  c->dev.n_ops4 = (int)(c->packed.size() / 4);
+  c->dev.ops = c->d_ops;
+  *out = c;
+  return 0;
+}
+
+extern "C" void qec_circuit_destroy(qec_circuit *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->d_ops) cudaFree(c->d_ops);
+  c->out_bits.release(); c->out_frame.release(); c->tally.release();
+  c->ev_off.release(); c->ev.release();
+  delete c;
+}
+
+extern "C" int qec_circuit_sizes(const qec_circuit *c, int *nq, int *nc, int *n_ops) {
+  if (!c) return fail(QEC_ERR_INVALID, "null circuit");
+  if (nq) *nq = c->nq;
+  if (nc) *nc = c->nc;
+  if (n_ops) *n_ops = c->n_ops;
+  return 0;
+}
+
+extern "C" int64_t qec_circuit_bit_ops(const qec_circuit *c) { return c ? c->bit_ops : -1; }
+
+// mask a 4-bit Pauli code by what the op can take (errorpropagator.cpp:272-310):
+// 1-qubit ops read only pauli[0]; barriers ignore faults altogether.
+static inline uint8_t mask_code(const qec_circuit *c, int op, uint8_t code) {
+  const uint8_t r = c->rop[op];
+  if (r == R_BARRIER) return 0;
+  if (r == R_CX) return code & 15;
+  return code & 3;
+}
+
+// ---- launch geometry -----------------------------------------------------------------------------
+// Pick threads per CTA (T lane words) and CTAs per SM so that the resident lane words per SM
+// (bounded by the shared-memory frames) are maximal; grid = SMs x CTAs/SM (persistent).
+static int pick_cfg(const qec_circuit *c, int kind, int order, uint32_t B, uint32_t K1,
+                    QecLaunchCfg *cfg) {
+  const DevInfo &d = *c->info;
+  int bestT = 0, bestCtas = 0, bestThreads = 0;
+  for (int T = 256; T >= 32; T -= 32) {
+    const size_t smem = qec_kernel_smem_bytes(kind, c->nq, c->nc, T, B, K1);
+    if (smem > d.smem_optin) continue;
+    int ctas = (int)(d.smem_sm / (smem + 1024));
+    ctas = std::min(ctas, std::min(2048 / T, 32));
+    if (ctas < 1) continue;
+    const int threads = ctas * T;
+    const bool better = threads > bestThreads ||
+                        (threads == bestThreads && std::abs(T - 128) < std::abs(bestT - 128));
+    if (better) { bestT = T; bestCtas = ctas; bestThreads = threads; }
+  }
+  if (!bestT)
+    return fail(QEC_ERR_LIMIT, "frame of %d qubits does not fit in shared memory", c->nq);
+  cfg->block = bestT;
+  cfg->grid = d.sms * bestCtas;
+  cfg->smem = qec_kernel_smem_bytes(kind, c->nq, c->nc, bestT, B, K1);
+  const int e = qec_kernel_set_smem_attr(kind, order, cfg->smem);
+  if (e) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)e));
+  return 0;
+}
+
+static inline void time_begin(qec_circuit *c, cudaStream_t s) { cudaEventRecord(c->info->ev0, s); }
+static inline void time_end(qec_circuit *c, cudaStream_t s) {
+  cudaEventRecord(c->info->ev1, s);
+  c->info->timed = true;
+}
+
+extern "C" int qec_last_kernel_ms(int device, float *ms) {
+  DevInfo *d;
+  int rc = dev_info(device, &d);
+  if (rc) return rc;
+  if (!d->timed) return fail(QEC_ERR_INVALID, "no timed launch on device %d yet", device);
+  CU(cudaEventSynchronize(d->ev1));
+  CU(cudaEventElapsedTime(ms, d->ev0, d->ev1));
+  return 0;
+}
+
+// ---- K1: batched propagate ------------------------------------------------------------------------
+extern "C" int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_t *path_off,
+                                   const int32_t *fault_op, const uint8_t *fault_pauli,
+                                   uint32_t *out_bits, uint32_t *out_frame) {
+  if (!c) return fail(QEC_ERR_INVALID, "null circuit");
+  if (n_paths < 0) return fail(QEC_ERR_INVALID, "negative path count");
+  if (n_paths == 0) return 0;
+  if (!path_off || !out_bits) return fail(QEC_ERR_INVALID, "null pointer");
+  const int64_t n_words = (n_paths + 31) / 32;
+  // marshal the fault lists into per-lane-word event lists, stably sorted by op so that a
+  // duplicated op index inside one path keeps the reference's "last one wins" order
+  std::vector<long long> off(n_words + 1, 0);
+  std::vector<uint32_t> ev;
+  ev.reserve((size_t)(path_off[n_paths] - path_off[0]));
+  std::vector<uint32_t> tmp;
+  for (int64_t w = 0; w < n_words; ++w) {
+    tmp.clear();
+    const int64_t p1 = std::min<int64_t>(n_paths, 32 * w + 32);
+    for (int64_t p = 32 * w; p < p1; ++p) {
+      for (int64_t j = path_off[p]; j < path_off[p + 1]; ++j) {
+        const int op = fault_op[j];
+        if (op < 0 || op >= c->n_ops)
+          return fail(QEC_ERR_LOGIC, "fault op index %d out of range [0, %d)", op, c->n_ops);
+        tmp.push_back(((uint32_t)op << QEC_EV_OP_SHIFT) | ((uint32_t)(p & 31) << 4) |
+                      mask_code(c, op, fault_pauli[j]));
+      }
+    }
+    std::stable_sort(tmp.begin(), tmp.end(), [](uint32_t a, uint32_t b) {
+      return (a >> QEC_EV_OP_SHIFT) < (b >> QEC_EV_OP_SHIFT);
+    });
+    ev.insert(ev.end(), tmp.begin(), tmp.end());
+    off[w + 1] = (long long)ev.size();
+  }
+  CU(cudaSetDevice(c->device));
+  QecLaunchCfg cfg;
+  int rc = pick_cfg(c, 0, 0, 0, 0, &cfg);
+  if (rc) return rc;
+  const size_t out_bytes = (size_t)c->nc * n_words * 4, fr_bytes = (size_t)2 * c->nq * n_words * 4;
+  if ((rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+  if (out_frame && (rc = c->out_frame.ensure(std::max<size_t>(fr_bytes, 4)))) return rc;
+  if ((rc = c->ev_off.ensure(off.size() * 8))) return rc;
+  if ((rc = c->ev.ensure(std::max<size_t>(ev.size(), 1) * 4))) return rc;
+  CU(cudaMemcpy(c->ev_off.p, off.data(), off.size() * 8, cudaMemcpyHostToDevice));
+  if (!ev.empty()) CU(cudaMemcpy(c->ev.p, ev.data(), ev.size() * 4, cudaMemcpyHostToDevice));
+  QecOutDev O{};
+  O.bits = (uint32_t *)c->out_bits.p;
+  O.frame = out_frame ? (uint32_t *)c->out_frame.p : nullptr;
+  O.tally = nullptr;
+  O.n_words = n_words;
+  time_begin(c, 0);
+  qec_launch_batch(cfg, 0, c->dev, O, (const long long *)c->ev_off.p, (const uint32_t *)c->ev.p);
+  time_end(c, 0);
+  CU(cudaGetLastError());
+  CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
+  if (out_frame) CU(cudaMemcpy(out_frame, c->out_frame.p, fr_bytes, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// ---- K2: enumerator -----------------------------------------------------------------------------
+struct qec_enumerator {
+  qec_circuit *c = nullptr;
+  int order = 0, L = 0;
+  std::vector<unsigned long long> E;  // [(order+1) * (L+2)]
+  std::vector<uint32_t> npaul, poff, lop;
+  std::vector<uint8_t> pcode;
+  int deferred = 0;                   // error raised at first use, as the reference does
+  std::string deferred_msg;
+  int64_t total = 0;
+  QecEnumDev dev{};
+  unsigned long long *d_E = nullptr;
+  uint32_t *d_npaul = nullptr, *d_poff = nullptr, *d_lop = nullptr;
+  uint8_t *d_pcode = nullptr;
+  DevBuf scratch;
+  QecLaunchCfg cfg{};
+};
+
+extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int32_t *loc_op,
+                                     const int32_t *pauli_off, const uint8_t *pauli_codes,
+                                     qec_enumerator **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  if (!c) return fail(QEC_ERR_INVALID, "null circuit");
+  if (L < 0) return fail(QEC_ERR_INVALID, "negative location count");
+  qec_enumerator *e = new qec_enumerator;
+  e->c = c; e->order = order; e->L = L;
+  // The reference constructor validates nothing; Combinations / ProductIterator throw at the
+  // first enumerate() (combinations.cpp:5-6, productiterator.cpp:6).  Keep that timing.
+  if (L <= 0) { e->deferred = QEC_ERR_INVALID; e->deferred_msg = "n must be positive"; }
+  else if (order < 0 || order > L) { e->deferred = QEC_ERR_INVALID; e->deferred_msg = "0 <= k <= n"; }
+  else if (order < 1) {
+    e->deferred = QEC_ERR_INVALID;
+    e->deferred_msg = "order must be >= 1 (the reference loops forever on order 0)";
+  } else if (order > QEC_KERNEL_MAX_ORDER) {
+    e->deferred = QEC_ERR_LIMIT;
+    e->deferred_msg = "order above " + std::to_string(QEC_KERNEL_MAX_ORDER) + " is not compiled in";
+  }
+  e->npaul.resize(L); e->poff.resize(L + 1); e->lop.resize(L);
+  for (int l = 0; l < L; ++l) {
+    if (loc_op[l] < 0 || loc_op[l] >= c->n_ops) {
+      delete e;
+      return fail(QEC_ERR_LOGIC, "faulty op index %d out of range [0, %d)", loc_op[l], c->n_ops);
+    }
+    e->lop[l] = (uint32_t)loc_op[l];
+    const int n = pauli_off[l + 1] - pauli_off[l];
+    e->npaul[l] = (uint32_t)n;
+    e->poff[l] = (uint32_t)(pauli_off[l] - pauli_off[0]);
+    if (n <= 0 && !e->deferred) {
+      e->deferred = QEC_ERR_INVALID;
+      e->deferred_msg = "each element must be positive";
+    }
+    for (int j = pauli_off[l]; j < pauli_off[l + 1]; ++j)
+      e->pcode.push_back(mask_code(c, loc_op[l], pauli_codes[j]));
+  }
+  if (L >= 0) e->poff[L] = (uint32_t)e->pcode.size();
+  if (!e->deferred) {
+    const int L2 = L + 2;
+    e->E.assign((size_t)(order + 1) * L2, 0ull);
+    for (int l = 0; l < L2; ++l) e->E[l] = 1ull;
+    for (int m = 1; m <= order; ++m) {
+      unsigned __int128 acc = 0;
+      for (int l = L - 1; l >= 0; --l) {
+        acc += (unsigned __int128)e->npaul[l] * e->E[(size_t)(m - 1) * L2 + l + 1];
+        if (acc >= ((unsigned __int128)1 << 62)) {
+          delete e;
+          return fail(QEC_ERR_LIMIT, "number of fault paths exceeds 2^62");
+        }
+        e->E[(size_t)m * L2 + l] = (unsigned long long)acc;
+      }
+    }
+    e->total = (int64_t)e->E[(size_t)order * L2];
+    CU(cudaSetDevice(c->device));
+    int rc = 0;
+    if ((rc = upload(e->E, &e->d_E)) || (rc = upload(e->npaul, &e->d_npaul)) ||
+        (rc = upload(e->poff, &e->d_poff)) || (rc = upload(e->lop, &e->d_lop)) ||
+        (rc = upload(e->pcode, &e->d_pcode)) || (rc = pick_cfg(c, 1, order, 0, 0, &e->cfg)) ||
+        (rc = e->scratch.ensure((size_t)e->cfg.grid * e->cfg.block * 32 * order * 4))) {
+      qec_enumerator_destroy(e);
+      return rc;
+    }
+    e->dev.order = order; e->dev.L = L; e->dev.E = e->d_E; e->dev.npaul = e->d_npaul;
+    e->dev.poff = e->d_poff; e->dev.pcode = e->d_pcode; e->dev.lop = e->d_lop;
+  }
+  *out = e;
+  return 0;
+}
+
+extern "C" void qec_enumerator_destroy(qec_enumerator *e) {
+  if (!e) return;
+  cudaSetDevice(e->c->device);
+  if (e->d_E) cudaFree(e->d_E);
+  if (e->d_npaul) cudaFree(e->d_npaul);
+  if (e->d_poff) cudaFree(e->d_poff);
+  if (e->d_lop) cudaFree(e->d_lop);
+  if (e->d_pcode) cudaFree(e->d_pcode);
+  e->scratch.release();
+  delete e;
+}
+
+#define ENUM_CHECK(e)                                                  \
+  if (!(e)) return fail(QEC_ERR_INVALID, "null enumerator");           \
+  if ((e)->deferred) return fail((e)->deferred, "%s", (e)->deferred_msg.c_str());
+
+extern "C" int qec_enumerator_num_paths(const qec_enumerator *e, int64_t *n) {
+  ENUM_CHECK(e);
+  *n = e->total;
+  return 0;
+}
+
+extern "C" int qec_enumerator_unrank(const qec_enumerator *e, int64_t index, int32_t *locs,
+                                     int32_t *digits) {
+  ENUM_CHECK(e);
+  if (index < 0 || index >= e->total)
+    return fail(QEC_ERR_INVALID, "path index %lld out of range [0, %lld)", (long long)index,
+                (long long)e->total);
+  const int K = e->order, L2 = e->L + 2;
+  unsigned long long r = (unsigned long long)index, mult = 1;
+  uint32_t start = 0;
+  for (int j = 0; j < K; ++j) {
+    const unsigned long long *Em = e->E.data() + (size_t)(K - j) * L2;
+    const unsigned long long thr = Em[start] - r / mult;
+    uint32_t lo = start, hi = (uint32_t)e->L;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (Em[mid] >= thr) lo = mid; else hi = mid;
+    }
+    r -= mult * (Em[start] - Em[lo]);
+    locs[j] = (int32_t)lo;
+    mult *= e->npaul[lo];
+    start = lo + 1;
+  }
+  for (int j = K - 1; j >= 0; --j) {
+    digits[j] = (int32_t)(r % e->npaul[locs[j]]);
+    r /= e->npaul[locs[j]];
+  }
+  return 0;
+}
+
+extern "C" int qec_enumerator_subset_rank(const qec_enumerator *e, const int32_t *locs,
+                                          int64_t *first, int64_t *count) {
+  ENUM_CHECK(e);
+  const int K = e->order, L2 = e->L + 2;
+  unsigned long long r = 0, mult = 1;
+  int start = 0;
+  for (int j = 0; j < K; ++j) {
+    const int l = locs[j];
+    if (l < start || l >= e->L) return fail(QEC_ERR_INVALID, "not a sorted k-subset of locations");
+    const unsigned long long *Em = e->E.data() + (size_t)(K - j) * L2;
+    r += mult * (Em[start] - Em[l]);
+    mult *= e->npaul[l];
+    start = l + 1;
+  }
+  if (first) *first = (int64_t)r;
+  if (count) *count = (int64_t)mult;
+  return 0;
+}
+
+static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bits,
+                       uint64_t *d_tally, cudaStream_t stream) {
+  QecOutDev O{};
+  O.bits = d_bits;
+  O.frame = nullptr;
+  O.tally = (unsigned long long *)d_tally;
+  O.n_words = (hi - lo + 31) / 32;
+  time_begin(e->c, stream);
+  qec_launch_enumerate(e->cfg, stream, e->c->dev, O, e->dev, lo, hi, (uint32_t *)e->scratch.p);
+  time_end(e->c, stream);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int qec_enumerator_range_dev(qec_enumerator *e, int64_t lo, int64_t hi,
+                                        uint32_t *d_out_bits, uint64_t *d_tally, void *stream) {
+  ENUM_CHECK(e);
+  if (lo < 0 || hi < lo || hi > e->total)
+    return fail(QEC_ERR_INVALID, "bad path range [%lld, %lld) of %lld", (long long)lo,
+                (long long)hi, (long long)e->total);
+  if (hi == lo) return 0;
+  CU(cudaSetDevice(e->c->device));
+  return enum_launch(e, lo, hi, d_out_bits, d_tally, (cudaStream_t)stream);
+}
+
+extern "C" int qec_enumerator_range(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *out_bits,
+                                    uint64_t *tally) {
+  ENUM_CHECK(e);
+  if (lo < 0 || hi < lo || hi > e->total)
+    return fail(QEC_ERR_INVALID, "bad path range [%lld, %lld) of %lld", (long long)lo,
+                (long long)hi, (long long)e->total);
+  qec_circuit *c = e->c;
+  const size_t tl = QEC_TALLY_LEN(c->nc);
+  if (tally) memset(tally, 0, tl * 8);
+  if (hi == lo) return 0;
+  CU(cudaSetDevice(c->device));
+  const int64_t n_words = (hi - lo + 31) / 32;
+  const size_t out_bytes = (size_t)c->nc * n_words * 4;
+  int rc;
+  if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+  if (tally) {
+    if ((rc = c->tally.ensure(tl * 8))) return rc;
+    CU(cudaMemsetAsync(c->tally.p, 0, tl * 8, 0));
+  }
+  if ((rc = enum_launch(e, lo, hi, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
+                        tally ? (uint64_t *)c->tally.p : nullptr, 0)))
+    return rc;
+  if (out_bits) CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
+  if (tally) CU(cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost));
+  CU(cudaDeviceSynchronize());
+  return 0;
+}
+
+// ---- K3: sampler ---------------------------------------------------------------------------------
+struct qec_sampler {
+  qec_circuit *c = nullptr;
+  int L = 0, n_classes = 0;
+  uint64_t seed = 0;
+  // host copies of every table (also served by qec_sampler_tables)
+  uint32_t B = 32, K1 = 1;
+  std::vector<uint32_t> T1, T2, slop, slloc, cls_acc, cls_off, cdf;
+  std::vector<uint16_t> slcls;
+  std::vector<uint8_t> cls_always, codes;
+  double mean_events = 0;  // expected events per 32-shot word
+  QecSamplerDev dev{};
+  uint32_t *d_T1 = nullptr, *d_T2 = nullptr, *d_slop = nullptr, *d_slloc = nullptr,
+           *d_cls_acc = nullptr, *d_cls_off = nullptr, *d_cdf = nullptr;
+  uint16_t *d_slcls = nullptr;
+  uint8_t *d_cls_always = nullptr, *d_codes = nullptr;
+  uint32_t *d_flag = nullptr;
+  DevBuf scratch, xcnt, xev;
+  int cap = 0;
+  QecLaunchCfg cfg{};
+};
+
+static inline uint32_t fix32(double x) {  // round(2^32 * x) clamped to [0, 2^32 - 1]
+  if (!(x > 0)) return 0u;
+  const double v = std::nearbyint(x * 4294967296.0);
+  return v >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)v;
+}
+
+extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
+                                  const int32_t *loc_class, int n_classes, const double *class_p,
+                                  const int32_t *class_off, const uint8_t *class_codes,
+                                  const double *class_weight, uint64_t seed, qec_sampler **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  if (!c) return fail(QEC_ERR_INVALID, "null circuit");
+  if (L < 0 || n_classes < 0 || n_classes > 65535) return fail(QEC_ERR_INVALID, "bad sizes");
+  if (L >= (1 << 18)) return fail(QEC_ERR_LIMIT, "at most 2^18 fault locations are supported");
+  qec_sampler *s = new qec_sampler;
+  s->c = c; s->L = L; s->n_classes = n_classes; s->seed = seed;
+  // locations in op order (stable): the slot space of a 32-shot word is (sorted location, shot)
+  std::vector<int> order(L);
+  for (int l = 0; l < L; ++l) order[l] = l;
+  for (int l = 0; l < L; ++l) {
+    if (loc_op[l] < 0 || loc_op[l] >= c->n_ops) {
+      delete s;
+      return fail(QEC_ERR_LOGIC, "faulty op index %d out of range [0, %d)", loc_op[l], c->n_ops);
+    }
+    if (loc_class[l] < 0 || loc_class[l] >= n_classes) {
+      delete s;
+      return fail(QEC_ERR_INVALID, "location class %d out of range", loc_class[l]);
+    }
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return loc_op[a] < loc_op[b]; });
+  double pmax = 0, psum = 0;
+  for (int i = 0; i < L; ++i) {
+    const int l = order[i];
+    s->slop.push_back((uint32_t)loc_op[l]);
+    s->slloc.push_back((uint32_t)l);
+    s->slcls.push_back((uint16_t)loc_class[l]);
+    double p = class_p[loc_class[l]];
+    if (!(p > 0)) p = 0;
+    if (p > 1) p = 1;
+    pmax = std::max(pmax, p);
+    psum += p;
+  }
+  s->mean_events = 32.0 * psum;
+  // classes
+  s->cls_off.assign(n_classes + 1, 0);
+  for (int k = 0; k < n_classes; ++k) {
+    const int n = class_off[k + 1] - class_off[k];
+    if (n <= 0 || n > 512) {
+      delete s;
+      return fail(QEC_ERR_INVALID, "class %d must offer between 1 and 512 Paulis", k);
+    }
+    double W = 0;
+    for (int j = class_off[k]; j < class_off[k + 1]; ++j) {
+      if (!(class_weight[j] >= 0)) { delete s; return fail(QEC_ERR_INVALID, "negative Pauli weight"); }
+      W += class_weight[j];
+    }
+    if (!(W > 0)) { delete s; return fail(QEC_ERR_INVALID, "class %d has zero total weight", k); }
+    double cum = 0;
+    for (int j = class_off[k]; j < class_off[k + 1]; ++j) {
+      cum += class_weight[j];
+      s->cdf.push_back(fix32(cum / W));
+      s->codes.push_back(class_codes[j] & 15);
+    }
+    s->cls_off[k + 1] = (uint32_t)s->cdf.size();
+    double p = class_p[k];
+    if (!(p > 0)) p = 0;
+    if (p > 1) p = 1;
+    const double ratio = pmax > 0 ? p / pmax : 0;
+    s->cls_always.push_back(ratio >= 1.0 ? 1 : 0);
+    s->cls_acc.push_back(fix32(ratio));
+  }
+  // two-level geometric gap tables at rate pmax
+  s->dev.n_slots = pmax > 0 ? (long long)L * 32 : 0;
+  const double lq = std::log1p(-pmax);  // -inf when pmax == 1
+  uint32_t B = 32;
+  while (B < 1024 && std::exp((double)B * lq) > 0.75) B *= 2;
+  s->B = B;
+  for (uint32_t i = 0; i < 1024; ++i) {
+    const uint32_t v = pmax > 0 ? fix32(std::exp((double)(i + 1) * B * lq)) : 0u;
+    s->T1.push_back(v);
+    if (v == 0) break;
+  }
+  s->K1 = (uint32_t)s->T1.size();
+  s->T2.assign(B, 0u);
+  s->T2[0] = 0xFFFFFFFFu;
+  if (pmax > 0) {
+    const double den = std::expm1((double)B * lq);  // in [-1, 0)
+    for (uint32_t j = 1; j < B; ++j) {
+      const double num = std::exp((double)j * lq) * std::expm1((double)(B - j) * lq);
+      s->T2[j] = (num == 0) ? 0u : fix32(num / den);
+    }
+  }
+  CU(cudaSetDevice(c->device));
+  int rc = 0;
+  if ((rc = upload(s->T1, &s->d_T1)) || (rc = upload(s->T2, &s->d_T2)) ||
+      (rc = upload(s->slop, &s->d_slop)) || (rc = upload(s->slloc, &s->d_slloc)) ||
+      (rc = upload(s->slcls, &s->d_slcls)) || (rc = upload(s->cls_acc, &s->d_cls_acc)) ||
+      (rc = upload(s->cls_always, &s->d_cls_always)) || (rc = upload(s->cls_off, &s->d_cls_off)) ||
+      (rc = upload(s->cdf, &s->d_cdf)) || (rc = upload(s->codes, &s->d_codes)) ||
+      (rc = pick_cfg(c, 2, 0, s->B, s->K1, &s->cfg))) {
+    qec_sampler_destroy(s);
+    return rc;
+  }
+  if (cudaMalloc((void **)&s->d_flag, 4) != cudaSuccess || cudaMemset(s->d_flag, 0, 4) != cudaSuccess) {
+    qec_sampler_destroy(s);
+    return fail(QEC_ERR_CUDA, "cudaMalloc failed");
+  }
+  const double mu = s->mean_events;
+  s->cap = (int)(std::ceil(mu + 10.0 * std::sqrt(mu) + 32.0) + 7) / 8 * 8;
+  if ((rc = s->scratch.ensure((size_t)s->cfg.grid * s->cfg.block * s->cap * 4))) {
+    qec_sampler_destroy(s);
+    return rc;
+  }
+  QecSamplerDev &d = s->dev;
+  d.L = L; d.B = s->B; d.K1 = s->K1; d.T1 = s->d_T1; d.T2 = s->d_T2; d.slop = s->d_slop;
+  d.slloc = s->d_slloc; d.slcls = s->d_slcls; d.cls_acc = s->d_cls_acc;
+  d.cls_always = s->d_cls_always; d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.codes = s->d_codes;
+  d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32);
+  *out = s;
+  return 0;
+}
+
+extern "C" void qec_sampler_destroy(qec_sampler *s) {
+  if (!s) return;
+  cudaSetDevice(s->c->device);
+  void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
+                  s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  s->scratch.release(); s->xcnt.release(); s->xev.release();
+  delete s;
+}
+
+extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, int *n) {
+  if (!s) return fail(QEC_ERR_INVALID, "null sampler");
+  std::vector<uint32_t> v;
+  const uint32_t ncls = (uint32_t)s->n_classes, np = (uint32_t)s->cdf.size();
+  v.insert(v.end(), {s->B, s->K1, ncls, (uint32_t)s->L, np, (uint32_t)s->seed,
+                     (uint32_t)(s->seed >> 32), (uint32_t)(s->dev.n_slots > 0)});
+  v.insert(v.end(), s->T1.begin(), s->T1.end());
+  v.insert(v.end(), s->T2.begin(), s->T2.end());
+  v.insert(v.end(), s->slop.begin(), s->slop.end());
+  v.insert(v.end(), s->slloc.begin(), s->slloc.end());
+  for (uint16_t x : s->slcls) v.push_back(x);
+  v.insert(v.end(), s->cls_acc.begin(), s->cls_acc.end());
+  for (uint8_t x : s->cls_always) v.push_back(x);
+  v.insert(v.end(), s->cls_off.begin(), s->cls_off.end());
+  v.insert(v.end(), s->cdf.begin(), s->cdf.end());
+  for (uint8_t x : s->codes) v.push_back(x);
+  if (n) *n = (int)v.size();
+  if (buf) {
+    if (cap < (int)v.size()) return fail(QEC_ERR_LIMIT, "table buffer too small (%zu needed)", v.size());
+    memcpy(buf, v.data(), v.size() * 4);
+  }
+  return 0;
+}
+
+static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint32_t *d_bits,
+                         uint64_t *d_tally, const QecSampleExport &X, cudaStream_t stream) {
+  QecOutDev O{};
+  O.bits = d_bits;
+  O.frame = nullptr;
+  O.tally = (unsigned long long *)d_tally;
+  O.n_words = (n_shots + 31) / 32;
+  time_begin(s->c, stream);
+  qec_launch_sample(s->cfg, stream, s->c->dev, O, s->dev, shot_lo / 32, n_shots,
+                    (uint32_t *)s->scratch.p, s->cap, X, s->d_flag);
+  time_end(s->c, stream);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+// grows the event buffer if an earlier launch overflowed it; returns QEC_ERR_OVERFLOW then
+static int sampler_check(qec_sampler *s) {
+  uint32_t flag = 0;
+  CU(cudaMemcpy(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost));
+  if (flag <= (uint32_t)s->cap) return 0;
+  CU(cudaMemset(s->d_flag, 0, 4));
+  s->cap = (int)((flag + 32 + 7) / 8 * 8);
+  int rc = s->scratch.ensure((size_t)s->cfg.grid * s->cfg.block * s->cap * 4);
+  if (rc) return rc;
+  return fail(QEC_ERR_OVERFLOW, "sampler event buffer overflowed (%u events in one word)", flag);
+}
+
+extern "C" int qec_sampler_check(qec_sampler *s) {
+  if (!s) return fail(QEC_ERR_INVALID, "null sampler");
+  CU(cudaSetDevice(s->c->device));
+  return sampler_check(s);
+}
+
+static int sample_args(const qec_sampler *s, int64_t shot_lo, int64_t n_shots) {
+  if (!s) return fail(QEC_ERR_INVALID, "null sampler");
+  if (shot_lo < 0 || (shot_lo & 31)) return fail(QEC_ERR_INVALID, "shot_lo must be a non-negative multiple of 32");
+  if (n_shots < 0) return fail(QEC_ERR_INVALID, "negative shot count");
+  return 0;
+}
+
+extern "C" int qec_sampler_sample_dev(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                      uint32_t *d_out_bits, uint64_t *d_tally, void *stream) {
+  int rc = sample_args(s, shot_lo, n_shots);
+  if (rc) return rc;
+  if (n_shots == 0) return 0;
+  CU(cudaSetDevice(s->c->device));
+  QecSampleExport X{nullptr, nullptr, 0};
+  return sample_launch(s, shot_lo, n_shots, d_out_bits, d_tally, X, (cudaStream_t)stream);
+}
+
+extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                  uint32_t *out_bits, uint64_t *tally, uint32_t *fault_cnt,
+                                  uint32_t *fault_ev, int fault_cap, int *fault_cap_needed) {
+  int rc = sample_args(s, shot_lo, n_shots);
+  if (rc) return rc;
+  qec_circuit *c = s->c;
+  const size_t tl = QEC_TALLY_LEN(c->nc);
+  if (tally) memset(tally, 0, tl * 8);
+  if (fault_cap_needed) *fault_cap_needed = 0;
+  if (n_shots == 0) return 0;
+  const bool exp = fault_cnt || fault_ev;
+  if (exp && (!fault_cnt || !fault_ev || fault_cap <= 0))
+    return fail(QEC_ERR_INVALID, "fault export needs fault_cnt, fault_ev and fault_cap > 0");
+  CU(cudaSetDevice(c->device));
+  const int64_t n_words = (n_shots + 31) / 32;
+  const size_t out_bytes = (size_t)c->nc * n_words * 4;
+  if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+  if (tally && (rc = c->tally.ensure(tl * 8))) return rc;
+  QecSampleExport X{nullptr, nullptr, 0};
+  if (exp) {
+    if ((rc = s->xcnt.ensure((size_t)n_words * 4))) return rc;
+    if ((rc = s->xev.ensure((size_t)n_words * fault_cap * 4))) return rc;
+    X.cnt = (uint32_t *)s->xcnt.p; X.ev = (uint32_t *)s->xev.p; X.cap = fault_cap;
+  }
+  for (int attempt = 0;; ++attempt) {
+    if (tally) CU(cudaMemsetAsync(c->tally.p, 0, tl * 8, 0));
+    if ((rc = sample_launch(s, shot_lo, n_shots, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
+                            tally ? (uint64_t *)c->tally.p : nullptr, X, 0)))
+      return rc;
+    rc = sampler_check(s);  // synchronises
+    if (rc == 0) break;
+    if (rc != QEC_ERR_OVERFLOW || attempt >= 4) return rc;  // deterministic RNG: safe to re-run
+  }
+  if (out_bits) CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
+  if (tally) CU(cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost));
+  if (exp) {
+    CU(cudaMemcpy(fault_cnt, s->xcnt.p, (size_t)n_words * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(fault_ev, s->xev.p, (size_t)n_words * fault_cap * 4, cudaMemcpyDeviceToHost));
+    uint32_t mx = 0;
+    for (int64_t w = 0; w < n_words; ++w) mx = std::max(mx, fault_cnt[w]);
+    if (fault_cap_needed) *fault_cap_needed = (int)mx;
+    if (mx > (uint32_t)fault_cap)
+      return fail(QEC_ERR_LIMIT, "fault export truncated: %u events in one word, fault_cap %d", mx, fault_cap);
+  }
+  return 0;
+}
+
+// ---- K4 + helpers --------------------------------------------------------------------------------
+extern "C" int qec_outcome_histogram_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                         uint64_t *d_keys, uint64_t *d_counts, int64_t table_cap,
+                                         void *stream) {
+  if (!c || !d_bits || !d_keys || !d_counts) return fail(QEC_ERR_INVALID, "null pointer");
+  if (table_cap <= 0 || (table_cap & (table_cap - 1)))
+    return fail(QEC_ERR_INVALID, "table_cap must be a power of two");
+  if (n_paths <= 0) return 0;
+  CU(cudaSetDevice(c->device));
+  qec_launch_outcome_hist((cudaStream_t)stream, d_bits, c->nc, n_paths, (unsigned long long *)d_keys,
+                          (unsigned long long *)d_counts, table_cap);
+  CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_s, double *sm_clock_mhz) {
+  DevInfo *d;
+  int rc = dev_info(device, &d);
+  if (rc) return rc;
+  CU(cudaSetDevice(device));
+  uint32_t *sink = nullptr;
+  CU(cudaMalloc((void **)&sink, 4));
+  const int grid = d->sms * 8, block = 256;
+  int iters = 2000;
+  double best = 0;
+  for (int pass = 0; pass < 4; ++pass) {
+    CU(cudaEventRecord(d->ev0, 0));
+    qec_launch_int_peak(0, grid, block, iters, sink);
+    CU(cudaEventRecord(d->ev1, 0));
+    CU(cudaEventSynchronize(d->ev1));
+    float t = 0;
+    CU(cudaEventElapsedTime(&t, d->ev0, d->ev1));
+    const double ops = (double)grid * block * (double)iters * 16.0 * 8.0;
+    if (t > 0) best = std::max(best, ops / (t * 1e-3));
+    if (pass == 0 && t > 0) iters = (int)std::max(2000.0, std::min(4e6, iters * (ms / t)));
+  }
+  cudaFree(sink);
+  int khz = 0;
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
+  if (lane_ops_per_s) *lane_ops_per_s = best;
+  if (sm_clock_mhz) *sm_clock_mhz = khz / 1000.0;
+  return 0;
+}
+
+#define DEV_ENTER(device) { DevInfo *d__; int rc__ = dev_info(device, &d__); if (rc__) return rc__; CU(cudaSetDevice(device)); }
+extern "C" int qec_dev_alloc(int device, size_t bytes, void **out) {
+  DEV_ENTER(device);
+  CU(cudaMalloc(out, bytes ? bytes : 1));
+  return 0;
+}
+extern "C" int qec_dev_free(int device, void *p) { DEV_ENTER(device); CU(cudaFree(p)); return 0; }
+extern "C" int qec_dev_memset(int device, void *p, int value, size_t bytes, void *stream) {
+  DEV_ENTER(device);
+  CU(cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int qec_dev_to_host(int device, void *host, const void *dev, size_t bytes, void *stream) {
+  DEV_ENTER(device);
+  CU(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int qec_host_to_dev(int device, void *dev, const void *host, size_t bytes, void *stream) {
+  DEV_ENTER(device);
+  CU(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return 0;
+}
+extern "C" int qec_host_alloc_pinned(size_t bytes, void **out) { CU(cudaMallocHost(out, bytes ? bytes : 1)); return 0; }
+extern "C" int qec_host_free_pinned(void *p) { CU(cudaFreeHost(p)); return 0; }
+extern "C" int qec_stream_sync(int device, void *stream) {
+  DEV_ENTER(device);
+  CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}

@@ -1,0 +1,186 @@
+// qec_device.cuh -- shared host/device definitions and the frame-propagation core.
+//
+// Data layout:
+//   * gate table: one packed uint32 per op, padded with NOPs to a multiple of 4 so a warp
+//     streams it with one uniform 128-bit load per 4 gates.
+//       bits 0..3  internal opcode (QOP_*), bits 4..17 operand a, bits 18..31 operand b
+//   * frame: bit-packed, 32 paths per uint32 "lane word".  One thread owns one lane word;
+//     its 2*nq frame words live in shared memory at frame[row * T + tid] (row = qubit for X,
+//     nq + qubit for Z), so consecutive threads hit consecutive banks.
+//   * fault events of one lane word: uint32 = op << 9 | path_bit << 4 | pauli_code, sorted by
+//     op (stable); inside one (op, path_bit) group the LAST event wins, which is the
+//     reference's `fail[icomb[j]] = j` rule (errorpropagator.cpp:265-267).
+//   * packed outcomes: out[c * n_words + w].
+#pragma once
+#include <stdint.h>
+
+#define QOP_NOP 0u    // x, y, z, id (b = 0: may host a fault); barrier, padding (b = 1)
+#define QOP_H 1u
+#define QOP_S 2u
+#define QOP_CX 3u
+#define QOP_RESET 4u
+#define QOP_MEAS 5u   // measure whose clbit is overwritten later (value is dead)
+#define QOP_MEASF 6u  // measure that is the final write to its clbit
+#define QOP_ZEROC 7u  // pseudo-op appended by the lowering: clbit `a` is never measured
+
+#define QEC_EV_SENTINEL 0xFFFFFFFFu
+#define QEC_EV_OP_SHIFT 9
+
+static inline __host__ __device__ uint32_t qec_pack_op(uint32_t opc, uint32_t a, uint32_t b) {
+  return (opc & 15u) | ((a & 0x3FFFu) << 4) | ((b & 0x3FFFu) << 18);
+}
+
+struct QecCircuitDev {
+  int nq, nc, n_ops, n_ops4;  // n_ops4 = padded op count / 4 (includes ZEROC pseudo-ops)
+  const uint32_t *ops;        // device, n_ops4 * 4 words
+};
+
+struct QecOutDev {
+  uint32_t *bits;              // [nc][n_words] or nullptr
+  uint32_t *frame;             // [2*nq][n_words] or nullptr
+  unsigned long long *tally;   // QEC_TALLY_LEN(nc) or nullptr (accumulated with atomics)
+  long long n_words;
+};
+
+#ifdef __CUDACC__
+
+// One lane word through the whole gate table.  `fr` points at this thread's column of the
+// shared-memory frame (stride T).  Events come from ev[k * ev_stride], k < n_ev.
+// Gate semantics: reference errorpropagator.cpp:211-254 (cx/h/s/reset/measure) and
+// :272-310 (fault after the gate, except measure where it comes first).
+template <bool TALLY>
+__device__ __forceinline__ void qec_propagate_word(const QecCircuitDev &C, uint32_t *fr,
+                                                   const int T, const uint32_t *ev,
+                                                   const long long ev_stride, const int n_ev,
+                                                   const bool valid, const long long w,
+                                                   const QecOutDev &O, uint32_t *s_tally,
+                                                   uint32_t &any_out) {
+  const int nq = C.nq;
+  for (int r = 0; r < 2 * nq; ++r) fr[r * T] = 0u;
+  int ei = 0;
+  uint32_t cur = (n_ev > 0) ? ev[0] : QEC_EV_SENTINEL;
+  uint32_t nxt = (n_ev > 1) ? ev[ev_stride] : QEC_EV_SENTINEL;
+  uint32_t cur_op = cur >> QEC_EV_OP_SHIFT;
+  const uint4 *ops4 = reinterpret_cast<const uint4 *>(C.ops);
+  uint32_t *obits = (valid && O.bits) ? O.bits + w : nullptr;
+  const long long ostride = O.n_words;
+  const unsigned lane = threadIdx.x & 31u;
+
+  uint4 g4 = __ldg(ops4);
+  for (int i4 = 0; i4 < C.n_ops4; ++i4) {
+    const uint4 gcur = g4;
+    if (i4 + 1 < C.n_ops4) g4 = __ldg(ops4 + i4 + 1);  // prefetch next 4 gates
+    const uint32_t gs[4] = {gcur.x, gcur.y, gcur.z, gcur.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t g = gs[j];
+      const uint32_t opc = g & 15u;
+      const uint32_t a = (g >> 4) & 0x3FFFu;
+      const uint32_t b = g >> 18;
+      const uint32_t idx = (uint32_t)(i4 * 4 + j);
+      uint32_t mxa = 0u, mza = 0u, mxb = 0u, mzb = 0u;
+      const bool hit = (cur_op == idx);
+      if (hit) {
+        // gather this op's events into per-bit masks; a later event on the same path bit
+        // overwrites an earlier one (last duplicate wins)
+        do {
+          const uint32_t bm = 1u << ((cur >> 4) & 31u);
+          const uint32_t code = cur & 15u;
+          mxa = (mxa & ~bm) | ((0u - (code & 1u)) & bm);
+          mza = (mza & ~bm) | ((0u - ((code >> 1) & 1u)) & bm);
+          mxb = (mxb & ~bm) | ((0u - ((code >> 2) & 1u)) & bm);
+          mzb = (mzb & ~bm) | ((0u - ((code >> 3) & 1u)) & bm);
+          ++ei;
+          cur = nxt;
+          nxt = (ei + 1 < n_ev) ? ev[(long long)(ei + 1) * ev_stride] : QEC_EV_SENTINEL;
+          cur_op = cur >> QEC_EV_OP_SHIFT;
+        } while (cur_op == idx);
+      }
+      uint32_t *xa = fr + a * T;
+      uint32_t *za = fr + (nq + a) * T;
+      if (opc == QOP_MEAS || opc == QOP_MEASF) {
+        uint32_t v = *xa;
+        if (hit) {  // fault BEFORE the measurement
+          v ^= mxa;
+          *xa = v;
+          *za ^= mza;
+        }
+        if (opc == QOP_MEASF) {
+          if (obits) obits[(long long)b * ostride] = v;
+          if (TALLY) {
+            any_out |= v;
+            int cnt = __popc(v);
+            cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+            if (lane == 0 && cnt) atomicAdd(&s_tally[b], (uint32_t)cnt);
+          }
+        }
+      } else if (opc == QOP_CX) {
+        uint32_t *xb = fr + b * T;
+        uint32_t *zb = fr + (nq + b) * T;
+        const uint32_t vxa = *xa, vzb = *zb;
+        uint32_t vxb = *xb ^ vxa;
+        uint32_t vza = *za ^ vzb;
+        if (hit) {
+          *xa = vxa ^ mxa;
+          *zb = vzb ^ mzb;
+          vxb ^= mxb;
+          vza ^= mza;
+        }
+        *xb = vxb;
+        *za = vza;
+      } else if (opc == QOP_H) {
+        const uint32_t vx = *xa, vz = *za;
+        *xa = vz ^ mxa;
+        *za = vx ^ mza;
+      } else if (opc == QOP_RESET) {
+        *xa = mxa;
+        *za = mza;
+      } else if (opc == QOP_S) {
+        const uint32_t vx = *xa;
+        *za = (*za ^ vx) ^ mza;
+        if (hit) *xa = vx ^ mxa;
+      } else if (opc == QOP_ZEROC) {
+        if (obits) obits[(long long)a * ostride] = 0u;
+      } else {  // NOP: only a fault, if any (b != 0 marks a barrier: faults ignored)
+        if (hit && b == 0u) {
+          *xa ^= mxa;
+          *za ^= mza;
+        }
+      }
+    }
+  }
+  if (valid && O.frame) {
+    for (int r = 0; r < 2 * nq; ++r) O.frame[(long long)r * O.n_words + w] = fr[r * T];
+  }
+}
+
+// ---- Philox4x32-10 (Salmon et al. 2011), counter-based ------------------------------
+struct QecPhilox {
+  uint32_t c[4];
+};
+__device__ __forceinline__ QecPhilox qec_philox(uint32_t c0, uint32_t c1, uint32_t c2,
+                                                uint32_t c3, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  QecPhilox o;
+  o.c[0] = c0; o.c[1] = c1; o.c[2] = c2; o.c[3] = c3;
+  return o;
+}
+
+// number of entries of the non-increasing table t[0..n) that are > r
+__device__ __forceinline__ uint32_t qec_count_greater(const uint32_t *t, uint32_t n, uint32_t r) {
+  uint32_t lo = 0, hi = n;  // invariant: t[<lo] > r, t[>=hi] <= r
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (t[mid] > r) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+#endif  // __CUDACC__

@@ -1,0 +1,426 @@
+// qec_kernels.cu -- sm_100a kernels of the fault-analysis hot path.
+//
+//   k_propagate_batch  (K1) explicit fault lists            <- ErrorPropagator::propagate
+//   k_enumerate<K>     (K2) in-kernel unranking of order-K  <- FaultEnumerator::enumerate
+//   k_sample           (K3) Philox fault sampling           <- FaultSampler::sample
+//   k_outcome_hist     (K4) hashed full-outcome histogram
+//   k_int_peak              LOP3 throughput microbenchmark (roofline denominator)
+//
+// All three propagation kernels are persistent: grid = SMs x resident CTAs, each CTA walks
+// chunks of T lane words (T*32 paths); one thread owns one lane word whose frame lives in
+// shared memory (qec_device.cuh).  GF(2) bit logic: no tensor cores by design.
+#include <cuda_runtime.h>
+#include "qec_kernels.cuh"
+
+namespace {
+
+// shared memory carve-up: [frame 2*nq*T][tally nc][hist 64][misc 4][tables ...]
+__device__ __forceinline__ uint32_t *smem_base() {
+  extern __shared__ __align__(16) uint32_t qec_smem[];
+  return qec_smem;
+}
+
+__device__ __forceinline__ void flush_tally(const QecCircuitDev &C, const QecOutDev &O,
+                                            uint32_t *s_tally, uint32_t *s_hist, bool with_hist,
+                                            unsigned long long nz_local, long long n_paths) {
+  // nonzero-outcome count: warp reduce then one atomic per warp
+  unsigned long long nz = nz_local;
+  for (int off = 16; off > 0; off >>= 1) nz += __shfl_down_sync(0xFFFFFFFFu, nz, off);
+  if ((threadIdx.x & 31) == 0 && nz) atomicAdd(&O.tally[C.nc], nz);
+  __syncthreads();
+  for (int c = threadIdx.x; c < C.nc; c += blockDim.x) {
+    const uint32_t v = s_tally[c];
+    if (v) atomicAdd(&O.tally[c], (unsigned long long)v);
+  }
+  if (with_hist) {
+    for (int c = threadIdx.x; c < 64; c += blockDim.x) {
+      const uint32_t v = s_hist[c];
+      if (v) atomicAdd(&O.tally[C.nc + 2 + c], (unsigned long long)v);
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    atomicAdd(&O.tally[C.nc + 1], (unsigned long long)n_paths);
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: explicit fault lists, prepared per lane word (CSR) by the host side of the C ABI.
+__global__ void __launch_bounds__(256)
+k_propagate_batch(const QecCircuitDev C, const QecOutDev O, const long long *__restrict__ ev_off,
+                  const uint32_t *__restrict__ ev) {
+  uint32_t *sm = smem_base();
+  const int T = blockDim.x;
+  uint32_t *fr = sm + threadIdx.x;
+  uint32_t any = 0;
+  for (long long ch = blockIdx.x; ch * T < O.n_words; ch += gridDim.x) {
+    const long long w = ch * T + threadIdx.x;
+    const bool valid = w < O.n_words;
+    long long base = 0;
+    int n = 0;
+    if (valid) {
+      base = ev_off[w];
+      n = (int)(ev_off[w + 1] - base);
+    }
+    qec_propagate_word<false>(C, fr, T, ev + base, 1, n, valid, w, O, nullptr, any);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: order-K enumeration.  Rank -> (k-subset, Pauli digits) by closed-form unranking over
+// the suffix tables E[m][l]; the following 31 paths of the lane word by successor steps.
+// Order of paths: reference combinations.cpp:18-32 (lexicographic subsets) and
+// productiterator.cpp:17-32 (last digit fastest).
+template <int K>
+struct EnumState {
+  uint32_t loc[K], dig[K], np[K], op[K], pb[K];
+};
+
+template <int K>
+__device__ __forceinline__ void enum_load(const QecEnumDev &E, EnumState<K> &s, int j) {
+  const uint32_t l = s.loc[j];
+  s.np[j] = E.npaul[l];
+  s.op[j] = E.lop[l];
+  s.pb[j] = E.poff[l];
+}
+
+template <int K>
+__device__ __forceinline__ void enum_unrank(const QecEnumDev &E, unsigned long long r,
+                                            EnumState<K> &s) {
+  const int L2 = E.L + 2;
+  unsigned long long mult = 1;
+  uint32_t start = 0;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    const unsigned long long *Em = E.E + (size_t)(K - j) * L2;
+    const unsigned long long u = r / mult;
+    const unsigned long long thr = Em[start] - u;  // >= 1
+    // largest l in [start, L] with Em[l] >= thr (Em non-increasing, Em[L] = 0 < thr)
+    uint32_t lo = start, hi = (uint32_t)E.L;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (Em[mid] >= thr) lo = mid; else hi = mid;
+    }
+    r -= mult * (Em[start] - Em[lo]);
+    s.loc[j] = lo;
+    enum_load<K>(E, s, j);
+    mult *= s.np[j];
+    start = lo + 1;
+  }
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    s.dig[j] = (uint32_t)(r % s.np[j]);
+    r /= s.np[j];
+  }
+}
+
+// advance to the next path; returns false past the last one
+template <int K>
+__device__ __forceinline__ bool enum_next(const QecEnumDev &E, EnumState<K> &s) {
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    if (++s.dig[j] < s.np[j]) return true;
+    s.dig[j] = 0;
+  }
+  int i = K - 1;
+  while (i >= 0 && s.loc[i] >= (uint32_t)(E.L - K + i)) --i;
+  if (i < 0) return false;
+  const uint32_t base = s.loc[i] + 1;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    if (j >= i) {
+      s.loc[j] = base + (uint32_t)(j - i);
+      enum_load<K>(E, s, j);
+    }
+  }
+  return true;
+}
+
+template <int K, bool TALLY>
+__global__ void __launch_bounds__(256)
+k_enumerate(const QecCircuitDev C, const QecOutDev O, const QecEnumDev E, const long long lo,
+            const long long hi, uint32_t *__restrict__ scratch) {
+  uint32_t *sm = smem_base();
+  const int T = blockDim.x;
+  uint32_t *fr = sm + threadIdx.x;
+  uint32_t *s_tally = sm + (size_t)2 * C.nq * T;
+  if (TALLY) {
+    for (int c = threadIdx.x; c < C.nc; c += T) s_tally[c] = 0;
+    __syncthreads();
+  }
+  const long long stride = (long long)gridDim.x * T;
+  uint32_t *ev = scratch + (long long)blockIdx.x * T + threadIdx.x;
+  unsigned long long nz = 0;
+  for (long long ch = blockIdx.x; ch * T < O.n_words; ch += gridDim.x) {
+    const long long w = ch * T + threadIdx.x;
+    const bool valid = w < O.n_words;
+    int n_ev = 0;
+    if (valid) {
+      const long long r0 = lo + 32 * w;
+      const int nv = (int)min((long long)32, hi - r0);
+      EnumState<K> s;
+      enum_unrank<K>(E, (unsigned long long)r0, s);
+      for (int bit = 0; bit < nv; ++bit) {
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          const uint32_t code = E.pcode[s.pb[j] + s.dig[j]];
+          const uint32_t e = (s.op[j] << QEC_EV_OP_SHIFT) | ((uint32_t)bit << 4) | code;
+          // stable insertion by op: emission is nearly sorted already
+          int p = n_ev;
+          while (p > 0) {
+            const uint32_t q = ev[(long long)(p - 1) * stride];
+            if ((q >> QEC_EV_OP_SHIFT) <= s.op[j]) break;
+            ev[(long long)p * stride] = q;
+            --p;
+          }
+          ev[(long long)p * stride] = e;
+          ++n_ev;
+        }
+        if (bit + 1 < nv) enum_next<K>(E, s);
+      }
+    }
+    uint32_t any = 0;
+    qec_propagate_word<TALLY>(C, fr, T, ev, stride, n_ev, valid, w, O, s_tally, any);
+    if (TALLY) nz += __popc(any);
+  }
+  if (TALLY) flush_tally(C, O, s_tally, nullptr, false, nz, hi - lo);
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: fault sampling.  Geometric-gap skipping over the word's slot space (sorted location x
+// 32 shots) at rate pmax, thinned to each class's probability; all 32 lanes of a warp draw
+// in lockstep.  Every random decision is a 32-bit integer compare against a host-built
+// table, so a CPU restatement reproduces the fault lists bit for bit.
+template <bool TALLY>
+__global__ void __launch_bounds__(256)
+k_sample(const QecCircuitDev C, const QecOutDev O, const QecSamplerDev S, const long long word_lo,
+         const long long n_shots, uint32_t *__restrict__ scratch, const int cap,
+         const QecSampleExport X, uint32_t *__restrict__ overflow_flag) {
+  uint32_t *sm = smem_base();
+  const int T = blockDim.x;
+  uint32_t *fr = sm + threadIdx.x;
+  uint32_t *s_tally = sm + (size_t)2 * C.nq * T;
+  uint32_t *s_hist = s_tally + C.nc;
+  uint32_t *s_T1 = s_hist + 64;
+  uint32_t *s_T2 = s_T1 + S.K1;
+  for (int c = threadIdx.x; c < C.nc + 64; c += T) s_tally[c] = 0;
+  for (uint32_t i = threadIdx.x; i < S.K1; i += T) s_T1[i] = S.T1[i];
+  for (uint32_t i = threadIdx.x; i < S.B; i += T) s_T2[i] = S.T2[i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * T;
+  uint32_t *ev = scratch + (long long)blockIdx.x * T + threadIdx.x;
+  unsigned long long nz = 0;
+  for (long long ch = blockIdx.x; ch * T < O.n_words; ch += gridDim.x) {
+    const long long w = ch * T + threadIdx.x;
+    const bool valid = w < O.n_words;
+    int n_ev = 0;
+    if (valid) {
+      const int nv = (int)min((long long)32, n_shots - 32 * w);
+      const unsigned long long gw = (unsigned long long)(word_lo + w);
+      const uint32_t wlo = (uint32_t)gw, whi = (uint32_t)(gw >> 32);
+      uint32_t draw = 0;
+      long long slot = -1;
+      uint32_t cp[6] = {0, 0, 0, 0, 0, 0};  // bit-sliced per-shot fault counters
+      uint32_t *xev = X.cnt ? X.ev + w * (long long)X.cap : nullptr;
+      for (;;) {
+        QecPhilox r;
+        unsigned long long skip = 0;
+        for (;;) {
+          r = qec_philox(wlo, whi, draw++, 0u, S.k0, S.k1);
+          const uint32_t a = qec_count_greater(s_T1, S.K1, r.c[0]);
+          skip += (unsigned long long)a * S.B;
+          if (a < S.K1 || skip >= (unsigned long long)S.n_slots) break;  // a == K1: truncated table, keep drawing
+        }
+        const uint32_t b = qec_count_greater(s_T2 + 1, S.B - 1, r.c[1]);
+        slot += 1 + (long long)skip + b;
+        if (slot >= S.n_slots) break;
+        const uint32_t sl = (uint32_t)(slot >> 5), bit = (uint32_t)slot & 31u;
+        const uint32_t cls = S.slcls[sl];
+        if (!S.cls_always[cls] && r.c[2] >= S.cls_acc[cls]) continue;
+        const uint32_t base = S.cls_off[cls], np = S.cls_off[cls + 1] - base;
+        uint32_t d = 0;
+        while (d + 1 < np && r.c[3] >= S.cdf[base + d]) ++d;
+        if ((int)bit >= nv) continue;  // shot past the end of the range
+        if (n_ev < cap)
+          ev[(long long)n_ev * stride] =
+              (S.slop[sl] << QEC_EV_OP_SHIFT) | (bit << 4) | S.codes[base + d];
+        if (xev && n_ev < X.cap) xev[n_ev] = (S.slloc[sl] << 14) | (bit << 9) | d;
+        ++n_ev;
+        if (TALLY) {
+          uint32_t carry = 1u << bit;
+#pragma unroll
+          for (int p = 0; p < 6; ++p) {
+            const uint32_t t = cp[p] & carry;
+            cp[p] ^= carry;
+            carry = t;
+          }
+          if (carry) {
+#pragma unroll
+            for (int p = 0; p < 6; ++p) cp[p] |= carry;  // saturate at 63
+          }
+        }
+      }
+      if (X.cnt) X.cnt[w] = (uint32_t)n_ev;
+      if (n_ev > cap) {
+        atomicMax(overflow_flag, (uint32_t)n_ev);
+        n_ev = cap;
+      }
+      if (TALLY) {
+        for (int bit = 0; bit < nv; ++bit) {
+          uint32_t k = 0;
+#pragma unroll
+          for (int p = 0; p < 6; ++p) k |= ((cp[p] >> bit) & 1u) << p;
+          atomicAdd(&s_hist[k], 1u);
+        }
+      }
+    }
+    uint32_t any = 0;
+    qec_propagate_word<TALLY>(C, fr, T, ev, stride, n_ev, valid, w, O, s_tally, any);
+    if (TALLY) nz += __popc(any);
+  }
+  if (TALLY) flush_tally(C, O, s_tally, s_hist, true, nz, n_shots);
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: hashed full-outcome histogram over a bit-sliced outcome buffer.  One warp per lane
+// word: lane j loads clbit row c0+j, 32 ballots transpose the 32x32 bit tile so lane b ends
+// up holding clbits c0..c0+31 of path b; tiles are folded into a 64-bit hash.
+__device__ __forceinline__ unsigned long long qec_mix64(unsigned long long h, uint32_t chunk) {
+  h ^= (unsigned long long)chunk;
+  h *= 0x9E3779B97F4A7C15ull;
+  h ^= h >> 29;
+  return h;
+}
+
+__global__ void __launch_bounds__(256)
+k_outcome_hist(const uint32_t *__restrict__ bits, const int nc, const long long n_paths,
+               unsigned long long *__restrict__ keys, unsigned long long *__restrict__ counts,
+               const long long table_cap) {
+  const long long n_words = (n_paths + 31) / 32;
+  const unsigned lane = threadIdx.x & 31u;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long w = warp; w < n_words; w += n_warps) {
+    unsigned long long h = 0x243F6A8885A308D3ull;
+    for (int c0 = 0; c0 < nc; c0 += 32) {
+      const int c = c0 + (int)lane;
+      const uint32_t row = (c < nc) ? bits[(long long)c * n_words + w] : 0u;
+      uint32_t mine = 0;
+#pragma unroll
+      for (int b = 0; b < 32; ++b) {
+        const uint32_t col = __ballot_sync(0xFFFFFFFFu, (row >> b) & 1u);
+        if ((int)lane == b) mine = col;
+      }
+      h = qec_mix64(h, mine);
+    }
+    h ^= h >> 32;
+    if (h == 0) h = 1;  // 0 marks an empty slot
+    if (32 * w + lane < n_paths) {
+      unsigned long long slot = h & (unsigned long long)(table_cap - 1);
+      for (long long probe = 0; probe < table_cap; ++probe) {
+        const unsigned long long prev = atomicCAS(&keys[slot], 0ull, h);
+        if (prev == 0ull || prev == h) {
+          atomicAdd(&counts[slot], 1ull);
+          break;
+        }
+        slot = (slot + 1) & (unsigned long long)(table_cap - 1);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Integer-pipe roofline denominator: 8 independent LOP3 chains per thread, no memory.
+__global__ void __launch_bounds__(256) k_int_peak(const int iters, uint32_t *__restrict__ sink) {
+  uint32_t a0 = threadIdx.x, a1 = a0 * 3u + 1u, a2 = a0 * 5u + 2u, a3 = a0 * 7u + 3u;
+  uint32_t a4 = a0 ^ 0x55u, a5 = a0 ^ 0xAAu, a6 = a0 + 11u, a7 = a0 + 13u;
+  const uint32_t k0 = blockIdx.x * 0x9E3779B9u + 1u, k1 = ~k0;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      // each statement is one 3-input logic op (LOP3) on an independent chain
+      a0 = (a0 & k0) ^ a1; a1 = (a1 | k1) ^ a2; a2 = (a2 & k0) ^ a3; a3 = (a3 | k1) ^ a4;
+      a4 = (a4 & k0) ^ a5; a5 = (a5 | k1) ^ a6; a6 = (a6 & k0) ^ a7; a7 = (a7 | k1) ^ a0;
+    }
+  }
+  const uint32_t r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+  if (r == 0x12345678u) sink[0] = r;  // practically never: keeps the chains live
+}
+
+}  // namespace
+
+// ---- launchers -----------------------------------------------------------------------------
+size_t qec_kernel_smem_bytes(int kind, int nq, int nc, int T, uint32_t B, uint32_t K1) {
+  size_t words = (size_t)2 * nq * T;
+  if (kind >= 1) words += (size_t)nc;            // tally
+  if (kind == 2) words += 64 + (size_t)B + K1;   // hist + gap tables
+  return words * sizeof(uint32_t) + 16;
+}
+
+void qec_launch_batch(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
+                      const QecOutDev &O, const long long *ev_off, const uint32_t *ev) {
+  k_propagate_batch<<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, ev_off, ev);
+}
+
+template <int K>
+static void launch_enum_k(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
+                          const QecOutDev &O, const QecEnumDev &E, long long lo, long long hi,
+                          uint32_t *scratch) {
+  if (O.tally)
+    k_enumerate<K, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch);
+  else
+    k_enumerate<K, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch);
+}
+
+void qec_launch_enumerate(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
+                          const QecOutDev &O, const QecEnumDev &E, long long lo, long long hi,
+                          uint32_t *scratch) {
+  switch (E.order) {
+    case 1: launch_enum_k<1>(cfg, stream, C, O, E, lo, hi, scratch); break;
+    case 2: launch_enum_k<2>(cfg, stream, C, O, E, lo, hi, scratch); break;
+    case 3: launch_enum_k<3>(cfg, stream, C, O, E, lo, hi, scratch); break;
+    default: launch_enum_k<4>(cfg, stream, C, O, E, lo, hi, scratch); break;
+  }
+}
+
+void qec_launch_sample(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
+                       const QecOutDev &O, const QecSamplerDev &S, long long word_lo,
+                       long long n_shots, uint32_t *scratch, int cap, const QecSampleExport &X,
+                       uint32_t *overflow_flag) {
+  if (O.tally)
+    k_sample<true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, S, word_lo, n_shots, scratch,
+                                                            cap, X, overflow_flag);
+  else
+    k_sample<false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, S, word_lo, n_shots, scratch,
+                                                             cap, X, overflow_flag);
+}
+
+void qec_launch_outcome_hist(cudaStream_t stream, const uint32_t *bits, int nc, long long n_paths,
+                             unsigned long long *keys, unsigned long long *counts,
+                             long long table_cap) {
+  const long long n_words = (n_paths + 31) / 32;
+  long long blocks = (n_words * 32 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  k_outcome_hist<<<(int)blocks, 256, 0, stream>>>(bits, nc, n_paths, keys, counts, table_cap);
+}
+
+void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink) {
+  k_int_peak<<<grid, block, 0, stream>>>(iters, sink);
+}
+
+int qec_kernel_set_smem_attr(int kind, int order, size_t smem) {
+  cudaError_t e = cudaSuccess;
+  const int s = (int)smem;
+#define QEC_SET(fn) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, s); \
+  if (e != cudaSuccess) return (int)e;
+  if (kind == 0) { QEC_SET(k_propagate_batch) }
+  else if (kind == 1) {
+    switch (order) {
+      case 1: QEC_SET((k_enumerate<1, true>)) QEC_SET((k_enumerate<1, false>)) break;
+      case 2: QEC_SET((k_enumerate<2, true>)) QEC_SET((k_enumerate<2, false>)) break;
+      case 3: QEC_SET((k_enumerate<3, true>)) QEC_SET((k_enumerate<3, false>)) break;
+      default: QEC_SET((k_enumerate<4, true>)) QEC_SET((k_enumerate<4, false>)) break;
+    }
+  } else { QEC_SET(k_sample<true>) QEC_SET(k_sample<false>) }
+#undef QEC_SET
+  return 0;
+}
