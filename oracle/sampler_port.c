@@ -1,0 +1,80 @@
+/*
+ * sampler_port.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement of THIS repository's counter-based fault sampler (the kernel k_sample in
+ * qiskit_qec_b200/csrc/qec_kernels.cu), so that tests can demand the GPU's sampled fault
+ * lists bit for bit.  It has no reference counterpart: the reference draws from one
+ * sequential std::mt19937 stream through libstdc++ distributions (reference
+ * src/qiskit_qec/analysis/intern/faultsampler.cpp:49-77), which no parallel sampler can
+ * reproduce; against the reference the sampler is checked statistically (binomial 5 sigma)
+ * and by replaying these fault lists through the reference propagate().
+ * What it keeps from the reference: per (shot, location) an independent Bernoulli(p_label)
+ * failure (:55-60), then a Pauli drawn from the label's discrete weights (:64-71).
+ *
+ * Input: the fixed-point tables exactly as qec_sampler_tables() serialises them
+ * (header[8] = B, K1, n_classes, L, n_paulis, seed_lo, seed_hi, active; then T1[K1], T2[B],
+ * slop[L], slloc[L], slcls[L], cls_acc[n], cls_always[n], cls_off[n+1], cdf[np], codes[np]).
+ */
+#include <stdint.h>
+
+static void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c[0], p1 = (uint64_t)0xCD9E8D57u * c[2];
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0, n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1;
+    c[0] = n0; c[1] = (uint32_t)p1; c[2] = n2; c[3] = (uint32_t)p0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+}
+
+/* entries of the non-increasing table t[0..n) that are > r */
+static uint32_t count_greater(const uint32_t *t, uint32_t n, uint32_t r) {
+  uint32_t k = 0;
+  while (k < n && t[k] > r) ++k;
+  return k;
+}
+
+/* Philox4x32-10 known-answer hook for the tests (Random123 kat vectors) */
+void orc_philox(uint32_t c[4], uint32_t k0, uint32_t k1) { philox4x32_10(c, k0, k1); }
+
+/*
+ * Fault events of the 32-shot word `gw` (global word index), of which the first `nv` shots
+ * are inside the requested range.  ev_out[cap] receives location << 14 | shot_bit << 9 |
+ * digit in generation order (sorted location major).  Returns the number of events (may
+ * exceed cap; extra events are counted but not stored).
+ */
+int orc_sample_word(const uint32_t *tab, uint64_t gw, int nv, uint32_t *ev_out, int cap) {
+  const uint32_t B = tab[0], K1 = tab[1], ncls = tab[2], L = tab[3], np = tab[4];
+  const uint32_t k0 = tab[5], k1 = tab[6], active = tab[7];
+  const uint32_t *T1 = tab + 8, *T2 = T1 + K1, *slop = T2 + B, *slloc = slop + L;
+  const uint32_t *slcls = slloc + L, *cls_acc = slcls + L, *cls_always = cls_acc + ncls;
+  const uint32_t *cls_off = cls_always + ncls, *cdf = cls_off + ncls + 1, *codes = cdf + np;
+  (void)slop; (void)codes;
+  const int64_t n_slots = active ? (int64_t)L * 32 : 0;
+  int64_t slot = -1;
+  uint32_t draw = 0;
+  int n = 0;
+  for (;;) {
+    uint32_t c[4];
+    uint64_t skip = 0;
+    for (;;) {
+      c[0] = (uint32_t)gw; c[1] = (uint32_t)(gw >> 32); c[2] = draw++; c[3] = 0;
+      philox4x32_10(c, k0, k1);
+      const uint32_t a = count_greater(T1, K1, c[0]);
+      skip += (uint64_t)a * B;
+      if (a < K1 || skip >= (uint64_t)n_slots) break;
+    }
+    const uint32_t b = count_greater(T2 + 1, B - 1, c[1]);
+    slot += 1 + (int64_t)skip + b;
+    if (slot >= n_slots) break;
+    const uint32_t sl = (uint32_t)(slot >> 5), bit = (uint32_t)slot & 31u;
+    const uint32_t cls = slcls[sl];
+    if (!cls_always[cls] && c[2] >= cls_acc[cls]) continue;
+    const uint32_t base = cls_off[cls], npc = cls_off[cls + 1] - base;
+    uint32_t d = 0;
+    while (d + 1 < npc && c[3] >= cdf[base + d]) ++d;
+    if ((int)bit >= nv) continue;
+    if (n < cap) ev_out[n] = (slloc[sl] << 14) | (bit << 9) | d;
+    ++n;
+  }
+  return n;
+}

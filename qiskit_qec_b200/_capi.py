@@ -265,6 +265,13 @@ class Sampler:
             _check(rc)
             return out, tally, cnt, ev
 
+    def sample_host_ptr(self, shot_lo: int, n_shots: int, out_ptr: int, tally_ptr: int = 0):
+        """Host entry point with raw (ideally pinned) host addresses: kernel + D2H inside."""
+        need = C.c_int()
+        _check(lib().qec_sampler_sample(self._h, C.c_int64(shot_lo), C.c_int64(n_shots),
+                                        C.c_void_p(out_ptr or None), C.c_void_p(tally_ptr or None),
+                                        None, None, C.c_int(0), C.byref(need)))
+
     def sample_dev(self, shot_lo: int, n_shots: int, d_bits: int, d_tally: int, stream: int = 0):
         _check(lib().qec_sampler_sample_dev(self._h, C.c_int64(shot_lo), C.c_int64(n_shots),
                                             C.c_void_p(d_bits or None), C.c_void_p(d_tally or None),

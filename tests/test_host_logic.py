@@ -1,0 +1,76 @@
+"""CPU checks of the host-side mirror: circuit emitters, noise model, location tagging."""
+
+import pytest
+
+from qiskit_qec_b200.circuits import (arc_circuit, heavy_hex_27_arc_layout,
+                                      repetition_code_circuit, surface_code_circuit)
+from qiskit_qec_b200.locations import tag_fault_locations
+from qiskit_qec_b200.noise import PauliNoiseModel, standard_depolarizing_model
+
+
+def test_baseline_circuit_shapes():
+    """sizes stated in SURVEY.md section 8 header"""
+    c = repetition_code_circuit(3, 2)
+    assert (c.nq, c.nc, len(c)) == (5, 7, 15)
+    assert c.ops == [[5, 2, 0], [5, 3, 1], [5, 3, 0], [5, 4, 1], [8, 0, 0], [8, 1, 1], [5, 2, 0],
+                     [5, 3, 1], [5, 3, 0], [5, 4, 1], [8, 0, 2], [8, 1, 3], [8, 2, 4], [8, 3, 5],
+                     [8, 4, 6]]
+    c = surface_code_circuit(5, 5)
+    assert (c.nq, c.nc, len(c)) == (49, 145, 761)
+    assert c.gate_counts() == {"h": 120, "cx": 400, "measure": 145, "reset": 96}
+    assert c.algorithmic_bit_ops() == 1377
+    assert c.creg_sizes == [12, 12] * 5 + [25]
+    c = surface_code_circuit(11, 11)
+    assert (c.nq, c.nc, len(c)) == (241, 1441, 8801) and c.algorithmic_bit_ops() == 16161
+    links, sched, color = heavy_hex_27_arc_layout()
+    c = arc_circuit(links, 3, "zx", sched, color)
+    assert c.nq == 21 and c.nc == 3 * 11 + 10
+    for layer in sched:  # a layer never touches a qubit twice
+        used = [q for pair in layer for q in pair]
+        assert len(used) == len(set(used))
+    assert all(color[a] != color[b] for a, _, b in links)
+
+
+def test_surface_code_x_basis_and_logical_one():
+    c = surface_code_circuit(3, 1, basis="x", logical="1")
+    assert [r[0] for r in c.ops[:9]] == [0] * 9 and [r[0] for r in c.ops[9:12]] == [4] * 3
+    assert repetition_code_circuit(3, 1, logical="1").ops[:3] == [[2, 2], [2, 3], [2, 4]]
+
+
+def test_noise_model_mirrors_reference():
+    """reference test/test_paulinoisemodel.py: normalisation, scale factors, errors"""
+    m = PauliNoiseModel()
+    m.add_operation("cx", {"ix": 1, "xi": 1, "xx": 1})
+    m.add_operation("h", {"x": 2, "z": 6})
+    assert m.get_pauli_weight("cx", "ix") == pytest.approx(1 / 3)
+    assert m.get_pauli_weight("h", "z") == pytest.approx(0.75)
+    assert m.get_pauli_weight("h", "y") == 0
+    assert m.get_operations() == ["cx", "h"]
+    assert m.get_pauli_error_types() == {"cx": ["ix", "xi", "xx"], "h": ["x", "z"]}
+    with pytest.raises(Exception, match="no error probability"):
+        m.get_error_probability("h")
+    m.set_scale_factor("h", 2)
+    m.set_scaled_error_probabilities(0.01)
+    assert m.get_error_probability("h") == pytest.approx(0.02)
+    assert m.get_pauli_error_probability("h", "x") == pytest.approx(0.005)
+    with pytest.raises(Exception):
+        m.set_error_probability("h", 1.5)
+    with pytest.raises(Exception):
+        m.add_operation("bad", {})
+    with pytest.raises(Exception):
+        m.add_operation("bad", {"x": 1, "xx": 1})
+    again = PauliNoiseModel(fromdict=m.to_dict())
+    assert again.to_dict() == m.to_dict()
+    d = standard_depolarizing_model(1e-3)
+    assert d.get_pauli_weight("cx", "zz") == pytest.approx(1 / 15)
+    assert len(d.get_pauli_error_types()["cx"]) == 15
+
+
+def test_location_tagging():
+    c = surface_code_circuit(5, 5)
+    idx, labels = tag_fault_locations(c.labels, standard_depolarizing_model())
+    assert idx == list(range(761))
+    m = PauliNoiseModel()
+    m.add_operation("measure", {"x": 1})
+    idx, labels = tag_fault_locations(c.labels, m)
+    assert len(idx) == 145 and set(labels) == {"measure"}
