@@ -1,0 +1,674 @@
+// bindings.cpp -- pybind11 module `_c_analysis`: the reference-facing names over the C ABI.
+//
+// Mirrors reference src/qiskit_qec/analysis/bindings/analysis_bindings.cpp:12-54 name for
+// name (_CErrorPropagator, _CFaultEnumerator, _CFaultSampler, same constructor and method
+// signatures, same return shapes, same exception types and messages), so the reference's
+// Python drivers (analysis/extensions.py, cerrorpropagator.py, faultenumerator.py,
+// faultsampler.py) work unmodified on top of it.  All propagation happens in libqecb200.so
+// kernels; this file only marshals and keeps the small host-side state the reference API
+// exposes (the interactive 1-shot frame, enumerator cursor).
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "qec_b200.h"
+
+namespace py = pybind11;
+
+namespace qecb200 {  // keeps these types distinct from the reference module's in one process
+
+typedef std::tuple<long, std::vector<std::string>, std::vector<std::string>, std::vector<int>>
+    FaultPath;  // reference faultenumerator.h:22-25
+
+static void check(int rc) {
+  if (rc == 0) return;
+  const std::string msg = qec_last_error();
+  if (rc == QEC_ERR_INVALID) throw std::invalid_argument(msg);  // -> ValueError
+  throw std::logic_error(msg);                                  // -> RuntimeError
+}
+
+static uint8_t pauli_code(const std::string &p) {
+  auto bits = [](char c) -> uint8_t { return c == 'x' ? 1 : c == 'z' ? 2 : c == 'y' ? 3 : 0; };
+  uint8_t code = 0;
+  if (p.size() > 0) code |= bits(p[0]);
+  if (p.size() > 1) code |= (uint8_t)(bits(p[1]) << 2);
+  return code;
+}
+
+struct CircuitHandle {
+  qec_circuit *h = nullptr;
+  CircuitHandle() = default;
+  CircuitHandle(const CircuitHandle &) = delete;
+  CircuitHandle &operator=(const CircuitHandle &) = delete;
+  ~CircuitHandle() { reset(); }
+  void reset() {
+    if (h) qec_circuit_destroy(h);
+    h = nullptr;
+  }
+  void create(int device, int nq, int nc, const std::vector<std::vector<int>> &rows) {
+    reset();
+    std::vector<int32_t> off(rows.size() + 1, 0), data;
+    for (size_t i = 0; i < rows.size(); ++i) {
+      off[i + 1] = off[i] + (int32_t)rows[i].size();
+      data.insert(data.end(), rows[i].begin(), rows[i].end());
+    }
+    if (data.empty()) data.push_back(0);
+    check(qec_circuit_create(device, nq, nc, (int)rows.size(), off.data(), data.data(), &h));
+  }
+};
+
+static int default_device() {
+  const char *e = std::getenv("QEC_B200_DEVICE");
+  return e ? std::atoi(e) : 0;
+}
+
+// unpack row `p` of a bit-sliced buffer [rows][n_words] into ints
+static std::vector<int> unpack_path(const std::vector<uint32_t> &bits, int rows, int64_t n_words,
+                                    int64_t p) {
+  std::vector<int> out(rows);
+  const int64_t w = p >> 5;
+  const int b = (int)(p & 31);
+  for (int r = 0; r < rows; ++r) out[r] = (int)((bits[(size_t)r * n_words + w] >> b) & 1u);
+  return out;
+}
+
+// ---------------------------------------------------------------------------------------------
+// _CErrorPropagator  (reference errorpropagator.h:9-42, errorpropagator.cpp)
+class ErrorPropagator {
+ public:
+  ErrorPropagator(int qreg_size, int creg_size)
+      : nq_(qreg_size), nc_(creg_size), qa_(2 * (size_t)std::max(qreg_size, 0), 0),
+        ca_((size_t)std::max(creg_size, 0), 0) {}
+
+  void load_circuit(int qreg_size, int creg_size, std::vector<std::vector<int>> encoded_circ) {
+    // same order as the reference (:106-111): sizes and circuit are stored before validation
+    nq_ = qreg_size;
+    nc_ = creg_size;
+    qa_.assign(2 * (size_t)std::max(nq_, 0), 0);
+    ca_.assign((size_t)std::max(nc_, 0), 0);
+    circ_ = std::move(encoded_circ);
+    loaded_ = false;
+    py::gil_scoped_release nogil;
+    handle_.create(default_device(), nq_, nc_, circ_);
+    loaded_ = true;
+  }
+
+  void apply_error(std::vector<int> qubits, std::string paulis) {
+    if (qubits.size() != paulis.length()) throw std::logic_error("qubits and pauli length disagree");
+    for (size_t i = 0; i < qubits.size(); ++i) {
+      const int q = rq(qubits[i]);
+      if (paulis[i] == 'x' || paulis[i] == 'y') qa_[q] ^= 1;
+      if (paulis[i] == 'y' || paulis[i] == 'z') qa_[q + nq_] ^= 1;
+    }
+  }
+  // interactive gates on the 1-shot host frame (:211-254); indices are range checked here,
+  // the reference leaves them undefined
+  void cx(int qc, int qt) {
+    rq(qc); rq(qt);
+    qa_[qt] ^= qa_[qc];
+    qa_[qc + nq_] ^= qa_[qt + nq_];
+  }
+  void h(int q) { rq(q); std::swap(qa_[q], qa_[q + nq_]); }
+  void s(int q) { rq(q); if (qa_[q] == 1) qa_[q + nq_] ^= 1; }
+  void reset(int q) { rq(q); qa_[q] = 0; qa_[q + nq_] = 0; }
+  int measure(int q, int c) {
+    rq(q);
+    if (c < 0 || c >= nc_) throw std::logic_error("bit index out of range");
+    ca_[c] = qa_[q];
+    return ca_[c];
+  }
+
+  // one path through the K1 kernel; like the reference it leaves the final frame and clbits
+  // in the object (:262-263, :312)
+  std::vector<int> propagate(std::vector<int> icomb, std::vector<std::string> error) {
+    std::vector<std::vector<int>> ic{std::move(icomb)};
+    std::vector<std::vector<std::string>> er{std::move(error)};
+    auto res = propagate_many(ic, er, true);
+    return res[0];
+  }
+
+  std::vector<std::vector<int>> propagate_many(const std::vector<std::vector<int>> &icombs,
+                                               const std::vector<std::vector<std::string>> &errors,
+                                               bool keep_last_frame = false) {
+    if (icombs.size() != errors.size()) throw std::logic_error("icomb and error lists disagree");
+    ensure_handle();
+    const int64_t n = (int64_t)icombs.size();
+    std::vector<int64_t> off(n + 1, 0);
+    std::vector<int32_t> ops;
+    std::vector<uint8_t> codes;
+    for (int64_t p = 0; p < n; ++p) {
+      if (errors[p].size() < icombs[p].size())
+        throw std::logic_error("fewer Pauli strings than failed operations");
+      for (size_t j = 0; j < icombs[p].size(); ++j) {
+        ops.push_back(icombs[p][j]);
+        codes.push_back(pauli_code(errors[p][j]));
+      }
+      off[p + 1] = (int64_t)ops.size();
+    }
+    if (ops.empty()) { ops.push_back(0); codes.push_back(0); }
+    const int64_t nw = (n + 31) / 32;
+    std::vector<uint32_t> bits((size_t)std::max(nc_, 0) * nw + 1), frame((size_t)2 * nq_ * nw + 1);
+    {
+      py::gil_scoped_release nogil;
+      check(qec_propagate_batch(handle_.h, n, off.data(), ops.data(), codes.data(), bits.data(),
+                                keep_last_frame ? frame.data() : nullptr));
+    }
+    std::vector<std::vector<int>> out((size_t)n);
+    for (int64_t p = 0; p < n; ++p) out[p] = unpack_path(bits, nc_, nw, p);
+    if (keep_last_frame && n > 0) {
+      qa_ = unpack_path(frame, 2 * nq_, nw, n - 1);
+      ca_ = out[n - 1];
+    }
+    return out;
+  }
+
+  std::vector<int> get_cbits() const { return ca_; }
+  std::vector<int> get_qubit_array() const { return qa_; }
+  std::string get_qubits() const {
+    std::string pauli;
+    for (int i = 0; i < nq_; ++i) pauli.push_back("izxy"[qa_[i + nq_] + 2 * qa_[i]]);
+    return pauli;
+  }
+  int get_qreg_size() const { return nq_; }
+  int get_creg_size() const { return nc_; }
+  size_t get_circuit_size() const { return circ_.size(); }
+
+ private:
+  int rq(int q) const {
+    if (q < 0 || q >= nq_) throw std::logic_error("qubit index out of range");
+    return q;
+  }
+  void ensure_handle() {
+    if (!loaded_) {  // no circuit loaded: the reference propagates through an empty circuit
+      handle_.create(default_device(), nq_, nc_, circ_);
+      loaded_ = true;
+    }
+  }
+  int nq_, nc_;
+  std::vector<int> qa_, ca_;
+  std::vector<std::vector<int>> circ_;
+  CircuitHandle handle_;
+  bool loaded_ = false;
+};
+
+// ---------------------------------------------------------------------------------------------
+// _CFaultEnumerator  (reference faultenumerator.h:27-67, faultenumerator.cpp)
+class FaultEnumerator {
+ public:
+  FaultEnumerator(int order, int qreg_size, int creg_size,
+                  std::vector<std::vector<int>> &encoded_circ, std::vector<int> &faulty_ops_indices,
+                  std::vector<std::string> &faulty_ops_labels,
+                  std::vector<std::vector<std::string>> &faulty_ops_pauli_errors)
+      : order_(order), nq_(qreg_size), nc_(creg_size), indices_(faulty_ops_indices),
+        labels_(faulty_ops_labels), paulis_(faulty_ops_pauli_errors) {
+    circuit_.create(default_device(), nq_, nc_, encoded_circ);  // validates like load_circuit
+    const size_t L = indices_.size();
+    if (labels_.size() < L || paulis_.size() < L)
+      throw std::logic_error("faulty_ops_labels / faulty_ops_pauli_errors shorter than faulty_ops_indices");
+    std::vector<int32_t> loc_op(indices_.begin(), indices_.end()), poff(L + 1, 0);
+    std::vector<uint8_t> codes;
+    for (size_t l = 0; l < L; ++l) {
+      for (const auto &p : paulis_[l]) codes.push_back(pauli_code(p));
+      poff[l + 1] = (int32_t)codes.size();
+    }
+    if (loc_op.empty()) loc_op.push_back(0);
+    if (codes.empty()) codes.push_back(0);
+    check(qec_enumerator_create(circuit_.h, order_, (int)L, loc_op.data(), poff.data(), codes.data(), &h_));
+  }
+  FaultEnumerator(const FaultEnumerator &) = delete;
+  ~FaultEnumerator() { if (h_) qec_enumerator_destroy(h_); }
+
+  void reset() { index_ = 0; state_.clear(); done_ = false; }
+  long get_index() const { return index_; }
+  std::vector<int> get_state() const { return state_; }
+  bool done() const { return done_; }
+
+  int64_t num_paths() const { int64_t n = 0; check(qec_enumerator_num_paths(h_, &n)); return n; }
+
+  std::pair<std::vector<int>, std::vector<int>> unrank(int64_t index) const {
+    std::vector<int32_t> l(std::max(order_, 1)), d(std::max(order_, 1));
+    check(qec_enumerator_unrank(h_, index, l.data(), d.data()));
+    return {std::vector<int>(l.begin(), l.begin() + order_), std::vector<int>(d.begin(), d.begin() + order_)};
+  }
+
+  // Blocks as the reference cuts them (faultenumerator.cpp:71-111): at least `blocksize`
+  // paths, ending only after a whole subset's product; `done` is raised only by the call
+  // that finds no further subset, so a stream ending exactly on a block boundary is followed
+  // by one empty block.
+  std::vector<FaultPath> enumerate(int blocksize) {
+    std::vector<FaultPath> block;
+    if (done_) return block;
+    if (state_.empty()) { index_ = 0; done_ = false; }
+    const int64_t total = num_paths();  // raises the Combinations / ProductIterator errors
+    const int64_t start = index_;
+    if (start >= total) { done_ = true; return block; }
+    const int64_t target = start + std::max<int64_t>(blocksize, 1) - 1;
+    int64_t end = total;
+    std::vector<int32_t> locs(order_), digs(order_);
+    if (target < total) {
+      int64_t first = 0, count = 0;
+      check(qec_enumerator_unrank(h_, target, locs.data(), digs.data()));
+      check(qec_enumerator_subset_rank(h_, locs.data(), &first, &count));
+      end = first + count;
+    }
+    const int64_t n = end - start, nw = (n + 31) / 32;
+    std::vector<uint32_t> bits((size_t)nc_ * nw + 1);
+    {
+      py::gil_scoped_release nogil;
+      check(qec_enumerator_range(h_, start, end, bits.data(), nullptr));
+    }
+    // labels / errors of each path: host successor walk from the unranked first path
+    check(qec_enumerator_unrank(h_, start, locs.data(), digs.data()));
+    const int L = (int)indices_.size();
+    block.reserve((size_t)n);
+    for (int64_t p = 0; p < n; ++p) {
+      std::vector<std::string> lab(order_), err(order_);
+      for (int j = 0; j < order_; ++j) {
+        lab[j] = labels_[locs[j]];
+        err[j] = paulis_[locs[j]][digs[j]];
+      }
+      block.emplace_back((long)(start + p), std::move(lab), std::move(err), unpack_path(bits, nc_, nw, p));
+      if (p + 1 == n) break;
+      int j = order_ - 1;
+      for (; j >= 0; --j) {
+        if (++digs[j] < (int)paulis_[locs[j]].size()) break;
+        digs[j] = 0;
+      }
+      if (j < 0) {
+        int i = order_ - 1;
+        while (locs[i] >= L - order_ + i) --i;
+        ++locs[i];
+        for (int k = i + 1; k < order_; ++k) locs[k] = locs[i] + k - i;
+      }
+    }
+    state_.assign(locs.begin(), locs.end());
+    index_ = (long)end;
+    if (target >= total) done_ = true;  // ran out of subsets inside this call
+    return block;
+  }
+
+  // bulk API: packed outcomes uint32[nc][ceil((hi-lo)/32)] and tallies for paths [lo, hi)
+  py::tuple enumerate_packed(int64_t lo, int64_t hi, bool want_tally) {
+    const int64_t nw = (std::max<int64_t>(hi - lo, 0) + 31) / 32;
+    py::array_t<uint32_t> bits({(py::ssize_t)nc_, (py::ssize_t)nw});
+    py::array_t<uint64_t> tally((py::ssize_t)QEC_TALLY_LEN(nc_));
+    {
+      uint32_t *pb = bits.mutable_data();
+      uint64_t *pt = want_tally ? tally.mutable_data() : nullptr;
+      py::gil_scoped_release nogil;
+      check(qec_enumerator_range(h_, lo, hi, pb, pt));
+    }
+    if (want_tally) return py::make_tuple(bits, tally);
+    return py::make_tuple(bits, py::none());
+  }
+
+ private:
+  int order_, nq_, nc_;
+  std::vector<int> indices_;
+  std::vector<std::string> labels_;
+  std::vector<std::vector<std::string>> paulis_;
+  CircuitHandle circuit_;
+  qec_enumerator *h_ = nullptr;
+  long index_ = 0;
+  std::vector<int> state_;
+  bool done_ = false;
+};
+
+// ---------------------------------------------------------------------------------------------
+// _CFaultSampler  (reference faultsampler.h:26-66, faultsampler.cpp)
+typedef std::vector<std::pair<std::string, double>> PauliWeight;
+typedef std::map<std::string, PauliWeight> LabelToPauliWeightMap;
+
+class FaultSampler {
+ public:
+  FaultSampler(int qreg_size, int creg_size, std::vector<std::vector<int>> &encoded_circ,
+               std::vector<int> &faulty_ops_indices, std::vector<std::string> &faulty_ops_labels,
+               LabelToPauliWeightMap &label_to_pauli_weight,
+               std::map<std::string, double> &label_to_error_probability, uint64_t seed)
+      : nq_(qreg_size), nc_(creg_size), indices_(faulty_ops_indices), labels_(faulty_ops_labels) {
+    circuit_.create(default_device(), nq_, nc_, encoded_circ);
+    const size_t L = indices_.size();
+    if (labels_.size() < L) throw std::logic_error("faulty_ops_labels shorter than faulty_ops_indices");
+    std::map<std::string, int> cls;
+    std::vector<int32_t> loc_op(indices_.begin(), indices_.end()), loc_cls(L);
+    for (size_t l = 0; l < L; ++l) {
+      auto it = cls.find(labels_[l]);
+      if (it == cls.end()) {
+        it = cls.emplace(labels_[l], (int)class_names_.size()).first;
+        class_names_.push_back(labels_[l]);
+      }
+      loc_cls[l] = it->second;
+    }
+    std::vector<double> p, w;
+    std::vector<int32_t> off{0};
+    std::vector<uint8_t> codes;
+    for (const auto &name : class_names_) {
+      // a label absent from the probability map never fails (the reference's
+      // std::map::operator[] default-inserts 0.0, faultsampler.cpp:58)
+      auto pit = label_to_error_probability.find(name);
+      const double pc = pit == label_to_error_probability.end() ? 0.0 : pit->second;
+      auto wit = label_to_pauli_weight.find(name);
+      std::vector<std::string> strs;
+      if (wit == label_to_pauli_weight.end() || wit->second.empty()) {
+        if (pc > 0) throw std::invalid_argument("no Pauli weights for faulty label \"" + name + "\"");
+        strs.push_back("i"); codes.push_back(0); w.push_back(1.0);
+      } else {
+        for (const auto &pw : wit->second) {
+          strs.push_back(pw.first); codes.push_back(pauli_code(pw.first)); w.push_back(pw.second);
+        }
+      }
+      class_paulis_.push_back(strs);
+      p.push_back(pc);
+      off.push_back((int32_t)codes.size());
+    }
+    if (loc_op.empty()) { loc_op.push_back(0); loc_cls.push_back(0); }
+    if (p.empty()) p.push_back(0.0);
+    if (codes.empty()) { codes.push_back(0); w.push_back(1.0); }
+    check(qec_sampler_create(circuit_.h, (int)L, loc_op.data(), loc_cls.data(), (int)class_names_.size(),
+                             p.data(), off.data(), codes.data(), w.data(), seed, &h_));
+    loc_cls_.assign(loc_cls.begin(), loc_cls.begin() + L);
+  }
+  FaultSampler(const FaultSampler &) = delete;
+  ~FaultSampler() { if (h_) qec_sampler_destroy(h_); }
+
+  // blocksize fresh shots; successive calls continue with new global shot ids (the cursor
+  // moves in whole 32-shot words), so blocks never repeat -- like the reference's RNG stream
+  std::vector<FaultPath> sample(int blocksize) {
+    std::vector<FaultPath> block;
+    if (blocksize <= 0) return block;
+    const int64_t n = blocksize, nw = (n + 31) / 32;
+    std::vector<uint32_t> bits((size_t)nc_ * nw + 1), cnt((size_t)nw), ev;
+    int cap = cap_, need = 0;
+    for (;;) {
+      ev.assign((size_t)nw * cap, 0u);
+      int rc;
+      {
+        py::gil_scoped_release nogil;
+        rc = qec_sampler_sample(h_, cursor_, n, bits.data(), nullptr, cnt.data(), ev.data(), cap, &need);
+      }
+      if (rc == QEC_ERR_LIMIT && need > cap) { cap = cap_ = need + 8; continue; }  // same seed, same shots
+      check(rc);
+      break;
+    }
+    cursor_ += nw * 32;
+    std::vector<std::vector<std::string>> labs((size_t)n), errs((size_t)n);
+    for (int64_t w = 0; w < nw; ++w)
+      for (uint32_t k = 0; k < cnt[w]; ++k) {
+        const uint32_t e = ev[(size_t)w * cap + k];
+        const uint32_t loc = e >> 14, bit = (e >> 9) & 31u, dig = e & 511u;
+        const int64_t s = 32 * w + bit;
+        labs[s].push_back(labels_[loc]);
+        errs[s].push_back(class_paulis_[loc_cls_[loc]][dig]);
+      }
+    block.reserve((size_t)n);
+    for (int64_t s = 0; s < n; ++s)
+      block.emplace_back(-1L, std::move(labs[s]), std::move(errs[s]), unpack_path(bits, nc_, nw, s));
+    return block;
+  }
+
+  // bulk API: packed outcomes + tallies of `n` fresh shots
+  py::tuple sample_packed(int64_t n, bool want_bits, bool want_tally) {
+    const int64_t nw = (std::max<int64_t>(n, 0) + 31) / 32;
+    py::array_t<uint32_t> bits({(py::ssize_t)(want_bits ? nc_ : 0), (py::ssize_t)nw});
+    py::array_t<uint64_t> tally((py::ssize_t)QEC_TALLY_LEN(nc_));
+    {
+      uint32_t *pb = want_bits ? bits.mutable_data() : nullptr;
+      uint64_t *pt = want_tally ? tally.mutable_data() : nullptr;
+      py::gil_scoped_release nogil;
+      check(qec_sampler_sample(h_, cursor_, n, pb, pt, nullptr, nullptr, 0, nullptr));
+    }
+    cursor_ += nw * 32;
+    return py::make_tuple(want_bits ? py::object(bits) : py::none(),
+                          want_tally ? py::object(tally) : py::none());
+  }
+  int64_t get_cursor() const { return cursor_; }
+  void set_cursor(int64_t c) {
+    if (c < 0 || (c & 31)) throw std::invalid_argument("cursor must be a non-negative multiple of 32");
+    cursor_ = c;
+  }
+
+ private:
+  int nq_, nc_;
+  std::vector<int> indices_;
+  std::vector<std::string> labels_, class_names_;
+  std::vector<std::vector<std::string>> class_paulis_;
+  std::vector<int> loc_cls_;
+  CircuitHandle circuit_;
+  qec_sampler *h_ = nullptr;
+  int64_t cursor_ = 0;
+  int cap_ = 64;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Free functions the reference module also exports (analysis_bindings.cpp:56-61).  They are
+// outside the accelerated path; these are small bit-packed host versions
+// with the reference's results (reference intern/linear.cpp:11-83, intern/distance.cpp:17-202)
+// so that analysis/extensions.py keeps every feature flag on.
+typedef std::vector<std::vector<int>> IntMatrix;
+
+struct BitRows {  // rows packed 64 columns per word
+  size_t cols = 0, words = 0;
+  std::vector<std::vector<uint64_t>> r;
+  explicit BitRows(const IntMatrix &m) {
+    cols = m.empty() ? 0 : m[0].size();
+    words = (cols + 63) / 64;
+    for (const auto &row : m) r.push_back(pack(row));
+  }
+  std::vector<uint64_t> pack(const std::vector<int> &row) const {
+    std::vector<uint64_t> w(std::max<size_t>(words, 1), 0);
+    for (size_t k = 0; k < row.size() && k < cols; ++k)
+      if (row[k] & 1) w[k >> 6] |= 1ull << (k & 63);
+    return w;
+  }
+};
+
+// reduce to echelon form in place; returns (rank, pivot column of each basis row)
+static int echelon(BitRows &b, std::vector<size_t> *pivots = nullptr) {
+  size_t i = 0;
+  for (size_t k = 0; k < b.cols && i < b.r.size(); ++k) {
+    size_t j = i;
+    while (j < b.r.size() && !((b.r[j][k >> 6] >> (k & 63)) & 1)) ++j;
+    if (j == b.r.size()) continue;
+    std::swap(b.r[i], b.r[j]);
+    for (size_t l = 0; l < b.r.size(); ++l)
+      if (l != i && ((b.r[l][k >> 6] >> (k & 63)) & 1))
+        for (size_t w = 0; w < b.words; ++w) b.r[l][w] ^= b.r[i][w];
+    if (pivots) pivots->push_back(k);
+    ++i;
+  }
+  return (int)i;
+}
+
+static int gf2_rank(IntMatrix vectors) {
+  if (vectors.empty()) throw std::logic_error("rank of an empty set of vectors");
+  BitRows b(vectors);
+  return echelon(b);
+}
+
+static inline int sip(const std::vector<int> &a, const std::vector<int> &b) {
+  const size_t n = a.size() / 2;
+  int s = 0;
+  for (size_t i = 0; i < n; ++i) s ^= (a[i] & b[i + n]) ^ (a[i + n] & b[i]);
+  return s & 1;
+}
+
+static bool gf2_isotropic(IntMatrix &v) {
+  for (size_t i = 0; i < v.size(); ++i)
+    for (size_t j = i + 1; j < v.size(); ++j)
+      if (sip(v[i], v[j])) return false;
+  return true;
+}
+
+static bool next_comb(int n, int k, std::vector<int> &s) {
+  if (s.empty()) { for (int j = 0; j < k; ++j) s.push_back(j); return true; }
+  if (s[0] == n - k) return false;
+  int i = k - 1;
+  while (s[i] >= n - k + i) --i;
+  ++s[i];
+  for (int j = i + 1; j < k; ++j) s[j] = s[i] + j - i;
+  return true;
+}
+
+static int min_distance(IntMatrix &stab, IntMatrix &gauge, int max_weight) {
+  if (!gf2_isotropic(stab)) throw std::logic_error("symplectic vectors must span isotropic space");
+  const int n = (int)stab[0].size() / 2;
+  const int rk = gf2_rank(stab);
+  BitRows V(gauge);
+  std::vector<size_t> piv;
+  const int rk2 = echelon(V, &piv);
+  const int k = n - (rk + rk2) / 2;
+  for (int weight = 1; weight <= std::min(max_weight, n); ++weight) {
+    std::vector<int> where;
+    while (next_comb(n, weight, where)) {
+      std::vector<int> dig(weight, 0);
+      for (;;) {
+        std::vector<int> err(2 * (size_t)n, 0);
+        for (int i = 0; i < weight; ++i) {
+          if (dig[i] == 0 || dig[i] == 2) err[where[i]] = 1;
+          if (dig[i] == 1 || dig[i] == 2) err[where[i] + n] = 1;
+        }
+        bool commutes = true;
+        for (const auto &srow : stab) if (sip(srow, err)) { commutes = false; break; }
+        if (commutes) {
+          std::vector<uint64_t> e = V.pack(err);  // membership in span(gauge): reduce by the basis
+          for (int b = 0; b < rk2; ++b)
+            if ((e[piv[b] >> 6] >> (piv[b] & 63)) & 1)
+              for (size_t w = 0; w < V.words; ++w) e[w] ^= V.r[b][w];
+          bool inV = true;
+          for (uint64_t w : e) if (w) { inV = false; break; }
+          if ((k > 0 && !inV) || (k == 0 && inV)) return weight;
+        }
+        int j = weight - 1;
+        for (; j >= 0; --j) { if (++dig[j] < 3) break; dig[j] = 0; }
+        if (j < 0) break;
+      }
+    }
+  }
+  return 0;
+}
+
+// exists a Pauli built from `weight` single-qubit terms that commutes with every stabilizer
+// row and anticommutes with `logical` (meet in the middle over syndromes)
+static bool distance_test(const IntMatrix &stab, const std::vector<int> &logical, int weight) {
+  const int n = (int)stab[0].size() / 2, m = (int)stab.size();
+  if (m >= 63) throw std::logic_error("n-k must be < 63 for this version not to overflow.");
+  std::vector<uint64_t> sq;
+  for (int q = 0; q < n; ++q) {
+    uint64_t sx = 0, sz = 0;
+    for (int i = 0; i < m; ++i) {
+      if (stab[i][n + q] == 1) sx |= 1ull << i;
+      if (stab[i][q] == 1) sz |= 1ull << i;
+    }
+    if (logical[n + q] == 1) sx |= 1ull << m;
+    if (logical[q] == 1) sz |= 1ull << m;
+    sq.push_back(sx); sq.push_back(sz); sq.push_back(sx ^ sz);
+  }
+  const int w1 = (weight + 1) / 2, w2 = weight / 2;
+  const uint64_t top = 1ull << m;
+  auto collect = [&](int w, std::vector<uint64_t> &comm, std::vector<uint64_t> &anti) {
+    if (w <= 0) return;
+    if (w > (int)sq.size()) throw std::invalid_argument("0 <= k <= n");
+    std::vector<int> s;
+    while (next_comb((int)sq.size(), w, s)) {
+      uint64_t synd = 0;
+      for (int i = 0; i < w; ++i) synd ^= sq[s[i]];
+      if (synd & top) anti.push_back(synd ^ top); else comm.push_back(synd);
+    }
+    std::sort(comm.begin(), comm.end());
+    std::sort(anti.begin(), anti.end());
+  };
+  std::vector<uint64_t> c1, a1, c2, a2;
+  collect(w1, c1, a1);
+  if (w1 != w2) collect(w2, c2, a2); else { c2 = c1; a2 = a1; }
+  auto meets = [](const std::vector<uint64_t> &x, const std::vector<uint64_t> &y) {
+    size_t i = 0, j = 0;
+    while (i < x.size() && j < y.size()) {
+      if (x[i] == y[j]) return true;
+      if (x[i] < y[j]) ++i; else ++j;
+    }
+    return false;
+  };
+  return meets(c1, a2) || meets(a1, c2);
+}
+
+static int min_distance_by_tests(IntMatrix &stab, IntMatrix &xl, IntMatrix &zl, int max_weight) {
+  int best = max_weight + 1;
+  for (const IntMatrix *ops : {&xl, &zl})
+    for (const auto &row : *ops)
+      for (int w = 1; w <= max_weight; ++w)
+        if (distance_test(stab, row, w)) { best = std::min(best, w); break; }
+  return best <= max_weight ? best : 0;
+}
+
+}  // namespace qecb200
+using namespace qecb200;
+
+PYBIND11_MODULE(_c_analysis, module) {
+  module.doc() = "qiskit-qec core analysis extensions -- B200-native (libqecb200.so) drop-in";
+  module.attr("backend") = "qec_b200/sm_100a";
+
+  py::class_<ErrorPropagator>(module, "_CErrorPropagator", py::module_local())
+      .def(py::init<int, int>())
+      .def("load_circuit", &ErrorPropagator::load_circuit)
+      .def("apply_error", &ErrorPropagator::apply_error)
+      .def("cx", &ErrorPropagator::cx)
+      .def("h", &ErrorPropagator::h)
+      .def("s", &ErrorPropagator::s)
+      .def("reset", &ErrorPropagator::reset)
+      .def("measure", &ErrorPropagator::measure)
+      .def("propagate", &ErrorPropagator::propagate)
+      .def("propagate_many", &ErrorPropagator::propagate_many, py::arg("icombs"), py::arg("errors"),
+           py::arg("keep_last_frame") = false)
+      .def("get_cbits", &ErrorPropagator::get_cbits)
+      .def("get_qubits", &ErrorPropagator::get_qubits)
+      .def("get_qubit_array", &ErrorPropagator::get_qubit_array)
+      .def("get_qreg_size", &ErrorPropagator::get_qreg_size)
+      .def("get_creg_size", &ErrorPropagator::get_creg_size)
+      .def("get_circuit_size", &ErrorPropagator::get_circuit_size)
+      .def("__repr__", [](const ErrorPropagator &a) {
+        return std::string("<ErrorPropagator with ") + std::to_string(a.get_qreg_size()) +
+               std::string(" qubits, ") + std::to_string(a.get_creg_size()) + std::string(" bits, ") +
+               std::to_string(a.get_circuit_size()) + std::string(" instructions>");
+      });
+
+  py::class_<FaultEnumerator>(module, "_CFaultEnumerator", py::module_local())
+      .def(py::init<int, int, int, std::vector<std::vector<int>> &, std::vector<int> &,
+                    std::vector<std::string> &, std::vector<std::vector<std::string>> &>())
+      .def("enumerate", &FaultEnumerator::enumerate)
+      .def("reset", &FaultEnumerator::reset)
+      .def("get_index", &FaultEnumerator::get_index)
+      .def("get_state", &FaultEnumerator::get_state)
+      .def("done", &FaultEnumerator::done)
+      .def("num_paths", &FaultEnumerator::num_paths)
+      .def("unrank", &FaultEnumerator::unrank)
+      .def("enumerate_packed", &FaultEnumerator::enumerate_packed, py::arg("lo"), py::arg("hi"),
+           py::arg("want_tally") = false);
+
+  py::class_<FaultSampler>(module, "_CFaultSampler", py::module_local())
+      .def(py::init<int, int, std::vector<std::vector<int>> &, std::vector<int> &,
+                    std::vector<std::string> &, LabelToPauliWeightMap &,
+                    std::map<std::string, double> &, uint64_t>())
+      .def("sample", &FaultSampler::sample)
+      .def("sample_packed", &FaultSampler::sample_packed, py::arg("n"), py::arg("want_bits") = true,
+           py::arg("want_tally") = false)
+      .def("get_cursor", &FaultSampler::get_cursor)
+      .def("set_cursor", &FaultSampler::set_cursor);
+
+  module.def("_c_minimum_distance", &min_distance,
+             "compute minimum distance of subsystem stabilizer code", py::arg("symplectic_vectors"),
+             py::arg("symplectic_gauge_vectors"), py::arg("max_weight") = 10);
+  module.def("_c_minimum_distance_by_tests", &min_distance_by_tests,
+             "compute minimum distance of subsystem stabilizer code", py::arg("symplectic_vectors"),
+             py::arg("symplectic_xl"), py::arg("symplectic_zl"), py::arg("max_weight") = 10);
+  module.def("_c_rank", &gf2_rank, "compute rank of set of vectors", py::arg("vectors"));
+  module.def("_c_isotropic", &gf2_isotropic, "test if set of symplectic vectors is isotropic",
+             py::arg("symplectic_vectors"));
+}
