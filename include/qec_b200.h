@@ -174,6 +174,21 @@ int qec_stream_sync(int device, void *stream);
 /* elapsed device time (ms) of the last *_dev / host call on handle, via CUDA events */
 int qec_last_kernel_ms(int device, float *ms);
 
+
+/* ---- circuit-specialised kernels ("JIT") ------------------------------------------------
+ * For circuits whose frame fits the register file the enumerator and the sampler run a
+ * kernel generated for that circuit (every frame word a register) and compiled for sm_100a
+ * with NVRTC at first use; otherwise, or with QEC_B200_JIT=0, the table-driven kernels run.
+ * Both produce identical bits.  qec_last_kernel() names the kernel that served this
+ * thread's latest enumerator/sampler launch.  qec_jit_compile_to_file() needs no device: it
+ * writes the generated gate-stream source and the sm_100a cubin of one variant
+ * (kind 1 = enumerator, 2 = sampler) so that the SASS can be inspected. */
+const char *qec_last_kernel(void);
+int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t *row_off,
+                            const int32_t *row_data, int L, const int32_t *loc_op, int kind,
+                            int order, int tally, int bits, int threads, int min_blocks,
+                            int group, const char *cubin_path, const char *source_path);
+
 #ifdef __cplusplus
 }
 #endif

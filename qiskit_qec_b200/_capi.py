@@ -34,6 +34,7 @@ SYMBOLS = [
     "qec_outcome_histogram_dev",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
+    "qec_last_kernel", "qec_jit_compile_to_file",
 ]
 
 _lib = None
@@ -54,6 +55,7 @@ def lib() -> C.CDLL:
         L = C.CDLL(LIB_PATH)
         L.qec_last_error.restype = C.c_char_p
         L.qec_version.restype = C.c_char_p
+        L.qec_last_kernel.restype = C.c_char_p
         L.qec_circuit_bit_ops.restype = C.c_int64
         L.qec_circuit_bit_ops.argtypes = [C.c_void_p]
         L.qec_circuit_destroy.restype = None
@@ -98,6 +100,26 @@ def last_kernel_ms(device: int = 0) -> float:
     ms = C.c_float()
     _check(lib().qec_last_kernel_ms(C.c_int(device), C.byref(ms)))
     return ms.value
+
+
+def last_kernel() -> str:
+    """Name of the kernel that served this thread's latest enumerator / sampler launch
+    ("...:specialised ..." = generated for the circuit, "...:table-driven (why)")."""
+    return lib().qec_last_kernel().decode()
+
+
+def jit_compile_to_file(nq: int, nc: int, encoded_circ, loc_op, kind: int, order: int = 1,
+                        tally: bool = False, bits: bool = True, threads: int = 128,
+                        min_blocks: int = 3, group: int = 8, cubin_path: str = "",
+                        source_path: str = "") -> None:
+    """Generate + compile (NVRTC, sm_100a) the specialised kernel of a circuit; no GPU needed."""
+    off, data = rows_to_csr(encoded_circ)
+    loc = _i32(loc_op)
+    _check(lib().qec_jit_compile_to_file(
+        C.c_int(nq), C.c_int(nc), C.c_int(len(encoded_circ)), _p(off), _p(data), C.c_int(len(loc)),
+        _p(loc), C.c_int(kind), C.c_int(order), C.c_int(int(tally)), C.c_int(int(bits)),
+        C.c_int(threads), C.c_int(min_blocks), C.c_int(group), cubin_path.encode(),
+        source_path.encode()))
 
 
 def rows_to_csr(encoded_circ: Sequence[Sequence[int]]) -> Tuple[np.ndarray, np.ndarray]:

@@ -10,12 +10,14 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "../../include/qec_b200.h"
 #include "qec_kernels.cuh"
+#include "qec_jit.h"
 
 // ---- error plumbing --------------------------------------------------------------------------
 static thread_local std::string g_err;
@@ -39,6 +41,10 @@ static int fail(int code, const char *fmt, ...) {
   } while (0)
 
 extern "C" const char *qec_last_error(void) { return g_err.c_str(); }
+
+// which kernel served the last enumerator / sampler launch of this thread
+static thread_local std::string g_last_kernel;
+extern "C" const char *qec_last_kernel(void) { return g_last_kernel.c_str(); }
 extern "C" const char *qec_version(void) { return "qec_b200 0.1.0 (sm_100a)"; }
 
 extern "C" int qec_device_count(void) {
@@ -125,20 +131,19 @@ struct qec_circuit {
   DevInfo *info = nullptr;
 };
 
-extern "C" int qec_circuit_create(int device, int nq, int nc, int n_ops, const int32_t *row_off,
-                                  const int32_t *row_data, qec_circuit **out) {
-  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
-  *out = nullptr;
+// host-only lowering of the reference's rows to the packed gate table (no device needed)
+static int lower_rows(int nq, int nc, int n_ops, const int32_t *row_off, const int32_t *row_data,
+                      std::vector<uint8_t> &rop, std::vector<uint32_t> &packed, int64_t &bit_ops) {
   if (nq < 0 || nc < 0 || n_ops < 0) return fail(QEC_ERR_INVALID, "negative size");
   if (nq > QEC_MAX_QUBITS || nc > QEC_MAX_CLBITS)
     return fail(QEC_ERR_LIMIT, "at most %d qubits and %d clbits are supported", QEC_MAX_QUBITS,
                 QEC_MAX_CLBITS);
   if (n_ops >= (1 << 22)) return fail(QEC_ERR_LIMIT, "at most 2^22 operations are supported");
-  std::vector<uint8_t> rop(n_ops);
-  std::vector<uint32_t> packed;
+  rop.assign(n_ops, 0);
+  packed.clear();
   packed.reserve(n_ops + nc + 4);
   std::vector<int> last_write(nc, -1);
-  int64_t bit_ops = 0;
+  bit_ops = 0;
   // validation: same checks, order and messages as errorpropagator.cpp:112-148
   for (int i = 0; i < n_ops; ++i) {
     const int32_t *row = row_data + row_off[i];
@@ -191,6 +196,21 @@ extern "C" int qec_circuit_create(int device, int nq, int nc, int n_ops, const i
       packed.push_back(qec_pack_op(QOP_ZEROC, c, 0));
   }
   while (packed.size() % 4 || packed.empty()) packed.push_back(qec_pack_op(QOP_NOP, 0, 1));
+
+  return 0;
+}
+
+extern "C" int qec_circuit_create(int device, int nq, int nc, int n_ops, const int32_t *row_off,
+                                  const int32_t *row_data, qec_circuit **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  std::vector<uint8_t> rop;
+  std::vector<uint32_t> packed;
+  int64_t bit_ops = 0;
+  {
+    const int rc0 = lower_rows(nq, nc, n_ops, row_off, row_data, rop, packed, bit_ops);
+    if (rc0) return rc0;
+  }
 
   DevInfo *info;
   int rc = dev_info(device, &info);
@@ -283,6 +303,70 @@ extern "C" int qec_last_kernel_ms(int device, float *ms) {
   return 0;
 }
 
+
+// ---- circuit-specialised kernels (qec_jit.cpp) ----------------------------------------------------
+// QEC_B200_JIT = 0: table-driven kernels only; 1 (default): specialise when the circuit is
+// eligible and fall back to the table-driven kernel otherwise; require: fail instead of falling back.
+static int jit_mode() {
+  const char *e = std::getenv("QEC_B200_JIT");
+  if (!e || !*e) return 1;
+  if (!strcmp(e, "0") || !strcmp(e, "off")) return 0;
+  if (!strcmp(e, "require")) return 2;
+  return 1;
+}
+static int env_int(const char *name, int dflt) {
+  const char *e = std::getenv(name);
+  return (e && *e) ? atoi(e) : dflt;
+}
+
+struct JitVariant {  // one compiled kernel per (tally, bits) combination, built on first use
+  bool tried = false, ok = false;
+  QecJitKernel k;
+  std::string why;
+};
+
+struct JitPlan {
+  bool eligible = false;
+  std::string why;          // why not, when not eligible
+  int threads = 128, min_blocks = 1, grid = 0, group = 8;
+  size_t smem = 0;
+  std::vector<uint8_t> is_loc;
+  JitVariant var[2][2];
+  void release() {
+    for (auto &a : var) for (auto &v : a) if (v.ok) { qec_jit_unload(&v.k); v.ok = false; }
+  }
+};
+
+// registers a specialised kernel needs: the frame plus cursor / addressing overhead
+static int jit_regs_estimate(int nq) { return 2 * nq + 56; }
+
+static void jit_plan_geometry(const qec_circuit *c, JitPlan &pl) {
+  const int regs = jit_regs_estimate(c->nq);
+  int minb = 65536 / (regs * pl.threads);
+  if (minb > 8) minb = 8;
+  if (minb < 1) minb = 1;
+  pl.min_blocks = minb;
+  pl.grid = c->info->sms * minb;
+}
+
+static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, bool tally, bool bits) {
+  JitVariant &v = pl.var[tally ? 1 : 0][bits ? 1 : 0];
+  if (v.tried) return &v;
+  v.tried = true;
+  QecJitSpec spec;
+  spec.nq = c->nq; spec.nc = c->nc; spec.packed = &c->packed; spec.is_loc = pl.is_loc;
+  spec.kind = kind; spec.order = order; spec.tally = tally; spec.bits = bits;
+  spec.threads = pl.threads; spec.min_blocks = pl.min_blocks; spec.group = pl.group;
+  std::vector<char> cubin;
+  std::string log;
+  if (qec_jit_compile(spec, &cubin, &log)) { v.why = "NVRTC: " + log; return &v; }
+  if (qec_jit_load(cubin, pl.smem, &v.k, &log)) { v.why = log; return &v; }
+  v.k.threads = pl.threads;
+  v.k.min_blocks = pl.min_blocks;
+  v.ok = true;
+  return &v;
+}
+
 // ---- K1: batched propagate ------------------------------------------------------------------------
 extern "C" int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_t *path_off,
                                    const int32_t *fault_op, const uint8_t *fault_pauli,
@@ -357,7 +441,46 @@ struct qec_enumerator {
   uint8_t *d_pcode = nullptr;
   DevBuf scratch;
   QecLaunchCfg cfg{};
+  // circuit-specialised path
+  std::vector<unsigned long long> tile;
+  unsigned long long *d_tile = nullptr;
+  JitPlan jit;
+  DevBuf jit_scratch;
 };
+
+// Can this enumerator run on the specialised kernel?  (the frame must fit the register file,
+// the location list must be in strictly increasing op order so that the mask events of a lane
+// word have unique, sorted ops, and every location must offer at most 32 Paulis for the tile
+// table.)
+static void enum_plan_jit(qec_enumerator *e) {
+  JitPlan &pl = e->jit;
+  qec_circuit *c = e->c;
+  if (jit_mode() == 0) { pl.why = "QEC_B200_JIT=0"; return; }
+  if (2 * c->nq > 200) { pl.why = "frame of " + std::to_string(2 * c->nq) + " words exceeds the register file"; return; }
+  for (int l = 0; l < e->L; ++l) {
+    if (e->npaul[l] > 32) { pl.why = "a location offers more than 32 Paulis"; return; }
+    if (l > 0 && e->lop[l] <= e->lop[l - 1]) { pl.why = "location ops are not strictly increasing"; return; }
+  }
+  std::string why;
+  if (!qec_jit_available(&why)) { pl.why = why; return; }
+  pl.is_loc.assign(c->packed.size(), 0);
+  for (int l = 0; l < e->L; ++l) pl.is_loc[e->lop[l]] = 1;
+  pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
+  pl.group = env_int("QEC_B200_JIT_GROUP", 8);
+  jit_plan_geometry(c, pl);
+  pl.smem = (size_t)c->nc * 4 + 16;
+  // tile[4 l + k]: bit i = bit k of the code of digit (i mod npaul[l])
+  e->tile.assign((size_t)4 * e->L, 0ull);
+  for (int l = 0; l < e->L; ++l) {
+    const uint32_t np = e->npaul[l];
+    for (int i = 0; i < 64; ++i) {
+      const uint8_t code = e->pcode[e->poff[l] + (uint32_t)i % np];
+      for (int k = 0; k < 4; ++k)
+        if ((code >> k) & 1) e->tile[(size_t)4 * l + k] |= 1ull << i;
+    }
+  }
+  pl.eligible = true;
+}
 
 extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int32_t *loc_op,
                                      const int32_t *pauli_off, const uint8_t *pauli_codes,
@@ -422,6 +545,15 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
       qec_enumerator_destroy(e);
       return rc;
     }
+    enum_plan_jit(e);
+    if (e->jit.eligible) {
+      const size_t words = (size_t)e->jit.grid * e->jit.threads * 5 * (32 * order + 2);
+      if ((rc = upload(e->tile, &e->d_tile)) || (rc = e->jit_scratch.ensure(words * 4))) {
+        qec_enumerator_destroy(e);
+        return rc;
+      }
+      e->dev.tile = e->d_tile;
+    }
     e->dev.order = order; e->dev.L = L; e->dev.E = e->d_E; e->dev.npaul = e->d_npaul;
     e->dev.poff = e->d_poff; e->dev.pcode = e->d_pcode; e->dev.lop = e->d_lop;
   }
@@ -437,7 +569,10 @@ extern "C" void qec_enumerator_destroy(qec_enumerator *e) {
   if (e->d_poff) cudaFree(e->d_poff);
   if (e->d_lop) cudaFree(e->d_lop);
   if (e->d_pcode) cudaFree(e->d_pcode);
+  if (e->d_tile) cudaFree(e->d_tile);
   e->scratch.release();
+  e->jit_scratch.release();
+  e->jit.release();
   delete e;
 }
 
@@ -506,6 +641,29 @@ static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bi
   O.frame = nullptr;
   O.tally = (unsigned long long *)d_tally;
   O.n_words = (hi - lo + 31) / 32;
+  if (e->jit.eligible) {
+    JitVariant *v = jit_get(e->c, e->jit, 1, e->order, d_tally != nullptr, d_bits != nullptr);
+    if (v->ok) {
+      long long lo_ = lo, hi_ = hi;
+      uint32_t *scr = (uint32_t *)e->jit_scratch.p;
+      void *args[] = {&O, &e->dev, &lo_, &hi_, &scr};
+      std::string err;
+      time_begin(e->c, stream);
+      const int rc = qec_jit_launch(v->k, e->jit.grid, e->jit.smem, stream, args, &err);
+      time_end(e->c, stream);
+      if (rc) return fail(QEC_ERR_CUDA, "%s", err.c_str());
+      g_last_kernel = "enumerate:specialised regs=" + std::to_string(v->k.regs) +
+                      " T=" + std::to_string(e->jit.threads) + " ctas/sm=" +
+                      std::to_string(e->jit.min_blocks) + " group=" + std::to_string(e->jit.group);
+      return 0;
+    }
+    if (jit_mode() == 2) return fail(QEC_ERR_CUDA, "QEC_B200_JIT=require: %s", v->why.c_str());
+    g_last_kernel = "enumerate:table-driven (" + v->why.substr(0, 200) + ")";
+  } else {
+    if (jit_mode() == 2)
+      return fail(QEC_ERR_CUDA, "QEC_B200_JIT=require: %s", e->jit.why.c_str());
+    g_last_kernel = "enumerate:table-driven (" + e->jit.why + ")";
+  }
   time_begin(e->c, stream);
   qec_launch_enumerate(e->cfg, stream, e->c->dev, O, e->dev, lo, hi, (uint32_t *)e->scratch.p);
   time_end(e->c, stream);
@@ -572,7 +730,55 @@ struct qec_sampler {
   DevBuf scratch, xcnt, xev;
   int cap = 0;
   QecLaunchCfg cfg{};
+  // circuit-specialised path: events of a lane word live in shared memory (jit_cap of them)
+  JitPlan jit;
+  int jit_cap = 0;
+  int last_cap = 0;  // event capacity of the kernel that served the latest launches
 };
+
+static void sampler_plan_jit(qec_sampler *s) {
+  JitPlan &pl = s->jit;
+  qec_circuit *c = s->c;
+  if (jit_mode() == 0) { pl.why = "QEC_B200_JIT=0"; return; }
+  if (2 * c->nq > 200) { pl.why = "frame of " + std::to_string(2 * c->nq) + " words exceeds the register file"; return; }
+  if (s->dev.n_slots <= 0) { pl.why = "no fault can occur"; return; }
+  for (int i = 1; i < s->L; ++i)
+    if (s->slop[i] <= s->slop[i - 1]) { pl.why = "two fault locations share one op"; return; }
+  std::string why;
+  if (!qec_jit_available(&why)) { pl.why = why; return; }
+  pl.is_loc.assign(c->packed.size(), 0);
+  for (int i = 0; i < s->L; ++i) pl.is_loc[s->slop[i]] = 1;
+  pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
+  jit_plan_geometry(c, pl);
+  // events per lane word: mean + 9.5 sigma if shared memory allows, never below mean + 6 sigma
+  const double mu = s->mean_events;
+  const int want = (int)std::ceil(mu + 9.5 * std::sqrt(mu) + 8.0);
+  const int least = (int)std::ceil(mu + 6.0 * std::sqrt(mu) + 8.0);
+  const size_t fixed = ((size_t)c->nc + 64 + s->K1 + s->B) * 4 + 16;
+  int cap = 0;
+  for (int minb = pl.min_blocks; minb >= 1; --minb) {
+    size_t per_cta = c->info->smem_sm / minb - 1024;
+    if (per_cta > c->info->smem_optin) per_cta = c->info->smem_optin;
+    if (per_cta <= fixed) continue;
+    const int fit = (int)((per_cta - fixed) / ((size_t)8 * pl.threads)) - 2;
+    if (fit >= least) {
+      cap = std::min(fit, want);
+      pl.min_blocks = minb;
+      break;
+    }
+  }
+  if (!cap) { pl.why = "the events of a lane word do not fit in shared memory"; return; }
+  pl.grid = c->info->sms * pl.min_blocks;
+  s->jit_cap = cap;
+  pl.smem = fixed + (size_t)8 * pl.threads * (cap + 2);
+  // one warp sees about 1024 * p events per location: a block test only pays when that is small
+  const double lam = 1024.0 * mu / 32.0 / std::max(1, s->L);
+  int group = lam > 0 ? (int)(0.25 / lam) : 8;
+  if (group > 8) group = 8;
+  if (group < 2) group = 0;
+  pl.group = env_int("QEC_B200_JIT_GROUP_SAMPLER", group);
+  pl.eligible = true;
+}
 
 static inline uint32_t fix32(double x) {  // round(2^32 * x) clamped to [0, 2^32 - 1]
   if (!(x > 0)) return 0u;
@@ -693,6 +899,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
   d.slloc = s->d_slloc; d.slcls = s->d_slcls; d.cls_acc = s->d_cls_acc;
   d.cls_always = s->d_cls_always; d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.codes = s->d_codes;
   d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32);
+  sampler_plan_jit(s);
   *out = s;
   return 0;
 }
@@ -704,6 +911,7 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
+  s->jit.release();
   delete s;
 }
 
@@ -738,6 +946,34 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
   O.frame = nullptr;
   O.tally = (unsigned long long *)d_tally;
   O.n_words = (n_shots + 31) / 32;
+  if (s->jit.eligible && !X.cnt) {
+    JitVariant *v = jit_get(s->c, s->jit, 2, 0, d_tally != nullptr, d_bits != nullptr);
+    if (v->ok) {
+      long long wlo = shot_lo / 32, ns = n_shots;
+      int cap = s->jit_cap;
+      void *args[] = {&O, &s->dev, &wlo, &ns, &cap, &s->d_flag};
+      std::string err;
+      time_begin(s->c, stream);
+      const int rc = qec_jit_launch(v->k, s->jit.grid, s->jit.smem, stream, args, &err);
+      time_end(s->c, stream);
+      if (rc) return fail(QEC_ERR_CUDA, "%s", err.c_str());
+      s->last_cap = cap;
+      g_last_kernel = "sample:specialised regs=" + std::to_string(v->k.regs) +
+                      " T=" + std::to_string(s->jit.threads) + " ctas/sm=" +
+                      std::to_string(s->jit.min_blocks) + " cap=" + std::to_string(cap) +
+                      " group=" + std::to_string(s->jit.group);
+      return 0;
+    }
+    if (jit_mode() == 2) return fail(QEC_ERR_CUDA, "QEC_B200_JIT=require: %s", v->why.c_str());
+    g_last_kernel = "sample:table-driven (" + v->why.substr(0, 200) + ")";
+  } else if (!X.cnt) {
+    if (jit_mode() == 2)
+      return fail(QEC_ERR_CUDA, "QEC_B200_JIT=require: %s", s->jit.why.c_str());
+    g_last_kernel = "sample:table-driven (" + s->jit.why + ")";
+  } else {
+    g_last_kernel = "sample:table-driven (fault export requested)";
+  }
+  s->last_cap = s->cap;
   time_begin(s->c, stream);
   qec_launch_sample(s->cfg, stream, s->c->dev, O, s->dev, shot_lo / 32, n_shots,
                     (uint32_t *)s->scratch.p, s->cap, X, s->d_flag);
@@ -750,9 +986,15 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
 static int sampler_check(qec_sampler *s) {
   uint32_t flag = 0;
   CU(cudaMemcpy(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost));
-  if (flag <= (uint32_t)s->cap) return 0;
+  if (flag <= (uint32_t)(s->last_cap ? s->last_cap : s->cap)) return 0;
   CU(cudaMemset(s->d_flag, 0, 4));
-  s->cap = (int)((flag + 32 + 7) / 8 * 8);
+  if (s->last_cap && s->last_cap != s->cap) {
+    // the specialised kernel's shared-memory event list was too small for one lane word:
+    // the re-run goes through the table-driven kernel, whose list is in global memory
+    s->jit.eligible = false;
+    s->jit.why = "a lane word drew more events than fit in shared memory";
+  }
+  if (flag > (uint32_t)s->cap) s->cap = (int)((flag + 32 + 7) / 8 * 8);
   int rc = s->scratch.ensure((size_t)s->cfg.grid * s->cfg.block * s->cap * 4);
   if (rc) return rc;
   return fail(QEC_ERR_OVERFLOW, "sampler event buffer overflowed (%u events in one word)", flag);
@@ -899,5 +1141,45 @@ extern "C" int qec_host_free_pinned(void *p) { CU(cudaFreeHost(p)); return 0; }
 extern "C" int qec_stream_sync(int device, void *stream) {
   DEV_ENTER(device);
   CU(cudaStreamSynchronize((cudaStream_t)stream));
+  return 0;
+}
+
+// ---- diagnostics: the specialised kernel of a circuit, compiled without a device -----------------
+extern "C" int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t *row_off,
+                                       const int32_t *row_data, int L, const int32_t *loc_op,
+                                       int kind, int order, int tally, int bits, int threads,
+                                       int min_blocks, int group, const char *cubin_path,
+                                       const char *source_path) {
+  std::vector<uint8_t> rop;
+  std::vector<uint32_t> packed;
+  int64_t bit_ops = 0;
+  int rc = lower_rows(nq, nc, n_ops, row_off, row_data, rop, packed, bit_ops);
+  if (rc) return rc;
+  QecJitSpec spec;
+  spec.nq = nq; spec.nc = nc; spec.packed = &packed;
+  spec.is_loc.assign(packed.size(), 0);
+  for (int l = 0; l < L; ++l) {
+    if (loc_op[l] < 0 || loc_op[l] >= n_ops)
+      return fail(QEC_ERR_LOGIC, "faulty op index %d out of range [0, %d)", loc_op[l], n_ops);
+    spec.is_loc[loc_op[l]] = 1;
+  }
+  spec.kind = kind; spec.order = order; spec.tally = tally != 0; spec.bits = bits != 0;
+  spec.threads = threads; spec.min_blocks = min_blocks; spec.group = group;
+  if (source_path && *source_path) {
+    FILE *f = fopen(source_path, "w");
+    if (!f) return fail(QEC_ERR_INVALID, "cannot write %s", source_path);
+    const std::string src = qec_jit_gates_source(spec);
+    fwrite(src.data(), 1, src.size(), f);
+    fclose(f);
+  }
+  std::vector<char> cubin;
+  std::string log;
+  if (qec_jit_compile(spec, &cubin, &log)) return fail(QEC_ERR_CUDA, "%s", log.c_str());
+  if (cubin_path && *cubin_path) {
+    FILE *f = fopen(cubin_path, "wb");
+    if (!f) return fail(QEC_ERR_INVALID, "cannot write %s", cubin_path);
+    fwrite(cubin.data(), 1, cubin.size(), f);
+    fclose(f);
+  }
   return 0;
 }

@@ -12,7 +12,18 @@
 //     reference's `fail[icomb[j]] = j` rule (errorpropagator.cpp:265-267).
 //   * packed outcomes: out[c * n_words + w].
 #pragma once
+#ifdef __CUDACC_RTC__
+// NVRTC has no <stdint.h>: this header is also compiled at run time for the
+// circuit-specialised kernels (qec_jit.cpp embeds its text)
+typedef unsigned char uint8_t;
+typedef unsigned short uint16_t;
+typedef unsigned int uint32_t;
+typedef int int32_t;
+typedef unsigned long long uint64_t;
+typedef long long int64_t;
+#else
 #include <stdint.h>
+#endif
 
 #define QOP_NOP 0u    // x, y, z, id (b = 0: may host a fault); barrier, padding (b = 1)
 #define QOP_H 1u
@@ -26,6 +37,10 @@
 #define QEC_EV_SENTINEL 0xFFFFFFFFu
 #define QEC_EV_OP_SHIFT 9
 
+#if !defined(__CUDACC__) && !defined(__host__)
+#define __host__
+#define __device__
+#endif
 static inline __host__ __device__ uint32_t qec_pack_op(uint32_t opc, uint32_t a, uint32_t b) {
   return (opc & 15u) | ((a & 0x3FFFu) << 4) | ((b & 0x3FFFu) << 18);
 }
@@ -40,6 +55,47 @@ struct QecOutDev {
   uint32_t *frame;             // [2*nq][n_words] or nullptr
   unsigned long long *tally;   // QEC_TALLY_LEN(nc) or nullptr (accumulated with atomics)
   long long n_words;
+};
+
+// FaultEnumerator tables (all device pointers).
+//   E[m * (L + 2) + l], m = 0..order:  E[0][l] = 1;  E[m][l] = sum_{j >= l} npaul[j] * E[m-1][j+1]
+//   = number of order-m paths whose first location is >= l.  Total = E[order][0].
+struct QecEnumDev {
+  int order, L;
+  const unsigned long long *E;
+  const uint32_t *npaul;  // [L]   Paulis offered by location l
+  const uint32_t *poff;   // [L+1] prefix of npaul
+  const uint8_t *pcode;   // [poff[L]] 4-bit Pauli codes in digit order
+  const uint32_t *lop;    // [L]   op index of location l
+  // [L][4] (specialised kernels only) bit i of tile[4 l + c] = bit c of the Pauli code of
+  // digit (i mod npaul[l]) of location l: the 32 consecutive paths of a lane word read their
+  // last-location masks from it with one funnel shift (needs npaul[l] <= 32)
+  const unsigned long long *tile;
+};
+
+// FaultSampler tables (all device pointers).  "sl" = location index after a stable sort of
+// the locations by op index; a 32-shot word owns the slot space slot = sl * 32 + shot_bit.
+struct QecSamplerDev {
+  int L;
+  long long n_slots;       // L * 32
+  uint32_t B, K1;          // two-level geometric gap tables: gap = a * B + b
+  const uint32_t *T1;      // [K1]  T1[i] = round(2^32 * Q^(i+1)), Q = (1-pmax)^B
+  const uint32_t *T2;      // [B]   T2[j] = round(2^32 * P(b >= j | b < B)), T2[0] unused
+  const uint32_t *slop;    // [L] op index of sorted location sl
+  const uint32_t *slloc;   // [L] original location index of sl (for the fault export)
+  const uint16_t *slcls;   // [L] class of sl
+  const uint32_t *cls_acc; // [n_classes] accept threshold round(2^32 * p_class / pmax)
+  const uint8_t *cls_always;  // [n_classes] 1 if p_class == pmax
+  const uint32_t *cls_off;    // [n_classes+1]
+  const uint32_t *cdf;        // [cls_off[n]] cumulative Pauli thresholds (digit d: r < cdf[d])
+  const uint8_t *codes;       // [cls_off[n]] Pauli codes
+  uint32_t k0, k1;            // Philox key = seed
+};
+
+struct QecSampleExport {
+  uint32_t *cnt;  // [n_words] or nullptr
+  uint32_t *ev;   // [n_words][cap]
+  int cap;
 };
 
 #ifdef __CUDACC__
@@ -152,6 +208,75 @@ __device__ __forceinline__ void qec_propagate_word(const QecCircuitDev &C, uint3
   if (valid && O.frame) {
     for (int r = 0; r < 2 * nq; ++r) O.frame[(long long)r * O.n_words + w] = fr[r * T];
   }
+}
+
+// ---- FaultEnumerator unranking ---------------------------------------------------------
+// Rank -> (k-subset, Pauli digits) by closed-form unranking over the suffix tables E[m][l];
+// successor steps for the following paths.  Order of paths: reference combinations.cpp:18-32
+// (lexicographic subsets) and productiterator.cpp:17-32 (last digit fastest).
+template <int K>
+struct EnumState {
+  uint32_t loc[K], dig[K], np[K], op[K], pb[K];
+};
+
+template <int K>
+__device__ __forceinline__ void enum_load(const QecEnumDev &E, EnumState<K> &s, int j) {
+  const uint32_t l = s.loc[j];
+  s.np[j] = E.npaul[l];
+  s.op[j] = E.lop[l];
+  s.pb[j] = E.poff[l];
+}
+
+template <int K>
+__device__ __forceinline__ void enum_unrank(const QecEnumDev &E, unsigned long long r,
+                                            EnumState<K> &s) {
+  const int L2 = E.L + 2;
+  unsigned long long mult = 1;
+  uint32_t start = 0;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    const unsigned long long *Em = E.E + (size_t)(K - j) * L2;
+    const unsigned long long u = r / mult;
+    const unsigned long long thr = Em[start] - u;  // >= 1
+    // largest l in [start, L] with Em[l] >= thr (Em non-increasing, Em[L] = 0 < thr)
+    uint32_t lo = start, hi = (uint32_t)E.L;
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (Em[mid] >= thr) lo = mid; else hi = mid;
+    }
+    r -= mult * (Em[start] - Em[lo]);
+    s.loc[j] = lo;
+    enum_load<K>(E, s, j);
+    mult *= s.np[j];
+    start = lo + 1;
+  }
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    s.dig[j] = (uint32_t)(r % s.np[j]);
+    r /= s.np[j];
+  }
+}
+
+// advance to the next path; returns false past the last one
+template <int K>
+__device__ __forceinline__ bool enum_next(const QecEnumDev &E, EnumState<K> &s) {
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    if (++s.dig[j] < s.np[j]) return true;
+    s.dig[j] = 0;
+  }
+  int i = K - 1;
+  while (i >= 0 && s.loc[i] >= (uint32_t)(E.L - K + i)) --i;
+  if (i < 0) return false;
+  const uint32_t base = s.loc[i] + 1;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    if (j >= i) {
+      s.loc[j] = base + (uint32_t)(j - i);
+      enum_load<K>(E, s, j);
+    }
+  }
+  return true;
 }
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based ------------------------------

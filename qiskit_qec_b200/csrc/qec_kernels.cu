@@ -69,71 +69,6 @@ k_propagate_batch(const QecCircuitDev C, const QecOutDev O, const long long *__r
 // the suffix tables E[m][l]; the following 31 paths of the lane word by successor steps.
 // Order of paths: reference combinations.cpp:18-32 (lexicographic subsets) and
 // productiterator.cpp:17-32 (last digit fastest).
-template <int K>
-struct EnumState {
-  uint32_t loc[K], dig[K], np[K], op[K], pb[K];
-};
-
-template <int K>
-__device__ __forceinline__ void enum_load(const QecEnumDev &E, EnumState<K> &s, int j) {
-  const uint32_t l = s.loc[j];
-  s.np[j] = E.npaul[l];
-  s.op[j] = E.lop[l];
-  s.pb[j] = E.poff[l];
-}
-
-template <int K>
-__device__ __forceinline__ void enum_unrank(const QecEnumDev &E, unsigned long long r,
-                                            EnumState<K> &s) {
-  const int L2 = E.L + 2;
-  unsigned long long mult = 1;
-  uint32_t start = 0;
-#pragma unroll
-  for (int j = 0; j < K; ++j) {
-    const unsigned long long *Em = E.E + (size_t)(K - j) * L2;
-    const unsigned long long u = r / mult;
-    const unsigned long long thr = Em[start] - u;  // >= 1
-    // largest l in [start, L] with Em[l] >= thr (Em non-increasing, Em[L] = 0 < thr)
-    uint32_t lo = start, hi = (uint32_t)E.L;
-    while (hi - lo > 1) {
-      const uint32_t mid = (lo + hi) >> 1;
-      if (Em[mid] >= thr) lo = mid; else hi = mid;
-    }
-    r -= mult * (Em[start] - Em[lo]);
-    s.loc[j] = lo;
-    enum_load<K>(E, s, j);
-    mult *= s.np[j];
-    start = lo + 1;
-  }
-#pragma unroll
-  for (int j = K - 1; j >= 0; --j) {
-    s.dig[j] = (uint32_t)(r % s.np[j]);
-    r /= s.np[j];
-  }
-}
-
-// advance to the next path; returns false past the last one
-template <int K>
-__device__ __forceinline__ bool enum_next(const QecEnumDev &E, EnumState<K> &s) {
-#pragma unroll
-  for (int j = K - 1; j >= 0; --j) {
-    if (++s.dig[j] < s.np[j]) return true;
-    s.dig[j] = 0;
-  }
-  int i = K - 1;
-  while (i >= 0 && s.loc[i] >= (uint32_t)(E.L - K + i)) --i;
-  if (i < 0) return false;
-  const uint32_t base = s.loc[i] + 1;
-#pragma unroll
-  for (int j = 0; j < K; ++j) {
-    if (j >= i) {
-      s.loc[j] = base + (uint32_t)(j - i);
-      enum_load<K>(E, s, j);
-    }
-  }
-  return true;
-}
-
 template <int K, bool TALLY>
 __global__ void __launch_bounds__(256)
 k_enumerate(const QecCircuitDev C, const QecOutDev O, const QecEnumDev E, const long long lo,

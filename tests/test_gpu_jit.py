@@ -1,0 +1,123 @@
+"""GPU parity of the circuit-specialised (run-time compiled) kernels against the table-driven
+kernels: same circuit, same faults -> identical packed outcomes and tallies, bit for bit.
+The table-driven kernels are themselves checked against the reference in test_gpu_parity.py,
+and with the default QEC_B200_JIT=1 those tests already run the specialised kernels wherever a
+circuit is eligible, so both kernel families are pinned to the reference."""
+
+import os
+
+import numpy as np
+import pytest
+
+from qiskit_qec_b200.circuits import (arc_circuit, heavy_hex_27_arc_layout, repetition_code_circuit,
+                                      surface_code_circuit)
+from qiskit_qec_b200.noise import standard_depolarizing_model
+
+from helpers import make_enumerator, make_sampler, noise_inputs, sampler_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+class jit_env:
+    def __init__(self, value):
+        self.value = value
+
+    def __enter__(self):
+        self.old = os.environ.get("QEC_B200_JIT")
+        os.environ["QEC_B200_JIT"] = self.value
+
+    def __exit__(self, *a):
+        if self.old is None:
+            os.environ.pop("QEC_B200_JIT", None)
+        else:
+            os.environ["QEC_B200_JIT"] = self.old
+
+
+def _circuit(name):
+    if name == "rep":
+        return repetition_code_circuit(3, 2)
+    if name == "surf3":
+        return surface_code_circuit(3, 3)
+    if name == "surf5":
+        return surface_code_circuit(5, 5)
+    if name == "surf3x":
+        return surface_code_circuit(3, 2, basis="x")
+    links, sched, color = heavy_hex_27_arc_layout()
+    return arc_circuit(links, 3, "zx", sched, color)
+
+
+@pytest.mark.parametrize("name,order,windows", [
+    ("rep", 1, None), ("rep", 2, None), ("rep", 3, None), ("surf3", 1, None), ("surf3", 2, None),
+    ("surf3x", 2, None), ("arc", 2, 6), ("arc", 3, 6), ("surf5", 1, None), ("surf5", 2, 10),
+    ("surf3", 3, 6),
+])
+def test_enumerator_specialised_equals_table_driven(capi, name, order, windows):
+    circ = _circuit(name)
+    idx, labels, paulis = noise_inputs(circ, standard_depolarizing_model())
+    with jit_env("require"):
+        gj = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        ej = make_enumerator(capi, gj, order, idx, paulis)
+    with jit_env("0"):
+        gt = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        et = make_enumerator(capi, gt, order, idx, paulis)
+    n = ej.num_paths()
+    rng = np.random.default_rng(17)
+    if windows is None:
+        ranges = [(0, n)] + [(int(lo), int(min(n, lo + rng.integers(0, 300))))
+                             for lo in rng.integers(0, n, size=5)]
+    else:
+        span = 40_000
+        ranges = [(0, span), (n - span, n)] + [(int(lo), int(lo) + span - int(rng.integers(0, 70)))
+                                               for lo in rng.integers(0, n - span, size=windows)]
+    for lo, hi in ranges:
+        with jit_env("require"):
+            bj, tj = ej.range(lo, hi, want_tally=True)
+            assert "specialised" in capi.last_kernel()
+            _, tj2 = ej.range(lo, hi, want_bits=False, want_tally=True)
+            bj3, _ = ej.range(lo, hi)
+        with jit_env("0"):
+            bt, tt = et.range(lo, hi, want_tally=True)
+            assert "table-driven" in capi.last_kernel()
+        np.testing.assert_array_equal(bj, bt)
+        np.testing.assert_array_equal(bj3, bt)
+        np.testing.assert_array_equal(tj, tt)
+        np.testing.assert_array_equal(tj2, tt)
+
+
+@pytest.mark.parametrize("name,p,n_shots", [("rep", 0.05, 40_000), ("surf3", 0.01, 100_000),
+                                            ("surf5", 1e-3, 1_000_000), ("arc", 2e-3, 200_000),
+                                            ("surf5", 1e-4, 300_000)])
+def test_sampler_specialised_equals_table_driven(capi, name, p, n_shots):
+    circ = _circuit(name)
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(p))
+    out = {}
+    for mode in ("require", "0"):
+        with jit_env(mode):
+            g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+            sm = make_sampler(capi, g, idx, labels, lw, lp, seed=1234)
+            res = []
+            for lo, n in ((0, n_shots), (64 * 977, n_shots - 13), (32, 1)):
+                bits, tally, _, _ = sm.sample(lo, n, want_tally=True)
+                _, tally2, _, _ = sm.sample(lo, n, want_bits=False, want_tally=True)
+                bits3, _, _, _ = sm.sample(lo, n)
+                np.testing.assert_array_equal(tally, tally2)
+                np.testing.assert_array_equal(bits, bits3)
+                res.append((bits, tally))
+            assert ("specialised" if mode == "require" else "table-driven") in capi.last_kernel()
+            out[mode] = res
+    for (bj, tj), (bt, tt) in zip(out["require"], out["0"]):
+        np.testing.assert_array_equal(bj, bt)
+        np.testing.assert_array_equal(tj, tt)
+
+
+def test_ineligible_circuit_falls_back_to_table_driven(capi):
+    """d=11 (482 frame words) cannot live in registers: table-driven kernel, and `require` fails."""
+    circ = surface_code_circuit(11, 2)
+    idx, labels, paulis = noise_inputs(circ, standard_depolarizing_model())
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    en = make_enumerator(capi, g, 1, idx, paulis)
+    en.range(0, 1000)
+    assert "table-driven" in capi.last_kernel() and "register" in capi.last_kernel()
+    with jit_env("require"):
+        with pytest.raises(RuntimeError, match="QEC_B200_JIT=require"):
+            en.range(0, 1000)
