@@ -225,6 +225,7 @@ def run_ours(args):
         ev[i + 1].record()
     torch.cuda.synchronize()
     sm.check()
+    sampler_kernel = _capi.last_kernel()
     if world > 1:
         dist.barrier()
     clk = clocks.stop() if rank == 0 else None
@@ -303,7 +304,8 @@ def run_ours(args):
         assert int(tally[nc + 1].item()) == total
         enum = {"metric": "FaultEnumerator order-2 faults/s", "value": total / (ems * 1e-3),
                 "unit": "faults/s", "paths": total, "ms": ems, "scaling": "strong",
-                "workload": "order=2 exhaustive, SurfaceCodeCircuit d=5 T=5 (BASELINE configs[2])"}
+                "workload": "order=2 exhaustive, SurfaceCodeCircuit d=5 T=5 (BASELINE configs[2])",
+                "kernel": _capi.last_kernel()}
 
     if rank == 0:
         peaks = {}
@@ -329,7 +331,7 @@ def run_ours(args):
                        "l2": "output per step (1.81 GB at 1e8 shots) is larger than L2; no reuse",
                        "timing": "CUDA events on the launching stream, max over ranks"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "kernel": "k_sample<true>",
+                         "frac": achieved / hbm_peak, "traffic": None, "kernel": sampler_kernel,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_shot": nc / 8.0},
             "int_roofline": {"bound": "int32-alu", "achieved": int_ach, "peak": int_peak,

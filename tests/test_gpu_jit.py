@@ -94,7 +94,7 @@ def test_sampler_specialised_equals_table_driven(capi, name, p, n_shots):
     for mode in ("require", "0"):
         with jit_env(mode):
             g = capi.Circuit(circ.nq, circ.nc, circ.ops)
-            sm = make_sampler(capi, g, idx, labels, lw, lp, seed=1234)
+            sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=1234)
             res = []
             for lo, n in ((0, n_shots), (64 * 977, n_shots - 13), (32, 1)):
                 bits, tally, _, _ = sm.sample(lo, n, want_tally=True)
