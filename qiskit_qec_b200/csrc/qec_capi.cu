@@ -328,7 +328,7 @@ struct JitVariant {  // one compiled kernel per (tally, bits) combination, built
 struct JitPlan {
   bool eligible = false;
   std::string why;          // why not, when not eligible
-  int threads = 128, min_blocks = 1, grid = 0, group = 8;
+  int threads = 128, min_blocks = 1, grid = 0, group = 8, sync_every = 96, segments = 1;
   size_t smem = 0;
   std::vector<uint8_t> is_loc;
   JitVariant var[2][2];
@@ -338,15 +338,20 @@ struct JitPlan {
 };
 
 // registers a specialised kernel needs: the frame plus cursor / addressing overhead
-static int jit_regs_estimate(int nq) { return 2 * nq + 56; }
+static int jit_regs_estimate(int nq) { return 2 * nq + 40; }
 
 static void jit_plan_geometry(const qec_circuit *c, JitPlan &pl) {
   const int regs = jit_regs_estimate(c->nq);
   int minb = 65536 / (regs * pl.threads);
   if (minb > 8) minb = 8;
   if (minb < 1) minb = 1;
+  minb = env_int("QEC_B200_JIT_MINB", minb);
   pl.min_blocks = minb;
   pl.grid = c->info->sms * minb;
+  pl.sync_every = env_int("QEC_B200_JIT_SYNC", 96);
+}
+static size_t jit_bitmap_words(const qec_circuit *c, const JitPlan &pl) {
+  return ((c->packed.size() + 31) / 32) * (size_t)pl.threads;
 }
 
 static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, bool tally, bool bits) {
@@ -357,6 +362,7 @@ static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, boo
   spec.nq = c->nq; spec.nc = c->nc; spec.packed = &c->packed; spec.is_loc = pl.is_loc;
   spec.kind = kind; spec.order = order; spec.tally = tally; spec.bits = bits;
   spec.threads = pl.threads; spec.min_blocks = pl.min_blocks; spec.group = pl.group;
+  spec.sync_every = pl.sync_every; spec.segments = pl.segments;
   std::vector<char> cubin;
   std::string log;
   if (qec_jit_compile(spec, &cubin, &log)) { v.why = "NVRTC: " + log; return &v; }
@@ -468,7 +474,7 @@ static void enum_plan_jit(qec_enumerator *e) {
   pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
   pl.group = env_int("QEC_B200_JIT_GROUP", 8);
   jit_plan_geometry(c, pl);
-  pl.smem = (size_t)c->nc * 4 + 16;
+  pl.smem = ((size_t)c->nc + jit_bitmap_words(c, pl)) * 4 + 16;
   // tile[4 l + k]: bit i = bit k of the code of digit (i mod npaul[l])
   e->tile.assign((size_t)4 * e->L, 0ull);
   for (int l = 0; l < e->L; ++l) {
@@ -732,45 +738,88 @@ struct qec_sampler {
   QecLaunchCfg cfg{};
   // circuit-specialised path: events of a lane word live in shared memory (jit_cap of them)
   JitPlan jit;
-  int jit_cap = 0;
+  int jit_cap = 0, jit_capw = 0;
+  uint32_t lgP = 1;
+  std::vector<uint32_t> seg_end;
+  uint32_t *d_seg_end = nullptr;
+  std::vector<double> loc_p;  // failure probability of sorted location sl
+  std::vector<uint32_t> slinf;
+  uint32_t *d_slinf = nullptr;
   int last_cap = 0;  // event capacity of the kernel that served the latest launches
 };
 
-static void sampler_plan_jit(qec_sampler *s) {
+static int sampler_plan_jit(qec_sampler *s) {
   JitPlan &pl = s->jit;
   qec_circuit *c = s->c;
-  if (jit_mode() == 0) { pl.why = "QEC_B200_JIT=0"; return; }
-  if (2 * c->nq > 200) { pl.why = "frame of " + std::to_string(2 * c->nq) + " words exceeds the register file"; return; }
-  if (s->dev.n_slots <= 0) { pl.why = "no fault can occur"; return; }
+  if (jit_mode() == 0) { pl.why = "QEC_B200_JIT=0"; return 0; }
+  if (2 * c->nq > 200) { pl.why = "frame of " + std::to_string(2 * c->nq) + " words exceeds the register file"; return 0; }
+  if (s->dev.n_slots <= 0) { pl.why = "no fault can occur"; return 0; }
+  if (s->n_classes > 1024 || c->packed.size() >= (1u << 20)) { pl.why = "too many classes / ops for the packed location word"; return 0; }
   for (int i = 1; i < s->L; ++i)
-    if (s->slop[i] <= s->slop[i - 1]) { pl.why = "two fault locations share one op"; return; }
+    if (s->slop[i] <= s->slop[i - 1]) { pl.why = "two fault locations share one op"; return 0; }
   std::string why;
-  if (!qec_jit_available(&why)) { pl.why = why; return; }
+  if (!qec_jit_available(&why)) { pl.why = why; return 0; }
   pl.is_loc.assign(c->packed.size(), 0);
   for (int i = 0; i < s->L; ++i) pl.is_loc[s->slop[i]] = 1;
   pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
   jit_plan_geometry(c, pl);
-  // events per lane word: mean + 9.5 sigma if shared memory allows, never below mean + 6 sigma
-  const double mu = s->mean_events;
-  const int want = (int)std::ceil(mu + 9.5 * std::sqrt(mu) + 8.0);
-  const int least = (int)std::ceil(mu + 6.0 * std::sqrt(mu) + 8.0);
-  const size_t fixed = ((size_t)c->nc + 64 + s->K1 + s->B) * 4 + 16;
-  int cap = 0;
-  for (int minb = pl.min_blocks; minb >= 1; --minb) {
+  const size_t tabw = qec_samp_tab_words(s->K1, s->B, (uint32_t)s->L, (uint32_t)s->n_classes, s->lgP);
+  // Gate-stream segments: the fewest for which the mask queue of one segment (2 words per
+  // event on a one-qubit op, 4 on a cx; mean + 9.5 sigma, never below mean + 6 sigma) leaves
+  // room for the CTAs the register budget allows.
+  QecJitSpec probe;
+  probe.packed = &c->packed;
+  const int seg_env = env_int("QEC_B200_JIT_SEGS", 0);
+  int capw = 0;
+  for (int minb = pl.min_blocks; minb >= 1 && !capw; --minb) {
     size_t per_cta = c->info->smem_sm / minb - 1024;
     if (per_cta > c->info->smem_optin) per_cta = c->info->smem_optin;
-    if (per_cta <= fixed) continue;
-    const int fit = (int)((per_cta - fixed) / ((size_t)8 * pl.threads)) - 2;
-    if (fit >= least) {
-      cap = std::min(fit, want);
-      pl.min_blocks = minb;
-      break;
+    for (int segs = seg_env > 0 ? seg_env : 1; segs <= (seg_env > 0 ? seg_env : 16); ++segs) {
+      probe.segments = segs;
+      const int SL = qec_jit_segment_ops(probe), NS = qec_jit_segment_count(probe);
+      double want_w = 0, least_w = 0;
+      for (int g = 0; g < NS; ++g) {
+        double mu_w = 0, var_w = 0;
+        for (int i = 0; i < s->L; ++i) {
+          if ((int)(s->slop[i] / (uint32_t)SL) != g) continue;
+          const double len = ((c->packed[s->slop[i]] & 15u) == QOP_CX) ? 4.0 : 2.0;
+          mu_w += 32.0 * s->loc_p[i] * len;
+          var_w += 32.0 * s->loc_p[i] * len * len;
+        }
+        want_w = std::max(want_w, mu_w + 9.5 * std::sqrt(var_w) + 16.0);
+        least_w = std::max(least_w, mu_w + 6.0 * std::sqrt(var_w) + 16.0);
+      }
+      const int want = ((int)std::ceil(want_w) + 3) / 4 * 4, least = ((int)std::ceil(least_w) + 3) / 4 * 4;
+      const size_t fixed = ((size_t)c->nc + 64 + tabw + (size_t)(SL / 32) * pl.threads + 4) * 4 + 16;
+      if (per_cta <= fixed) continue;
+      int fit = (int)((per_cta - fixed) / ((size_t)4 * pl.threads)) / 4 * 4;
+      if (fit >= want || (fit >= least && (segs == 16 || seg_env > 0))) {
+        capw = std::min(fit, want);
+        if ((capw / 4) % 2 == 0) capw -= 4;  // odd number of 16-byte units per lane word: no bank pile-up
+        pl.min_blocks = minb;
+        pl.segments = NS;
+        pl.smem = fixed + (size_t)4 * pl.threads * capw;
+        s->seg_end.clear();
+        for (int g = 0; g < NS; ++g) {
+          int i = 0;
+          while (i < s->L && s->slop[i] < (uint32_t)((g + 1) * SL)) ++i;
+          s->seg_end.push_back((uint32_t)i * 32u);
+        }
+        s->seg_end.back() = (uint32_t)s->dev.n_slots;
+        break;
+      }
     }
   }
-  if (!cap) { pl.why = "the events of a lane word do not fit in shared memory"; return; }
+  if (capw < 8) { pl.why = "the events of a lane word do not fit in shared memory"; return 0; }
   pl.grid = c->info->sms * pl.min_blocks;
-  s->jit_cap = cap;
-  pl.smem = fixed + (size_t)8 * pl.threads * (cap + 2);
+  s->jit_capw = capw;
+  s->jit_cap = capw / 2;
+  if (s->d_seg_end) { cudaFree(s->d_seg_end); s->d_seg_end = nullptr; }
+  int rc = upload(s->seg_end, &s->d_seg_end);
+  if (rc) return rc;
+  s->dev.n_seg = pl.segments;
+  s->dev.seg_end = s->d_seg_end;
+  const double mu = s->mean_events;
   // one warp sees about 1024 * p events per location: a block test only pays when that is small
   const double lam = 1024.0 * mu / 32.0 / std::max(1, s->L);
   int group = lam > 0 ? (int)(0.25 / lam) : 8;
@@ -778,6 +827,7 @@ static void sampler_plan_jit(qec_sampler *s) {
   if (group < 2) group = 0;
   pl.group = env_int("QEC_B200_JIT_GROUP_SAMPLER", group);
   pl.eligible = true;
+  return 0;
 }
 
 static inline uint32_t fix32(double x) {  // round(2^32 * x) clamped to [0, 2^32 - 1]
@@ -822,6 +872,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
     if (p > 1) p = 1;
     pmax = std::max(pmax, p);
     psum += p;
+    s->loc_p.push_back(p);
   }
   s->mean_events = 32.0 * psum;
   // classes
@@ -852,11 +903,24 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
     s->cls_always.push_back(ratio >= 1.0 ? 1 : 0);
     s->cls_acc.push_back(fix32(ratio));
   }
+  // per sorted location: op | class << 20 | cx << 30 | always << 31 (specialised kernels)
+  uint32_t maxnp = 1;
+  for (int k = 0; k < n_classes; ++k) maxnp = std::max(maxnp, s->cls_off[k + 1] - s->cls_off[k]);
+  s->lgP = 1;
+  while ((1u << s->lgP) < maxnp) ++s->lgP;
+  for (int i = 0; i < L; ++i) {
+    const uint32_t op = s->slop[i], cls = s->slcls[i];
+    s->slinf.push_back((op & 0xFFFFFu) | ((cls & 1023u) << 20) |
+                       (((c->packed[op] & 15u) == QOP_CX) ? (1u << 30) : 0u) |
+                       (s->cls_always[cls] ? (1u << 31) : 0u));
+  }
   // two-level geometric gap tables at rate pmax
   s->dev.n_slots = pmax > 0 ? (long long)L * 32 : 0;
   const double lq = std::log1p(-pmax);  // -inf when pmax == 1
+  // B: large enough that the first-level draw is almost always 0 (Q^B <= 0.15), so the gap is
+  // one guided lookup in T2
   uint32_t B = 32;
-  while (B < 1024 && std::exp((double)B * lq) > 0.75) B *= 2;
+  while (B < 4096 && std::exp((double)B * lq) > 0.15) B *= 2;
   s->B = B;
   for (uint32_t i = 0; i < 1024; ++i) {
     const uint32_t v = pmax > 0 ? fix32(std::exp((double)(i + 1) * B * lq)) : 0u;
@@ -877,6 +941,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
   int rc = 0;
   if ((rc = upload(s->T1, &s->d_T1)) || (rc = upload(s->T2, &s->d_T2)) ||
       (rc = upload(s->slop, &s->d_slop)) || (rc = upload(s->slloc, &s->d_slloc)) ||
+      (rc = upload(s->slinf, &s->d_slinf)) ||
       (rc = upload(s->slcls, &s->d_slcls)) || (rc = upload(s->cls_acc, &s->d_cls_acc)) ||
       (rc = upload(s->cls_always, &s->d_cls_always)) || (rc = upload(s->cls_off, &s->d_cls_off)) ||
       (rc = upload(s->cdf, &s->d_cdf)) || (rc = upload(s->codes, &s->d_codes)) ||
@@ -896,10 +961,14 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
   }
   QecSamplerDev &d = s->dev;
   d.L = L; d.B = s->B; d.K1 = s->K1; d.T1 = s->d_T1; d.T2 = s->d_T2; d.slop = s->d_slop;
+  d.slinf = s->d_slinf; d.n_classes = n_classes; d.lgP = s->lgP; d.n_seg = 1; d.seg_end = nullptr;
   d.slloc = s->d_slloc; d.slcls = s->d_slcls; d.cls_acc = s->d_cls_acc;
   d.cls_always = s->d_cls_always; d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.codes = s->d_codes;
   d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32);
-  sampler_plan_jit(s);
+  if ((rc = sampler_plan_jit(s))) {
+    qec_sampler_destroy(s);
+    return rc;
+  }
   *out = s;
   return 0;
 }
@@ -908,7 +977,8 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   if (!s) return;
   cudaSetDevice(s->c->device);
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
-                  s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag};
+                  s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
+                  s->d_seg_end};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -950,8 +1020,8 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
     JitVariant *v = jit_get(s->c, s->jit, 2, 0, d_tally != nullptr, d_bits != nullptr);
     if (v->ok) {
       long long wlo = shot_lo / 32, ns = n_shots;
-      int cap = s->jit_cap;
-      void *args[] = {&O, &s->dev, &wlo, &ns, &cap, &s->d_flag};
+      int cap = s->jit_cap, capw = s->jit_capw;
+      void *args[] = {&O, &s->dev, &wlo, &ns, &cap, &capw, &s->d_flag};
       std::string err;
       time_begin(s->c, stream);
       const int rc = qec_jit_launch(v->k, s->jit.grid, s->jit.smem, stream, args, &err);
@@ -960,8 +1030,8 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
       s->last_cap = cap;
       g_last_kernel = "sample:specialised regs=" + std::to_string(v->k.regs) +
                       " T=" + std::to_string(s->jit.threads) + " ctas/sm=" +
-                      std::to_string(s->jit.min_blocks) + " cap=" + std::to_string(cap) +
-                      " group=" + std::to_string(s->jit.group);
+                      std::to_string(s->jit.min_blocks) + " segs=" + std::to_string(s->jit.segments) +
+                      " queue=" + std::to_string(capw) + "w group=" + std::to_string(s->jit.group);
       return 0;
     }
     if (jit_mode() == 2) return fail(QEC_ERR_CUDA, "QEC_B200_JIT=require: %s", v->why.c_str());
@@ -1165,6 +1235,8 @@ extern "C" int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t 
   }
   spec.kind = kind; spec.order = order; spec.tally = tally != 0; spec.bits = bits != 0;
   spec.threads = threads; spec.min_blocks = min_blocks; spec.group = group;
+  spec.segments = env_int("QEC_B200_JIT_SEGS", 1);      // (inspection only: the launch path
+  spec.sync_every = env_int("QEC_B200_JIT_SYNC", 96);   //  plans these itself)
   if (source_path && *source_path) {
     FILE *f = fopen(source_path, "w");
     if (!f) return fail(QEC_ERR_INVALID, "cannot write %s", source_path);

@@ -134,7 +134,7 @@ struct Namer {  // frame word -> register name; h() renames instead of moving
   }
 };
 
-inline void reg(std::ostringstream &o, int id) { o << 'f' << id; }
+inline void reg(std::ostringstream &o, int id) { o << "F.f" << id; }
 
 // emit ops [s, e) of the table; with_faults = also the injection tests
 void emit_range(std::ostringstream &o, const QecJitSpec &spec, Namer &nm, size_t s, size_t e,
@@ -143,9 +143,11 @@ void emit_range(std::ostringstream &o, const QecJitSpec &spec, Namer &nm, size_t
   for (size_t i = s; i < e; ++i) {
     const uint32_t g = tab[i], opc = g & 15u, a = (g >> 4) & 0x3FFFu, b = g >> 18;
     const bool loc = with_faults && i < spec.is_loc.size() && spec.is_loc[i];
+    // bit (i & 31) of the bitmap word loaded by cur.word(i >> 5): the lanes that hit pop their
+    // queue entry into the named registers (ptxas predicates these few instructions)
     auto inj1 = [&]() {
       if (!loc) return;
-      o << ind << "if (cur.hit(" << i << "u)) cur.inj1(" << i << "u, ";
+      o << ind << "if (cur.hit(0x" << std::hex << (1u << (i & 31)) << std::dec << "u)) cur.inj1(";
       reg(o, nm.x[a]); o << ", "; reg(o, nm.z[a]); o << ");\n";
     };
     switch (opc) {
@@ -161,7 +163,7 @@ void emit_range(std::ostringstream &o, const QecJitSpec &spec, Namer &nm, size_t
         o << ind; reg(o, nm.x[b]); o << " ^= "; reg(o, nm.x[a]); o << "; ";
         reg(o, nm.z[a]); o << " ^= "; reg(o, nm.z[b]); o << ";\n";
         if (loc) {
-          o << ind << "if (cur.hit(" << i << "u)) cur.inj2(" << i << "u, ";
+          o << ind << "if (cur.hit(0x" << std::hex << (1u << (i & 31)) << std::dec << "u)) cur.inj2(";
           reg(o, nm.x[a]); o << ", "; reg(o, nm.z[a]); o << ", ";
           reg(o, nm.x[b]); o << ", "; reg(o, nm.z[b]); o << ");\n";
         }
@@ -190,40 +192,90 @@ void emit_range(std::ostringstream &o, const QecJitSpec &spec, Namer &nm, size_t
 
 }  // namespace
 
+// ops per gate-stream segment (a multiple of 32, so that segments own whole bitmap words)
+static size_t seg_len(const QecJitSpec &spec) {
+  const size_t n = spec.packed->size();
+  const size_t S = spec.segments > 1 ? (size_t)spec.segments : 1;
+  size_t len = ((n + S - 1) / S + 31) / 32 * 32;
+  return len ? len : 32;
+}
+
+int qec_jit_segment_ops(const QecJitSpec &spec) { return (int)seg_len(spec); }
+int qec_jit_segment_count(const QecJitSpec &spec) {
+  const size_t n = spec.packed->size(), len = seg_len(spec);
+  const size_t S = (n + len - 1) / len;
+  return S ? (int)S : 1;
+}
+
 std::string qec_jit_gates_source(const QecJitSpec &spec) {
   const std::vector<uint32_t> &tab = *spec.packed;
   std::ostringstream o;
+  const size_t n = tab.size(), SL = seg_len(spec);
+  const int NSEG = qec_jit_segment_count(spec);
   o << "// generated: gate stream of a " << spec.nq << "-qubit, " << spec.nc << "-clbit circuit, "
-    << tab.size() << " table entries\n";
-  o << "template <class CUR, bool TALLY, bool BITS>\n"
-       "__device__ __forceinline__ void qec_jit_gates(CUR &cur, const bool valid,\n"
-       "    uint32_t *__restrict__ ob, const long long os, uint32_t *s_tally, uint32_t &any_out) {\n";
-  for (int r = 0; r < 2 * spec.nq; ++r) {
-    o << (r % 8 == 0 ? "  uint32_t " : " ") << 'f' << r << " = 0u" << ((r % 8 == 7 || r == 2 * spec.nq - 1) ? ";\n" : ",");
-  }
+    << tab.size() << " table entries, " << NSEG << " segment(s) of " << SL << " ops\n";
+  o << "#define QEC_JIT_NSEG " << NSEG << "\n#define QEC_JIT_SEGW " << SL / 32 << "\n";
+  o << "struct QecFrame {\n";
+  for (int r = 0; r < 2 * spec.nq; ++r)
+    o << (r % 8 == 0 ? "  uint32_t " : " ") << 'f' << r << ((r % 8 == 7 || r == 2 * spec.nq - 1) ? ";\n" : ",");
+  o << "};\n__device__ __forceinline__ void qec_jit_frame_zero(QecFrame &F) {\n";
+  for (int r = 0; r < 2 * spec.nq; ++r)
+    o << (r % 8 == 0 ? "  " : " ") << "F.f" << r << " = 0u;" << ((r % 8 == 7 || r == 2 * spec.nq - 1) ? "\n" : "");
+  o << "}\n";
   Namer nm(spec.nq);
-  const size_t n = tab.size();
-  if (spec.group <= 0) {
-    emit_range(o, spec, nm, 0, n, true, "  ");
-  } else {
-    for (size_t s = 0; s < n; s += (size_t)spec.group) {
-      const size_t e = std::min(n, s + (size_t)spec.group);
-      bool any_loc = false;
-      for (size_t i = s; i < e; ++i) any_loc |= (i < spec.is_loc.size() && spec.is_loc[i]);
-      if (!any_loc) {
-        emit_range(o, spec, nm, s, e, false, "  ");
+  // a block never straddles a bitmap word: its size is a power of two <= 32
+  size_t G = 0;
+  if (spec.group > 0) {
+    G = 1;
+    while (2 * G <= (size_t)spec.group && 2 * G <= 32) G *= 2;
+    if (G < 2) G = 0;
+  }
+  const size_t step = G ? G : 32;
+  for (int seg = 0; seg < NSEG; ++seg) {
+    const size_t s0 = (size_t)seg * SL, s1 = std::min(n, s0 + SL);
+    o << "template <class CUR, bool TALLY, bool BITS>\n"
+         "__device__ __forceinline__ void qec_jit_seg" << seg << "(QecFrame &F, CUR &cur, const bool valid,\n"
+         "    uint32_t *__restrict__ ob, const long long os, uint32_t *s_tally, uint32_t &any_out) {\n";
+    size_t since_sync = 0;
+    for (size_t s = s0; s < s1; s += step) {
+      const size_t e = std::min(s1, s + step);
+      uint32_t mask = 0;
+      for (size_t i = s; i < e; ++i)
+        if (i < spec.is_loc.size() && spec.is_loc[i]) mask |= 1u << (i & 31);
+      // keep the warps of a CTA within one stretch of the code (instruction-cache locality)
+      if (spec.sync_every > 0 && since_sync >= (size_t)spec.sync_every) {
+        o << "  __syncthreads();\n";
+        since_sync = 0;
+      }
+      since_sync += e - s;
+      if ((s & 31) == 0) {
+        bool word_has_loc = false;
+        for (size_t i = s; i < std::min(s1, s + 32); ++i)
+          word_has_loc |= (i < spec.is_loc.size() && spec.is_loc[i]);
+        if (word_has_loc) o << "  cur.word(" << ((s - s0) >> 5) << ");\n";
+      }
+      if (!G || !mask) {
+        emit_range(o, spec, nm, s, e, mask != 0, "  ");
         continue;
       }
-      // one warp vote per block: does any lane word have an event in [s, e)?
-      o << "  if (!__any_sync(0xFFFFFFFFu, cur.before(" << e << "u))) {\n";
+      // one warp vote per block: does any lane word have an event on ops [s, e)?
+      o << "  if (!__any_sync(0xFFFFFFFFu, cur.any(0x" << std::hex << mask << std::dec << "u))) {\n";
       Namer fast = nm;
       emit_range(o, spec, fast, s, e, false, "    ");
       o << "  } else {\n";
       emit_range(o, spec, nm, s, e, true, "    ");
       o << "  }\n";
     }
+    o << "}\n";
   }
-  o << "}\n";
+  o << "template <class CUR, bool TALLY, bool BITS>\n"
+       "__device__ __forceinline__ void qec_jit_seg(const int seg, QecFrame &F, CUR &cur, const bool valid,\n"
+       "    uint32_t *__restrict__ ob, const long long os, uint32_t *s_tally, uint32_t &any_out) {\n"
+       "  switch (seg) {\n";
+  for (int seg = 0; seg < NSEG; ++seg)
+    o << "    case " << seg << ": qec_jit_seg" << seg
+      << "<CUR, TALLY, BITS>(F, cur, valid, ob, os, s_tally, any_out); break;\n";
+  o << "  }\n}\n";
   return o.str();
 }
 
@@ -270,6 +322,7 @@ int qec_jit_compile(const QecJitSpec &spec, std::vector<char> *cubin, std::strin
            << "#define QEC_JIT_TALLY " << (spec.tally ? 1 : 0) << "\n"
            << "#define QEC_JIT_BITS " << (spec.bits ? 1 : 0) << "\n"
            << "#define QEC_JIT_NC " << spec.nc << "\n"
+           << "#define QEC_JIT_NOPS " << spec.packed->size() << "\n"
            << "#include \"qec_device.cuh\"\n"
            << "#include \"qec_jit_kernels.cuh\"\n";
   const std::string src = main_src.str();

@@ -15,6 +15,8 @@ struct QecJitSpec {
   bool tally = false, bits = true;
   int threads = 128, min_blocks = 3;
   int group = 8;  // ops per "any event in here?" block; 0 = test every location
+  int segments = 1;     // the sampler draws the faults of one gate-stream segment at a time
+  int sync_every = 96;  // a CTA barrier every so many ops (keeps its warps in one stretch of code)
 };
 
 struct QecJitKernel {
@@ -29,6 +31,9 @@ struct QecJitKernel {
 bool qec_jit_available(std::string *why);
 // the CUDA C text of the gate stream (exposed for tests and for reading the generated code)
 std::string qec_jit_gates_source(const QecJitSpec &spec);
+// ops per segment (a multiple of 32) and number of segments the generator will emit
+int qec_jit_segment_ops(const QecJitSpec &spec);
+int qec_jit_segment_count(const QecJitSpec &spec);
 // generate + compile to a cubin for sm_100a (works without a GPU)
 int qec_jit_compile(const QecJitSpec &spec, std::vector<char> *cubin, std::string *log);
 // load a cubin on the current device and look the kernel up

@@ -21,10 +21,22 @@
 
 #define QEC_OP_END 0x7FFFFFFFu
 #define QEC_EVW 5  // words per mask event: op, X/Z masks of operand a, X/Z masks of operand b
+#define QEC_BMW (QEC_JIT_NSEG * QEC_JIT_SEGW)  // words of a lane word's "an event sits on op i" bitmap
+
+// How a lane word meets its events in the generated gate stream
+// ------------------------------------------------------------
+// Every lane word (thread) owns a bitmap over the op indices, one bit per op that carries
+// an event of this lane word, at s_bm[(i >> 5) * QEC_JIT_T + tid], and a queue of mask
+// entries in op order.  The generated code loads bitmap word k once per 32 ops
+// (`cur.word(k)`), tests bit j of it at a fault location (one LOP3 with a predicate result),
+// votes (`__any_sync`) so that the warp skips the few instructions of the injection as a
+// whole, and the lanes that hit pop their next queue entry and XOR it into the (statically
+// named) frame registers.  No per-event op compare, no loop, no out-of-line code: the hit
+// path is 4 (one-qubit op) or 7 (cx) predicated instructions placed right behind the gate.
 
 // ---- mask events (enumerator): one event per distinct op, 32 path bits per mask ----------
 // word k of event e lives at p[(5 e + k) * es] (es = threads in the grid: coalesced).
-// The list is sorted by op, ops are unique, and two END headers follow the last event.
+// The list is sorted by op and ops are unique.
 struct QecEvList {
   uint32_t *p;
   long long es;
@@ -46,84 +58,58 @@ struct QecEvList {
     at(q, 0) = op; at(q, 1) = a0; at(q, 2) = a1; at(q, 3) = a2; at(q, 4) = a3;
     ++n;
   }
-  __device__ __forceinline__ void finish() {
-    at(n, 0) = QEC_OP_END;
-    at(n + 1, 0) = QEC_OP_END;
-  }
 };
 
+// cursor over a QecEvList (global memory, L2 resident): the entry under the cursor is held in
+// registers and the next one is fetched when it is consumed, so a hit never waits for memory
 struct QecCurMask {
+  const uint32_t *bmp;  // this lane word's bitmap column in shared memory
   const uint32_t *p;
   long long es;
-  uint32_t nop, m0, m1, m2, m3;   // event under the cursor
-  uint32_t n_op, n0, n1, n2, n3;  // the one after it, already loaded
-  __device__ __forceinline__ void init(const uint32_t *base, long long stride) {
-    p = base; es = stride;
-    nop = p[0]; m0 = p[es]; m1 = p[2 * es]; m2 = p[3 * es]; m3 = p[4 * es];
+  uint32_t bm, m0, m1, m2, m3;
+  __device__ __forceinline__ void init(const uint32_t *bitmap, const uint32_t *base, long long stride) {
+    bmp = bitmap; p = base; es = stride; bm = 0u;
+    m0 = p[es]; m1 = p[2 * es]; m2 = p[3 * es]; m3 = p[4 * es];
+  }
+  __device__ __forceinline__ void word(int k) { bm = bmp[k * QEC_JIT_T]; }
+  __device__ __forceinline__ bool hit(uint32_t bit) const { return (bm & bit) != 0u; }
+  __device__ __forceinline__ bool any(uint32_t mask) const { return (bm & mask) != 0u; }
+  __device__ __forceinline__ void adv() {  // (reads one entry past the list at the end: scratch has room)
     p += QEC_EVW * es;
-    n_op = p[0]; n0 = p[es]; n1 = p[2 * es]; n2 = p[3 * es]; n3 = p[4 * es];
+    m0 = p[es]; m1 = p[2 * es]; m2 = p[3 * es]; m3 = p[4 * es];
   }
-  __device__ __forceinline__ void adv() {
-    // only called on a hit, i.e. with a real event under the cursor: the event two
-    // places on is at worst the second END header
-    nop = n_op; m0 = n0; m1 = n1; m2 = n2; m3 = n3;
-    p += QEC_EVW * es;
-    n_op = p[0]; n0 = p[es]; n1 = p[2 * es]; n2 = p[3 * es]; n3 = p[4 * es];
+  __device__ __forceinline__ void inj1(uint32_t &xa, uint32_t &za) {
+    xa ^= m0; za ^= m1;
+    adv();
   }
-  __device__ __forceinline__ bool hit(uint32_t i) const { return nop == i; }
-  __device__ __forceinline__ bool before(uint32_t end) const { return nop < end; }
-  // (ops are unique in the list, so these loops run once; written as loops because ptxas
-  // turns a plain `if` body into ~18 predicated instructions that every lane word then pays
-  // for at every location, and a loop stays a branch)
-  __device__ __forceinline__ void inj1(uint32_t i, uint32_t &xa, uint32_t &za) {
-    do {
-      xa ^= m0; za ^= m1;
-      adv();
-    } while (nop == i);
-  }
-  __device__ __forceinline__ void inj2(uint32_t i, uint32_t &xa, uint32_t &za, uint32_t &xb,
-                                       uint32_t &zb) {
-    do {
-      xa ^= m0; za ^= m1; xb ^= m2; zb ^= m3;
-      adv();
-    } while (nop == i);
+  __device__ __forceinline__ void inj2(uint32_t &xa, uint32_t &za, uint32_t &xb, uint32_t &zb) {
+    xa ^= m0; za ^= m1; xb ^= m2; zb ^= m3;
+    adv();
   }
 };
 
-// ---- bit events (sampler): (op << 4 | code, 1 << shot_bit), in shared memory --------------
-// word k of event e at p[(2 e + k) * QEC_JIT_T]; sorted by op; two 0xFFFFFFFF headers follow.
-struct QecCurBit {
-  const uint32_t *p;
-  uint32_t nop, hdr, msk, nh, nm;
-  __device__ __forceinline__ void init(const uint32_t *base) {
-    p = base;
-    hdr = p[0]; msk = p[QEC_JIT_T]; nop = hdr >> 4;
-    p += 2 * QEC_JIT_T;
-    nh = p[0]; nm = p[QEC_JIT_T];
+// ---- mask queue (sampler), in shared memory, one contiguous run per lane word --------------
+// entry of a one-qubit op: {X mask, Z mask}; of a cx: {X a, Z a, X b, Z b}; entries in op order
+struct QecCurQueue {
+  const uint32_t *bmp;
+  const uint32_t *pe;
+  uint32_t bm;
+  __device__ __forceinline__ void init(const uint32_t *bitmap, const uint32_t *queue) {
+    bmp = bitmap; pe = queue; bm = 0u;
   }
-  __device__ __forceinline__ void adv() {
-    hdr = nh; msk = nm; nop = hdr >> 4;
-    p += 2 * QEC_JIT_T;
-    nh = p[0]; nm = p[QEC_JIT_T];
+  __device__ __forceinline__ void word(int k) { bm = bmp[k * QEC_JIT_T]; }
+  __device__ __forceinline__ bool hit(uint32_t bit) const { return (bm & bit) != 0u; }
+  __device__ __forceinline__ bool any(uint32_t mask) const { return (bm & mask) != 0u; }
+  __device__ __forceinline__ void inj1(uint32_t &xa, uint32_t &za) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(pe);
+    pe += 2;
+    xa ^= t.x; za ^= t.y;
   }
-  __device__ __forceinline__ bool hit(uint32_t i) const { return nop == i; }
-  __device__ __forceinline__ bool before(uint32_t end) const { return nop < end; }
-  __device__ __forceinline__ void inj1(uint32_t i, uint32_t &xa, uint32_t &za) {
-    do {
-      if (hdr & 1u) xa ^= msk;
-      if (hdr & 2u) za ^= msk;
-      adv();
-    } while (nop == i);
-  }
-  __device__ __forceinline__ void inj2(uint32_t i, uint32_t &xa, uint32_t &za, uint32_t &xb,
-                                       uint32_t &zb) {
-    do {
-      if (hdr & 1u) xa ^= msk;
-      if (hdr & 2u) za ^= msk;
-      if (hdr & 4u) xb ^= msk;
-      if (hdr & 8u) zb ^= msk;
-      adv();
-    } while (nop == i);
+  __device__ __forceinline__ void inj2(uint32_t &xa, uint32_t &za, uint32_t &xb, uint32_t &zb) {
+    const uint2 t = *reinterpret_cast<const uint2 *>(pe);
+    const uint2 u = *reinterpret_cast<const uint2 *>(pe + 2);
+    pe += 4;
+    xa ^= t.x; za ^= t.y; xb ^= u.x; zb ^= u.y;
   }
 };
 
@@ -142,8 +128,10 @@ __device__ __forceinline__ void qec_jit_out(const uint32_t c, const uint32_t v, 
   }
 }
 
-// qec_jit_gates<CUR, TALLY, BITS>(cur, valid, ob, os, s_tally, any_out): the gate stream of
-// the circuit at hand, generated by qec_jit.cpp and handed to NVRTC as a virtual header
+// struct QecFrame (every frame word a member, i.e. a register), qec_jit_frame_zero(F) and
+// qec_jit_seg<CUR, TALLY, BITS>(seg, F, cur, valid, ob, os, s_tally, any_out): segment `seg`
+// (QEC_JIT_SEGW * 32 ops) of the gate stream of the circuit at hand, generated by qec_jit.cpp
+// and handed to NVRTC as a virtual header
 #include "qec_jit_gates.inc"
 
 __device__ __forceinline__ void qec_jit_flush_tally(const QecOutDev &O, uint32_t *s_tally,
@@ -215,7 +203,7 @@ __device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsi
       const uint32_t base = s.loc[i] + 1;
 #pragma unroll
       for (int j = 0; j < K; ++j) {
-        if (j >= i) {
+          if (j >= i) {
           l.insert(s.op[j], acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
           acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0u;
           s.loc[j] = base + (uint32_t)(j - i);
@@ -233,6 +221,7 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const 
                uint32_t *__restrict__ scratch) {
   extern __shared__ __align__(16) uint32_t qec_smem[];
   uint32_t *s_tally = qec_smem;
+  uint32_t *bmw = qec_smem + QEC_JIT_NC + threadIdx.x;  // bitmap column of this lane word
   if (QEC_JIT_TALLY) {
     for (int c = threadIdx.x; c < QEC_JIT_NC; c += QEC_JIT_T) s_tally[c] = 0;
     __syncthreads();
@@ -245,17 +234,28 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const 
     const bool valid = w < O.n_words;
     QecEvList l;
     l.p = ev; l.es = es; l.n = 0;
+#pragma unroll
+    for (int k = 0; k < QEC_BMW; ++k) bmw[k * QEC_JIT_T] = 0u;
     if (valid) {
       const long long r0 = lo + 32 * w;
       const int nv = (int)min((long long)32, hi - r0);
       qec_jit_enum_gen<QEC_JIT_ORDER>(E, (unsigned long long)r0, nv, l);
+      for (int e = 0; e < l.n; ++e) {
+        const uint32_t op = l.at(e, 0);
+        bmw[(op >> 5) * QEC_JIT_T] |= 1u << (op & 31u);
+      }
     }
-    l.finish();
     QecCurMask cur;
-    cur.init(ev, es);
+    cur.init(bmw, ev, es);
     uint32_t any = 0;
-    qec_jit_gates<QecCurMask, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
-        cur, valid, O.bits + w, O.n_words, s_tally, any);
+    QecFrame F;
+    qec_jit_frame_zero(F);
+#pragma unroll
+    for (int seg = 0; seg < QEC_JIT_NSEG; ++seg) {
+      cur.bmp = bmw + seg * QEC_JIT_SEGW * QEC_JIT_T;
+      qec_jit_seg<QecCurMask, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
+          seg, F, cur, valid, O.bits + w, O.n_words, s_tally, any);
+    }
     if (QEC_JIT_TALLY) nz += __popc(any);
   }
   if (QEC_JIT_TALLY) qec_jit_flush_tally(O, s_tally, nullptr, false, nz, hi - lo);
@@ -265,98 +265,116 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const 
 #if QEC_JIT_KIND == 2
 // ---- FaultSampler ------------------------------------------------------------------------------
 // Same random decisions, in the same order, as k_sample in qec_kernels.cu (so both kernels
-// return identical bits for one (seed, shot id)); the events land in shared memory as
-// (op << 4 | code, 1 << shot_bit) pairs.  `cap` = events a lane word can hold.
+// return identical bits for one (seed, shot id)); the table lookups are the accelerated ones
+// of qec_device.cuh.  The gate stream runs segment by segment: before a segment the lane word
+// draws the faults that fall on its ops into its mask queue (`capw` words of shared memory)
+// and bitmap, so the queue only ever holds one segment's faults.  `cap` = events per segment
+// the host sized the queue for (reported back on overflow).
 extern "C" __global__ void __launch_bounds__(QEC_JIT_T, QEC_JIT_MINB)
 qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo,
-               const long long n_shots, const int cap, uint32_t *__restrict__ overflow_flag) {
+               const long long n_shots, const int cap, const int capw,
+               uint32_t *__restrict__ overflow_flag) {
   extern __shared__ __align__(16) uint32_t qec_smem[];
   uint32_t *s_tally = qec_smem;
   uint32_t *s_hist = s_tally + QEC_JIT_NC;
-  uint32_t *s_T1 = s_hist + 64;
-  uint32_t *s_T2 = s_T1 + S.K1;
-  uint32_t *s_ev = s_T2 + S.B;  // [2 * (cap + 2)][QEC_JIT_T]
+  uint32_t *s_tab = s_hist + 64;
+  uint32_t *s_bm = s_tab + qec_samp_tab_words(S.K1, S.B, (uint32_t)S.L, (uint32_t)S.n_classes, S.lgP);
+  uint32_t *s_q = s_bm + QEC_JIT_SEGW * QEC_JIT_T;       // [QEC_JIT_T][capw]
+  s_q += (4u - ((uint32_t)(s_q - qec_smem) & 3u)) & 3u;  // 16-byte aligned
+  QecSampTabs tabs;
+  qec_samp_tabs_fill(tabs, s_tab, S, threadIdx.x, QEC_JIT_T);
   for (int c = threadIdx.x; c < QEC_JIT_NC + 64; c += QEC_JIT_T) s_tally[c] = 0;
-  for (uint32_t i = threadIdx.x; i < S.K1; i += QEC_JIT_T) s_T1[i] = S.T1[i];
-  for (uint32_t i = threadIdx.x; i < S.B; i += QEC_JIT_T) s_T2[i] = S.T2[i];
   __syncthreads();
-  uint32_t *ev = s_ev + threadIdx.x;
+  uint32_t *bmw = s_bm + threadIdx.x;
+  uint32_t *q = s_q + (size_t)threadIdx.x * capw;
+  const int n_slots = (int)S.n_slots;
   unsigned long long nz = 0;
   for (long long ch = blockIdx.x; ch * QEC_JIT_T < O.n_words; ch += gridDim.x) {
     const long long w = ch * QEC_JIT_T + threadIdx.x;
     const bool valid = w < O.n_words;
-    int n_ev = 0;    // faults drawn (for the fault-count histogram and the overflow check)
-    int n_st = 0;    // events stored
-    if (valid) {
-      const int nv = (int)min((long long)32, n_shots - 32 * w);
+    const int nv = valid ? (int)min((long long)32, n_shots - 32 * w) : 0;
+    QecRng g;
+    {
       const unsigned long long gw = (unsigned long long)(word_lo + w);
-      const uint32_t wlo = (uint32_t)gw, whi = (uint32_t)(gw >> 32);
-      uint32_t draw = 0;
-      long long slot = -1;
-      uint32_t cp[6] = {0, 0, 0, 0, 0, 0};  // bit-sliced per-shot fault counters
-      for (;;) {
-        QecPhilox r;
-        unsigned long long skip = 0;
-        for (;;) {
-          r = qec_philox(wlo, whi, draw++, 0u, S.k0, S.k1);
-          const uint32_t a = qec_count_greater(s_T1, S.K1, r.c[0]);
-          skip += (unsigned long long)a * S.B;
-          if (a < S.K1 || skip >= (unsigned long long)S.n_slots) break;
-        }
-        const uint32_t b = qec_count_greater(s_T2 + 1, S.B - 1, r.c[1]);
-        slot += 1 + (long long)skip + b;
-        if (slot >= S.n_slots) break;
-        const uint32_t sl = (uint32_t)(slot >> 5), bit = (uint32_t)slot & 31u;
-        const uint32_t cls = S.slcls[sl];
-        if (!S.cls_always[cls] && r.c[2] >= S.cls_acc[cls]) continue;
-        const uint32_t base = S.cls_off[cls], np = S.cls_off[cls + 1] - base;
-        uint32_t d = 0;
-        while (d + 1 < np && r.c[3] >= S.cdf[base + d]) ++d;
-        if ((int)bit >= nv) continue;  // shot past the end of the range
-        const uint32_t code = S.codes[base + d];
-        if (code != 0u && n_st < cap) {
-          ev[(2 * n_st) * QEC_JIT_T] = (S.slop[sl] << 4) | code;
-          ev[(2 * n_st + 1) * QEC_JIT_T] = 1u << bit;
-          ++n_st;
-        } else if (code != 0u) {
-          n_st = cap + 1;  // remembered as an overflow below
-        }
-        ++n_ev;
-        if (QEC_JIT_TALLY) {
-          uint32_t carry = 1u << bit;
+      g.wlo = (uint32_t)gw; g.whi = (uint32_t)(gw >> 32); g.draw = 0u; g.slot = -1;
+      g.r2 = g.r3 = 0u;
+    }
+    if (valid) qec_rng_advance(g, tabs, S);
+    else g.slot = n_slots;
+    int n_ev = 0;  // faults drawn (fault-count histogram, overflow report)
+    bool overflow = false;
+    uint32_t cp[6] = {0, 0, 0, 0, 0, 0};  // bit-sliced per-shot fault counters
+    uint32_t any = 0;
+    QecFrame F;
+    qec_jit_frame_zero(F);
 #pragma unroll
-          for (int p = 0; p < 6; ++p) {
-            const uint32_t t = cp[p] & carry;
-            cp[p] ^= carry;
-            carry = t;
+    for (int seg = 0; seg < QEC_JIT_NSEG; ++seg) {
+#pragma unroll
+      for (int k = 0; k < QEC_JIT_SEGW; ++k) bmw[k * QEC_JIT_T] = 0u;
+      const int slot_end = (int)S.seg_end[seg];
+      const uint32_t op0 = (uint32_t)seg * (QEC_JIT_SEGW * 32u);
+      int nw = 0, base = 0;  // queue words in use; first word of the entry being filled
+      uint32_t last_op = 0xFFFFFFFFu;
+      while (g.slot < slot_end) {
+        uint32_t info, code;
+        const uint32_t bit = (uint32_t)g.slot & 31u;
+        if (qec_rng_resolve(g, tabs, info, code) && (int)bit < nv) {
+          ++n_ev;
+          const uint32_t msk = 1u << bit;
+          if (code != 0u) {
+            const uint32_t op = info & 0xFFFFFu;
+            if (op != last_op) {  // a new entry (events arrive in op order)
+              const int len = ((info >> 30) & 1u) ? 4 : 2;
+              if (nw + len > capw) {
+                overflow = true;
+              } else {
+                base = nw;
+                nw += len;
+                last_op = op;
+                q[base] = 0u; q[base + 1] = 0u;
+                if (len == 4) { q[base + 2] = 0u; q[base + 3] = 0u; }
+                const uint32_t rel = op - op0;
+                bmw[(rel >> 5) * QEC_JIT_T] |= 1u << (rel & 31u);
+              }
+            }
+            if (!overflow) {
+              if (code & 1u) q[base] |= msk;
+              if (code & 2u) q[base + 1] |= msk;
+              if (code & 4u) q[base + 2] |= msk;
+              if (code & 8u) q[base + 3] |= msk;
+            }
           }
-          if (carry) {
+          if (QEC_JIT_TALLY) {
+            uint32_t carry = msk;
 #pragma unroll
-            for (int p = 0; p < 6; ++p) cp[p] |= carry;  // saturate at 63
+            for (int p = 0; p < 6; ++p) {
+              const uint32_t t = cp[p] & carry;
+              cp[p] ^= carry;
+              carry = t;
+            }
+            if (carry) {
+#pragma unroll
+              for (int p = 0; p < 6; ++p) cp[p] |= carry;  // saturate at 63
+            }
           }
         }
+        qec_rng_advance(g, tabs, S);
       }
-      if (n_st > cap) {
-        atomicMax(overflow_flag, (uint32_t)n_ev);
-        n_st = cap;
-      }
-      if (QEC_JIT_TALLY) {
-        for (int bit = 0; bit < nv; ++bit) {
-          uint32_t k = 0;
+      QecCurQueue cur;
+      cur.init(bmw, q);
+      qec_jit_seg<QecCurQueue, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
+          seg, F, cur, valid, O.bits + w, O.n_words, s_tally, any);
+    }
+    if (overflow) atomicMax(overflow_flag, (uint32_t)max(n_ev, cap + 1));
+    if (QEC_JIT_TALLY) {
+      nz += __popc(any);
+      for (int bit = 0; bit < nv; ++bit) {
+        uint32_t k = 0;
 #pragma unroll
-          for (int p = 0; p < 6; ++p) k |= ((cp[p] >> bit) & 1u) << p;
-          atomicAdd(&s_hist[k], 1u);
-        }
+        for (int p = 0; p < 6; ++p) k |= ((cp[p] >> bit) & 1u) << p;
+        atomicAdd(&s_hist[k], 1u);
       }
     }
-    ev[(2 * n_st) * QEC_JIT_T] = 0xFFFFFFFFu;
-    ev[(2 * n_st + 2) * QEC_JIT_T] = 0xFFFFFFFFu;
-    QecCurBit cur;
-    cur.init(ev);
-    uint32_t any = 0;
-    qec_jit_gates<QecCurBit, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
-        cur, valid, O.bits + w, O.n_words, s_tally, any);
-    if (QEC_JIT_TALLY) nz += __popc(any);
   }
   if (QEC_JIT_TALLY) qec_jit_flush_tally(O, s_tally, s_hist, true, nz, n_shots);
 }
