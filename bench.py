@@ -158,19 +158,8 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     cores = host_cores()
 
-    # CPU baseline first (rank 0, N=1 only), before this process touches CUDA (fork-safe)
-    cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        from oracle import ref
-        if ref.available():
-            per_proc = args.ref_shots
-            r, total, wall = reference_rate(cores, per_proc)
-            cpu_baseline = {"value": r, "unit": "shots/s", "cores": cores, "kind": "reference",
-                            "sample": f"{cores} processes x {per_proc} shots of the same workload "
-                                      f"through reference _CFaultSampler.sample (oracle/_ref), "
-                                      f"{wall:.1f} s wall"}
-
     from qiskit_qec_b200 import _capi
+    from qiskit_qec_b200.sharding import allreduce_tally, shard_range
     if not torch.cuda.is_available() or _capi.device_count() < 1:
         raise RuntimeError("bench.py: no CUDA device; the product has no CPU fallback")
     torch.cuda.set_device(local)
@@ -204,8 +193,7 @@ def run_ours(args):
         lo = ((rank * 1_000_003 + i) * n_words) * 32
         tally.zero_()
         sm.sample_dev(lo, n_shots, bits.data_ptr(), tally.data_ptr(), stream)
-        if world > 1:
-            dist.all_reduce(tally)
+        allreduce_tally(tally)
 
     for i in range(args.warmup):
         step(i)
@@ -277,15 +265,13 @@ def run_ours(args):
         paulis = [types[lab] for lab in labels]
         en = _capi.Enumerator(g, 2, idx, [[_capi.pauli_code(p) for p in pl] for pl in paulis])
         total = en.num_paths()
-        lo = total * rank // world
-        hi = total * (rank + 1) // world
+        lo, hi = shard_range(total, rank, world)
         ebits = torch.empty((nc, (hi - lo + 31) // 32), dtype=torch.int32, device=dev)
 
         def estep():
             tally.zero_()
             en.range_dev(lo, hi, ebits.data_ptr(), tally.data_ptr(), stream)
-            if world > 1:
-                dist.all_reduce(tally)
+            allreduce_tally(tally)
 
         for _ in range(3):
             estep()
@@ -306,6 +292,20 @@ def run_ours(args):
                 "unit": "faults/s", "paths": total, "ms": ems, "scaling": "strong",
                 "workload": "order=2 exhaustive, SurfaceCodeCircuit d=5 T=5 (BASELINE configs[2])",
                 "kernel": _capi.last_kernel()}
+
+    # CPU baseline (rank 0, N=1 only): the unmodified reference in a child process, after
+    # the GPU measurements so that its worker processes cannot disturb them
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference",
+                                  "--steps", "1", "--warmup", "0", "--ref-shots",
+                                  str(args.ref_shots)], capture_output=True, text=True,
+                                 timeout=600).stdout.strip().splitlines()
+            ref = json.loads(out[-1]) if out else {}
+            cpu_baseline = ref.get("cpu_baseline")
+        except (subprocess.SubprocessError, ValueError, OSError):
+            cpu_baseline = None
 
     if rank == 0:
         peaks = {}

@@ -128,8 +128,48 @@ struct qec_circuit {
   QecCircuitDev dev{};
   uint32_t *d_ops = nullptr;
   DevBuf out_bits, out_frame, tally, ev_off, ev;  // staging for the host-pointer entry points
+  DevBuf pipe_buf[2];                             // double-buffered outcome chunks (host entry points)
+  cudaStream_t pipe_stream[2] = {nullptr, nullptr};
   DevInfo *info = nullptr;
 };
+
+// Host-pointer entry points stream their packed outcomes back in chunks of lane words:
+// chunk i is computed on stream i & 1 into its own device buffer and copied out (a strided
+// 2-D copy: the host array is [nc][n_words]) while chunk i + 1 computes on the other stream,
+// so the device->host copy (PCIe) hides the kernels and the device never holds more than
+// two chunks.  launch(w0, words, d_bits, stream) runs lane words [w0, w0 + words).
+static int64_t pipe_chunk_words(const qec_circuit *c, int64_t n_words) {
+  const char *e = std::getenv("QEC_B200_PIPE_MB");
+  const int64_t mb = (e && *e) ? atoll(e) : 64;
+  int64_t cw = (mb << 20) / ((int64_t)std::max(c->nc, 1) * 4);
+  cw = std::max<int64_t>(cw / 1024 * 1024, 1024);
+  return std::min(cw, n_words);
+}
+
+template <class Launch>
+static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, Launch launch) {
+  const int64_t cw = pipe_chunk_words(c, n_words);
+  const size_t buf_bytes = (size_t)c->nc * cw * 4;
+  for (int i = 0; i < 2; ++i) {
+    if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    int rc = c->pipe_buf[i].ensure(std::max<size_t>(buf_bytes, 4));
+    if (rc) return rc;
+  }
+  CU(cudaStreamSynchronize(0));  // table uploads / memsets issued on the default stream
+  int k = 0;
+  for (int64_t w0 = 0; w0 < n_words; w0 += cw, k ^= 1) {
+    const int64_t words = std::min(cw, n_words - w0);
+    cudaStream_t st = c->pipe_stream[k];
+    uint32_t *d = (uint32_t *)c->pipe_buf[k].p;
+    int rc = launch(w0, words, d, st);
+    if (rc) return rc;
+    CU(cudaMemcpy2DAsync(host_bits + w0, (size_t)n_words * 4, d, (size_t)words * 4,
+                         (size_t)words * 4, (size_t)c->nc, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(c->pipe_stream[0]));
+  CU(cudaStreamSynchronize(c->pipe_stream[1]));
+  return 0;
+}
 
 // host-only lowering of the reference's rows to the packed gate table (no device needed)
 static int lower_rows(int nq, int nc, int n_ops, const int32_t *row_off, const int32_t *row_data,
@@ -237,6 +277,10 @@ extern "C" void qec_circuit_destroy(qec_circuit *c) {
   if (c->d_ops) cudaFree(c->d_ops);
   c->out_bits.release(); c->out_frame.release(); c->tally.release();
   c->ev_off.release(); c->ev.release();
+  for (int i = 0; i < 2; ++i) {
+    c->pipe_buf[i].release();
+    if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
+  }
   delete c;
 }
 
@@ -702,16 +746,26 @@ extern "C" int qec_enumerator_range(qec_enumerator *e, int64_t lo, int64_t hi, u
   const int64_t n_words = (hi - lo + 31) / 32;
   const size_t out_bytes = (size_t)c->nc * n_words * 4;
   int rc;
-  if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+  (void)out_bytes;
   if (tally) {
     if ((rc = c->tally.ensure(tl * 8))) return rc;
     CU(cudaMemsetAsync(c->tally.p, 0, tl * 8, 0));
   }
-  if ((rc = enum_launch(e, lo, hi, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
-                        tally ? (uint64_t *)c->tally.p : nullptr, 0)))
+  uint64_t *d_tally = tally ? (uint64_t *)c->tally.p : nullptr;
+  if (out_bits) {
+    rc = pipelined_out(c, n_words, out_bits,
+                       [&](int64_t w0, int64_t words, uint32_t *d, cudaStream_t st) {
+                         const int64_t clo = lo + 32 * w0;
+                         return enum_launch(e, clo, std::min<int64_t>(hi, clo + 32 * words), d,
+                                            d_tally, st);
+                       });
+    if (rc) return rc;
+  } else if ((rc = enum_launch(e, lo, hi, nullptr, d_tally, 0))) {
     return rc;
-  if (out_bits) CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
-  if (tally) CU(cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost));
+  }
+  if (tally) {
+    CU(cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost));
+  }
   CU(cudaDeviceSynchronize());
   return 0;
 }
@@ -765,7 +819,7 @@ static int sampler_plan_jit(qec_sampler *s) {
   jit_plan_geometry(c, pl);
   const size_t tabw = qec_samp_tab_words(s->K1, s->B, (uint32_t)s->L, (uint32_t)s->n_classes, s->lgP);
   // Gate-stream segments: the fewest for which the mask queue of one segment (2 words per
-  // event on a one-qubit op, 4 on a cx; mean + 9.5 sigma, never below mean + 6 sigma) leaves
+  // event on a one-qubit op, 4 on a cx; mean + 7.5 sigma, never below mean + 6 sigma) leaves
   // room for the CTAs the register budget allows.
   QecJitSpec probe;
   probe.packed = &c->packed;
@@ -786,7 +840,7 @@ static int sampler_plan_jit(qec_sampler *s) {
           mu_w += 32.0 * s->loc_p[i] * len;
           var_w += 32.0 * s->loc_p[i] * len * len;
         }
-        want_w = std::max(want_w, mu_w + 9.5 * std::sqrt(var_w) + 16.0);
+        want_w = std::max(want_w, mu_w + 7.5 * std::sqrt(var_w) + 16.0);
         least_w = std::max(least_w, mu_w + 6.0 * std::sqrt(var_w) + 16.0);
       }
       const int want = ((int)std::ceil(want_w) + 3) / 4 * 4, least = ((int)std::ceil(least_w) + 3) / 4 * 4;
@@ -1109,7 +1163,7 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
   CU(cudaSetDevice(c->device));
   const int64_t n_words = (n_shots + 31) / 32;
   const size_t out_bytes = (size_t)c->nc * n_words * 4;
-  if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+  (void)out_bytes;
   if (tally && (rc = c->tally.ensure(tl * 8))) return rc;
   QecSampleExport X{nullptr, nullptr, 0};
   if (exp) {
@@ -1119,14 +1173,26 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
   }
   for (int attempt = 0;; ++attempt) {
     if (tally) CU(cudaMemsetAsync(c->tally.p, 0, tl * 8, 0));
-    if ((rc = sample_launch(s, shot_lo, n_shots, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
-                            tally ? (uint64_t *)c->tally.p : nullptr, X, 0)))
-      return rc;
+    uint64_t *d_tally = tally ? (uint64_t *)c->tally.p : nullptr;
+    if (out_bits && !exp) {
+      rc = pipelined_out(c, n_words, out_bits,
+                         [&](int64_t w0, int64_t words, uint32_t *d, cudaStream_t st) {
+                           return sample_launch(s, shot_lo + 32 * w0,
+                                                std::min<int64_t>(n_shots - 32 * w0, 32 * words), d,
+                                                d_tally, X, st);
+                         });
+    } else {
+      if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
+      rc = sample_launch(s, shot_lo, n_shots, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
+                         d_tally, X, 0);
+      if (!rc && out_bits)
+        CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
+    }
+    if (rc) return rc;
     rc = sampler_check(s);  // synchronises
     if (rc == 0) break;
     if (rc != QEC_ERR_OVERFLOW || attempt >= 4) return rc;  // deterministic RNG: safe to re-run
   }
-  if (out_bits) CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
   if (tally) CU(cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost));
   if (exp) {
     CU(cudaMemcpy(fault_cnt, s->xcnt.p, (size_t)n_words * 4, cudaMemcpyDeviceToHost));
