@@ -382,14 +382,25 @@ struct JitPlan {
 };
 
 // registers a specialised kernel needs: the frame plus cursor / addressing overhead
-static int jit_regs_estimate(int nq) { return 2 * nq + 40; }
+static int jit_regs_estimate(int nq) { return 2 * nq + 70; }
 
+// One CTA per SM, as many warps as the register file holds: the generated gate stream is
+// ~100 KB of straight-line code, and warps that walk it together (CTA barriers every
+// `sync_every` ops) share its instruction fetches -- measured: 3 CTAs x 128 threads 0.87 ms,
+// 1 CTA x 384 threads 0.70 ms for 2e7 shots at d=5.
 static void jit_plan_geometry(const qec_circuit *c, JitPlan &pl) {
   const int regs = jit_regs_estimate(c->nq);
-  int minb = 65536 / (regs * pl.threads);
-  if (minb > 8) minb = 8;
-  if (minb < 1) minb = 1;
-  minb = env_int("QEC_B200_JIT_MINB", minb);
+  int threads = env_int("QEC_B200_JIT_THREADS", 0);
+  int minb = env_int("QEC_B200_JIT_MINB", 0);
+  if (threads <= 0) {
+    threads = 65536 / regs / 32 * 32;
+    if (threads > 512) threads = 512;
+    if (threads < 64) threads = 64;
+    if (minb <= 0) minb = 1;
+  }
+  threads = std::max(32, threads / 32 * 32);
+  if (minb <= 0) minb = std::max(1, std::min(8, 65536 / (regs * threads)));
+  pl.threads = threads;
   pl.min_blocks = minb;
   pl.grid = c->info->sms * minb;
   pl.sync_every = env_int("QEC_B200_JIT_SYNC", 96);
@@ -398,7 +409,8 @@ static size_t jit_bitmap_words(const qec_circuit *c, const JitPlan &pl) {
   return ((c->packed.size() + 31) / 32) * (size_t)pl.threads;
 }
 
-static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, bool tally, bool bits) {
+static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, bool tally, bool bits,
+                           const QecJitSpec *extra = nullptr) {
   JitVariant &v = pl.var[tally ? 1 : 0][bits ? 1 : 0];
   if (v.tried) return &v;
   v.tried = true;
@@ -407,6 +419,10 @@ static JitVariant *jit_get(qec_circuit *c, JitPlan &pl, int kind, int order, boo
   spec.kind = kind; spec.order = order; spec.tally = tally; spec.bits = bits;
   spec.threads = pl.threads; spec.min_blocks = pl.min_blocks; spec.group = pl.group;
   spec.sync_every = pl.sync_every; spec.segments = pl.segments;
+  if (extra) {
+    spec.K1 = extra->K1; spec.B = extra->B; spec.L = extra->L; spec.n_classes = extra->n_classes;
+    spec.lgP = extra->lgP; spec.n_slots = extra->n_slots;
+  }
   std::vector<char> cubin;
   std::string log;
   if (qec_jit_compile(spec, &cubin, &log)) { v.why = "NVRTC: " + log; return &v; }
@@ -496,6 +512,7 @@ struct qec_enumerator {
   unsigned long long *d_tile = nullptr;
   JitPlan jit;
   DevBuf jit_scratch;
+  int jit_tab_in_smem = 0;
 };
 
 // Can this enumerator run on the specialised kernel?  (the frame must fit the register file,
@@ -515,10 +532,15 @@ static void enum_plan_jit(qec_enumerator *e) {
   if (!qec_jit_available(&why)) { pl.why = why; return; }
   pl.is_loc.assign(c->packed.size(), 0);
   for (int l = 0; l < e->L; ++l) pl.is_loc[e->lop[l]] = 1;
-  pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
-  pl.group = env_int("QEC_B200_JIT_GROUP", 8);
+  pl.group = env_int("QEC_B200_JIT_GROUP", 32);
   jit_plan_geometry(c, pl);
-  pl.smem = ((size_t)c->nc + jit_bitmap_words(c, pl)) * 4 + 16;
+  pl.smem = ((size_t)c->nc * (pl.threads / 32) + jit_bitmap_words(c, pl)) * 4 + 16;
+  {  // the enumerator's tables ride along in shared memory when they fit
+    const size_t tab = ((size_t)(e->order + 1) * (e->L + 2) + (size_t)4 * e->L) * 8 +
+                       ((size_t)3 * e->L + 1) * 4 + e->pcode.size() + 16;
+    e->jit_tab_in_smem = pl.smem + tab <= c->info->smem_optin ? 1 : 0;
+    if (e->jit_tab_in_smem) pl.smem += tab;
+  }
   // tile[4 l + k]: bit i = bit k of the code of digit (i mod npaul[l])
   e->tile.assign((size_t)4 * e->L, 0ull);
   for (int l = 0; l < e->L; ++l) {
@@ -570,6 +592,17 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
       e->pcode.push_back(mask_code(c, loc_op[l], pauli_codes[j]));
   }
   if (L >= 0) e->poff[L] = (uint32_t)e->pcode.size();
+  if (!e->deferred) {
+    // the kernels index inside one subset's Pauli product with 32-bit arithmetic
+    double prod = 1;
+    uint32_t maxnp = 1;
+    for (int l = 0; l < L; ++l) maxnp = std::max(maxnp, e->npaul[l]);
+    for (int j = 0; j < order; ++j) prod *= (double)maxnp;
+    if (prod >= 2147483648.0) {
+      delete e;
+      return fail(QEC_ERR_LIMIT, "a location offers %u Paulis: too many for order %d", maxnp, order);
+    }
+  }
   if (!e->deferred) {
     const int L2 = L + 2;
     e->E.assign((size_t)(order + 1) * L2, 0ull);
@@ -696,7 +729,7 @@ static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bi
     if (v->ok) {
       long long lo_ = lo, hi_ = hi;
       uint32_t *scr = (uint32_t *)e->jit_scratch.p;
-      void *args[] = {&O, &e->dev, &lo_, &hi_, &scr};
+      void *args[] = {&O, &e->dev, &lo_, &hi_, &scr, &e->jit_tab_in_smem};
       std::string err;
       time_begin(e->c, stream);
       const int rc = qec_jit_launch(v->k, e->jit.grid, e->jit.smem, stream, args, &err);
@@ -815,7 +848,6 @@ static int sampler_plan_jit(qec_sampler *s) {
   if (!qec_jit_available(&why)) { pl.why = why; return 0; }
   pl.is_loc.assign(c->packed.size(), 0);
   for (int i = 0; i < s->L; ++i) pl.is_loc[s->slop[i]] = 1;
-  pl.threads = env_int("QEC_B200_JIT_THREADS", 128);
   jit_plan_geometry(c, pl);
   const size_t tabw = qec_samp_tab_words(s->K1, s->B, (uint32_t)s->L, (uint32_t)s->n_classes, s->lgP);
   // Gate-stream segments: the fewest for which the mask queue of one segment (2 words per
@@ -825,7 +857,11 @@ static int sampler_plan_jit(qec_sampler *s) {
   probe.packed = &c->packed;
   const int seg_env = env_int("QEC_B200_JIT_SEGS", 0);
   int capw = 0;
+  // (when even 16 segments do not fit, the CTA shrinks: fewer lane words share the memory)
+  const int threads0 = pl.threads;
+  for (int tq = 4; tq >= 1 && !capw; --tq)
   for (int minb = pl.min_blocks; minb >= 1 && !capw; --minb) {
+    pl.threads = std::max(32, threads0 * tq / 4 / 32 * 32);
     size_t per_cta = c->info->smem_sm / minb - 1024;
     if (per_cta > c->info->smem_optin) per_cta = c->info->smem_optin;
     for (int segs = seg_env > 0 ? seg_env : 1; segs <= (seg_env > 0 ? seg_env : 16); ++segs) {
@@ -844,7 +880,8 @@ static int sampler_plan_jit(qec_sampler *s) {
         least_w = std::max(least_w, mu_w + 6.0 * std::sqrt(var_w) + 16.0);
       }
       const int want = ((int)std::ceil(want_w) + 3) / 4 * 4, least = ((int)std::ceil(least_w) + 3) / 4 * 4;
-      const size_t fixed = ((size_t)c->nc + 64 + tabw + (size_t)(SL / 32) * pl.threads + 4) * 4 + 16;
+      const size_t fixed = ((size_t)c->nc * (pl.threads / 32) + 64 + tabw +
+                            (size_t)(SL / 32) * pl.threads + 4) * 4 + 16;
       if (per_cta <= fixed) continue;
       int fit = (int)((per_cta - fixed) / ((size_t)4 * pl.threads)) / 4 * 4;
       if (fit >= want || (fit >= least && (segs == 16 || seg_env > 0))) {
@@ -1071,7 +1108,10 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
   O.tally = (unsigned long long *)d_tally;
   O.n_words = (n_shots + 31) / 32;
   if (s->jit.eligible && !X.cnt) {
-    JitVariant *v = jit_get(s->c, s->jit, 2, 0, d_tally != nullptr, d_bits != nullptr);
+    QecJitSpec extra;
+    extra.K1 = s->K1; extra.B = s->B; extra.L = (unsigned)s->L; extra.n_classes = (unsigned)s->n_classes;
+    extra.lgP = s->lgP; extra.n_slots = (unsigned)s->dev.n_slots;
+    JitVariant *v = jit_get(s->c, s->jit, 2, 0, d_tally != nullptr, d_bits != nullptr, &extra);
     if (v->ok) {
       long long wlo = shot_lo / 32, ns = n_shots;
       int cap = s->jit_cap, capw = s->jit_capw;
@@ -1301,6 +1341,8 @@ extern "C" int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t 
   }
   spec.kind = kind; spec.order = order; spec.tally = tally != 0; spec.bits = bits != 0;
   spec.threads = threads; spec.min_blocks = min_blocks; spec.group = group;
+  spec.K1 = 11; spec.B = 2048; spec.L = (unsigned)L; spec.n_classes = 4; spec.lgP = 4;  // (typical
+  spec.n_slots = (unsigned)L * 32u;                      //  d=5 values: inspection only)
   spec.segments = env_int("QEC_B200_JIT_SEGS", 1);      // (inspection only: the launch path
   spec.sync_every = env_int("QEC_B200_JIT_SYNC", 96);   //  plans these itself)
   if (source_path && *source_path) {

@@ -103,6 +103,14 @@ struct QecSampleExport {
   int cap;
 };
 
+// words of shared memory the specialised sampler keeps its small tables in:
+// T1[K1] T2[B] guide[2B x u16] info[L] cacc[n] cnp1[n] cdf[n][P] code[n][P x u8]
+static inline __host__ __device__ uint32_t qec_samp_tab_words(uint32_t K1, uint32_t B, uint32_t L,
+                                                               uint32_t ncls, uint32_t lgP) {
+  const uint32_t P = 1u << lgP;
+  return K1 + B + B + L + 2u * ncls + ncls * P + (ncls * P + 3u) / 4u;
+}
+
 #ifdef __CUDACC__
 
 // One lane word through the whole gate table.  `fr` points at this thread's column of the
@@ -232,16 +240,23 @@ __device__ __forceinline__ void enum_load(const QecEnumDev &E, EnumState<K> &s, 
   s.pb[j] = E.poff[l];
 }
 
+// (64-bit / 32-bit division costs ~100 instructions; ranks below 2^32 -- every BASELINE
+// enumeration except order 3 -- take the 32-bit divide)
+__device__ __forceinline__ unsigned long long qec_div_u64_u32(unsigned long long a, uint32_t b) {
+  if ((a >> 32) == 0ull) return (unsigned long long)((uint32_t)a / b);
+  return a / b;
+}
+
 template <int K>
 __device__ __forceinline__ void enum_unrank(const QecEnumDev &E, unsigned long long r,
                                             EnumState<K> &s) {
   const int L2 = E.L + 2;
-  unsigned long long mult = 1;
+  uint32_t mult = 1;  // product of the Pauli counts of the locations chosen so far (<= 512^(K-1))
   uint32_t start = 0;
 #pragma unroll
   for (int j = 0; j < K; ++j) {
     const unsigned long long *Em = E.E + (size_t)(K - j) * L2;
-    const unsigned long long u = r / mult;
+    const unsigned long long u = qec_div_u64_u32(r, mult);
     const unsigned long long thr = Em[start] - u;  // >= 1
     // largest l in [start, L] with Em[l] >= thr (Em non-increasing, Em[L] = 0 < thr)
     uint32_t lo = start, hi = (uint32_t)E.L;
@@ -249,16 +264,19 @@ __device__ __forceinline__ void enum_unrank(const QecEnumDev &E, unsigned long l
       const uint32_t mid = (lo + hi) >> 1;
       if (Em[mid] >= thr) lo = mid; else hi = mid;
     }
-    r -= mult * (Em[start] - Em[lo]);
+    r -= (unsigned long long)mult * (Em[start] - Em[lo]);
     s.loc[j] = lo;
     enum_load<K>(E, s, j);
     mult *= s.np[j];
     start = lo + 1;
   }
+  // r is now the index inside the subset's product: below prod(np) < 2^32
+  uint32_t rr = (uint32_t)r;
 #pragma unroll
   for (int j = K - 1; j >= 0; --j) {
-    s.dig[j] = (uint32_t)(r % s.np[j]);
-    r /= s.np[j];
+    const uint32_t q = rr / s.np[j];
+    s.dig[j] = rr - q * s.np[j];
+    rr = q;
   }
 }
 
@@ -311,100 +329,6 @@ __device__ __forceinline__ uint32_t qec_count_greater(const uint32_t *t, uint32_
     if (t[mid] > r) lo = mid + 1; else hi = mid;
   }
   return lo;
-}
-
-// ---- sampler draw machinery of the specialised kernel --------------------------------------
-// The sampler's small tables, copied to shared memory once per CTA.  The lookups below return
-// exactly what qec_count_greater / the linear cdf scan of k_sample return (the guide table
-// and the padded binary search only get there in fewer steps), so every kernel and the CPU
-// restatement (oracle/sampler_port.c) draw identical fault lists.
-struct QecSampTabs {
-  const uint32_t *T1, *T2;
-  const uint16_t *G;     // [B] G[k] = entries of T2[1..B) greater than the largest r with r >> gshift == k
-  const uint32_t *info;  // [L] QecSamplerDev::slinf
-  const uint32_t *cacc;  // [n_classes] accept thresholds
-  const uint32_t *cnp1;  // [n_classes] Paulis of the class - 1
-  const uint32_t *cdf;   // [n_classes][P] cumulative thresholds, padded with 0xFFFFFFFF
-  const uint8_t *code;   // [n_classes][P]
-  uint32_t K1, B, gshift, lgP;
-};
-
-__host__ __device__ inline uint32_t qec_samp_tab_words(uint32_t K1, uint32_t B, uint32_t L,
-                                                        uint32_t ncls, uint32_t lgP) {
-  const uint32_t P = 1u << lgP;
-  return K1 + B + (B + 1) / 2 + L + 2 * ncls + ncls * P + (ncls * P + 3) / 4;
-}
-
-// cooperative fill by the whole CTA; the caller synchronises afterwards
-__device__ __forceinline__ void qec_samp_tabs_fill(QecSampTabs &t, uint32_t *base,
-                                                   const QecSamplerDev &S, int tid, int T) {
-  const uint32_t P = 1u << S.lgP, ncls = (uint32_t)S.n_classes, L = (uint32_t)S.L;
-  uint32_t *sT1 = base, *sT2 = sT1 + S.K1;
-  uint16_t *sG = reinterpret_cast<uint16_t *>(sT2 + S.B);
-  uint32_t *sinfo = sT2 + S.B + (S.B + 1) / 2, *scacc = sinfo + L, *scnp1 = scacc + ncls;
-  uint32_t *scdf = scnp1 + ncls;
-  uint8_t *scode = reinterpret_cast<uint8_t *>(scdf + ncls * P);
-  uint32_t gshift = 32;
-  while ((1u << (32 - gshift)) < S.B) --gshift;  // B = 2^(32 - gshift)
-  for (uint32_t i = tid; i < S.K1; i += T) sT1[i] = S.T1[i];
-  for (uint32_t i = tid; i < S.B; i += T) sT2[i] = S.T2[i];
-  for (uint32_t k = tid; k < S.B; k += T) {
-    const uint32_t rmax = (k << gshift) | ((gshift >= 32) ? 0xFFFFFFFFu : ((1u << gshift) - 1u));
-    sG[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1, rmax);
-  }
-  for (uint32_t i = tid; i < L; i += T) sinfo[i] = S.slinf[i];
-  for (uint32_t c = tid; c < ncls; c += T) {
-    scacc[c] = S.cls_acc[c];
-    scnp1[c] = S.cls_off[c + 1] - S.cls_off[c] - 1u;
-  }
-  for (uint32_t i = tid; i < ncls * P; i += T) {
-    const uint32_t c = i >> S.lgP, d = i & (P - 1u), o = S.cls_off[c], n = S.cls_off[c + 1] - o;
-    scdf[i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
-    scode[i] = d < n ? S.codes[o + d] : (uint8_t)0;
-  }
-  t.T1 = sT1; t.T2 = sT2; t.G = sG; t.info = sinfo; t.cacc = scacc; t.cnp1 = scnp1;
-  t.cdf = scdf; t.code = scode; t.K1 = S.K1; t.B = S.B; t.gshift = gshift; t.lgP = S.lgP;
-}
-
-// the draw stream of one 32-shot word: candidate slots in increasing order
-struct QecRng {
-  uint32_t wlo, whi, draw;
-  int slot;          // candidate under the cursor (>= n_slots: none left)
-  uint32_t r2, r3;   // its accept / digit words
-};
-
-__device__ __forceinline__ void qec_rng_advance(QecRng &g, const QecSampTabs &t,
-                                                const QecSamplerDev &S) {
-  QecPhilox r;
-  unsigned long long skip = 0;
-  for (;;) {
-    r = qec_philox(g.wlo, g.whi, g.draw++, 0u, S.k0, S.k1);
-    uint32_t a = 0;
-    while (a < t.K1 && t.T1[a] > r.c[0]) ++a;
-    skip += (unsigned long long)a * t.B;
-    if (a < t.K1 || skip >= (unsigned long long)S.n_slots) break;  // a == K1: truncated table, draw on
-  }
-  uint32_t b = t.G[r.c[1] >> t.gshift];
-  while (b < t.B - 1u && t.T2[1u + b] > r.c[1]) ++b;
-  const unsigned long long s = (unsigned long long)(long long)(g.slot + 1) + skip + b;
-  g.slot = s >= (unsigned long long)S.n_slots ? (int)S.n_slots : (int)s;
-  g.r2 = r.c[2];
-  g.r3 = r.c[3];
-}
-
-// class thinning and Pauli digit of the candidate under the cursor; false = no fault there
-__device__ __forceinline__ bool qec_rng_resolve(const QecRng &g, const QecSampTabs &t,
-                                                uint32_t &info, uint32_t &code) {
-  info = t.info[(uint32_t)g.slot >> 5];
-  const uint32_t cls = (info >> 20) & 1023u;
-  if (!(info >> 31) && g.r2 >= t.cacc[cls]) return false;
-  const uint32_t *c = t.cdf + (cls << t.lgP);
-  uint32_t d = 0;
-  for (uint32_t step = 1u << (t.lgP - 1u); step; step >>= 1)
-    if (c[d + step - 1u] <= g.r3) d += step;
-  d = min(d, t.cnp1[cls]);
-  code = t.code[(cls << t.lgP) + d];
-  return true;
 }
 
 #endif  // __CUDACC__

@@ -178,7 +178,7 @@ void emit_range(std::ostringstream &o, const QecJitSpec &spec, Namer &nm, size_t
       case QOP_MEASF:
         inj1();
         o << ind << "qec_jit_out<TALLY, BITS>(" << b << "u, "; reg(o, nm.x[a]);
-        o << ", valid, ob, os, s_tally, any_out);\n";
+        o << ", valid, cur.lane0, ob, os, s_tally, any_out);\n";
         break;
       case QOP_ZEROC:
         o << ind << "if (BITS) { if (valid) ob[" << a << "ll * os] = 0u; }\n";
@@ -259,7 +259,7 @@ std::string qec_jit_gates_source(const QecJitSpec &spec) {
         continue;
       }
       // one warp vote per block: does any lane word have an event on ops [s, e)?
-      o << "  if (!__any_sync(0xFFFFFFFFu, cur.any(0x" << std::hex << mask << std::dec << "u))) {\n";
+      o << "  if (__builtin_expect(!__any_sync(0xFFFFFFFFu, cur.any(0x" << std::hex << mask << std::dec << "u)), 1)) {\n";
       Namer fast = nm;
       emit_range(o, spec, fast, s, e, false, "    ");
       o << "  } else {\n";
@@ -323,6 +323,9 @@ int qec_jit_compile(const QecJitSpec &spec, std::vector<char> *cubin, std::strin
            << "#define QEC_JIT_BITS " << (spec.bits ? 1 : 0) << "\n"
            << "#define QEC_JIT_NC " << spec.nc << "\n"
            << "#define QEC_JIT_NOPS " << spec.packed->size() << "\n"
+           << "#define QEC_JIT_K1 " << spec.K1 << "u\n#define QEC_JIT_B " << spec.B << "u\n"
+           << "#define QEC_JIT_L " << spec.L << "u\n#define QEC_JIT_NCLS " << spec.n_classes << "u\n"
+           << "#define QEC_JIT_LGP " << spec.lgP << "u\n#define QEC_JIT_NSLOTS " << spec.n_slots << "\n"
            << "#include \"qec_device.cuh\"\n"
            << "#include \"qec_jit_kernels.cuh\"\n";
   const std::string src = main_src.str();

@@ -16,7 +16,9 @@ struct QecJitSpec {
   int threads = 128, min_blocks = 3;
   int group = 8;  // ops per "any event in here?" block; 0 = test every location
   int segments = 1;     // the sampler draws the faults of one gate-stream segment at a time
-  int sync_every = 96;  // a CTA barrier every so many ops (keeps its warps in one stretch of code)
+  int sync_every = 96;
+  // sampler only: table sizes become compile-time constants of the generated kernel
+  unsigned K1 = 0, B = 0, L = 0, n_classes = 0, lgP = 1, n_slots = 0;  // a CTA barrier every so many ops (keeps its warps in one stretch of code)
 };
 
 struct QecJitKernel {

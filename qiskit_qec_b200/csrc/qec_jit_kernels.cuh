@@ -21,6 +21,8 @@
 
 #define QEC_OP_END 0x7FFFFFFFu
 #define QEC_EVW 5  // words per mask event: op, X/Z masks of operand a, X/Z masks of operand b
+#define QEC_NWARP (QEC_JIT_T / 32)
+#define QEC_TALLYW (QEC_JIT_NC * QEC_NWARP)  // shared tally words: one row of clbit counts per warp
 #define QEC_BMW (QEC_JIT_NSEG * QEC_JIT_SEGW)  // words of a lane word's "an event sits on op i" bitmap
 
 // How a lane word meets its events in the generated gate stream
@@ -63,12 +65,13 @@ struct QecEvList {
 // cursor over a QecEvList (global memory, L2 resident): the entry under the cursor is held in
 // registers and the next one is fetched when it is consumed, so a hit never waits for memory
 struct QecCurMask {
+  bool lane0;
   const uint32_t *bmp;  // this lane word's bitmap column in shared memory
   const uint32_t *p;
   long long es;
   uint32_t bm, m0, m1, m2, m3;
   __device__ __forceinline__ void init(const uint32_t *bitmap, const uint32_t *base, long long stride) {
-    bmp = bitmap; p = base; es = stride; bm = 0u;
+    bmp = bitmap; p = base; es = stride; bm = 0u; lane0 = (threadIdx.x & 31u) == 0u;
     m0 = p[es]; m1 = p[2 * es]; m2 = p[3 * es]; m3 = p[4 * es];
   }
   __device__ __forceinline__ void word(int k) { bm = bmp[k * QEC_JIT_T]; }
@@ -91,11 +94,12 @@ struct QecCurMask {
 // ---- mask queue (sampler), in shared memory, one contiguous run per lane word --------------
 // entry of a one-qubit op: {X mask, Z mask}; of a cx: {X a, Z a, X b, Z b}; entries in op order
 struct QecCurQueue {
+  bool lane0;
   const uint32_t *bmp;
   const uint32_t *pe;
   uint32_t bm;
   __device__ __forceinline__ void init(const uint32_t *bitmap, const uint32_t *queue) {
-    bmp = bitmap; pe = queue; bm = 0u;
+    bmp = bitmap; pe = queue; bm = 0u; lane0 = (threadIdx.x & 31u) == 0u;
   }
   __device__ __forceinline__ void word(int k) { bm = bmp[k * QEC_JIT_T]; }
   __device__ __forceinline__ bool hit(uint32_t bit) const { return (bm & bit) != 0u; }
@@ -114,17 +118,21 @@ struct QecCurQueue {
 };
 
 // ---- what a final measurement does with its value ------------------------------------------
+// (the marginal of clbit c: POPC, one REDUX warp sum, and lane 0 adds it to its WARP's row of
+// the shared tally, s_tally[warp][c] -- a plain read-modify-write, no atomic: ptxas expands a
+// shared-memory RED on a uniform address into a ~12-instruction warp aggregation)
 template <bool TALLY, bool BITS>
 __device__ __forceinline__ void qec_jit_out(const uint32_t c, const uint32_t v, const bool valid,
-                                            uint32_t *__restrict__ ob, const long long os,
-                                            uint32_t *s_tally, uint32_t &any_out) {
+                                            const bool lane0, uint32_t *__restrict__ ob,
+                                            const long long os, uint32_t *s_tally,
+                                            uint32_t &any_out) {
   if (BITS) {
     if (valid) ob[(long long)c * os] = v;
   }
   if (TALLY) {
     any_out |= v;
-    const int cnt = __reduce_add_sync(0xFFFFFFFFu, __popc(v));
-    if ((threadIdx.x & 31u) == 0u && cnt) atomicAdd(&s_tally[c], (uint32_t)cnt);
+    const uint32_t cnt = (uint32_t)__reduce_add_sync(0xFFFFFFFFu, __popc(v));
+    if (lane0) s_tally[c] += cnt;
   }
 }
 
@@ -143,7 +151,9 @@ __device__ __forceinline__ void qec_jit_flush_tally(const QecOutDev &O, uint32_t
   if ((threadIdx.x & 31) == 0 && nz) atomicAdd(&O.tally[QEC_JIT_NC], nz);
   __syncthreads();
   for (int c = threadIdx.x; c < QEC_JIT_NC; c += QEC_JIT_T) {
-    const uint32_t v = s_tally[c];
+    uint32_t v = 0;
+#pragma unroll
+    for (int wp = 0; wp < QEC_NWARP; ++wp) v += s_tally[wp * QEC_JIT_NC + c];
     if (v) atomicAdd(&O.tally[c], (unsigned long long)v);
   }
   if (with_hist) {
@@ -177,7 +187,7 @@ __device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsi
     const unsigned long long *Wl = E.tile + 4 * (size_t)s.loc[K - 1];
 #pragma unroll
     for (int c = 0; c < 4; ++c)
-      acc[K - 1][c] |= (((uint32_t)(__ldg(Wl + c) >> s.dig[K - 1])) << b) & segmask;
+      acc[K - 1][c] |= (((uint32_t)(Wl[c] >> s.dig[K - 1])) << b) & segmask;
 #pragma unroll
     for (int j = 0; j < K - 1; ++j) {
       const uint32_t code = E.pcode[s.pb[j] + s.dig[j]];
@@ -216,16 +226,37 @@ __device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsi
   for (int j = 0; j < K; ++j) l.insert(s.op[j], acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
 }
 
+// The enumerator's tables (suffix sums E, per-location Pauli counts / ops / code lists, tile
+// masks) are copied to shared memory once per CTA when the host found room for them
+// (`tab_in_smem`): unranking is a chain of dependent binary-search loads, 30 cycles each from
+// shared memory against ~300+ from L2.
 extern "C" __global__ void __launch_bounds__(QEC_JIT_T, QEC_JIT_MINB)
-qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const long long hi,
-               uint32_t *__restrict__ scratch) {
+qec_jit_kernel(const QecOutDev O, const QecEnumDev Eg, const long long lo, const long long hi,
+               uint32_t *__restrict__ scratch, const int tab_in_smem) {
   extern __shared__ __align__(16) uint32_t qec_smem[];
   uint32_t *s_tally = qec_smem;
-  uint32_t *bmw = qec_smem + QEC_JIT_NC + threadIdx.x;  // bitmap column of this lane word
-  if (QEC_JIT_TALLY) {
-    for (int c = threadIdx.x; c < QEC_JIT_NC; c += QEC_JIT_T) s_tally[c] = 0;
-    __syncthreads();
+  uint32_t *w_tally = s_tally + (threadIdx.x >> 5) * QEC_JIT_NC;  // this warp's row
+  uint32_t *bmw = qec_smem + QEC_TALLYW + threadIdx.x;  // bitmap column of this lane word
+  QecEnumDev E = Eg;
+  if (tab_in_smem) {
+    uint32_t *t = qec_smem + QEC_TALLYW + QEC_BMW * QEC_JIT_T;
+    t += (uint32_t)(t - qec_smem) & 1u;  // 8-byte aligned
+    const int L = Eg.L, nE = (QEC_JIT_ORDER + 1) * (L + 2), nP = (int)Eg.poff[L];
+    unsigned long long *sE = reinterpret_cast<unsigned long long *>(t);
+    unsigned long long *sTile = sE + nE;
+    uint32_t *sNp = reinterpret_cast<uint32_t *>(sTile + 4 * L), *sPoff = sNp + L, *sLop = sPoff + L + 1;
+    uint8_t *sCode = reinterpret_cast<uint8_t *>(sLop + L);
+    for (int i = threadIdx.x; i < nE; i += QEC_JIT_T) sE[i] = Eg.E[i];
+    for (int i = threadIdx.x; i < 4 * L; i += QEC_JIT_T) sTile[i] = Eg.tile[i];
+    for (int i = threadIdx.x; i < L; i += QEC_JIT_T) { sNp[i] = Eg.npaul[i]; sLop[i] = Eg.lop[i]; }
+    for (int i = threadIdx.x; i <= L; i += QEC_JIT_T) sPoff[i] = Eg.poff[i];
+    for (int i = threadIdx.x; i < nP; i += QEC_JIT_T) sCode[i] = Eg.pcode[i];
+    E.E = sE; E.tile = sTile; E.npaul = sNp; E.poff = sPoff; E.lop = sLop; E.pcode = sCode;
   }
+  if (QEC_JIT_TALLY) {
+    for (int c = threadIdx.x; c < QEC_TALLYW; c += QEC_JIT_T) s_tally[c] = 0;
+  }
+  __syncthreads();
   const long long es = (long long)gridDim.x * QEC_JIT_T;
   uint32_t *ev = scratch + (long long)blockIdx.x * QEC_JIT_T + threadIdx.x;
   unsigned long long nz = 0;
@@ -254,7 +285,7 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const 
     for (int seg = 0; seg < QEC_JIT_NSEG; ++seg) {
       cur.bmp = bmw + seg * QEC_JIT_SEGW * QEC_JIT_T;
       qec_jit_seg<QecCurMask, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
-          seg, F, cur, valid, O.bits + w, O.n_words, s_tally, any);
+          seg, F, cur, valid, O.bits + w, O.n_words, w_tally, any);
     }
     if (QEC_JIT_TALLY) nz += __popc(any);
   }
@@ -265,29 +296,121 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev E, const long long lo, const 
 #if QEC_JIT_KIND == 2
 // ---- FaultSampler ------------------------------------------------------------------------------
 // Same random decisions, in the same order, as k_sample in qec_kernels.cu (so both kernels
-// return identical bits for one (seed, shot id)); the table lookups are the accelerated ones
-// of qec_device.cuh.  The gate stream runs segment by segment: before a segment the lane word
-// draws the faults that fall on its ops into its mask queue (`capw` words of shared memory)
-// and bitmap, so the queue only ever holds one segment's faults.  `cap` = events per segment
-// the host sized the queue for (reported back on overflow).
+// return identical bits for one (seed, shot id)); only the table lookups are quicker here: the
+// sampler's small tables sit in shared memory at compile-time offsets (the table sizes are
+// constants of the generated kernel), the second-level gap comes from a guide table plus
+// ~1 step instead of a binary search, and the Pauli digit from an unrolled binary search over
+// the class's cdf padded to P = 2^QEC_JIT_LGP entries.  All of them return exactly what
+// qec_count_greater / the linear cdf scan return.
+//
+// The gate stream runs segment by segment: before a segment the lane word draws the faults
+// that fall on its ops into its mask queue (`capw` words of shared memory) and bitmap, so the
+// queue only ever holds one segment's faults.  `cap` = events per segment the host sized the
+// queue for (reported back on overflow).
+#define QEC_P (1u << QEC_JIT_LGP)
+#define QEC_TAB_T1 0u
+#define QEC_TAB_T2 (QEC_TAB_T1 + QEC_JIT_K1)
+#define QEC_TAB_G (QEC_TAB_T2 + QEC_JIT_B)        // uint16[2 B]
+#define QEC_TAB_INFO (QEC_TAB_G + QEC_JIT_B)
+#define QEC_TAB_CACC (QEC_TAB_INFO + QEC_JIT_L)
+#define QEC_TAB_CNP1 (QEC_TAB_CACC + QEC_JIT_NCLS)
+#define QEC_TAB_CDF (QEC_TAB_CNP1 + QEC_JIT_NCLS)
+#define QEC_TAB_CODE (QEC_TAB_CDF + QEC_JIT_NCLS * QEC_P)  // uint8[n][P]
+#define QEC_TAB_WORDS (QEC_TAB_CODE + (QEC_JIT_NCLS * QEC_P + 3u) / 4u)
+
+__device__ __forceinline__ uint32_t qec_jit_gshift() {  // 2 B = 2^(32 - gshift) guide buckets
+  uint32_t g = 32;
+  while ((1u << (32 - g)) < 2u * QEC_JIT_B) --g;
+  return g;
+}
+
+__device__ __forceinline__ void qec_jit_tabs_fill(uint32_t *tab, const QecSamplerDev &S) {
+  const uint32_t gshift = qec_jit_gshift();
+  uint16_t *sG = reinterpret_cast<uint16_t *>(tab + QEC_TAB_G);
+  uint8_t *scode = reinterpret_cast<uint8_t *>(tab + QEC_TAB_CODE);
+  for (uint32_t i = threadIdx.x; i < QEC_JIT_K1; i += QEC_JIT_T) tab[QEC_TAB_T1 + i] = S.T1[i];
+  for (uint32_t i = threadIdx.x; i < QEC_JIT_B; i += QEC_JIT_T) tab[QEC_TAB_T2 + i] = S.T2[i];
+  for (uint32_t k = threadIdx.x; k < 2u * QEC_JIT_B; k += QEC_JIT_T) {
+    // entries of T2[1..B) greater than the largest r of bucket k: where the scan for any r of
+    // the bucket may start
+    const uint32_t rmax = (k << gshift) | ((1u << gshift) - 1u);
+    sG[k] = (uint16_t)qec_count_greater(S.T2 + 1, QEC_JIT_B - 1u, rmax);
+  }
+  for (uint32_t i = threadIdx.x; i < QEC_JIT_L; i += QEC_JIT_T) tab[QEC_TAB_INFO + i] = S.slinf[i];
+  for (uint32_t c = threadIdx.x; c < QEC_JIT_NCLS; c += QEC_JIT_T) {
+    tab[QEC_TAB_CACC + c] = S.cls_acc[c];
+    tab[QEC_TAB_CNP1 + c] = S.cls_off[c + 1] - S.cls_off[c] - 1u;
+  }
+  for (uint32_t i = threadIdx.x; i < QEC_JIT_NCLS * QEC_P; i += QEC_JIT_T) {
+    const uint32_t c = i >> QEC_JIT_LGP, d = i & (QEC_P - 1u), o = S.cls_off[c], n = S.cls_off[c + 1] - o;
+    tab[QEC_TAB_CDF + i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
+    scode[i] = d < n ? S.codes[o + d] : (uint8_t)0;
+  }
+}
+
+// the draw stream of one 32-shot word: candidate slots in increasing order
+struct QecRng {
+  uint32_t wlo, whi, draw;
+  int slot;          // candidate under the cursor (QEC_JIT_NSLOTS: none left)
+  uint32_t r2, r3;   // its accept / digit words
+};
+
+__device__ __forceinline__ void qec_rng_advance(QecRng &g, const uint32_t *tab, const uint32_t k0,
+                                                const uint32_t k1) {
+  const uint16_t *sG = reinterpret_cast<const uint16_t *>(tab + QEC_TAB_G);
+  QecPhilox r;
+  uint32_t skip = 0;  // (saturates at QEC_JIT_NSLOTS < 2^24: 32 bits are plenty)
+  for (;;) {
+    r = qec_philox(g.wlo, g.whi, g.draw++, 0u, k0, k1);
+    uint32_t a = 0;
+    if (tab[QEC_TAB_T1] > r.c[0]) {  // first-level gap > 0: uncommon by the choice of B
+      a = 1;
+      while (a < QEC_JIT_K1 && tab[QEC_TAB_T1 + a] > r.c[0]) ++a;
+      skip = min(skip + a * QEC_JIT_B, (uint32_t)QEC_JIT_NSLOTS);
+    }
+    if (a < QEC_JIT_K1 || skip >= (uint32_t)QEC_JIT_NSLOTS) break;  // a == K1: truncated table, draw on
+  }
+  uint32_t b = sG[r.c[1] >> qec_jit_gshift()];
+  while (b < QEC_JIT_B - 1u && tab[QEC_TAB_T2 + 1u + b] > r.c[1]) ++b;
+  g.slot = (int)min((uint32_t)(g.slot + 1) + skip + b, (uint32_t)QEC_JIT_NSLOTS);
+  g.r2 = r.c[2];
+  g.r3 = r.c[3];
+}
+
+// class thinning and Pauli digit of the candidate under the cursor; false = no fault there
+__device__ __forceinline__ bool qec_rng_resolve(const QecRng &g, const uint32_t *tab, uint32_t &info,
+                                                uint32_t &code) {
+  info = tab[QEC_TAB_INFO + ((uint32_t)g.slot >> 5)];
+  const uint32_t cls = (info >> 20) & 1023u;
+  if (!(info >> 31) && g.r2 >= tab[QEC_TAB_CACC + cls]) return false;
+  const uint32_t *c = tab + QEC_TAB_CDF + (cls << QEC_JIT_LGP);
+  uint32_t d = 0;
+#pragma unroll
+  for (uint32_t step = QEC_P >> 1; step; step >>= 1)
+    if (c[d + step - 1u] <= g.r3) d += step;
+  d = min(d, tab[QEC_TAB_CNP1 + cls]);
+  code = reinterpret_cast<const uint8_t *>(tab + QEC_TAB_CODE)[(cls << QEC_JIT_LGP) + d];
+  return true;
+}
+
 extern "C" __global__ void __launch_bounds__(QEC_JIT_T, QEC_JIT_MINB)
 qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo,
                const long long n_shots, const int cap, const int capw,
                uint32_t *__restrict__ overflow_flag) {
   extern __shared__ __align__(16) uint32_t qec_smem[];
   uint32_t *s_tally = qec_smem;
-  uint32_t *s_hist = s_tally + QEC_JIT_NC;
+  uint32_t *w_tally = s_tally + (threadIdx.x >> 5) * QEC_JIT_NC;  // this warp's row
+  uint32_t *s_hist = s_tally + QEC_TALLYW;
   uint32_t *s_tab = s_hist + 64;
-  uint32_t *s_bm = s_tab + qec_samp_tab_words(S.K1, S.B, (uint32_t)S.L, (uint32_t)S.n_classes, S.lgP);
+  uint32_t *s_bm = s_tab + QEC_TAB_WORDS;                // [QEC_JIT_SEGW][QEC_JIT_T]
   uint32_t *s_q = s_bm + QEC_JIT_SEGW * QEC_JIT_T;       // [QEC_JIT_T][capw]
   s_q += (4u - ((uint32_t)(s_q - qec_smem) & 3u)) & 3u;  // 16-byte aligned
-  QecSampTabs tabs;
-  qec_samp_tabs_fill(tabs, s_tab, S, threadIdx.x, QEC_JIT_T);
-  for (int c = threadIdx.x; c < QEC_JIT_NC + 64; c += QEC_JIT_T) s_tally[c] = 0;
+  qec_jit_tabs_fill(s_tab, S);
+  for (int c = threadIdx.x; c < QEC_TALLYW + 64; c += QEC_JIT_T) s_tally[c] = 0;
   __syncthreads();
+  const uint32_t k0 = S.k0, k1 = S.k1;
   uint32_t *bmw = s_bm + threadIdx.x;
   uint32_t *q = s_q + (size_t)threadIdx.x * capw;
-  const int n_slots = (int)S.n_slots;
   unsigned long long nz = 0;
   for (long long ch = blockIdx.x; ch * QEC_JIT_T < O.n_words; ch += gridDim.x) {
     const long long w = ch * QEC_JIT_T + threadIdx.x;
@@ -299,8 +422,8 @@ qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo
       g.wlo = (uint32_t)gw; g.whi = (uint32_t)(gw >> 32); g.draw = 0u; g.slot = -1;
       g.r2 = g.r3 = 0u;
     }
-    if (valid) qec_rng_advance(g, tabs, S);
-    else g.slot = n_slots;
+    if (valid) qec_rng_advance(g, s_tab, k0, k1);
+    else g.slot = QEC_JIT_NSLOTS;
     int n_ev = 0;  // faults drawn (fault-count histogram, overflow report)
     bool overflow = false;
     uint32_t cp[6] = {0, 0, 0, 0, 0, 0};  // bit-sliced per-shot fault counters
@@ -313,35 +436,36 @@ qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo
       for (int k = 0; k < QEC_JIT_SEGW; ++k) bmw[k * QEC_JIT_T] = 0u;
       const int slot_end = (int)S.seg_end[seg];
       const uint32_t op0 = (uint32_t)seg * (QEC_JIT_SEGW * 32u);
-      int nw = 0, base = 0;  // queue words in use; first word of the entry being filled
+      int nw = 0;              // queue words in use
+      uint32_t *ent = q;       // the entry being filled
       uint32_t last_op = 0xFFFFFFFFu;
       while (g.slot < slot_end) {
         uint32_t info, code;
         const uint32_t bit = (uint32_t)g.slot & 31u;
-        if (qec_rng_resolve(g, tabs, info, code) && (int)bit < nv) {
+        if (qec_rng_resolve(g, s_tab, info, code) && (int)bit < nv) {
           ++n_ev;
           const uint32_t msk = 1u << bit;
           if (code != 0u) {
             const uint32_t op = info & 0xFFFFFu;
+            const uint32_t m0 = (code & 1u) ? msk : 0u, m1 = (code & 2u) ? msk : 0u;
+            const uint32_t m2 = (code & 4u) ? msk : 0u, m3 = (code & 8u) ? msk : 0u;
+            const bool two = (info >> 30) & 1u;
             if (op != last_op) {  // a new entry (events arrive in op order)
-              const int len = ((info >> 30) & 1u) ? 4 : 2;
+              const int len = two ? 4 : 2;
               if (nw + len > capw) {
                 overflow = true;
               } else {
-                base = nw;
+                ent = q + nw;
                 nw += len;
                 last_op = op;
-                q[base] = 0u; q[base + 1] = 0u;
-                if (len == 4) { q[base + 2] = 0u; q[base + 3] = 0u; }
+                *reinterpret_cast<uint2 *>(ent) = make_uint2(m0, m1);
+                if (two) *reinterpret_cast<uint2 *>(ent + 2) = make_uint2(m2, m3);
                 const uint32_t rel = op - op0;
                 bmw[(rel >> 5) * QEC_JIT_T] |= 1u << (rel & 31u);
               }
-            }
-            if (!overflow) {
-              if (code & 1u) q[base] |= msk;
-              if (code & 2u) q[base + 1] |= msk;
-              if (code & 4u) q[base + 2] |= msk;
-              if (code & 8u) q[base + 3] |= msk;
+            } else if (!overflow) {  // another shot of the same lane word on the same op
+              ent[0] |= m0; ent[1] |= m1;
+              if (two) { ent[2] |= m2; ent[3] |= m3; }
             }
           }
           if (QEC_JIT_TALLY) {
@@ -358,12 +482,12 @@ qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo
             }
           }
         }
-        qec_rng_advance(g, tabs, S);
+        qec_rng_advance(g, s_tab, k0, k1);
       }
       QecCurQueue cur;
       cur.init(bmw, q);
       qec_jit_seg<QecCurQueue, QEC_JIT_TALLY != 0, QEC_JIT_BITS != 0>(
-          seg, F, cur, valid, O.bits + w, O.n_words, s_tally, any);
+          seg, F, cur, valid, O.bits + w, O.n_words, w_tally, any);
     }
     if (overflow) atomicMax(overflow_flag, (uint32_t)max(n_ev, cap + 1));
     if (QEC_JIT_TALLY) {
