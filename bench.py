@@ -199,12 +199,12 @@ def run_ours(args):
         step(i)
     torch.cuda.synchronize()
     sm.check()
-    if world > 1:
-        dist.barrier()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
         time.sleep(0.3)
+    if world > 1:
+        dist.barrier()  # (after rank 0's pause: every rank enters the timed region together)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     torch.cuda.synchronize()
     ev[0].record()

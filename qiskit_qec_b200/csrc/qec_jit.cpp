@@ -237,6 +237,7 @@ std::string qec_jit_gates_source(const QecJitSpec &spec) {
          "__device__ __forceinline__ void qec_jit_seg" << seg << "(QecFrame &F, CUR &cur, const bool valid,\n"
          "    uint32_t *__restrict__ ob, const long long os, uint32_t *s_tally, uint32_t &any_out) {\n";
     size_t since_sync = 0;
+    std::vector<std::string> slow_blocks;
     for (size_t s = s0; s < s1; s += step) {
       const size_t e = std::min(s1, s + step);
       uint32_t mask = 0;
@@ -258,14 +259,23 @@ std::string qec_jit_gates_source(const QecJitSpec &spec) {
         emit_range(o, spec, nm, s, e, mask != 0, "  ");
         continue;
       }
-      // one warp vote per block: does any lane word have an event on ops [s, e)?
-      o << "  if (__builtin_expect(!__any_sync(0xFFFFFFFFu, cur.any(0x" << std::hex << mask << std::dec << "u)), 1)) {\n";
+      // one warp vote per block: does any lane word have an event on ops [s, e)?  The copy
+      // with the injection tests is placed behind the end of the function (goto), so that the
+      // common path is one contiguous run of code that the instruction prefetcher can follow.
+      const size_t id = slow_blocks.size();
+      o << "  if (__any_sync(0xFFFFFFFFu, cur.any(0x" << std::hex << mask << std::dec
+        << "u))) goto qslow_" << seg << "_" << id << ";\n  {\n";
       Namer fast = nm;
       emit_range(o, spec, fast, s, e, false, "    ");
-      o << "  } else {\n";
-      emit_range(o, spec, nm, s, e, true, "    ");
-      o << "  }\n";
+      o << "  }\n  qback_" << seg << "_" << id << ":;\n";
+      std::ostringstream sl;
+      sl << "  qslow_" << seg << "_" << id << ": {\n";
+      emit_range(sl, spec, nm, s, e, true, "    ");
+      sl << "  }\n  goto qback_" << seg << "_" << id << ";\n";
+      slow_blocks.push_back(sl.str());
     }
+    o << "  return;\n";
+    for (const std::string &b : slow_blocks) o << b;
     o << "}\n";
   }
   o << "template <class CUR, bool TALLY, bool BITS>\n"

@@ -42,22 +42,28 @@
 struct QecEvList {
   uint32_t *p;
   long long es;
+  uint32_t *bmw;   // this lane word's bitmap column: the bit of an op is set when its entry is made
   int n;
+  uint32_t last;   // op of the last entry: an op beyond it is appended without reading the list
   __device__ __forceinline__ uint32_t &at(int e, int k) { return p[(long long)(e * QEC_EVW + k) * es]; }
   __device__ __forceinline__ void insert(uint32_t op, uint32_t a0, uint32_t a1, uint32_t a2,
                                          uint32_t a3) {
     if ((a0 | a1 | a2 | a3) == 0u) return;  // identity Paulis only
     int q = n;
-    while (q > 0 && at(q - 1, 0) > op) --q;
-    if (q > 0 && at(q - 1, 0) == op) {  // same op reached again by a later subset: other bits
-      at(q - 1, 1) |= a0; at(q - 1, 2) |= a1; at(q - 1, 3) |= a2; at(q - 1, 4) |= a3;
-      return;
-    }
-    for (int i = n; i > q; --i) {
+    if (n > 0 && op <= last) {  // (rare: the slower locations of a later subset)
+      while (q > 0 && at(q - 1, 0) > op) --q;
+      if (q > 0 && at(q - 1, 0) == op) {  // same op reached again by a later subset: other bits
+        at(q - 1, 1) |= a0; at(q - 1, 2) |= a1; at(q - 1, 3) |= a2; at(q - 1, 4) |= a3;
+        return;
+      }
+      for (int i = n; i > q; --i) {
 #pragma unroll
-      for (int k = 0; k < QEC_EVW; ++k) at(i, k) = at(i - 1, k);
+        for (int k = 0; k < QEC_EVW; ++k) at(i, k) = at(i - 1, k);
+      }
     }
+    if (q == n) last = op;
     at(q, 0) = op; at(q, 1) = a0; at(q, 2) = a1; at(q, 3) = a2; at(q, 4) = a3;
+    bmw[(op >> 5) * QEC_JIT_T] |= 1u << (op & 31u);
     ++n;
   }
 };
@@ -264,17 +270,13 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev Eg, const long long lo, const
     const long long w = ch * QEC_JIT_T + threadIdx.x;
     const bool valid = w < O.n_words;
     QecEvList l;
-    l.p = ev; l.es = es; l.n = 0;
+    l.p = ev; l.es = es; l.n = 0; l.bmw = bmw; l.last = 0u;
 #pragma unroll
     for (int k = 0; k < QEC_BMW; ++k) bmw[k * QEC_JIT_T] = 0u;
     if (valid) {
       const long long r0 = lo + 32 * w;
       const int nv = (int)min((long long)32, hi - r0);
       qec_jit_enum_gen<QEC_JIT_ORDER>(E, (unsigned long long)r0, nv, l);
-      for (int e = 0; e < l.n; ++e) {
-        const uint32_t op = l.at(e, 0);
-        bmw[(op >> 5) * QEC_JIT_T] |= 1u << (op & 31u);
-      }
     }
     QecCurMask cur;
     cur.init(bmw, ev, es);
