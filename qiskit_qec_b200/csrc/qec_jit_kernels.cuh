@@ -494,7 +494,21 @@ qec_jit_kernel(const QecOutDev O, const QecSamplerDev S, const long long word_lo
     if (overflow) atomicMax(overflow_flag, (uint32_t)max(n_ev, cap + 1));
     if (QEC_JIT_TALLY) {
       nz += __popc(any);
-      for (int bit = 0; bit < nv; ++bit) {
+      // faults-per-shot histogram: shots with 0..3 faults are counted with bit logic on the
+      // counter planes and one warp sum per bin; the few shots with more go one by one
+      const uint32_t live = nv >= 32 ? 0xFFFFFFFFu : ((1u << nv) - 1u);
+      const uint32_t hi4 = cp[2] | cp[3] | cp[4] | cp[5];
+      const uint32_t lo4 = live & ~hi4;
+      const int c0 = __reduce_add_sync(0xFFFFFFFFu, __popc(lo4 & ~cp[1] & ~cp[0]));
+      const int c1 = __reduce_add_sync(0xFFFFFFFFu, __popc(lo4 & ~cp[1] & cp[0]));
+      const int c2 = __reduce_add_sync(0xFFFFFFFFu, __popc(lo4 & cp[1] & ~cp[0]));
+      const int c3 = __reduce_add_sync(0xFFFFFFFFu, __popc(lo4 & cp[1] & cp[0]));
+      if ((threadIdx.x & 31u) == 0u) {
+        atomicAdd(&s_hist[0], (uint32_t)c0); atomicAdd(&s_hist[1], (uint32_t)c1);
+        atomicAdd(&s_hist[2], (uint32_t)c2); atomicAdd(&s_hist[3], (uint32_t)c3);
+      }
+      for (uint32_t m = live & hi4; m; m &= m - 1u) {
+        const int bit = __ffs(m) - 1;
         uint32_t k = 0;
 #pragma unroll
         for (int p = 0; p < 6; ++p) k |= ((cp[p] >> bit) & 1u) << p;
