@@ -195,16 +195,20 @@ def run_ours(args):
         sm.sample_dev(lo, n_shots, bits.data_ptr(), tally.data_ptr(), stream)
         allreduce_tally(tally)
 
+    # clocks / throttle reasons are sampled (nvidia-smi, 100 ms period) from before the warm-up
+    # to the end of the end-to-end steps: the timed region itself lasts only a few tens of ms
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        t_wait = time.perf_counter()
+        while not clocks.rows and time.perf_counter() - t_wait < 3.0:
+            time.sleep(0.05)
     for i in range(args.warmup):
         step(i)
     torch.cuda.synchronize()
     sm.check()
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
-        time.sleep(0.3)
     if world > 1:
-        dist.barrier()  # (after rank 0's pause: every rank enters the timed region together)
+        dist.barrier()  # every rank enters the timed region together
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     torch.cuda.synchronize()
     ev[0].record()
@@ -216,7 +220,6 @@ def run_ours(args):
     sampler_kernel = _capi.last_kernel()
     if world > 1:
         dist.barrier()
-    clk = clocks.stop() if rank == 0 else None
     total_ms = ev[0].elapsed_time(ev[-1])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
@@ -257,6 +260,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * n_shots * e2e_steps / float(t.item())
     assert int(host_tally[nc + 1].item()) == n_shots
+    clk = clocks.stop() if rank == 0 else None
 
     # secondary metric: FaultEnumerator order 2 on the same circuit (BASELINE configs[2]),
     # index range sharded evenly across ranks, outcomes + tallies on device
@@ -316,6 +320,12 @@ def run_ours(args):
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"
         int_peak, clk_mhz = _capi.measure_int_peak(local, 40.0)
+        traffic = None
+        try:  # dram bytes per shot of the dominant kernel, from the committed ncu --set full capture
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r01", "ncu_dominant_kernel.json")))
+            traffic = float(cap["dram_bytes_per_shot"]) * n_shots
+        except (OSError, ValueError, KeyError):
+            pass
         bytes_per_launch = n_shots * nc / 8.0
         achieved = bytes_per_launch / (kern_ms * 1e-3) / 1e9
         ops_per_launch = n_shots * w_bit / 32.0
@@ -331,7 +341,10 @@ def run_ours(args):
                        "l2": "output per step (1.81 GB at 1e8 shots) is larger than L2; no reuse",
                        "timing": "CUDA events on the launching stream, max over ranks"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "kernel": sampler_kernel,
+                         "frac": achieved / hbm_peak, "traffic": traffic,
+                         "traffic_source": "profiles/r01/ncu_dominant_kernel.json (dram read+write "
+                                           "bytes per shot x shots per launch)",
+                         "kernel": sampler_kernel,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_shot": nc / 8.0},
             "int_roofline": {"bound": "int32-alu", "achieved": int_ach, "peak": int_peak,
