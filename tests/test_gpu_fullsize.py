@@ -115,3 +115,36 @@ def test_cfg2_sampler_1e8_shots_statistics_and_shard_invariance(capi, order1):
     lut = torch.tensor([bin(i).count("1") for i in range(256)], dtype=torch.int64, device=dev)
     pop = torch.stack([lut[bits[c].view(torch.uint8).long()].sum() for c in range(nc)]).cpu().numpy()
     np.testing.assert_array_equal(pop, tw.cpu().numpy()[:nc])
+
+
+def test_host_entry_points_stream_in_chunks(capi, order1, monkeypatch):
+    """The host-pointer entry points stream their outcomes back chunk by chunk on two streams
+    (qec_capi.cu pipelined_out); with 1 MiB chunks a 1e6-shot call is ~31 chunks, the last one
+    ragged.  Results must equal the single-launch device path bit for bit."""
+    circ, idx, labels, paulis, a, n = order1
+    _, _, lw, lp = sampler_inputs(circ, standard_depolarizing_model(P))
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=5)
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.current_stream().cuda_stream
+    n_shots, lo = 1_000_003, 64 * 12345
+    n_words = (n_shots + 31) // 32
+    tally = torch.zeros(capi.tally_len(circ.nc), dtype=torch.int64, device=dev)
+    bits = torch.empty((circ.nc, n_words), dtype=torch.int32, device=dev)
+    sm.sample_dev(lo, n_shots, bits.data_ptr(), tally.data_ptr(), stream)
+    torch.cuda.synchronize()
+    monkeypatch.setenv("QEC_B200_PIPE_MB", "1")
+    hbits, htally, _, _ = sm.sample(lo, n_shots, want_tally=True)
+    np.testing.assert_array_equal(hbits.view(np.int32).reshape(circ.nc, n_words), bits.cpu().numpy())
+    np.testing.assert_array_equal(htally.astype(np.int64), tally.cpu().numpy())
+    # enumerator: a ragged window of order-2 paths
+    en = make_enumerator(capi, g, 2, idx, paulis)
+    plo, phi = 1_000_001, 1_000_001 + 2_000_037
+    pw = (phi - plo + 31) // 32
+    etally = torch.zeros_like(tally)
+    ebits = torch.empty((circ.nc, pw), dtype=torch.int32, device=dev)
+    en.range_dev(plo, phi, ebits.data_ptr(), etally.data_ptr(), stream)
+    torch.cuda.synchronize()
+    hb, ht = en.range(plo, phi, want_tally=True)
+    np.testing.assert_array_equal(hb.view(np.int32).reshape(circ.nc, pw), ebits.cpu().numpy())
+    np.testing.assert_array_equal(ht.astype(np.int64), etally.cpu().numpy())
