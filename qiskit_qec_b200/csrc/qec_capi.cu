@@ -130,6 +130,7 @@ struct qec_circuit {
   DevBuf out_bits, out_frame, tally, ev_off, ev;  // staging for the host-pointer entry points
   DevBuf pipe_buf[2];                             // double-buffered outcome chunks (host entry points)
   cudaStream_t pipe_stream[2] = {nullptr, nullptr};
+  cudaEvent_t pipe_done[2] = {nullptr, nullptr};  // kernels of a chunk finished (not its copy)
   DevInfo *info = nullptr;
 };
 
@@ -152,6 +153,7 @@ static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, L
   const size_t buf_bytes = (size_t)c->nc * cw * 4;
   for (int i = 0; i < 2; ++i) {
     if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    if (!c->pipe_done[i]) CU(cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
     int rc = c->pipe_buf[i].ensure(std::max<size_t>(buf_bytes, 4));
     if (rc) return rc;
   }
@@ -161,8 +163,12 @@ static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, L
     const int64_t words = std::min(cw, n_words - w0);
     cudaStream_t st = c->pipe_stream[k];
     uint32_t *d = (uint32_t *)c->pipe_buf[k].p;
+    // the kernels of successive chunks share per-object scratch (event lists, deferred-word
+    // list): chunk i + 1 computes after chunk i's kernels, while chunk i's copy is in flight
+    if (w0 > 0) CU(cudaStreamWaitEvent(st, c->pipe_done[k ^ 1], 0));
     int rc = launch(w0, words, d, st);
     if (rc) return rc;
+    CU(cudaEventRecord(c->pipe_done[k], st));
     CU(cudaMemcpy2DAsync(host_bits + w0, (size_t)n_words * 4, d, (size_t)words * 4,
                          (size_t)words * 4, (size_t)c->nc, cudaMemcpyDeviceToHost, st));
   }
@@ -280,6 +286,7 @@ extern "C" void qec_circuit_destroy(qec_circuit *c) {
   for (int i = 0; i < 2; ++i) {
     c->pipe_buf[i].release();
     if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
+    if (c->pipe_done[i]) cudaEventDestroy(c->pipe_done[i]);
   }
   delete c;
 }
@@ -513,6 +520,8 @@ struct qec_enumerator {
   JitPlan jit;
   DevBuf jit_scratch;
   int jit_tab_in_smem = 0;
+  DevBuf redo_list;                    // lane words the specialised kernel deferred
+  unsigned int *d_redo_count = nullptr;
 };
 
 // Can this enumerator run on the specialised kernel?  (the frame must fit the register file,
@@ -655,6 +664,8 @@ extern "C" void qec_enumerator_destroy(qec_enumerator *e) {
   if (e->d_tile) cudaFree(e->d_tile);
   e->scratch.release();
   e->jit_scratch.release();
+  e->redo_list.release();
+  if (e->d_redo_count) cudaFree(e->d_redo_count);
   e->jit.release();
   delete e;
 }
@@ -729,12 +740,31 @@ static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bi
     if (v->ok) {
       long long lo_ = lo, hi_ = hi;
       uint32_t *scr = (uint32_t *)e->jit_scratch.p;
-      void *args[] = {&O, &e->dev, &lo_, &hi_, &scr, &e->jit_tab_in_smem};
+      // lane words that would need more than max_seg unranking segments are listed by the
+      // specialised kernel and run by the table-driven one right behind it (same stream)
+      // (off by default: at d=5 order 2 about 9 % of the lane words need 11+ segments, and the
+      // second pass then costs more than the imbalance it removes: profiles/r01/tune13.log)
+      const int max_seg_env = env_int("QEC_B200_JIT_MAXSEG", 0);
+      int max_seg = max_seg_env > 0 ? max_seg_env : (1 << 30);
+      int rc2 = e->redo_list.ensure((size_t)std::max<int64_t>(O.n_words, 1) * 8);
+      if (rc2) return rc2;
+      if (!e->d_redo_count) CU(cudaMalloc((void **)&e->d_redo_count, 4));
+      CU(cudaMemsetAsync(e->d_redo_count, 0, 4, stream));
+      long long *redo = (long long *)e->redo_list.p;
+      void *args[] = {&O, &e->dev, &lo_, &hi_, &scr, &e->jit_tab_in_smem, &max_seg, &redo,
+                      &e->d_redo_count};
       std::string err;
       time_begin(e->c, stream);
       const int rc = qec_jit_launch(v->k, e->jit.grid, e->jit.smem, stream, args, &err);
+      if (!rc && max_seg_env > 0) {
+        QecLaunchCfg small = e->cfg;
+        small.grid = std::min(small.grid, e->c->info->sms);
+        qec_launch_enumerate(small, stream, e->c->dev, O, e->dev, lo, hi, (uint32_t *)e->scratch.p,
+                             redo, e->d_redo_count);
+      }
       time_end(e->c, stream);
       if (rc) return fail(QEC_ERR_CUDA, "%s", err.c_str());
+      CU(cudaGetLastError());
       g_last_kernel = "enumerate:specialised regs=" + std::to_string(v->k.regs) +
                       " T=" + std::to_string(e->jit.threads) + " ctas/sm=" +
                       std::to_string(e->jit.min_blocks) + " group=" + std::to_string(e->jit.group);

@@ -178,16 +178,21 @@ __device__ __forceinline__ void qec_jit_flush_tally(const QecOutDev &O, uint32_t
 // stretch in which only the LAST location's digit moves (productiterator.cpp:23-29: last digit
 // fastest), so its masks come from the tile table with one 64-bit shift and every other
 // location contributes a constant code over the segment's bit range.
+// Returns false when the lane word would need more than `max_seg` segments (its 32 paths step
+// through a run of one-Pauli locations): such words are rare but cost a warp -- and, through
+// the CTA barriers, the whole CTA -- ten times the usual prologue, so the kernel leaves them
+// to a second pass of the table-driven kernel over the list of deferred words.
 template <int K>
-__device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsigned long long r0,
-                                                 const int nv, QecEvList &l) {
+__device__ __forceinline__ bool qec_jit_enum_gen(const QecEnumDev &E, const unsigned long long r0,
+                                                 const int nv, QecEvList &l, const int max_seg) {
   EnumState<K> s;
   enum_unrank<K>(E, r0, s);
   uint32_t acc[K][4];
 #pragma unroll
   for (int j = 0; j < K; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0u; }
-  int b = 0;
+  int b = 0, n_seg = 0;
   for (;;) {
+    if (++n_seg > max_seg) return false;
     const int seg = min((int)(s.np[K - 1] - s.dig[K - 1]), nv - b);
     const uint32_t segmask = (seg >= 32 ? 0xFFFFFFFFu : ((1u << seg) - 1u)) << b;
     const unsigned long long *Wl = E.tile + 4 * (size_t)s.loc[K - 1];
@@ -230,6 +235,7 @@ __device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsi
   }
 #pragma unroll
   for (int j = 0; j < K; ++j) l.insert(s.op[j], acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+  return true;
 }
 
 // The enumerator's tables (suffix sums E, per-location Pauli counts / ops / code lists, tile
@@ -238,7 +244,8 @@ __device__ __forceinline__ void qec_jit_enum_gen(const QecEnumDev &E, const unsi
 // shared memory against ~300+ from L2.
 extern "C" __global__ void __launch_bounds__(QEC_JIT_T, QEC_JIT_MINB)
 qec_jit_kernel(const QecOutDev O, const QecEnumDev Eg, const long long lo, const long long hi,
-               uint32_t *__restrict__ scratch, const int tab_in_smem) {
+               uint32_t *__restrict__ scratch, const int tab_in_smem, const int max_seg,
+               long long *__restrict__ redo_list, unsigned int *__restrict__ redo_count) {
   extern __shared__ __align__(16) uint32_t qec_smem[];
   uint32_t *s_tally = qec_smem;
   uint32_t *w_tally = s_tally + (threadIdx.x >> 5) * QEC_JIT_NC;  // this warp's row
@@ -268,7 +275,7 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev Eg, const long long lo, const
   unsigned long long nz = 0;
   for (long long ch = blockIdx.x; ch * QEC_JIT_T < O.n_words; ch += gridDim.x) {
     const long long w = ch * QEC_JIT_T + threadIdx.x;
-    const bool valid = w < O.n_words;
+    bool valid = w < O.n_words;
     QecEvList l;
     l.p = ev; l.es = es; l.n = 0; l.bmw = bmw; l.last = 0u;
 #pragma unroll
@@ -276,7 +283,13 @@ qec_jit_kernel(const QecOutDev O, const QecEnumDev Eg, const long long lo, const
     if (valid) {
       const long long r0 = lo + 32 * w;
       const int nv = (int)min((long long)32, hi - r0);
-      qec_jit_enum_gen<QEC_JIT_ORDER>(E, (unsigned long long)r0, nv, l);
+      if (!qec_jit_enum_gen<QEC_JIT_ORDER>(E, (unsigned long long)r0, nv, l, max_seg)) {
+        // deferred: this lane word runs empty here (zero frame, no stores, nothing tallied)
+        redo_list[atomicAdd(redo_count, 1u)] = w;
+        valid = false;
+#pragma unroll
+        for (int k = 0; k < QEC_BMW; ++k) bmw[k * QEC_JIT_T] = 0u;
+      }
     }
     QecCurMask cur;
     cur.init(bmw, ev, es);

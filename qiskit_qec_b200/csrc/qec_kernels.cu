@@ -72,7 +72,9 @@ k_propagate_batch(const QecCircuitDev C, const QecOutDev O, const long long *__r
 template <int K, bool TALLY>
 __global__ void __launch_bounds__(256)
 k_enumerate(const QecCircuitDev C, const QecOutDev O, const QecEnumDev E, const long long lo,
-            const long long hi, uint32_t *__restrict__ scratch) {
+            const long long hi, uint32_t *__restrict__ scratch,
+            const long long *__restrict__ word_list, const unsigned int *__restrict__ list_count,
+            const long long count_paths) {
   uint32_t *sm = smem_base();
   const int T = blockDim.x;
   uint32_t *fr = sm + threadIdx.x;
@@ -84,9 +86,13 @@ k_enumerate(const QecCircuitDev C, const QecOutDev O, const QecEnumDev E, const 
   const long long stride = (long long)gridDim.x * T;
   uint32_t *ev = scratch + (long long)blockIdx.x * T + threadIdx.x;
   unsigned long long nz = 0;
-  for (long long ch = blockIdx.x; ch * T < O.n_words; ch += gridDim.x) {
-    const long long w = ch * T + threadIdx.x;
-    const bool valid = w < O.n_words;
+  // items: every lane word of the range, or (word_list) the lane words the specialised
+  // kernel deferred to this one
+  const long long n_items = word_list ? (long long)*list_count : O.n_words;
+  for (long long ch = blockIdx.x; ch * T < n_items; ch += gridDim.x) {
+    const long long it = ch * T + threadIdx.x;
+    const bool valid = it < n_items;
+    const long long w = !valid ? 0 : (word_list ? word_list[it] : it);
     int n_ev = 0;
     if (valid) {
       const long long r0 = lo + 32 * w;
@@ -116,7 +122,7 @@ k_enumerate(const QecCircuitDev C, const QecOutDev O, const QecEnumDev E, const 
     qec_propagate_word<TALLY>(C, fr, T, ev, stride, n_ev, valid, w, O, s_tally, any);
     if (TALLY) nz += __popc(any);
   }
-  if (TALLY) flush_tally(C, O, s_tally, nullptr, false, nz, hi - lo);
+  if (TALLY) flush_tally(C, O, s_tally, nullptr, false, nz, count_paths);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -298,21 +304,26 @@ void qec_launch_batch(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCir
 template <int K>
 static void launch_enum_k(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
                           const QecOutDev &O, const QecEnumDev &E, long long lo, long long hi,
-                          uint32_t *scratch) {
+                          uint32_t *scratch, const long long *word_list,
+                          const unsigned int *list_count) {
+  const long long count_paths = word_list ? 0 : hi - lo;  // (a deferred-word pass adds no path count)
   if (O.tally)
-    k_enumerate<K, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch);
+    k_enumerate<K, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch,
+                                                                    word_list, list_count, count_paths);
   else
-    k_enumerate<K, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch);
+    k_enumerate<K, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(C, O, E, lo, hi, scratch,
+                                                                     word_list, list_count, count_paths);
 }
 
 void qec_launch_enumerate(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
                           const QecOutDev &O, const QecEnumDev &E, long long lo, long long hi,
-                          uint32_t *scratch) {
+                          uint32_t *scratch, const long long *word_list,
+                          const unsigned int *list_count) {
   switch (E.order) {
-    case 1: launch_enum_k<1>(cfg, stream, C, O, E, lo, hi, scratch); break;
-    case 2: launch_enum_k<2>(cfg, stream, C, O, E, lo, hi, scratch); break;
-    case 3: launch_enum_k<3>(cfg, stream, C, O, E, lo, hi, scratch); break;
-    default: launch_enum_k<4>(cfg, stream, C, O, E, lo, hi, scratch); break;
+    case 1: launch_enum_k<1>(cfg, stream, C, O, E, lo, hi, scratch, word_list, list_count); break;
+    case 2: launch_enum_k<2>(cfg, stream, C, O, E, lo, hi, scratch, word_list, list_count); break;
+    case 3: launch_enum_k<3>(cfg, stream, C, O, E, lo, hi, scratch, word_list, list_count); break;
+    default: launch_enum_k<4>(cfg, stream, C, O, E, lo, hi, scratch, word_list, list_count); break;
   }
 }
 

@@ -15,7 +15,8 @@ void qec_launch_batch(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCir
                       const QecOutDev &O, const long long *ev_off, const uint32_t *ev);
 void qec_launch_enumerate(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
                           const QecOutDev &O, const QecEnumDev &E, long long lo, long long hi,
-                          uint32_t *scratch);
+                          uint32_t *scratch, const long long *word_list = nullptr,
+                          const unsigned int *list_count = nullptr);
 void qec_launch_sample(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCircuitDev &C,
                        const QecOutDev &O, const QecSamplerDev &S, long long word_lo,
                        long long n_shots, uint32_t *scratch, int cap, const QecSampleExport &X,
