@@ -121,3 +121,25 @@ def test_ineligible_circuit_falls_back_to_table_driven(capi):
     with jit_env("require"):
         with pytest.raises(RuntimeError, match="QEC_B200_JIT=require"):
             en.range(0, 1000)
+
+
+@pytest.mark.parametrize("name,order,max_seg", [("surf3", 2, 3), ("surf5", 2, 8), ("arc", 3, 2)])
+def test_enumerator_deferred_words_second_pass(capi, name, order, max_seg, monkeypatch):
+    """QEC_B200_JIT_MAXSEG: lane words that need more unranking segments than the limit are
+    listed by the specialised kernel and run by the table-driven kernel behind it; outcomes and
+    tallies must not change."""
+    circ = _circuit(name)
+    idx, labels, paulis = noise_inputs(circ, standard_depolarizing_model())
+    with jit_env("require"):
+        g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        en = make_enumerator(capi, g, order, idx, paulis)
+        n = en.num_paths()
+        lo, hi = max(0, n // 3 - 17), min(n, n // 3 + 150_000)
+        monkeypatch.delenv("QEC_B200_JIT_MAXSEG", raising=False)
+        b0, t0 = en.range(lo, hi, want_tally=True)
+        monkeypatch.setenv("QEC_B200_JIT_MAXSEG", str(max_seg))
+        b1, t1 = en.range(lo, hi, want_tally=True)
+        _, t2 = en.range(lo, hi, want_bits=False, want_tally=True)
+    np.testing.assert_array_equal(b1, b0)
+    np.testing.assert_array_equal(t1, t0)
+    np.testing.assert_array_equal(t2, t0)
