@@ -916,6 +916,10 @@ static int sampler_plan_jit(qec_sampler *s) {
       int fit = (int)((per_cta - fixed) / ((size_t)4 * pl.threads)) / 4 * 4;
       if (fit >= want || (fit >= least && (segs == 16 || seg_env > 0))) {
         capw = std::min(fit, want);
+        {  // test hook: a deliberately short queue exercises the overflow -> table-driven re-run
+          const int forced = env_int("QEC_B200_JIT_CAPW", 0);
+          if (forced >= 8 && forced < capw) capw = forced / 4 * 4;
+        }
         if ((capw / 4) % 2 == 0) capw -= 4;  // odd number of 16-byte units per lane word: no bank pile-up
         pl.min_blocks = minb;
         pl.segments = NS;

@@ -143,3 +143,25 @@ def test_enumerator_deferred_words_second_pass(capi, name, order, max_seg, monke
     np.testing.assert_array_equal(b1, b0)
     np.testing.assert_array_equal(t1, t0)
     np.testing.assert_array_equal(t2, t0)
+
+
+def test_sampler_queue_overflow_reruns_on_table_driven(capi, monkeypatch):
+    """A lane word that draws more faults than its shared-memory queue holds raises the
+    overflow flag; the host entry point re-runs the call on the table-driven kernel (the RNG
+    is counter based, so the re-run draws the same faults).  QEC_B200_JIT_CAPW shortens the
+    queue to force this."""
+    circ = _circuit("surf3")
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.02))
+    n = 200_000
+    with jit_env("0"):
+        g0 = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        s0, _ = make_sampler(capi, g0, idx, labels, lw, lp, seed=77)
+        b0, t0, _, _ = s0.sample(0, n, want_tally=True)
+    monkeypatch.setenv("QEC_B200_JIT_CAPW", "12")
+    with jit_env("1"):
+        g1 = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        s1, _ = make_sampler(capi, g1, idx, labels, lw, lp, seed=77)
+        b1, t1, _, _ = s1.sample(0, n, want_tally=True)
+        assert "table-driven" in capi.last_kernel() and "more events" in capi.last_kernel()
+    np.testing.assert_array_equal(b1, b0)
+    np.testing.assert_array_equal(t1, t0)
