@@ -107,8 +107,38 @@ def philox(counter, key):
     return list(c)
 
 
+_batch_cache = {}
+
+
+def sample_batch(tables: np.ndarray, batch: int, cap: int = 1 << 16):
+    """Accepted faults of one batch of the linear-response draw order: int array [n][3] of
+    (sorted location, shot in batch, digit), in stream order."""
+    ev = np.zeros(3 * cap, dtype=np.uint32)
+    n = lib().orc_sample_batch(_p(tables), C.c_uint64(batch), _p(ev), C.c_int(cap))
+    if n < 0:
+        raise ValueError("tables are not those of a linear-response sampler")
+    if n > cap:
+        return sample_batch(tables, batch, n)
+    return ev[:3 * n].reshape(n, 3).copy()
+
+
 def sample_word(tables: np.ndarray, gw: int, nv: int = 32, cap: int = 4096):
-    """Fault events (location << 14 | bit << 9 | digit) of global 32-shot word ``gw``."""
+    """Fault events (location << 14 | bit << 9 | digit) of global 32-shot word ``gw`` in slot
+    order (sorted location, shot), for whichever draw order the tables describe."""
+    if int(tables[7]) & 2:
+        lgb = (int(tables[7]) >> 8) & 255
+        batch, wb = gw >> (lgb - 5), gw & ((1 << (lgb - 5)) - 1)
+        key = (tables.tobytes()[:64], int(tables.sum()), batch)
+        if key not in _batch_cache:
+            if len(_batch_cache) > 8:
+                _batch_cache.clear()
+            _batch_cache[key] = sample_batch(tables, batch)
+        ev = _batch_cache[key]
+        B, K1, L = int(tables[0]), int(tables[1]), int(tables[3])
+        slloc = tables[8 + K1 + B + L: 8 + K1 + B + 2 * L]
+        sel = ev[((ev[:, 1] >> 5) == wb) & ((ev[:, 1] & 31) < nv)]
+        sel = sel[np.lexsort((sel[:, 1] & 31, sel[:, 0]))]
+        return ((slloc[sel[:, 0]] << 14) | ((sel[:, 1] & 31) << 9) | sel[:, 2]).astype(np.uint32)
     ev = np.zeros(cap, dtype=np.uint32)
     n = lib().orc_sample_word(_p(tables), C.c_uint64(gw), C.c_int(nv), _p(ev), C.c_int(cap))
     if n > cap:

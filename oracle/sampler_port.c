@@ -78,3 +78,48 @@ int orc_sample_word(const uint32_t *tab, uint64_t gw, int nv, uint32_t *ev_out, 
   }
   return n;
 }
+
+/*
+ * Draw order of the linear-response sampler (qec_linear.cu): batches of 2^lgb shots, slot =
+ * sorted location << lgb | shot in batch, the slot space cut into n_streams equal ranges, one
+ * Philox stream (counter = batch lo, batch hi, draw index, 0x4C000000 | stream) per range.
+ * A draw advances by a * B + b + 1 slots to a candidate fault, or -- when the first-level
+ * table is exhausted (a == K1) -- by K1 * B slots without one.  Writes the accepted faults of
+ * batch `batch` as triples (sorted location, shot in batch, digit) in stream order; returns
+ * their number (may exceed cap).  The same tables as above; tab[7] carries lgb and n_streams.
+ */
+int orc_sample_batch(const uint32_t *tab, uint64_t batch, uint32_t *ev_out, int cap) {
+  const uint32_t B = tab[0], K1 = tab[1], ncls = tab[2], L = tab[3], np = tab[4];
+  const uint32_t k0 = tab[5], k1 = tab[6];
+  const uint32_t lgb = (tab[7] >> 8) & 255u, ns = tab[7] >> 16;
+  const uint32_t *T1 = tab + 8, *T2 = T1 + K1, *slop = T2 + B, *slloc = slop + L;
+  const uint32_t *slcls = slloc + L, *cls_acc = slcls + L, *cls_always = cls_acc + ncls;
+  const uint32_t *cls_off = cls_always + ncls, *cdf = cls_off + ncls + 1;
+  (void)np;
+  if (!(tab[7] & 2u)) return -1;
+  const int64_t n_slots = (int64_t)L << lgb;
+  const int64_t slen = (n_slots + ns - 1) / ns;
+  int n = 0;
+  for (uint32_t s = 0; s < ns; ++s) {
+    const int64_t start = (int64_t)s * slen;
+    const int64_t end = start + slen < n_slots ? start + slen : n_slots;
+    int64_t pos = start - 1;
+    for (uint32_t draw = 0; pos < end; ++draw) {
+      uint32_t c[4] = {(uint32_t)batch, (uint32_t)(batch >> 32), draw, 0x4C000000u | s};
+      philox4x32_10(c, k0, k1);
+      const uint32_t a = count_greater(T1, K1, c[0]);
+      if (a == K1) { pos += (int64_t)K1 * B; continue; }
+      pos += (int64_t)a * B + count_greater(T2 + 1, B - 1, c[1]) + 1;
+      if (pos >= end) break;
+      const uint32_t sl = (uint32_t)(pos >> lgb), shot = (uint32_t)(pos & ((1u << lgb) - 1u));
+      const uint32_t cls = slcls[sl];
+      if (!cls_always[cls] && c[2] >= cls_acc[cls]) continue;
+      const uint32_t base = cls_off[cls], npc = cls_off[cls + 1] - base;
+      uint32_t d = 0;
+      while (d + 1 < npc && c[3] >= cdf[base + d]) ++d;
+      if (n < cap) { ev_out[3 * n] = sl; ev_out[3 * n + 1] = shot; ev_out[3 * n + 2] = d; }
+      ++n;
+    }
+  }
+  return n;
+}

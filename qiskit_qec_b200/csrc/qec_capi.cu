@@ -863,6 +863,18 @@ struct qec_sampler {
   std::vector<uint32_t> slinf;
   uint32_t *d_slinf = nullptr;
   int last_cap = 0;  // event capacity of the kernel that served the latest launches
+  // linear-response path (qec_linear.cu): the default when the circuit is eligible
+  struct Lin {
+    bool eligible = false;
+    std::string why;
+    int ctas = 1;
+    QecLaunchCfg cfg{};
+    QecLinDev dev{};
+    std::vector<uint32_t> info, sigdesc, loc2sl;
+    std::vector<uint16_t> siglist;
+    uint32_t *d_info = nullptr, *d_sigdesc = nullptr;
+    uint16_t *d_siglist = nullptr;
+  } lin;
 };
 
 static int sampler_plan_jit(qec_sampler *s) {
@@ -952,6 +964,131 @@ static int sampler_plan_jit(qec_sampler *s) {
   if (group < 2) group = 0;
   pl.group = env_int("QEC_B200_JIT_GROUP_SAMPLER", group);
   pl.eligible = true;
+  return 0;
+}
+
+// Linear-response sampler: fault signatures (one frame propagation per single fault, on the
+// GPU, through the same kernel that serves qec_propagate_batch), batch / stream geometry and
+// the shared-memory budget.  QEC_B200_SAMPLER=frame keeps the frame-propagation kernels.
+static int sampler_plan_linear(qec_sampler *s) {
+  qec_sampler::Lin &ln = s->lin;
+  qec_circuit *c = s->c;
+  const char *mode = std::getenv("QEC_B200_SAMPLER");
+  if (mode && !strcmp(mode, "frame")) { ln.why = "QEC_B200_SAMPLER=frame"; return 0; }
+  if (s->dev.n_slots <= 0) { ln.why = "no fault can occur"; return 0; }
+  if (s->L >= 65536 || s->n_classes > 1024 || c->nc > 65535 || c->nc < 1) {
+    ln.why = "too many locations / classes / clbits for the packed tables";
+    return 0;
+  }
+  // faults f = (sorted location, digit); info[sl] = first fault | class << 21 | always << 31
+  std::vector<int64_t> path_off;
+  std::vector<int32_t> fop;
+  std::vector<uint8_t> fpauli;
+  ln.info.clear();
+  for (int sl = 0; sl < s->L; ++sl) {
+    const uint32_t cls = s->slcls[sl], o = s->cls_off[cls], n = s->cls_off[cls + 1] - o;
+    if (fop.size() + n >= (1u << 21)) { ln.why = "more than 2^21 distinct faults"; return 0; }
+    ln.info.push_back((uint32_t)fop.size() | (cls << 21) | (s->cls_always[cls] ? (1u << 31) : 0u));
+    for (uint32_t d = 0; d < n; ++d) {
+      fop.push_back((int32_t)s->slop[sl]);
+      fpauli.push_back(s->codes[o + d]);
+    }
+  }
+  const int64_t F = (int64_t)fop.size();
+  path_off.resize(F + 1);
+  for (int64_t f = 0; f <= F; ++f) path_off[f] = f;
+  const int64_t FW = (F + 31) / 32;
+  std::vector<uint32_t> bits((size_t)c->nc * FW);
+  int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), fpauli.data(), bits.data(), nullptr);
+  if (rc) return rc;
+  std::vector<std::vector<uint16_t>> lists((size_t)F);
+  for (int cb = 0; cb < c->nc; ++cb)
+    for (int64_t fw = 0; fw < FW; ++fw)
+      for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u)
+        lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
+  ln.sigdesc.clear();
+  ln.siglist.clear();
+  for (int64_t f = 0; f < F; ++f) {
+    const size_t len = lists[f].size();
+    if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
+      ln.why = "fault signatures too long for the packed descriptor";
+      return 0;
+    }
+    ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
+    ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
+  }
+  const uint32_t n_sig = (uint32_t)ln.siglist.size();
+  ln.siglist.resize((n_sig + 2u) & ~1u, 0);  // whole 32-bit words, never empty
+  ln.loc2sl.assign(s->L, 0);
+  for (int sl = 0; sl < s->L; ++sl) ln.loc2sl[s->slloc[sl]] = (uint32_t)sl;
+
+  // geometry: the largest batch whose accumulator fits, two CTAs per SM when they fit with
+  // 4096-shot batches (one streams its accumulator out while the other draws)
+  const DevInfo &di = *c->info;
+  const int T = env_int("QEC_B200_LIN_THREADS", 512);
+  if (T < 256 || T > 1024 || (T & (T - 1))) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_THREADS must be 256, 512 or 1024");
+  int maxlgb = 13;
+  while (maxlgb > 8 && ((long long)s->L << maxlgb) >= (1ll << 30)) --maxlgb;
+  const int cand[][2] = {{2, 12}, {1, 13}, {1, 12}, {1, 11}, {1, 10}, {1, 9}, {1, 8}};
+  const int f_ctas = env_int("QEC_B200_LIN_CTAS", 0), f_lgb = env_int("QEC_B200_LIN_LGB", 0);
+  const int f_sig = env_int("QEC_B200_LIN_SIGSMEM", -1);
+  int lgb = 0, ctas = 0, info_s = 0, sig_s = 0;
+  size_t smem = 0;
+  auto words = [&](int lg, int is, int ss) {
+    return qec_lin_smem_words(c->nc, lg, T, s->K1, s->B, (uint32_t)s->L, (uint32_t)s->n_classes,
+                              s->lgP, (uint32_t)F, n_sig, is, ss) * 4 + 16;
+  };
+  auto try_cfg = [&](int ct, int lg) {
+    if (lg > maxlgb || (1 << (lg - 5)) > T) return false;
+    size_t per = di.smem_sm / ct - 1024;
+    if (per > di.smem_optin) per = di.smem_optin;
+    if (words(lg, 0, 0) > per) return false;
+    ctas = ct; lgb = lg;
+    info_s = words(lg, 1, 0) <= per;
+    sig_s = info_s && words(lg, 1, 1) <= per && f_sig != 0;
+    if (f_sig == 1 && !sig_s) return false;
+    smem = words(lg, info_s, sig_s);
+    return true;
+  };
+  bool found = false;
+  if (f_ctas > 0 && f_lgb > 0) found = try_cfg(f_ctas, f_lgb);
+  else for (const auto &cd : cand) if ((found = try_cfg(cd[0], cd[1]))) break;
+  if (!found) { ln.why = "the outcome accumulator of a 256-shot batch does not fit in shared memory"; return 0; }
+  // streams per batch: the most (power of two, at most 64) that still carry >= 128 faults each
+  double psum = 0;
+  for (double p : s->loc_p) psum += p;
+  const double mean_batch = psum * (double)(1 << lgb);
+  int ns = 64;
+  while (ns > 1 && mean_batch / ns < 128.0) ns >>= 1;
+  ns = env_int("QEC_B200_LIN_STREAMS", ns);
+  if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
+
+  if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
+      (rc = upload(ln.siglist, &ln.d_siglist)))
+    return rc;
+  {
+    const int e = qec_lin_set_smem_attr(smem);
+    if (e) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)e));
+  }
+  QecLinDev &d = ln.dev;
+  d.nc = c->nc; d.L = s->L; d.lgb = lgb; d.n_streams = ns;
+  d.n_slots = (uint32_t)s->L << lgb;
+  d.slen = (d.n_slots + (uint32_t)ns - 1u) / (uint32_t)ns;
+  d.B = s->B; d.K1 = s->K1;
+  d.gshift = 32;
+  while ((1u << (32 - d.gshift)) < 2u * s->B) --d.gshift;
+  d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
+  d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
+  d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;
+  d.sigdesc = ln.d_sigdesc; d.siglist = ln.d_siglist;
+  d.n_faults = (uint32_t)F; d.n_sig = n_sig;
+  d.info_in_smem = info_s; d.sig_in_smem = sig_s;
+  d.k0 = (uint32_t)s->seed; d.k1 = (uint32_t)(s->seed >> 32);
+  ln.ctas = ctas;
+  ln.cfg.block = T;
+  ln.cfg.grid = di.sms * ctas;
+  ln.cfg.smem = smem;
+  ln.eligible = true;
   return 0;
 }
 
@@ -1090,7 +1227,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
   d.slloc = s->d_slloc; d.slcls = s->d_slcls; d.cls_acc = s->d_cls_acc;
   d.cls_always = s->d_cls_always; d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.codes = s->d_codes;
   d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32);
-  if ((rc = sampler_plan_jit(s))) {
+  if ((rc = sampler_plan_jit(s)) || (rc = sampler_plan_linear(s))) {
     qec_sampler_destroy(s);
     return rc;
   }
@@ -1103,7 +1240,7 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   cudaSetDevice(s->c->device);
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
-                  s->d_seg_end};
+                  s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1115,7 +1252,13 @@ extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, 
   std::vector<uint32_t> v;
   const uint32_t ncls = (uint32_t)s->n_classes, np = (uint32_t)s->cdf.size();
   v.insert(v.end(), {s->B, s->K1, ncls, (uint32_t)s->L, np, (uint32_t)s->seed,
-                     (uint32_t)(s->seed >> 32), (uint32_t)(s->dev.n_slots > 0)});
+                     (uint32_t)(s->seed >> 32),
+                     // bit 0: some fault can occur; bit 1: linear-response draw order (batches
+                     // of 2^lgb shots, n_streams streams each), lgb << 8, n_streams << 16
+                     (uint32_t)(s->dev.n_slots > 0) |
+                         (s->lin.eligible ? (2u | ((uint32_t)s->lin.dev.lgb << 8) |
+                                                 ((uint32_t)s->lin.dev.n_streams << 16))
+                                          : 0u)});
   v.insert(v.end(), s->T1.begin(), s->T1.end());
   v.insert(v.end(), s->T2.begin(), s->T2.end());
   v.insert(v.end(), s->slop.begin(), s->slop.end());
@@ -1141,6 +1284,22 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
   O.frame = nullptr;
   O.tally = (unsigned long long *)d_tally;
   O.n_words = (n_shots + 31) / 32;
+  if (s->lin.eligible) {
+    const QecLinDev &d = s->lin.dev;
+    QecLaunchCfg cfg = s->lin.cfg;
+    const long long n_batches = ((shot_lo + n_shots - 1) >> d.lgb) - (shot_lo >> d.lgb) + 1;
+    if (cfg.grid > n_batches) cfg.grid = (int)n_batches;
+    time_begin(s->c, stream);
+    qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
+    time_end(s->c, stream);
+    CU(cudaGetLastError());
+    s->last_cap = 0;
+    g_last_kernel = "sample:linear batch=" + std::to_string(1 << d.lgb) + " streams=" +
+                    std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
+                    std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
+                    (d.sig_in_smem ? " sig=smem" : " sig=global");
+    return 0;
+  }
   if (s->jit.eligible && !X.cnt) {
     QecJitSpec extra;
     extra.K1 = s->K1; extra.B = s->B; extra.L = (unsigned)s->L; extra.n_classes = (unsigned)s->n_classes;
@@ -1244,6 +1403,7 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
     if ((rc = s->xcnt.ensure((size_t)n_words * 4))) return rc;
     if ((rc = s->xev.ensure((size_t)n_words * fault_cap * 4))) return rc;
     X.cnt = (uint32_t *)s->xcnt.p; X.ev = (uint32_t *)s->xev.p; X.cap = fault_cap;
+    CU(cudaMemsetAsync(s->xcnt.p, 0, (size_t)n_words * 4, 0));  // the linear kernel counts with atomics
   }
   for (int attempt = 0;; ++attempt) {
     if (tally) CU(cudaMemsetAsync(c->tally.p, 0, tl * 8, 0));
@@ -1276,6 +1436,18 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
     if (fault_cap_needed) *fault_cap_needed = (int)mx;
     if (mx > (uint32_t)fault_cap)
       return fail(QEC_ERR_LIMIT, "fault export truncated: %u events in one word, fault_cap %d", mx, fault_cap);
+    if (s->lin.eligible) {
+      // the linear kernel appends a word's events in arrival order: put them in slot order
+      // (sorted location, shot), the order the frame kernels export
+      const std::vector<uint32_t> &l2s = s->lin.loc2sl;
+      for (int64_t w = 0; w < n_words; ++w) {
+        uint32_t *e = fault_ev + (size_t)w * fault_cap;
+        std::sort(e, e + fault_cnt[w], [&](uint32_t a, uint32_t b) {
+          const uint32_t ka = (l2s[a >> 14] << 5) | ((a >> 9) & 31u), kb = (l2s[b >> 14] << 5) | ((b >> 9) & 31u);
+          return ka < kb;
+        });
+      }
+    }
   }
   return 0;
 }

@@ -97,6 +97,47 @@ struct QecSamplerDev {
   uint32_t k0, k1;            // Philox key = seed
 };
 
+// Linear-response sampler (qec_linear.cu).  Every gate of the path (cx, h, s, reset, measure,
+// Pauli injection) is GF(2)-linear in the frame, so the outcome of a shot is the XOR of the
+// outcome signatures of its faults.  The signature of fault f = (sorted location sl, digit d)
+// is the list of clbits it flips, computed once per sampler by the frame-propagation kernel.
+//   batch  = 2^lgb consecutive shots; its slot space is (sorted location, shot in batch),
+//            location major: slot = sl << lgb | shot
+//   stream = one of n_streams equal slot ranges of a batch; a warp walks a stream with 32
+//            geometric gaps per step (Philox counter = batch, draw index, stream) and a warp
+//            prefix sum, so every lane carries one fault per step
+struct QecLinDev {
+  int nc, L, lgb, n_streams;
+  uint32_t slen;            // slots per stream = ceil(n_slots / n_streams)
+  uint32_t n_slots;         // L << lgb  (< 2^30)
+  uint32_t B, K1, gshift;   // gap tables as in QecSamplerDev; 2B = 2^(32 - gshift) guide buckets
+  uint32_t n_classes, lgP;
+  const uint32_t *T1, *T2;
+  const uint32_t *info;     // [L] first fault index of sl | class << 21 | cls_always << 31
+  const uint32_t *cls_acc, *cls_off, *cdf;
+  const uint32_t *slloc;    // [L] original location index (fault export)
+  const uint32_t *sigdesc;  // [n_faults] offset into siglist | length << 22
+  const uint16_t *siglist;  // clbits flipped by each fault
+  uint32_t n_faults, n_sig;
+  int info_in_smem, sig_in_smem;
+  uint32_t k0, k1;
+};
+
+// shared-memory words of the linear sampler's CTA (T threads)
+static inline __host__ __device__ size_t qec_lin_smem_words(int nc, int lgb, int T, uint32_t K1,
+                                                            uint32_t B, uint32_t L, uint32_t ncls,
+                                                            uint32_t lgP, uint32_t n_faults,
+                                                            uint32_t n_sig, int info_in_smem,
+                                                            int sig_in_smem) {
+  const size_t BW = (size_t)1 << (lgb - 5);
+  size_t w = (size_t)nc * BW + ((size_t)1 << (lgb - 1)) + BW;  // acc, per-shot fault counts, any
+  w += (size_t)(T / 32) * nc + 64;                              // per-warp tallies, histogram
+  w += (size_t)K1 + 2u * B + 2u * ncls + ((size_t)ncls << lgP); // T1 T2 guide cacc cnp1 cdf
+  if (info_in_smem) w += L;
+  if (sig_in_smem) w += (size_t)n_faults + (n_sig + 1u) / 2u;
+  return w;
+}
+
 struct QecSampleExport {
   uint32_t *cnt;  // [n_words] or nullptr
   uint32_t *ev;   // [n_words][cap]

@@ -21,6 +21,11 @@ void qec_launch_sample(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCi
                        const QecOutDev &O, const QecSamplerDev &S, long long word_lo,
                        long long n_shots, uint32_t *scratch, int cap, const QecSampleExport &X,
                        uint32_t *overflow_flag);
+// linear-response sampler (qec_linear.cu)
+void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
+                           const QecLinDev &S, long long shot_lo, long long n_shots,
+                           const QecSampleExport &X);
+int qec_lin_set_smem_attr(size_t smem);
 void qec_launch_outcome_hist(cudaStream_t stream, const uint32_t *bits, int nc, long long n_paths,
                              unsigned long long *keys, unsigned long long *counts,
                              long long table_cap);

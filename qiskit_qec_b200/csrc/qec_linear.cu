@@ -1,0 +1,339 @@
+// qec_linear.cu -- linear-response fault sampler for sm_100a (FaultSampler::sample, bulk path).
+//
+// Frame propagation is linear over GF(2): cx / h / s are linear maps of the frame, reset is a
+// projection, measure reads one frame bit, a fault XORs a Pauli in (reference
+// errorpropagator.cpp:211-254, :272-310).  So
+//     outcome(shot) = XOR over the shot's faults f of signature(f),
+// signature(f) = the outcome of the circuit with the single fault f, which qec_capi.cu
+// computes once per sampler with the frame-propagation kernel (k_propagate_batch).  A shot at
+// p = 1e-3 carries ~0.8 faults, each flipping a handful of clbits, against ~760 gates per shot
+// for explicit propagation: this kernel never touches the gate list.
+//
+// One CTA owns a batch of 2^lgb shots: a bit-sliced accumulator acc[nc][batch / 32] in shared
+// memory (the layout of the packed output).  Warps walk the batch's fault streams -- 32
+// geometric gaps per step, one warp prefix sum, every lane ends up with one fault -- and XOR
+// the fault's clbit list into the accumulator with shared-memory atomics.  After a CTA barrier
+// all threads stream the accumulator out (coalesced 128-byte rows), count ones per clbit, and
+// clear it for the next batch.
+#include <cuda_runtime.h>
+#include "qec_kernels.cuh"
+
+namespace {
+
+struct LinSmem {
+  uint32_t *acc, *cnt, *anyw, *tally, *hist, *T1, *T2, *cacc, *cnp1, *cdf;
+  uint16_t *G;
+  const uint32_t *info, *desc;
+  const uint16_t *list;
+};
+
+__device__ __forceinline__ LinSmem lin_carve(uint32_t *sm, const QecLinDev &S, int T) {
+  LinSmem m;
+  const size_t BW = (size_t)1 << (S.lgb - 5);
+  m.acc = sm;
+  m.cnt = m.acc + (size_t)S.nc * BW;
+  m.anyw = m.cnt + ((size_t)1 << (S.lgb - 1));
+  m.tally = m.anyw + BW;
+  m.hist = m.tally + (size_t)(T / 32) * S.nc;
+  m.T1 = m.hist + 64;
+  m.T2 = m.T1 + S.K1;
+  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B);
+  m.cacc = m.T2 + 2u * S.B;
+  m.cnp1 = m.cacc + S.n_classes;
+  m.cdf = m.cnp1 + S.n_classes;
+  uint32_t *p = m.cdf + ((size_t)S.n_classes << S.lgP);
+  if (S.info_in_smem) { m.info = p; p += S.L; } else m.info = S.info;
+  if (S.sig_in_smem) {
+    m.desc = p;
+    p += S.n_faults;
+    m.list = reinterpret_cast<const uint16_t *>(p);
+  } else {
+    m.desc = S.sigdesc;
+    m.list = S.siglist;
+  }
+  return m;
+}
+
+// shared-memory accesses by 32-bit shared-window address: the hot loops do their own address
+// arithmetic (one IMAD per access) instead of 64-bit generic pointers
+__device__ __forceinline__ void red_xor_s(uint32_t addr, uint32_t v) {
+  asm volatile("red.shared.xor.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_s(uint32_t addr, uint32_t v) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_s(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_s16(uint32_t addr) {
+  uint32_t v;
+  asm volatile("{ .reg .u16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_s(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// Pauli digit: entries of the class's cdf (padded to 2^LGP with 0xFFFFFFFF) that are <= r
+template <int LGP>
+__device__ __forceinline__ uint32_t lin_digit(uint32_t cdf_s, uint32_t r) {
+  uint32_t d = 0;
+#pragma unroll
+  for (int k = LGP - 1; k >= 0; --k)
+    if (ld_s(cdf_s + ((d + (1u << k) - 1u) << 2)) <= r) d += 1u << k;
+  return d;
+}
+
+// One thread's share of the accumulator read-out: `n_it` row pieces, `a` / `po` / `tl` walk
+// the accumulator column, the output column and this warp's tally row.
+template <bool TALLY, bool BITS, bool FULL>
+__device__ __forceinline__ uint32_t lin_out_rows(int n_it, uint32_t a, const uint32_t a_step,
+                                                 uint32_t *po, const long long po_step, uint32_t tl,
+                                                 const uint32_t tl_step, const bool inr,
+                                                 const bool head, const uint32_t grp) {
+  uint32_t anyv = 0;
+#pragma unroll 2
+  for (; n_it > 0; --n_it, a += a_step, po += po_step, tl += tl_step) {
+    const uint32_t v = ld_s(a);
+    st_s(a, 0u);
+    if (BITS && inr) *po = v;
+    if (TALLY) {
+      anyv |= v;
+      int cnt = __popc(v);
+      if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+      else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+      if (head) st_s(tl, ld_s(tl) + (uint32_t)cnt);
+    }
+  }
+  return anyv;
+}
+
+template <bool TALLY, bool BITS>
+__global__ void __launch_bounds__(1024, 1)
+k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
+             const QecSampleExport X) {
+  extern __shared__ __align__(16) uint32_t qec_lin_smem[];
+  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
+  const LinSmem m = lin_carve(qec_lin_smem, S, T);
+  const int lgb = S.lgb, lgw = lgb - 5;
+  const uint32_t BATCH = 1u << lgb, BW = 1u << lgw;
+  const uint32_t P = 1u << S.lgP;
+
+  // ---- tables into shared memory, accumulators cleared
+  {
+    uint32_t *w = const_cast<uint32_t *>(m.info);
+    if (S.info_in_smem) for (uint32_t i = tid; i < (uint32_t)S.L; i += T) w[i] = S.info[i];
+    if (S.sig_in_smem) {
+      uint32_t *d = const_cast<uint32_t *>(m.desc);
+      for (uint32_t i = tid; i < S.n_faults; i += T) d[i] = S.sigdesc[i];
+      uint32_t *l = reinterpret_cast<uint32_t *>(const_cast<uint16_t *>(m.list));
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(S.siglist);  // padded to a word
+      for (uint32_t i = tid; i < (S.n_sig + 1u) / 2u; i += T) l[i] = src[i];
+    }
+  }
+  for (uint32_t i = tid; i < S.K1; i += T) m.T1[i] = S.T1[i];
+  for (uint32_t i = tid; i < S.B; i += T) m.T2[i] = S.T2[i];
+  for (uint32_t k = tid; k < 2u * S.B; k += T) {
+    // entries of T2[1..B) greater than the largest r of guide bucket k: where the scan for
+    // any r of the bucket may start
+    const uint32_t rmax = (k << S.gshift) | ((1u << S.gshift) - 1u);
+    m.G[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1u, rmax);
+  }
+  for (uint32_t c = tid; c < S.n_classes; c += T) {
+    m.cacc[c] = S.cls_acc[c];
+    m.cnp1[c] = S.cls_off[c + 1] - S.cls_off[c] - 1u;
+  }
+  for (uint32_t i = tid; i < (S.n_classes << S.lgP); i += T) {
+    const uint32_t c = i >> S.lgP, d = i & (P - 1u), o = S.cls_off[c], n = S.cls_off[c + 1] - o;
+    m.cdf[i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
+  }
+  {
+    const size_t nz = (size_t)S.nc * BW + (BATCH >> 1) + BW + (size_t)NW * S.nc + 64;
+    for (size_t i = tid; i < nz; i += T) m.acc[i] = 0u;  // acc, cnt, anyw, tally, hist are contiguous
+  }
+  __syncthreads();
+
+  const uint32_t t1_0 = m.T1[0], t1_1 = S.K1 > 1 ? m.T1[1] : 0u, t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
+  const uint32_t kb = S.K1 * S.B;
+  const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(m.acc);
+  const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(m.cnt);
+  const uint32_t cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
+  const uint32_t desc_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.desc) : 0u;
+  const uint32_t list_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.list) : 0u;
+  const uint32_t bw4 = 4u << lgw;  // bytes per accumulator row
+  uint32_t *w_tally = m.tally + (size_t)warp * S.nc;
+  unsigned long long nz_shots = 0;
+  const long long b0 = shot_lo >> lgb, b1 = (shot_lo + n_shots - 1) >> lgb;
+  const long long w_lo = shot_lo >> 5;
+
+  for (long long b = b0 + blockIdx.x; b <= b1; b += gridDim.x) {
+    const long long base_shot = b << lgb;
+    // shots of this batch inside the requested range: [slo, shi)
+    const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
+    const uint32_t shi = (uint32_t)min((long long)BATCH, shot_lo + n_shots - base_shot);
+    const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
+
+    // ---- draw the batch's faults, XOR their signatures into acc
+    for (int s = warp; s < S.n_streams; s += NW) {
+      const int start = (int)((uint32_t)s * S.slen);
+      const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
+      int pos = start - 1;
+      for (uint32_t it = 0; pos < end; ++it) {
+        const QecPhilox r = qec_philox(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
+                                       S.k0, S.k1);
+        // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
+        // next K1 * B slots -- exact by memorylessness)
+        uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
+        if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
+        uint32_t g = m.G[r.c[1] >> S.gshift];
+        while (g < S.B - 1u && m.T2[1u + g] > r.c[1]) ++g;
+        const bool has = a < S.K1;
+        uint32_t incl = has ? a * S.B + g + 1u : kb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const int p = pos + (int)incl;
+        pos = __shfl_sync(0xFFFFFFFFu, p, 31);
+        // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
+        const uint32_t sl = (uint32_t)p >> lgb, shot = (uint32_t)p & (BATCH - 1u);
+        bool ok = has && p < end && shot >= slo && shot < shi;  // inside the requested range
+        uint32_t inf = 0, cls = 0;
+        if (ok) {
+          inf = m.info[sl];
+          cls = (inf >> 21) & 1023u;
+          ok = (inf >> 31) || r.c[2] < m.cacc[cls];  // class thinning
+        }
+        if (ok) {
+          const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
+          uint32_t d;
+          switch (S.lgP) {
+            case 0: d = 0; break;
+            case 1: d = lin_digit<1>(cd, r.c[3]); break;
+            case 2: d = lin_digit<2>(cd, r.c[3]); break;
+            case 3: d = lin_digit<3>(cd, r.c[3]); break;
+            case 4: d = lin_digit<4>(cd, r.c[3]); break;
+            default:
+              d = 0;
+              for (uint32_t step = P >> 1; step; step >>= 1)
+                if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
+          }
+          d = min(d, m.cnp1[cls]);
+          const uint32_t f = (inf & 0x1FFFFFu) + d;
+          const uint32_t colb = acc_s + ((shot >> 5) << 2);
+          const uint32_t msk = 1u << (shot & 31u);
+          if (S.sig_in_smem) {
+            const uint32_t desc = ld_s(desc_s + (f << 2));
+            uint32_t li = list_s + ((desc & 0x3FFFFFu) << 1);
+            for (uint32_t n = desc >> 22; n; --n, li += 2u) red_xor_s(colb + ld_s16(li) * bw4, msk);
+          } else {
+            const uint32_t desc = __ldg(S.sigdesc + f);
+            const uint16_t *li = S.siglist + (desc & 0x3FFFFFu);
+            for (uint32_t n = desc >> 22; n; --n, ++li) red_xor_s(colb + (uint32_t)__ldg(li) * bw4, msk);
+          }
+          if (TALLY) red_add_s(cnt_s + ((shot >> 1) << 2), 1u << ((shot & 1u) << 4));
+          if (X.cnt) {
+            const long long wr = ((base_shot + shot) >> 5) - w_lo;
+            const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+            if (k < (uint32_t)X.cap)
+              X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
+          }
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- stream the accumulator out: thread -> fixed word column wb, clbits c0, c0 + T/BW, ...
+    {
+      const uint32_t wb = (uint32_t)tid & (BW - 1u);
+      const long long w = ((b << lgw) + wb) - w_lo;
+      const bool inr = w >= 0 && w < O.n_words;
+      const uint32_t grp = BW < 32u ? BW : 32u;  // lanes of a warp that share one clbit
+      uint32_t anyv = 0;
+      // (pointer walks: one LDS / STS / STG, a popcount, a warp sum and lane 0's tally update
+      // per 32-word row piece)
+      const uint32_t rpp = (uint32_t)T >> lgw;  // rows per pass of the CTA
+      uint32_t c = (uint32_t)tid >> lgw;
+      uint32_t a = acc_s + ((uint32_t)tid << 2);
+      const uint32_t a_step = (uint32_t)T << 2;
+      uint32_t *po = O.bits + ((long long)c * O.n_words + (inr ? w : 0));
+      const long long po_step = (long long)rpp * O.n_words;
+      uint32_t tl = (uint32_t)__cvta_generic_to_shared(w_tally) + (c << 2);
+      const uint32_t tl_step = rpp << 2;
+      const bool head = (lane & (grp - 1u)) == 0u;
+      const int n_it = c < (uint32_t)S.nc ? (int)(((uint32_t)S.nc - c + rpp - 1u) / rpp) : 0;
+      if (grp == 32u) anyv = lin_out_rows<TALLY, BITS, true>(n_it, a, a_step, po, po_step, tl, tl_step, inr, head, grp);
+      else anyv = lin_out_rows<TALLY, BITS, false>(n_it, a, a_step, po, po_step, tl, tl_step, inr, head, grp);
+      if (TALLY) {
+        if (anyv) atomicOr(m.anyw + wb, anyv);
+        // faults-per-shot histogram from the 16-bit counters (two shots per word)
+        uint32_t h0 = 0, h1 = 0, h2 = 0;
+        for (uint32_t i = tid; i < (BATCH >> 1); i += T) {
+          const uint32_t cw = m.cnt[i];
+          m.cnt[i] = 0u;
+#pragma unroll
+          for (uint32_t h = 0; h < 2u; ++h) {
+            const uint32_t shot = 2u * i + h, k = (cw >> (16u * h)) & 0xFFFFu;
+            if (shot < slo || shot >= shi) continue;
+            if (k == 0u) ++h0;
+            else if (k == 1u) ++h1;
+            else if (k == 2u) ++h2;
+            else atomicAdd(m.hist + min(k, 63u), 1u);
+          }
+        }
+        h0 = __reduce_add_sync(0xFFFFFFFFu, h0);
+        h1 = __reduce_add_sync(0xFFFFFFFFu, h1);
+        h2 = __reduce_add_sync(0xFFFFFFFFu, h2);
+        if (lane == 0) {
+          atomicAdd(m.hist + 0, h0); atomicAdd(m.hist + 1, h1); atomicAdd(m.hist + 2, h2);
+        }
+      }
+    }
+    __syncthreads();
+    if (TALLY && (uint32_t)tid < BW) {
+      nz_shots += __popc(m.anyw[tid]);
+      m.anyw[tid] = 0u;
+    }
+  }
+
+  // ---- tallies: per-warp rows -> global (layout: QEC_TALLY_LEN in qec_b200.h)
+  if (TALLY) {
+    __syncthreads();
+    for (int off = 16; off > 0; off >>= 1) nz_shots += __shfl_down_sync(0xFFFFFFFFu, nz_shots, off);
+    if (lane == 0 && nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
+    for (int c = tid; c < S.nc; c += T) {
+      unsigned long long v = 0;
+      for (int k = 0; k < NW; ++k) v += m.tally[(size_t)k * S.nc + c];
+      if (v) atomicAdd(&O.tally[c], v);
+    }
+    for (int c = tid; c < 64; c += T)
+      if (m.hist[c]) atomicAdd(&O.tally[S.nc + 2 + c], (unsigned long long)m.hist[c]);
+    if (blockIdx.x == 0 && tid == 0) atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
+  }
+}
+
+}  // namespace
+
+int qec_lin_set_smem_attr(size_t smem) {
+  const int s = (int)smem;
+  cudaError_t e;
+#define QEC_SET(fn) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, s); \
+  if (e != cudaSuccess) return (int)e;
+  QEC_SET((k_sample_lin<true, true>)) QEC_SET((k_sample_lin<true, false>))
+  QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
+#undef QEC_SET
+  return 0;
+}
+
+void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
+                           const QecLinDev &S, long long shot_lo, long long n_shots,
+                           const QecSampleExport &X) {
+  const bool t = O.tally != nullptr, b = O.bits != nullptr;
+  if (t && b) k_sample_lin<true, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
+  else if (t) k_sample_lin<true, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
+  else if (b) k_sample_lin<false, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
+  else k_sample_lin<false, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
+}
