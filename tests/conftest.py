@@ -23,6 +23,15 @@ def ref():
 
 
 @pytest.fixture(scope="session")
+def port():
+    """The CPU restatement (oracle/): the checker, never the thing under test."""
+    from oracle import port as _port
+
+    _port.lib()
+    return _port
+
+
+@pytest.fixture(scope="session")
 def capi():
     """The ctypes binding of libqecb200.so with a usable GPU, or fail loudly."""
     from qiskit_qec_b200 import _capi

@@ -87,7 +87,8 @@ def test_enumerator_specialised_equals_table_driven(capi, name, order, windows):
 @pytest.mark.parametrize("name,p,n_shots", [("rep", 0.05, 40_000), ("surf3", 0.01, 100_000),
                                             ("surf5", 1e-3, 1_000_000), ("arc", 2e-3, 200_000),
                                             ("surf5", 1e-4, 300_000)])
-def test_sampler_specialised_equals_table_driven(capi, name, p, n_shots):
+def test_sampler_specialised_equals_table_driven(capi, name, p, n_shots, monkeypatch):
+    monkeypatch.setenv("QEC_B200_SAMPLER", "frame")  # the frame-propagation samplers, not the linear one
     circ = _circuit(name)
     idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(p))
     out = {}
@@ -150,6 +151,7 @@ def test_sampler_queue_overflow_reruns_on_table_driven(capi, monkeypatch):
     overflow flag; the host entry point re-runs the call on the table-driven kernel (the RNG
     is counter based, so the re-run draws the same faults).  QEC_B200_JIT_CAPW shortens the
     queue to force this."""
+    monkeypatch.setenv("QEC_B200_SAMPLER", "frame")
     circ = _circuit("surf3")
     idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.02))
     n = 200_000

@@ -1,0 +1,208 @@
+"""GPU parity of the linear-response sampler (qec_linear.cu).
+
+The kernel never walks the gate list: it XORs per-fault outcome signatures.  These tests pin
+that shortcut to explicit propagation:
+  * the premise -- every order-2 outcome of the frame kernels is the XOR of two order-1
+    outcomes -- over whole enumerations;
+  * every sampled shot: packed outcome == explicit propagation (CPU oracle) of the shot's
+    exported fault list, and the fault lists == the CPU restatement of the draw order;
+  * window / shard invariance, tallies vs bits, thinning with unequal class probabilities,
+    tiny p (first-level gap table exhausted), p close to 1;
+  * fault rates against the closed form, 5 sigma.
+test_gpu_parity.py::test_k3_replay_parity additionally replays the exported faults through the
+compiled reference's propagate()."""
+
+import numpy as np
+import pytest
+
+from qiskit_qec_b200.circuits import (arc_circuit, heavy_hex_27_arc_layout, repetition_code_circuit,
+                                      surface_code_circuit)
+from qiskit_qec_b200.noise import standard_depolarizing_model
+
+from helpers import make_enumerator, make_sampler, noise_inputs, sampler_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def _circuit(name):
+    if name == "rep":
+        return repetition_code_circuit(3, 2)
+    if name == "surf3":
+        return surface_code_circuit(3, 3)
+    if name == "surf5":
+        return surface_code_circuit(5, 5)
+    if name == "surf3x":
+        return surface_code_circuit(3, 2, basis="x")
+    if name == "surf7":
+        return surface_code_circuit(7, 3)
+    links, sched, color = heavy_hex_27_arc_layout()
+    return arc_circuit(links, 3, "zx", sched, color)
+
+
+@pytest.mark.parametrize("name", ["rep", "surf3", "surf3x", "arc"])
+def test_order2_outcomes_are_xors_of_order1_outcomes(capi, name):
+    """GF(2) linearity of the frame kernels, path by path, over a whole order-2 enumeration
+    (or its first 300 000 paths)."""
+    circ = _circuit(name)
+    idx, labels, paulis = noise_inputs(circ, standard_depolarizing_model())
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    e1 = make_enumerator(capi, g, 1, idx, paulis)
+    n1 = e1.num_paths()
+    sig = capi.unpack_bits(e1.range(0, n1)[0], n1)  # [fault][clbit]
+    first = np.cumsum([0] + [len(p) for p in paulis])
+    e2 = make_enumerator(capi, g, 2, idx, paulis)
+    n2 = min(e2.num_paths(), 300_000)
+    got = capi.unpack_bits(e2.range(0, n2)[0], n2)
+    step = max(1, n2 // 4000)
+    for r in range(0, n2, step):
+        locs, digs = e2.unrank(r)
+        want = sig[first[locs[0]] + digs[0]] ^ sig[first[locs[1]] + digs[1]]
+        assert np.array_equal(got[r], want), f"path {r}"
+
+
+@pytest.mark.parametrize("name,p,n_shots,lo", [
+    ("rep", 0.05, 20_000, 0), ("surf3", 0.01, 30_000, 4096 * 3 + 32 * 5), ("surf3x", 0.3, 6_000, 32),
+    ("surf5", 1e-3, 40_000, 8192 - 64), ("arc", 2e-3, 20_000, 0), ("surf7", 5e-3, 9_000, 0)])
+def test_linear_sampler_equals_explicit_propagation(capi, port, name, p, n_shots, lo):
+    circ = _circuit(name)
+    model = standard_depolarizing_model(p)
+    idx, labels, lw, lp = sampler_inputs(circ, model)
+    _, _, paulis = noise_inputs(circ, model)
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=99)
+    bits, tally, cnt, ev = sm.sample(lo, n_shots, want_tally=True, fault_cap=64)
+    assert "sample:linear" in capi.last_kernel()
+    tab = sm.tables()
+    assert int(tab[7]) & 2
+    nw = (n_shots + 31) // 32
+    paths = [([], []) for _ in range(n_shots)]
+    for w in range(nw):
+        nv = min(32, n_shots - 32 * w)
+        want_ev = port.sample_word(tab, lo // 32 + w, nv)
+        assert np.array_equal(ev[w, :cnt[w]], want_ev), f"fault list of word {w} differs from the port"
+        for e in want_ev:
+            loc, bit, dig = int(e) >> 14, (int(e) >> 9) & 31, int(e) & 511
+            paths[32 * w + bit][0].append(idx[loc])
+            paths[32 * w + bit][1].append(paulis[loc][dig])
+    want = port.propagate_batch(circ.nq, circ.nc, circ.ops, paths)
+    got = capi.unpack_bits(bits, n_shots)
+    assert np.array_equal(got, want), "linear-response outcomes differ from explicit propagation"
+    # tallies: per-clbit ones, shots with any 1, shot count, faults-per-shot histogram
+    nc = circ.nc
+    assert np.array_equal(tally[:nc], want.sum(axis=0).astype(np.uint64))
+    assert int(tally[nc]) == int(want.any(axis=1).sum()) and int(tally[nc + 1]) == n_shots
+    k = np.minimum(np.array([len(pp[0]) for pp in paths]), 63)
+    assert np.array_equal(tally[nc + 2:nc + 66], np.bincount(k, minlength=64).astype(np.uint64))
+    # the bulk call (no export) returns the same bits
+    bits2, tally2, _, _ = sm.sample(lo, n_shots, want_tally=True)
+    assert np.array_equal(bits2, bits) and np.array_equal(tally2, tally)
+
+
+def test_linear_sampler_windows_and_shards(capi):
+    """Any 32-aligned window of the shot stream, cut anywhere relative to the kernel's batches,
+    returns the bits of the one big call; shard tallies add up."""
+    circ = _circuit("surf5")
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(2e-3))
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=5)
+    n = 3 * 4096 * 7 + 32 * 11 + 5
+    bits, tally, _, _ = sm.sample(0, n, want_tally=True)
+    full = capi.unpack_bits(bits, n)
+    rng = np.random.default_rng(0)
+    for _ in range(6):
+        lo = int(rng.integers(0, n // 32 - 8)) * 32
+        m = int(rng.integers(1, n - lo + 1))
+        b, _, _, _ = sm.sample(lo, m)
+        assert np.array_equal(capi.unpack_bits(b, m), full[lo:lo + m]), (lo, m)
+    cuts = [0, 32 * 100, 4096 * 5 + 64, 4096 * 11, n]
+    acc = np.zeros_like(tally)
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        _, t, _, _ = sm.sample(a, b - a, want_bits=False, want_tally=True)
+        acc += t
+    assert np.array_equal(acc, tally)
+
+
+def test_linear_sampler_class_thinning_and_rates(capi):
+    """Unequal class probabilities (thinning at pmax), a zero-probability class and non-uniform
+    Pauli weights: per-class fault counts and per-Pauli shares within 5 sigma."""
+    circ = _circuit("surf3")
+    model = standard_depolarizing_model(0.0)
+    for lab, pp in (("h", 0.02), ("cx", 0.004), ("reset", 0.0), ("measure", 0.03), ("id", 0.001)):
+        model.set_error_probability(lab, pp)
+    model.add_operation("cx", {"ix": 3, "zz": 1, "yy": 0, "xi": 2})
+    model.set_error_probability("cx", 0.004)
+    idx, labels, lw, lp = sampler_inputs(circ, model)
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, names = make_sampler(capi, g, idx, labels, lw, lp, seed=11)
+    n = 400_000
+    _, _, cnt, ev = sm.sample(0, n, want_bits=False, fault_cap=96)
+    assert "sample:linear" in capi.last_kernel()
+    evs = np.concatenate([ev[w, :cnt[w]] for w in range(len(cnt))])
+    loc, dig = evs >> 14, evs & 511
+    lab_of = np.array([names.index(l) for l in labels])
+    for k, name in enumerate(names):
+        sel = lab_of[loc] == k
+        n_loc = int((lab_of == k).sum())
+        p = lp.get(name, 0.0)
+        mean, sd = n * n_loc * p, np.sqrt(n * n_loc * p * (1 - p))
+        assert abs(int(sel.sum()) - mean) <= 5 * sd + 1e-9, (name, int(sel.sum()), mean)
+        if p > 0:
+            ws = np.array([w for _, w in lw[name]], dtype=float)
+            share = np.bincount(dig[sel], minlength=len(ws)) / max(1, int(sel.sum()))
+            want = ws / ws.sum()
+            sd_s = np.sqrt(want * (1 - want) / max(1, int(sel.sum())))
+            assert np.all(np.abs(share - want) <= 5 * sd_s + 1e-12), (name, share, want)
+
+
+def test_linear_sampler_tiny_and_huge_p(capi, port):
+    """p = 1e-7: the first-level gap table is exhausted by most draws (advance K1 * B slots,
+    no fault); p = 0.9: a fault on nearly every slot.  Both match the port and explicit
+    propagation."""
+    circ = _circuit("surf3")
+    for p, n in ((1e-7, 2_000_000), (0.9, 2_048)):
+        model = standard_depolarizing_model(p)
+        idx, labels, lw, lp = sampler_inputs(circ, model)
+        _, _, paulis = noise_inputs(circ, model)
+        g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=3)
+        cap = 16 if p < 0.5 else 32 * len(idx) + 8
+        bits, tally, cnt, ev = sm.sample(0, n, want_tally=True, fault_cap=cap)
+        assert "sample:linear" in capi.last_kernel()
+        tab = sm.tables()
+        total = int(cnt.sum())
+        mean = n * len(idx) * p
+        assert abs(total - mean) <= 5 * np.sqrt(mean) + 5
+        got = capi.unpack_bits(bits, n)
+        words = np.nonzero(cnt)[0][:200] if p < 0.5 else np.arange(len(cnt))
+        paths, rows = [], []
+        for w in words:
+            want_ev = port.sample_word(tab, int(w), min(32, n - 32 * int(w)))
+            assert np.array_equal(ev[w, :cnt[w]], want_ev)
+            per = {}
+            for e in want_ev:
+                loc, bit, dig = int(e) >> 14, (int(e) >> 9) & 31, int(e) & 511
+                per.setdefault(bit, ([], []))
+                per[bit][0].append(idx[loc])
+                per[bit][1].append(paulis[loc][dig])
+            for bit, pth in per.items():
+                paths.append(pth)
+                rows.append(32 * int(w) + bit)
+        want = port.propagate_batch(circ.nq, circ.nc, circ.ops, paths)
+        assert np.array_equal(got[rows], want)
+        if p < 0.5:  # every shot without a fault reads all zeros
+            mask = np.ones(n, dtype=bool)
+            for w in np.nonzero(cnt)[0]:
+                mask[32 * w:32 * w + 32] = False
+            assert not got[mask].any()
+
+
+def test_frame_mode_switch(capi, monkeypatch):
+    """QEC_B200_SAMPLER=frame keeps the frame-propagation samplers (their own draw order)."""
+    circ = _circuit("surf3")
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.01))
+    monkeypatch.setenv("QEC_B200_SAMPLER", "frame")
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=1)
+    sm.sample(0, 4096)
+    assert "sample:linear" not in capi.last_kernel()
+    assert not int(sm.tables()[7]) & 2
