@@ -874,6 +874,8 @@ struct qec_sampler {
     std::vector<uint16_t> siglist;
     uint32_t *d_info = nullptr, *d_sigdesc = nullptr;
     uint16_t *d_siglist = nullptr;
+    std::vector<uint16_t> sigrec;
+    uint16_t *d_sigrec = nullptr;
   } lin;
 };
 
@@ -1008,6 +1010,7 @@ static int sampler_plan_linear(qec_sampler *s) {
         lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
   ln.sigdesc.clear();
   ln.siglist.clear();
+  ln.sigrec.clear();
   for (int64_t f = 0; f < F; ++f) {
     const size_t len = lists[f].size();
     if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
@@ -1015,6 +1018,8 @@ static int sampler_plan_linear(qec_sampler *s) {
       return 0;
     }
     ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
+    ln.sigrec.push_back((uint16_t)len);
+    for (size_t k = 0; k < 15; ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
     ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
   }
   const uint32_t n_sig = (uint32_t)ln.siglist.size();
@@ -1051,8 +1056,28 @@ static int sampler_plan_linear(qec_sampler *s) {
     return true;
   };
   bool found = false;
-  if (f_ctas > 0 && f_lgb > 0) found = try_cfg(f_ctas, f_lgb);
-  else for (const auto &cd : cand) if ((found = try_cfg(cd[0], cd[1]))) break;
+  int warp_mode = 0, threads = T;
+  {
+    // warp-autonomous variant (256-shot batches, one warp each) when at least 24 warps'
+    // accumulators fit next to the tables: no CTA barriers, row-parallel read-out
+    const char *lm = std::getenv("QEC_B200_LIN_MODE");
+    const bool allow = !(lm && !strcmp(lm, "cta")) && f_lgb == 0 && ((long long)s->L << 8) < (1ll << 30);
+    const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
+    for (int wz = (w_env > 0 ? w_env : 32); allow && wz >= (w_env > 0 ? w_env : 24) && !found; --wz) {
+      for (int is = 1; is >= 0 && !found; --is) {
+        const size_t need = qec_linw_smem_words(c->nc, wz, s->K1, s->B, (uint32_t)s->L,
+                                                (uint32_t)s->n_classes, s->lgP, is) * 4 + 16;
+        if (need > di.smem_optin) continue;
+        found = true; warp_mode = 1; threads = 32 * wz; ctas = 1; lgb = 8; info_s = is; sig_s = 0;
+        smem = need;
+      }
+    }
+    if (lm && !strcmp(lm, "warp") && !found) { ln.why = "QEC_B200_LIN_MODE=warp: accumulators do not fit"; return 0; }
+  }
+  if (!found) {
+    if (f_ctas > 0 && f_lgb > 0) found = try_cfg(f_ctas, f_lgb);
+    else for (const auto &cd : cand) if ((found = try_cfg(cd[0], cd[1]))) break;
+  }
   if (!found) { ln.why = "the outcome accumulator of a 256-shot batch does not fit in shared memory"; return 0; }
   // streams per batch: the most (power of two, at most 64) that still carry >= 128 faults each
   double psum = 0;
@@ -1060,11 +1085,12 @@ static int sampler_plan_linear(qec_sampler *s) {
   const double mean_batch = psum * (double)(1 << lgb);
   int ns = 64;
   while (ns > 1 && mean_batch / ns < 128.0) ns >>= 1;
+  if (warp_mode) ns = 1;
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
-      (rc = upload(ln.siglist, &ln.d_siglist)))
+      (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)))
     return rc;
   {
     const int e = qec_lin_set_smem_attr(smem);
@@ -1081,11 +1107,12 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
   d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;
   d.sigdesc = ln.d_sigdesc; d.siglist = ln.d_siglist;
+  d.sigrec = reinterpret_cast<const uint4 *>(ln.d_sigrec);
   d.n_faults = (uint32_t)F; d.n_sig = n_sig;
-  d.info_in_smem = info_s; d.sig_in_smem = sig_s;
+  d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
   d.k0 = (uint32_t)s->seed; d.k1 = (uint32_t)(s->seed >> 32);
   ln.ctas = ctas;
-  ln.cfg.block = T;
+  ln.cfg.block = threads;
   ln.cfg.grid = di.sms * ctas;
   ln.cfg.smem = smem;
   ln.eligible = true;
@@ -1240,7 +1267,8 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   cudaSetDevice(s->c->device);
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
-                  s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist};
+                  s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
+                  s->lin.d_sigrec};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1287,14 +1315,16 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
   if (s->lin.eligible) {
     const QecLinDev &d = s->lin.dev;
     QecLaunchCfg cfg = s->lin.cfg;
-    const long long n_batches = ((shot_lo + n_shots - 1) >> d.lgb) - (shot_lo >> d.lgb) + 1;
+    long long n_batches = ((shot_lo + n_shots - 1) >> d.lgb) - (shot_lo >> d.lgb) + 1;
+    if (d.warp_mode) n_batches = (n_batches + cfg.block / 32 - 1) / (cfg.block / 32);  // one per warp
     if (cfg.grid > n_batches) cfg.grid = (int)n_batches;
     time_begin(s->c, stream);
     qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
     time_end(s->c, stream);
     CU(cudaGetLastError());
     s->last_cap = 0;
-    g_last_kernel = "sample:linear batch=" + std::to_string(1 << d.lgb) + " streams=" +
+    g_last_kernel = std::string("sample:linear ") + (d.warp_mode ? "warp-batches" : "cta-batches") +
+                    " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
                     (d.sig_in_smem ? " sig=smem" : " sig=global");

@@ -118,10 +118,22 @@ struct QecLinDev {
   const uint32_t *slloc;    // [L] original location index (fault export)
   const uint32_t *sigdesc;  // [n_faults] offset into siglist | length << 22
   const uint16_t *siglist;  // clbits flipped by each fault
+  const uint4 *sigrec;      // [n_faults][2] uint16 x 16: length, first 15 clbits of the fault
   uint32_t n_faults, n_sig;
   int info_in_smem, sig_in_smem;
+  int warp_mode;            // 1: k_sample_linw (lgb = 8, one warp per batch)
   uint32_t k0, k1;
 };
+
+// shared-memory words of the warp-autonomous variant (256-shot batches, `warps` warps per CTA)
+static inline __host__ __device__ size_t qec_linw_smem_words(int nc, int warps, uint32_t K1, uint32_t B,
+                                                             uint32_t L, uint32_t ncls, uint32_t lgP,
+                                                             int info_in_smem) {
+  const size_t per_warp = (size_t)nc * 8u + 128u + (((size_t)nc + 3u) & ~(size_t)3u);
+  size_t w = (size_t)warps * per_warp + 64u + K1 + 2u * B + 2u * ncls + ((size_t)ncls << lgP);
+  if (info_in_smem) w += L;
+  return w;
+}
 
 // shared-memory words of the linear sampler's CTA (T threads)
 static inline __host__ __device__ size_t qec_lin_smem_words(int nc, int lgb, int T, uint32_t K1,

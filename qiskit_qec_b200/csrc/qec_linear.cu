@@ -110,6 +110,114 @@ __device__ __forceinline__ uint32_t lin_out_rows(int n_it, uint32_t a, const uin
   return anyv;
 }
 
+// Constants of the draw loop that both kernels keep in registers.
+struct LinDraw {
+  uint32_t t1_0, t1_1, t1_2, kb, cdf_s, desc_s, list_s, bw4, P;
+  int lgb;
+};
+
+// One fault stream of one batch, walked by one warp: 32 draws per step (lane = draw), a warp
+// prefix sum of the gaps, then every lane resolves its candidate (class thinning, Pauli digit)
+// and XORs the fault's clbit list into the accumulator at shared address acc_s (row pitch
+// dc.bw4 bytes) with shared-memory reductions.
+template <bool TALLY>
+__device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m, const LinDraw &dc,
+                                           const int s, const int lane, const uint32_t blo,
+                                           const uint32_t bhi, const uint32_t slo, const uint32_t shi,
+                                           const long long base_shot, const long long w_lo,
+                                           const uint32_t acc_s, const uint32_t cnt_s,
+                                           const QecSampleExport &X) {
+  const int lgb = dc.lgb;
+  const uint32_t BATCH = 1u << lgb, P = dc.P, bw4 = dc.bw4, kb = dc.kb;
+  const uint32_t t1_0 = dc.t1_0, t1_1 = dc.t1_1, t1_2 = dc.t1_2;
+  const uint32_t cdf_s = dc.cdf_s, desc_s = dc.desc_s, list_s = dc.list_s;
+  const int start = (int)((uint32_t)s * S.slen);
+  const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
+  int pos = start - 1;
+  for (uint32_t it = 0; pos < end; ++it) {
+    const QecPhilox r = qec_philox(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
+                                   S.k0, S.k1);
+    // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
+    // next K1 * B slots -- exact by memorylessness)
+    uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
+    if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
+    uint32_t g = m.G[r.c[1] >> S.gshift];
+    while (g < S.B - 1u && m.T2[1u + g] > r.c[1]) ++g;
+    const bool has = a < S.K1;
+    uint32_t incl = has ? a * S.B + g + 1u : kb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int p = pos + (int)incl;
+    pos = __shfl_sync(0xFFFFFFFFu, p, 31);
+    // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
+    const uint32_t sl = (uint32_t)p >> lgb, shot = (uint32_t)p & (BATCH - 1u);
+    bool ok = has && p < end && shot >= slo && shot < shi;  // inside the requested range
+    uint32_t inf = 0, cls = 0;
+    if (ok) {
+      inf = m.info[sl];
+      cls = (inf >> 21) & 1023u;
+      ok = (inf >> 31) || r.c[2] < m.cacc[cls];  // class thinning
+    }
+    if (ok) {
+      const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
+      uint32_t d;
+      switch (S.lgP) {
+        case 0: d = 0; break;
+        case 1: d = lin_digit<1>(cd, r.c[3]); break;
+        case 2: d = lin_digit<2>(cd, r.c[3]); break;
+        case 3: d = lin_digit<3>(cd, r.c[3]); break;
+        case 4: d = lin_digit<4>(cd, r.c[3]); break;
+        default:
+          d = 0;
+          for (uint32_t step = P >> 1; step; step >>= 1)
+            if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
+      }
+      d = min(d, m.cnp1[cls]);
+      const uint32_t f = (inf & 0x1FFFFFu) + d;
+      const uint32_t colb = acc_s + ((shot >> 5) << 2);
+      const uint32_t msk = 1u << (shot & 31u);
+      if (S.sig_in_smem) {
+        const uint32_t desc = ld_s(desc_s + (f << 2));
+        uint32_t li = list_s + ((desc & 0x3FFFFFu) << 1);
+        for (uint32_t n = desc >> 22; n; --n, li += 2u) red_xor_s(colb + ld_s16(li) * bw4, msk);
+      } else {
+        // 32-byte record: length, then the first 15 clbits (one or two 128-bit loads per
+        // fault instead of a descriptor and one 16-bit load per clbit)
+        const uint4 *rec = S.sigrec + 2u * f;
+        const uint4 q0 = __ldg(rec);
+        const uint32_t len = q0.x & 0xFFFFu;
+#define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
+        QEC_RED(0u, q0.x >> 16);
+        QEC_RED(1u, q0.y & 0xFFFFu); QEC_RED(2u, q0.y >> 16);
+        QEC_RED(3u, q0.z & 0xFFFFu); QEC_RED(4u, q0.z >> 16);
+        QEC_RED(5u, q0.w & 0xFFFFu); QEC_RED(6u, q0.w >> 16);
+        if (len > 7u) {
+          const uint4 q1 = __ldg(rec + 1);
+          QEC_RED(7u, q1.x & 0xFFFFu); QEC_RED(8u, q1.x >> 16);
+          QEC_RED(9u, q1.y & 0xFFFFu); QEC_RED(10u, q1.y >> 16);
+          QEC_RED(11u, q1.z & 0xFFFFu); QEC_RED(12u, q1.z >> 16);
+          QEC_RED(13u, q1.w & 0xFFFFu); QEC_RED(14u, q1.w >> 16);
+          if (len > 15u) {
+            const uint16_t *li = S.siglist + (__ldg(S.sigdesc + f) & 0x3FFFFFu) + 15u;
+            for (uint32_t n = len - 15u; n; --n, ++li) red_xor_s(colb + (uint32_t)__ldg(li) * bw4, msk);
+          }
+        }
+#undef QEC_RED
+      }
+      if (TALLY) red_add_s(cnt_s + ((shot >> 1) << 2), 1u << ((shot & 1u) << 4));
+      if (X.cnt) {
+        const long long wr = ((base_shot + shot) >> 5) - w_lo;
+        const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+        if (k < (uint32_t)X.cap)
+          X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
+      }
+    }
+  }
+}
+
 template <bool TALLY, bool BITS>
 __global__ void __launch_bounds__(1024, 1)
 k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
@@ -155,14 +263,17 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
   }
   __syncthreads();
 
-  const uint32_t t1_0 = m.T1[0], t1_1 = S.K1 > 1 ? m.T1[1] : 0u, t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
-  const uint32_t kb = S.K1 * S.B;
   const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(m.acc);
   const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(m.cnt);
-  const uint32_t cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
-  const uint32_t desc_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.desc) : 0u;
-  const uint32_t list_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.list) : 0u;
-  const uint32_t bw4 = 4u << lgw;  // bytes per accumulator row
+  LinDraw dc;
+  dc.t1_0 = m.T1[0]; dc.t1_1 = S.K1 > 1 ? m.T1[1] : 0u; dc.t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
+  dc.kb = S.K1 * S.B;
+  dc.cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
+  dc.desc_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.desc) : 0u;
+  dc.list_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.list) : 0u;
+  dc.bw4 = 4u << lgw;  // bytes per accumulator row
+  dc.P = P;
+  dc.lgb = lgb;
   uint32_t *w_tally = m.tally + (size_t)warp * S.nc;
   unsigned long long nz_shots = 0;
   const long long b0 = shot_lo >> lgb, b1 = (shot_lo + n_shots - 1) >> lgb;
@@ -176,74 +287,8 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
 
     // ---- draw the batch's faults, XOR their signatures into acc
-    for (int s = warp; s < S.n_streams; s += NW) {
-      const int start = (int)((uint32_t)s * S.slen);
-      const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
-      int pos = start - 1;
-      for (uint32_t it = 0; pos < end; ++it) {
-        const QecPhilox r = qec_philox(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
-                                       S.k0, S.k1);
-        // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
-        // next K1 * B slots -- exact by memorylessness)
-        uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
-        if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
-        uint32_t g = m.G[r.c[1] >> S.gshift];
-        while (g < S.B - 1u && m.T2[1u + g] > r.c[1]) ++g;
-        const bool has = a < S.K1;
-        uint32_t incl = has ? a * S.B + g + 1u : kb;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-          if (lane >= o) incl += t;
-        }
-        const int p = pos + (int)incl;
-        pos = __shfl_sync(0xFFFFFFFFu, p, 31);
-        // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
-        const uint32_t sl = (uint32_t)p >> lgb, shot = (uint32_t)p & (BATCH - 1u);
-        bool ok = has && p < end && shot >= slo && shot < shi;  // inside the requested range
-        uint32_t inf = 0, cls = 0;
-        if (ok) {
-          inf = m.info[sl];
-          cls = (inf >> 21) & 1023u;
-          ok = (inf >> 31) || r.c[2] < m.cacc[cls];  // class thinning
-        }
-        if (ok) {
-          const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
-          uint32_t d;
-          switch (S.lgP) {
-            case 0: d = 0; break;
-            case 1: d = lin_digit<1>(cd, r.c[3]); break;
-            case 2: d = lin_digit<2>(cd, r.c[3]); break;
-            case 3: d = lin_digit<3>(cd, r.c[3]); break;
-            case 4: d = lin_digit<4>(cd, r.c[3]); break;
-            default:
-              d = 0;
-              for (uint32_t step = P >> 1; step; step >>= 1)
-                if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
-          }
-          d = min(d, m.cnp1[cls]);
-          const uint32_t f = (inf & 0x1FFFFFu) + d;
-          const uint32_t colb = acc_s + ((shot >> 5) << 2);
-          const uint32_t msk = 1u << (shot & 31u);
-          if (S.sig_in_smem) {
-            const uint32_t desc = ld_s(desc_s + (f << 2));
-            uint32_t li = list_s + ((desc & 0x3FFFFFu) << 1);
-            for (uint32_t n = desc >> 22; n; --n, li += 2u) red_xor_s(colb + ld_s16(li) * bw4, msk);
-          } else {
-            const uint32_t desc = __ldg(S.sigdesc + f);
-            const uint16_t *li = S.siglist + (desc & 0x3FFFFFu);
-            for (uint32_t n = desc >> 22; n; --n, ++li) red_xor_s(colb + (uint32_t)__ldg(li) * bw4, msk);
-          }
-          if (TALLY) red_add_s(cnt_s + ((shot >> 1) << 2), 1u << ((shot & 1u) << 4));
-          if (X.cnt) {
-            const long long wr = ((base_shot + shot) >> 5) - w_lo;
-            const uint32_t k = atomicAdd(X.cnt + wr, 1u);
-            if (k < (uint32_t)X.cap)
-              X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
-          }
-        }
-      }
-    }
+    for (int s = warp; s < S.n_streams; s += NW)
+      lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
     __syncthreads();
 
     // ---- stream the accumulator out: thread -> fixed word column wb, clbits c0, c0 + T/BW, ...
@@ -315,6 +360,176 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Warp-autonomous variant for circuits with few clbits: batch = 256 shots, one stream, owned by
+// ONE warp with a private accumulator acc[nc][8 words] -- no CTA barrier between drawing and
+// read-out, no accumulator traffic between warps.  Read-out is row-parallel: lane = clbit, a
+// lane moves its row's 32 bytes with two 128-bit loads / stores, sums its popcounts in
+// registers and updates its own tally entry without a warp reduction.
+// Shared memory: [warp regions: acc nc*8 | cnt 128 | tally nc (padded to 4)] then the tables.
+#define QEC_LINW_LGB 8
+#define QEC_LINW_BW 8u
+
+__device__ __forceinline__ uint4 ld_s128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_s128z(uint32_t addr) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(addr), "r"(0u) : "memory");
+}
+
+template <bool TALLY, bool BITS>
+__global__ void __launch_bounds__(1024, 1)
+k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
+              const QecSampleExport X) {
+  extern __shared__ __align__(16) uint32_t qec_lin_smem[];
+  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
+  const uint32_t ncp = ((uint32_t)S.nc + 3u) & ~3u;
+  const uint32_t wwords = (uint32_t)S.nc * QEC_LINW_BW + 128u + ncp;  // words per warp region
+  const uint32_t P = 1u << S.lgP;
+  LinSmem m;
+  m.acc = qec_lin_smem + (size_t)warp * wwords;
+  m.cnt = m.acc + (size_t)S.nc * QEC_LINW_BW;
+  m.tally = m.cnt + 128;
+  m.anyw = nullptr;
+  m.hist = qec_lin_smem + (size_t)NW * wwords;
+  m.T1 = m.hist + 64;
+  m.T2 = m.T1 + S.K1;
+  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B);
+  m.cacc = m.T2 + 2u * S.B;
+  m.cnp1 = m.cacc + S.n_classes;
+  m.cdf = m.cnp1 + S.n_classes;
+  {
+    uint32_t *p = m.cdf + ((size_t)S.n_classes << S.lgP);
+    if (S.info_in_smem) {
+      m.info = p;
+      for (uint32_t i = tid; i < (uint32_t)S.L; i += T) p[i] = S.info[i];
+    } else {
+      m.info = S.info;
+    }
+    m.desc = S.sigdesc;
+    m.list = S.siglist;
+  }
+  for (uint32_t i = tid; i < S.K1; i += T) m.T1[i] = S.T1[i];
+  for (uint32_t i = tid; i < S.B; i += T) m.T2[i] = S.T2[i];
+  for (uint32_t k = tid; k < 2u * S.B; k += T) {
+    const uint32_t rmax = (k << S.gshift) | ((1u << S.gshift) - 1u);
+    m.G[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1u, rmax);
+  }
+  for (uint32_t c = tid; c < S.n_classes; c += T) {
+    m.cacc[c] = S.cls_acc[c];
+    m.cnp1[c] = S.cls_off[c + 1] - S.cls_off[c] - 1u;
+  }
+  for (uint32_t i = tid; i < (S.n_classes << S.lgP); i += T) {
+    const uint32_t c = i >> S.lgP, d = i & (P - 1u), o = S.cls_off[c], n = S.cls_off[c + 1] - o;
+    m.cdf[i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
+  }
+  for (uint32_t i = tid; i < (uint32_t)NW * wwords + 64u; i += T) qec_lin_smem[i] = 0u;
+  __syncthreads();
+
+  const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(m.acc);
+  const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(m.cnt);
+  const uint32_t tal_s = (uint32_t)__cvta_generic_to_shared(m.tally);
+  LinDraw dc;
+  dc.t1_0 = m.T1[0]; dc.t1_1 = S.K1 > 1 ? m.T1[1] : 0u; dc.t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
+  dc.kb = S.K1 * S.B;
+  dc.cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
+  dc.desc_s = 0u; dc.list_s = 0u;
+  dc.bw4 = 4u * QEC_LINW_BW;
+  dc.P = P;
+  dc.lgb = QEC_LINW_LGB;
+  unsigned long long nz_shots = 0;
+  uint32_t h0 = 0, h1 = 0, h2 = 0;
+  const long long b0 = shot_lo >> QEC_LINW_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LINW_LGB;
+  const long long w_lo = shot_lo >> 5;
+  const bool vec_ok = ((O.n_words | w_lo) & 3) == 0 && ((size_t)O.bits & 15) == 0;
+
+  for (long long b = b0 + (long long)blockIdx.x * NW + warp; b <= b1; b += (long long)gridDim.x * NW) {
+    const long long base_shot = b << QEC_LINW_LGB;
+    const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
+    const uint32_t shi = (uint32_t)min(256ll, shot_lo + n_shots - base_shot);
+    const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
+    for (int s = 0; s < S.n_streams; ++s)
+      lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    __syncwarp();
+
+    // ---- read-out: lane = clbit row
+    const long long w0 = (b << 3) - w_lo;  // first output word of the batch (may be < 0 at the range start)
+    const bool whole = w0 >= 0 && w0 + 8 <= O.n_words;
+    uint32_t any0 = 0, any1 = 0, any2 = 0, any3 = 0, any4 = 0, any5 = 0, any6 = 0, any7 = 0;
+    for (uint32_t c = (uint32_t)lane; c < (uint32_t)S.nc; c += 32u) {
+      const uint32_t a = acc_s + c * 32u;
+      const uint4 lo4 = ld_s128(a), hi4 = ld_s128(a + 16u);
+      st_s128z(a);
+      st_s128z(a + 16u);
+      if (BITS) {
+        uint32_t *po = O.bits + ((long long)c * O.n_words + w0);
+        if (whole && vec_ok) {
+          *reinterpret_cast<uint4 *>(po) = lo4;
+          *reinterpret_cast<uint4 *>(po + 4) = hi4;
+        } else {
+          const uint32_t v[8] = {lo4.x, lo4.y, lo4.z, lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (w0 + j >= 0 && w0 + j < O.n_words) po[j] = v[j];
+        }
+      }
+      if (TALLY) {
+        any0 |= lo4.x; any1 |= lo4.y; any2 |= lo4.z; any3 |= lo4.w;
+        any4 |= hi4.x; any5 |= hi4.y; any6 |= hi4.z; any7 |= hi4.w;
+        const uint32_t cnt = __popc(lo4.x) + __popc(lo4.y) + __popc(lo4.z) + __popc(lo4.w) +
+                             __popc(hi4.x) + __popc(hi4.y) + __popc(hi4.z) + __popc(hi4.w);
+        const uint32_t ta = tal_s + (c << 2);
+        st_s(ta, ld_s(ta) + cnt);
+      }
+    }
+    if (TALLY) {
+      uint32_t nzb = __popc(__reduce_or_sync(0xFFFFFFFFu, any0)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any1)) +
+                     __popc(__reduce_or_sync(0xFFFFFFFFu, any2)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any3)) +
+                     __popc(__reduce_or_sync(0xFFFFFFFFu, any4)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any5)) +
+                     __popc(__reduce_or_sync(0xFFFFFFFFu, any6)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any7));
+      if (lane == 0) nz_shots += nzb;
+      // faults-per-shot histogram: 128 counter words (two shots each), four per lane
+#pragma unroll
+      for (uint32_t q = 0; q < 4u; ++q) {
+        const uint32_t i = q * 32u + (uint32_t)lane;
+        const uint32_t cw = ld_s(cnt_s + (i << 2));
+        st_s(cnt_s + (i << 2), 0u);
+#pragma unroll
+        for (uint32_t h = 0; h < 2u; ++h) {
+          const uint32_t shot = 2u * i + h, k = (cw >> (16u * h)) & 0xFFFFu;
+          if (shot < slo || shot >= shi) continue;
+          if (k == 0u) ++h0;
+          else if (k == 1u) ++h1;
+          else if (k == 2u) ++h2;
+          else atomicAdd(m.hist + min(k, 63u), 1u);
+        }
+      }
+    }
+    __syncwarp();
+  }
+
+  if (TALLY) {
+    h0 = __reduce_add_sync(0xFFFFFFFFu, h0);
+    h1 = __reduce_add_sync(0xFFFFFFFFu, h1);
+    h2 = __reduce_add_sync(0xFFFFFFFFu, h2);
+    if (lane == 0) {
+      atomicAdd(m.hist + 0, h0); atomicAdd(m.hist + 1, h1); atomicAdd(m.hist + 2, h2);
+      if (nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
+    }
+    __syncthreads();
+    for (int c = tid; c < S.nc; c += T) {
+      unsigned long long v = 0;
+      for (int k = 0; k < NW; ++k) v += qec_lin_smem[(size_t)k * wwords + (size_t)S.nc * QEC_LINW_BW + 128u + c];
+      if (v) atomicAdd(&O.tally[c], v);
+    }
+    for (int c = tid; c < 64; c += T)
+      if (m.hist[c]) atomicAdd(&O.tally[S.nc + 2 + c], (unsigned long long)m.hist[c]);
+    if (blockIdx.x == 0 && tid == 0) atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
+  }
+}
+
 }  // namespace
 
 int qec_lin_set_smem_attr(size_t smem) {
@@ -324,6 +539,8 @@ int qec_lin_set_smem_attr(size_t smem) {
   if (e != cudaSuccess) return (int)e;
   QEC_SET((k_sample_lin<true, true>)) QEC_SET((k_sample_lin<true, false>))
   QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
+  QEC_SET((k_sample_linw<true, true>)) QEC_SET((k_sample_linw<true, false>))
+  QEC_SET((k_sample_linw<false, true>)) QEC_SET((k_sample_linw<false, false>))
 #undef QEC_SET
   return 0;
 }
@@ -332,8 +549,17 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecLinDev &S, long long shot_lo, long long n_shots,
                            const QecSampleExport &X) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
-  if (t && b) k_sample_lin<true, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
-  else if (t) k_sample_lin<true, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
-  else if (b) k_sample_lin<false, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
-  else k_sample_lin<false, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X);
+#define QEC_GO(K) K<<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X)
+  if (S.warp_mode) {
+    if (t && b) QEC_GO((k_sample_linw<true, true>));
+    else if (t) QEC_GO((k_sample_linw<true, false>));
+    else if (b) QEC_GO((k_sample_linw<false, true>));
+    else QEC_GO((k_sample_linw<false, false>));
+  } else {
+    if (t && b) QEC_GO((k_sample_lin<true, true>));
+    else if (t) QEC_GO((k_sample_lin<true, false>));
+    else if (b) QEC_GO((k_sample_lin<false, true>));
+    else QEC_GO((k_sample_lin<false, false>));
+  }
+#undef QEC_GO
 }
