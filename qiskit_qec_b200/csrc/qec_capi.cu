@@ -876,6 +876,8 @@ struct qec_sampler {
     uint16_t *d_siglist = nullptr;
     std::vector<uint16_t> sigrec;
     uint16_t *d_sigrec = nullptr;
+    std::vector<uint32_t> rowprog;
+    uint32_t *d_rowprog = nullptr;
   } lin;
 };
 
@@ -1008,22 +1010,8 @@ static int sampler_plan_linear(qec_sampler *s) {
     for (int64_t fw = 0; fw < FW; ++fw)
       for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u)
         lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
-  ln.sigdesc.clear();
-  ln.siglist.clear();
-  ln.sigrec.clear();
-  for (int64_t f = 0; f < F; ++f) {
-    const size_t len = lists[f].size();
-    if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
-      ln.why = "fault signatures too long for the packed descriptor";
-      return 0;
-    }
-    ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
-    ln.sigrec.push_back((uint16_t)len);
-    for (size_t k = 0; k < 15; ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
-    ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
-  }
-  const uint32_t n_sig = (uint32_t)ln.siglist.size();
-  ln.siglist.resize((n_sig + 2u) & ~1u, 0);  // whole 32-bit words, never empty
+  uint32_t n_sig = 0;  // (clbit-list entries before any change of basis: sizes the CTA variant's tables)
+  for (int64_t f = 0; f < F; ++f) n_sig += (uint32_t)lists[f].size();
   ln.loc2sl.assign(s->L, 0);
   for (int sl = 0; sl < s->L; ++sl) ln.loc2sl[s->slloc[sl]] = (uint32_t)sl;
 
@@ -1089,6 +1077,81 @@ static int sampler_plan_linear(qec_sampler *s) {
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
+  // Warp-autonomous variant: time-difference basis.  A fault that flips a stabiliser flips every
+  // later measurement of it, so raw signatures are long; with clbit c re-expressed as
+  // c ^ pred(c) (pred = the previous final measurement of the same qubit) the same fault touches
+  // one or two entries.  The read-out undoes it: each lane walks whole chains
+  // c0 -> succ(c0) -> ... with a running XOR (rowprog).  Kept only when it shortens the lists.
+  ln.rowprog.clear();
+  int n_steps = 0;
+  if (warp_mode) {
+    std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
+    for (size_t i = 0; i < c->packed.size(); ++i) {
+      const uint32_t g = c->packed[i];
+      if ((g & 15u) != QOP_MEASF) continue;
+      const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
+      if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
+      last[q] = cb;
+    }
+    std::vector<std::vector<uint16_t>> tr((size_t)F);
+    size_t raw_total = 0, tr_total = 0;
+    std::vector<uint8_t> mark(c->nc, 0);
+    for (int64_t f = 0; f < F; ++f) {
+      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
+      for (uint16_t cb : lists[f]) {
+        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
+        const int sc = succ[cb];
+        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
+      }
+      std::sort(tr[f].begin(), tr[f].end());
+      raw_total += lists[f].size();
+      tr_total += tr[f].size();
+    }
+    const bool use = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
+    if (use) lists.swap(tr);
+    // chains -> 32 lanes, longest first onto the least loaded lane
+    std::vector<std::vector<int>> chains;
+    for (int cb = 0; cb < c->nc; ++cb) {
+      if (use && pred[cb] >= 0) continue;
+      chains.emplace_back();
+      for (int x = cb; x >= 0; x = use ? succ[x] : -1) chains.back().push_back(x);
+    }
+    std::stable_sort(chains.begin(), chains.end(),
+                     [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
+    std::vector<std::vector<uint32_t>> lanes(32);
+    for (const auto &ch : chains) {
+      int best = 0;
+      for (int l = 1; l < 32; ++l) if (lanes[l].size() < lanes[best].size()) best = l;
+      for (size_t k = 0; k < ch.size(); ++k)
+        lanes[best].push_back((uint32_t)ch[k] | (k == 0 ? (1u << 30) : 0u) | (1u << 31));
+    }
+    for (const auto &l : lanes) n_steps = std::max(n_steps, (int)l.size());
+    ln.rowprog.assign((size_t)n_steps * 32, 0u);
+    for (int l = 0; l < 32; ++l)
+      for (size_t k = 0; k < lanes[l].size(); ++k) ln.rowprog[k * 32 + l] = lanes[l][k];
+  }
+  // descriptor + list (CTA variant with tables in shared memory, overflow of long lists) and
+  // fixed-size records: 16 bytes (length + 7 clbits) when no list is longer, else 32 (+15)
+  ln.sigdesc.clear();
+  ln.siglist.clear();
+  ln.sigrec.clear();
+  size_t maxlen = 0;
+  for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
+  const int rec2 = maxlen > 7 ? 1 : 0;
+  for (int64_t f = 0; f < F; ++f) {
+    const size_t len = lists[f].size();
+    if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
+      ln.why = "fault signatures too long for the packed descriptor";
+      return 0;
+    }
+    ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
+    ln.sigrec.push_back((uint16_t)len);
+    for (size_t k = 0; k < (rec2 ? 15u : 7u); ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
+    ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
+  }
+  ln.siglist.resize((ln.siglist.size() + 2u) & ~(size_t)1u, 0);  // whole 32-bit words, never empty
+  if (ln.rowprog.empty()) ln.rowprog.push_back(0u);
+  if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
       (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)))
     return rc;
@@ -1110,6 +1173,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.sigrec = reinterpret_cast<const uint4 *>(ln.d_sigrec);
   d.n_faults = (uint32_t)F; d.n_sig = n_sig;
   d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
+  d.rec2 = rec2; d.rowprog = ln.d_rowprog; d.n_steps = n_steps;
   d.k0 = (uint32_t)s->seed; d.k1 = (uint32_t)(s->seed >> 32);
   ln.ctas = ctas;
   ln.cfg.block = threads;
@@ -1268,7 +1332,7 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
-                  s->lin.d_sigrec};
+                  s->lin.d_sigrec, s->lin.d_rowprog};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();

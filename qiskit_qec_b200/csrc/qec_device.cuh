@@ -118,7 +118,12 @@ struct QecLinDev {
   const uint32_t *slloc;    // [L] original location index (fault export)
   const uint32_t *sigdesc;  // [n_faults] offset into siglist | length << 22
   const uint16_t *siglist;  // clbits flipped by each fault
-  const uint4 *sigrec;      // [n_faults][2] uint16 x 16: length, first 15 clbits of the fault
+  const uint4 *sigrec;      // [n_faults][1 << rec2] uint16 x 8: length, first 7 (15) clbits of the fault
+  int rec2;
+  // warp-autonomous variant: read-out program, [n_steps][32 lanes]: clbit row | chain start << 30
+  // | valid << 31.  A lane XORs the rows of a chain cumulatively (time-difference basis).
+  const uint32_t *rowprog;
+  int n_steps;
   uint32_t n_faults, n_sig;
   int info_in_smem, sig_in_smem;
   int warp_mode;            // 1: k_sample_linw (lgb = 8, one warp per batch)

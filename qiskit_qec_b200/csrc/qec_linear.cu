@@ -186,7 +186,7 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
       } else {
         // 32-byte record: length, then the first 15 clbits (one or two 128-bit loads per
         // fault instead of a descriptor and one 16-bit load per clbit)
-        const uint4 *rec = S.sigrec + 2u * f;
+        const uint4 *rec = S.sigrec + (f << S.rec2);
         const uint4 q0 = __ldg(rec);
         const uint32_t len = q0.x & 0xFFFFu;
 #define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
@@ -194,7 +194,7 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
         QEC_RED(1u, q0.y & 0xFFFFu); QEC_RED(2u, q0.y >> 16);
         QEC_RED(3u, q0.z & 0xFFFFu); QEC_RED(4u, q0.z >> 16);
         QEC_RED(5u, q0.w & 0xFFFFu); QEC_RED(6u, q0.w >> 16);
-        if (len > 7u) {
+        if (len > 7u) {  // (only with 32-byte records)
           const uint4 q1 = __ldg(rec + 1);
           QEC_RED(7u, q1.x & 0xFFFFu); QEC_RED(8u, q1.x >> 16);
           QEC_RED(9u, q1.y & 0xFFFFu); QEC_RED(10u, q1.y >> 16);
@@ -458,28 +458,37 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     const long long w0 = (b << 3) - w_lo;  // first output word of the batch (may be < 0 at the range start)
     const bool whole = w0 >= 0 && w0 + 8 <= O.n_words;
     uint32_t any0 = 0, any1 = 0, any2 = 0, any3 = 0, any4 = 0, any5 = 0, any6 = 0, any7 = 0;
-    for (uint32_t c = (uint32_t)lane; c < (uint32_t)S.nc; c += 32u) {
+    uint4 mlo = make_uint4(0u, 0u, 0u, 0u), mhi = mlo;  // running XOR along the lane's chain
+    for (int step = 0; step < S.n_steps; ++step) {
+      const uint32_t e = __ldg(S.rowprog + step * 32 + lane);
+      if (!(e >> 31)) continue;
+      const uint32_t c = e & 0xFFFFu;
       const uint32_t a = acc_s + c * 32u;
       const uint4 lo4 = ld_s128(a), hi4 = ld_s128(a + 16u);
       st_s128z(a);
       st_s128z(a + 16u);
+      if (e & (1u << 30)) { mlo = lo4; mhi = hi4; }
+      else {
+        mlo.x ^= lo4.x; mlo.y ^= lo4.y; mlo.z ^= lo4.z; mlo.w ^= lo4.w;
+        mhi.x ^= hi4.x; mhi.y ^= hi4.y; mhi.z ^= hi4.z; mhi.w ^= hi4.w;
+      }
       if (BITS) {
         uint32_t *po = O.bits + ((long long)c * O.n_words + w0);
         if (whole && vec_ok) {
-          *reinterpret_cast<uint4 *>(po) = lo4;
-          *reinterpret_cast<uint4 *>(po + 4) = hi4;
+          *reinterpret_cast<uint4 *>(po) = mlo;
+          *reinterpret_cast<uint4 *>(po + 4) = mhi;
         } else {
-          const uint32_t v[8] = {lo4.x, lo4.y, lo4.z, lo4.w, hi4.x, hi4.y, hi4.z, hi4.w};
+          const uint32_t v[8] = {mlo.x, mlo.y, mlo.z, mlo.w, mhi.x, mhi.y, mhi.z, mhi.w};
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             if (w0 + j >= 0 && w0 + j < O.n_words) po[j] = v[j];
         }
       }
       if (TALLY) {
-        any0 |= lo4.x; any1 |= lo4.y; any2 |= lo4.z; any3 |= lo4.w;
-        any4 |= hi4.x; any5 |= hi4.y; any6 |= hi4.z; any7 |= hi4.w;
-        const uint32_t cnt = __popc(lo4.x) + __popc(lo4.y) + __popc(lo4.z) + __popc(lo4.w) +
-                             __popc(hi4.x) + __popc(hi4.y) + __popc(hi4.z) + __popc(hi4.w);
+        any0 |= mlo.x; any1 |= mlo.y; any2 |= mlo.z; any3 |= mlo.w;
+        any4 |= mhi.x; any5 |= mhi.y; any6 |= mhi.z; any7 |= mhi.w;
+        const uint32_t cnt = __popc(mlo.x) + __popc(mlo.y) + __popc(mlo.z) + __popc(mlo.w) +
+                             __popc(mhi.x) + __popc(mhi.y) + __popc(mhi.z) + __popc(mhi.w);
         const uint32_t ta = tal_s + (c << 2);
         st_s(ta, ld_s(ta) + cnt);
       }
