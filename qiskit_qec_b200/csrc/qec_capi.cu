@@ -1015,6 +1015,62 @@ static int sampler_plan_linear(qec_sampler *s) {
   ln.loc2sl.assign(s->L, 0);
   for (int sl = 0; sl < s->L; ++sl) ln.loc2sl[s->slloc[sl]] = (uint32_t)sl;
 
+  // Warp-autonomous variant: time-difference basis.  A fault that flips a stabiliser flips every
+  // later measurement of it, so raw signatures are long; with clbit c re-expressed as
+  // c ^ pred(c) (pred = the previous final measurement of the same qubit) the same fault touches
+  // one or two entries.  The read-out undoes it: each lane walks whole chains
+  // c0 -> succ(c0) -> ... with a running XOR (rowprog).  Kept only when it shortens the lists.
+  ln.rowprog.clear();
+  int n_steps = 0;
+  bool use_diff = false;
+  size_t maxlen_w = 0;  // longest list the warp variant would see
+  std::vector<std::vector<uint16_t>> tr((size_t)F);
+  {
+    std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
+    for (size_t i = 0; i < c->packed.size(); ++i) {
+      const uint32_t g = c->packed[i];
+      if ((g & 15u) != QOP_MEASF) continue;
+      const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
+      if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
+      last[q] = cb;
+    }
+    size_t raw_total = 0, tr_total = 0;
+    std::vector<uint8_t> mark(c->nc, 0);
+    for (int64_t f = 0; f < F; ++f) {
+      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
+      for (uint16_t cb : lists[f]) {
+        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
+        const int sc = succ[cb];
+        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
+      }
+      std::sort(tr[f].begin(), tr[f].end());
+      raw_total += lists[f].size();
+      tr_total += tr[f].size();
+    }
+    use_diff = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
+    const bool use = use_diff;
+    for (int64_t f = 0; f < F; ++f) maxlen_w = std::max(maxlen_w, use ? tr[f].size() : lists[f].size());
+    // chains -> 32 lanes, longest first onto the least loaded lane
+    std::vector<std::vector<int>> chains;
+    for (int cb = 0; cb < c->nc; ++cb) {
+      if (use && pred[cb] >= 0) continue;
+      chains.emplace_back();
+      for (int x = cb; x >= 0; x = use ? succ[x] : -1) chains.back().push_back(x);
+    }
+    std::stable_sort(chains.begin(), chains.end(),
+                     [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
+    std::vector<std::vector<uint32_t>> lanes(32);
+    for (const auto &ch : chains) {
+      int best = 0;
+      for (int l = 1; l < 32; ++l) if (lanes[l].size() < lanes[best].size()) best = l;
+      for (size_t k = 0; k < ch.size(); ++k)
+        lanes[best].push_back((uint32_t)ch[k] | (k == 0 ? (1u << 30) : 0u) | (1u << 31));
+    }
+    for (const auto &l : lanes) n_steps = std::max(n_steps, (int)l.size());
+    ln.rowprog.assign((size_t)n_steps * 32, 0u);
+    for (int l = 0; l < 32; ++l)
+      for (size_t k = 0; k < lanes[l].size(); ++k) ln.rowprog[k * 32 + l] = lanes[l][k];
+  }
   // geometry: the largest batch whose accumulator fits, two CTAs per SM when they fit with
   // 4096-shot batches (one streams its accumulator out while the other draws)
   const DevInfo &di = *c->info;
@@ -1044,22 +1100,27 @@ static int sampler_plan_linear(qec_sampler *s) {
     return true;
   };
   bool found = false;
-  int warp_mode = 0, threads = T;
+  int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0;
   {
     // warp-autonomous variant (256-shot batches, one warp each) when at least 24 warps'
     // accumulators fit next to the tables: no CTA barriers, row-parallel read-out
     const char *lm = std::getenv("QEC_B200_LIN_MODE");
     const bool allow = !(lm && !strcmp(lm, "cta")) && f_lgb == 0 && ((long long)s->L << 8) < (1ll << 30);
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
+    rec8 = (maxlen_w <= 7 && c->nc <= 255) ? 1 : 0;
+    const int want_rs = rec8 ? env_int("QEC_B200_LIN_RECSMEM", 0) : 0;
     for (int wz = (w_env > 0 ? w_env : 32); allow && wz >= (w_env > 0 ? w_env : 24) && !found; --wz) {
       for (int is = 1; is >= 0 && !found; --is) {
         const size_t need = qec_linw_smem_words(c->nc, wz, s->K1, s->B, (uint32_t)s->L,
-                                                (uint32_t)s->n_classes, s->lgP, is) * 4 + 16;
+                                                (uint32_t)s->n_classes, s->lgP, is,
+                                                want_rs ? 2u * (uint32_t)F : 0u) * 4 + 16;
         if (need > di.smem_optin) continue;
         found = true; warp_mode = 1; threads = 32 * wz; ctas = 1; lgb = 8; info_s = is; sig_s = 0;
+        rec_s = want_rs;
         smem = need;
       }
     }
+    if (!found) rec8 = 0;
     if (lm && !strcmp(lm, "warp") && !found) { ln.why = "QEC_B200_LIN_MODE=warp: accumulators do not fit"; return 0; }
   }
   if (!found) {
@@ -1077,59 +1138,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
-  // Warp-autonomous variant: time-difference basis.  A fault that flips a stabiliser flips every
-  // later measurement of it, so raw signatures are long; with clbit c re-expressed as
-  // c ^ pred(c) (pred = the previous final measurement of the same qubit) the same fault touches
-  // one or two entries.  The read-out undoes it: each lane walks whole chains
-  // c0 -> succ(c0) -> ... with a running XOR (rowprog).  Kept only when it shortens the lists.
-  ln.rowprog.clear();
-  int n_steps = 0;
-  if (warp_mode) {
-    std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
-    for (size_t i = 0; i < c->packed.size(); ++i) {
-      const uint32_t g = c->packed[i];
-      if ((g & 15u) != QOP_MEASF) continue;
-      const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
-      if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
-      last[q] = cb;
-    }
-    std::vector<std::vector<uint16_t>> tr((size_t)F);
-    size_t raw_total = 0, tr_total = 0;
-    std::vector<uint8_t> mark(c->nc, 0);
-    for (int64_t f = 0; f < F; ++f) {
-      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
-      for (uint16_t cb : lists[f]) {
-        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
-        const int sc = succ[cb];
-        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
-      }
-      std::sort(tr[f].begin(), tr[f].end());
-      raw_total += lists[f].size();
-      tr_total += tr[f].size();
-    }
-    const bool use = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
-    if (use) lists.swap(tr);
-    // chains -> 32 lanes, longest first onto the least loaded lane
-    std::vector<std::vector<int>> chains;
-    for (int cb = 0; cb < c->nc; ++cb) {
-      if (use && pred[cb] >= 0) continue;
-      chains.emplace_back();
-      for (int x = cb; x >= 0; x = use ? succ[x] : -1) chains.back().push_back(x);
-    }
-    std::stable_sort(chains.begin(), chains.end(),
-                     [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
-    std::vector<std::vector<uint32_t>> lanes(32);
-    for (const auto &ch : chains) {
-      int best = 0;
-      for (int l = 1; l < 32; ++l) if (lanes[l].size() < lanes[best].size()) best = l;
-      for (size_t k = 0; k < ch.size(); ++k)
-        lanes[best].push_back((uint32_t)ch[k] | (k == 0 ? (1u << 30) : 0u) | (1u << 31));
-    }
-    for (const auto &l : lanes) n_steps = std::max(n_steps, (int)l.size());
-    ln.rowprog.assign((size_t)n_steps * 32, 0u);
-    for (int l = 0; l < 32; ++l)
-      for (size_t k = 0; k < lanes[l].size(); ++k) ln.rowprog[k * 32 + l] = lanes[l][k];
-  }
+  if (warp_mode && use_diff) lists.swap(tr);
   // descriptor + list (CTA variant with tables in shared memory, overflow of long lists) and
   // fixed-size records: 16 bytes (length + 7 clbits) when no list is longer, else 32 (+15)
   ln.sigdesc.clear();
@@ -1138,6 +1147,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   size_t maxlen = 0;
   for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
   const int rec2 = maxlen > 7 ? 1 : 0;
+  if (rec8 && (maxlen > 7 || !warp_mode)) return fail(QEC_ERR_LOGIC, "linear sampler: record plan out of step");
   for (int64_t f = 0; f < F; ++f) {
     const size_t len = lists[f].size();
     if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
@@ -1145,8 +1155,14 @@ static int sampler_plan_linear(qec_sampler *s) {
       return 0;
     }
     ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
-    ln.sigrec.push_back((uint16_t)len);
-    for (size_t k = 0; k < (rec2 ? 15u : 7u); ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
+    if (rec8) {  // bytes: length, 7 clbits
+      uint8_t by[8] = {(uint8_t)len, 0, 0, 0, 0, 0, 0, 0};
+      for (size_t k = 0; k < len; ++k) by[1 + k] = (uint8_t)lists[f][k];
+      for (int k = 0; k < 4; ++k) ln.sigrec.push_back((uint16_t)(by[2 * k] | (by[2 * k + 1] << 8)));
+    } else {
+      ln.sigrec.push_back((uint16_t)len);
+      for (size_t k = 0; k < (rec2 ? 15u : 7u); ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
+    }
     ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
   }
   ln.siglist.resize((ln.siglist.size() + 2u) & ~(size_t)1u, 0);  // whole 32-bit words, never empty
@@ -1174,6 +1190,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.n_faults = (uint32_t)F; d.n_sig = n_sig;
   d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
   d.rec2 = rec2; d.rowprog = ln.d_rowprog; d.n_steps = n_steps;
+  d.rec8 = rec8; d.rec_in_smem = rec_s;
   d.k0 = (uint32_t)s->seed; d.k1 = (uint32_t)(s->seed >> 32);
   ln.ctas = ctas;
   ln.cfg.block = threads;
@@ -1391,7 +1408,8 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
                     " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
-                    (d.sig_in_smem ? " sig=smem" : " sig=global");
+                    (d.sig_in_smem ? " sig=smem" : " sig=global") +
+                    (d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B"));
     return 0;
   }
   if (s->jit.eligible && !X.cnt) {

@@ -120,6 +120,7 @@ struct QecLinDev {
   const uint16_t *siglist;  // clbits flipped by each fault
   const uint4 *sigrec;      // [n_faults][1 << rec2] uint16 x 8: length, first 7 (15) clbits of the fault
   int rec2;
+  int rec8, rec_in_smem;    // 8-byte records (length + 7 clbits as bytes), optionally in shared memory
   // warp-autonomous variant: read-out program, [n_steps][32 lanes]: clbit row | chain start << 30
   // | valid << 31.  A lane XORs the rows of a chain cumulatively (time-difference basis).
   const uint32_t *rowprog;
@@ -133,11 +134,11 @@ struct QecLinDev {
 // shared-memory words of the warp-autonomous variant (256-shot batches, `warps` warps per CTA)
 static inline __host__ __device__ size_t qec_linw_smem_words(int nc, int warps, uint32_t K1, uint32_t B,
                                                              uint32_t L, uint32_t ncls, uint32_t lgP,
-                                                             int info_in_smem) {
+                                                             int info_in_smem, uint32_t rec_words) {
   const size_t per_warp = (size_t)nc * 8u + 128u + (((size_t)nc + 3u) & ~(size_t)3u);
-  size_t w = (size_t)warps * per_warp + 64u + K1 + 2u * B + 2u * ncls + ((size_t)ncls << lgP);
+  size_t w = (size_t)warps * per_warp + 64u + K1 + 2u * B + 1u + 2u * ncls + ((size_t)ncls << lgP);
   if (info_in_smem) w += L;
-  return w;
+  return w + 2u + rec_words;  // (records of the faults, when they sit in shared memory)
 }
 
 // shared-memory words of the linear sampler's CTA (T threads)
@@ -149,7 +150,7 @@ static inline __host__ __device__ size_t qec_lin_smem_words(int nc, int lgb, int
   const size_t BW = (size_t)1 << (lgb - 5);
   size_t w = (size_t)nc * BW + ((size_t)1 << (lgb - 1)) + BW;  // acc, per-shot fault counts, any
   w += (size_t)(T / 32) * nc + 64;                              // per-warp tallies, histogram
-  w += (size_t)K1 + 2u * B + 2u * ncls + ((size_t)ncls << lgP); // T1 T2 guide cacc cnp1 cdf
+  w += (size_t)K1 + 2u * B + 1u + 2u * ncls + ((size_t)ncls << lgP); // T1 T2 guide cacc cnp1 cdf
   if (info_in_smem) w += L;
   if (sig_in_smem) w += (size_t)n_faults + (n_sig + 1u) / 2u;
   return w;

@@ -37,8 +37,8 @@ __device__ __forceinline__ LinSmem lin_carve(uint32_t *sm, const QecLinDev &S, i
   m.hist = m.tally + (size_t)(T / 32) * S.nc;
   m.T1 = m.hist + 64;
   m.T2 = m.T1 + S.K1;
-  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B);
-  m.cacc = m.T2 + 2u * S.B;
+  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B + 1u);
+  m.cacc = m.T2 + 2u * S.B + 1u;
   m.cnp1 = m.cacc + S.n_classes;
   m.cdf = m.cnp1 + S.n_classes;
   uint32_t *p = m.cdf + ((size_t)S.n_classes << S.lgP);
@@ -70,6 +70,11 @@ __device__ __forceinline__ uint32_t ld_s(uint32_t addr) {
 __device__ __forceinline__ uint32_t ld_s16(uint32_t addr) {
   uint32_t v;
   asm volatile("{ .reg .u16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 ld_s64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
   return v;
 }
 __device__ __forceinline__ void st_s(uint32_t addr, uint32_t v) {
@@ -112,7 +117,7 @@ __device__ __forceinline__ uint32_t lin_out_rows(int n_it, uint32_t a, const uin
 
 // Constants of the draw loop that both kernels keep in registers.
 struct LinDraw {
-  uint32_t t1_0, t1_1, t1_2, kb, cdf_s, desc_s, list_s, bw4, P;
+  uint32_t t1_0, t1_1, t1_2, kb, cdf_s, desc_s, list_s, rec_s, bw4, P;
   int lgb;
 };
 
@@ -141,8 +146,12 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
     // next K1 * B slots -- exact by memorylessness)
     uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
     if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
+    // second-level gap: guide bucket, two unconditional steps, then the (rare) rest of the
+    // scan; T2 carries a 0 sentinel at index B, so the steps need no bound check
     uint32_t g = m.G[r.c[1] >> S.gshift];
-    while (g < S.B - 1u && m.T2[1u + g] > r.c[1]) ++g;
+    g += m.T2[1u + g] > r.c[1];
+    g += m.T2[1u + g] > r.c[1];
+    while (m.T2[1u + g] > r.c[1]) ++g;
     const bool has = a < S.K1;
     uint32_t incl = has ? a * S.B + g + 1u : kb;
 #pragma unroll
@@ -164,16 +173,12 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
     if (ok) {
       const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
       uint32_t d;
-      switch (S.lgP) {
-        case 0: d = 0; break;
-        case 1: d = lin_digit<1>(cd, r.c[3]); break;
-        case 2: d = lin_digit<2>(cd, r.c[3]); break;
-        case 3: d = lin_digit<3>(cd, r.c[3]); break;
-        case 4: d = lin_digit<4>(cd, r.c[3]); break;
-        default:
-          d = 0;
-          for (uint32_t step = P >> 1; step; step >>= 1)
-            if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
+      if (S.lgP == 4u) d = lin_digit<4>(cd, r.c[3]);
+      else if (S.lgP == 2u) d = lin_digit<2>(cd, r.c[3]);
+      else {
+        d = 0;
+        for (uint32_t step = P >> 1; step; step >>= 1)
+          if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
       }
       d = min(d, m.cnp1[cls]);
       const uint32_t f = (inf & 0x1FFFFFu) + d;
@@ -186,10 +191,18 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
       } else {
         // 32-byte record: length, then the first 15 clbits (one or two 128-bit loads per
         // fault instead of a descriptor and one 16-bit load per clbit)
+        if (S.rec8) {
+          // 8-byte record: length and up to 7 clbits, one byte each (circuits with <= 255 clbits)
+          const uint2 q = S.rec_in_smem ? ld_s64(dc.rec_s + (f << 3)) : __ldg(reinterpret_cast<const uint2 *>(S.sigrec) + f);
+          const uint32_t len = q.x & 0xFFu;
+#define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
+          QEC_RED(0u, (q.x >> 8) & 0xFFu); QEC_RED(1u, (q.x >> 16) & 0xFFu); QEC_RED(2u, q.x >> 24);
+          QEC_RED(3u, q.y & 0xFFu); QEC_RED(4u, (q.y >> 8) & 0xFFu);
+          QEC_RED(5u, (q.y >> 16) & 0xFFu); QEC_RED(6u, q.y >> 24);
+        } else {
         const uint4 *rec = S.sigrec + (f << S.rec2);
         const uint4 q0 = __ldg(rec);
         const uint32_t len = q0.x & 0xFFFFu;
-#define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
         QEC_RED(0u, q0.x >> 16);
         QEC_RED(1u, q0.y & 0xFFFFu); QEC_RED(2u, q0.y >> 16);
         QEC_RED(3u, q0.z & 0xFFFFu); QEC_RED(4u, q0.z >> 16);
@@ -204,6 +217,7 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
             const uint16_t *li = S.siglist + (__ldg(S.sigdesc + f) & 0x3FFFFFu) + 15u;
             for (uint32_t n = len - 15u; n; --n, ++li) red_xor_s(colb + (uint32_t)__ldg(li) * bw4, msk);
           }
+        }
         }
 #undef QEC_RED
       }
@@ -242,7 +256,7 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     }
   }
   for (uint32_t i = tid; i < S.K1; i += T) m.T1[i] = S.T1[i];
-  for (uint32_t i = tid; i < S.B; i += T) m.T2[i] = S.T2[i];
+  for (uint32_t i = tid; i <= S.B; i += T) m.T2[i] = i < S.B ? S.T2[i] : 0u;
   for (uint32_t k = tid; k < 2u * S.B; k += T) {
     // entries of T2[1..B) greater than the largest r of guide bucket k: where the scan for
     // any r of the bucket may start
@@ -271,6 +285,7 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
   dc.cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
   dc.desc_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.desc) : 0u;
   dc.list_s = S.sig_in_smem ? (uint32_t)__cvta_generic_to_shared(m.list) : 0u;
+  dc.rec_s = 0u;
   dc.bw4 = 4u << lgw;  // bytes per accumulator row
   dc.P = P;
   dc.lgb = lgb;
@@ -389,6 +404,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   const uint32_t wwords = (uint32_t)S.nc * QEC_LINW_BW + 128u + ncp;  // words per warp region
   const uint32_t P = 1u << S.lgP;
   LinSmem m;
+  uint32_t *rec_sm = nullptr;
   m.acc = qec_lin_smem + (size_t)warp * wwords;
   m.cnt = m.acc + (size_t)S.nc * QEC_LINW_BW;
   m.tally = m.cnt + 128;
@@ -396,8 +412,8 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   m.hist = qec_lin_smem + (size_t)NW * wwords;
   m.T1 = m.hist + 64;
   m.T2 = m.T1 + S.K1;
-  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B);
-  m.cacc = m.T2 + 2u * S.B;
+  m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B + 1u);
+  m.cacc = m.T2 + 2u * S.B + 1u;
   m.cnp1 = m.cacc + S.n_classes;
   m.cdf = m.cnp1 + S.n_classes;
   {
@@ -410,9 +426,16 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     }
     m.desc = S.sigdesc;
     m.list = S.siglist;
+    if (S.info_in_smem) p += S.L;
+    p += (2u - ((uint32_t)(p - qec_lin_smem) & 1u)) & 1u;  // 8-byte aligned
+    rec_sm = p;
+    if (S.rec_in_smem) {
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(S.sigrec);
+      for (uint32_t i = tid; i < 2u * S.n_faults; i += T) p[i] = src[i];
+    }
   }
   for (uint32_t i = tid; i < S.K1; i += T) m.T1[i] = S.T1[i];
-  for (uint32_t i = tid; i < S.B; i += T) m.T2[i] = S.T2[i];
+  for (uint32_t i = tid; i <= S.B; i += T) m.T2[i] = i < S.B ? S.T2[i] : 0u;
   for (uint32_t k = tid; k < 2u * S.B; k += T) {
     const uint32_t rmax = (k << S.gshift) | ((1u << S.gshift) - 1u);
     m.G[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1u, rmax);
@@ -436,6 +459,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   dc.kb = S.K1 * S.B;
   dc.cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
   dc.desc_s = 0u; dc.list_s = 0u;
+  dc.rec_s = (uint32_t)__cvta_generic_to_shared(rec_sm);
   dc.bw4 = 4u * QEC_LINW_BW;
   dc.P = P;
   dc.lgb = QEC_LINW_LGB;
@@ -443,7 +467,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   uint32_t h0 = 0, h1 = 0, h2 = 0;
   const long long b0 = shot_lo >> QEC_LINW_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LINW_LGB;
   const long long w_lo = shot_lo >> 5;
-  const bool vec_ok = ((O.n_words | w_lo) & 3) == 0 && ((size_t)O.bits & 15) == 0;
+  const bool vec_ok = ((O.n_words | w_lo) & 7) == 0 && ((size_t)O.bits & 31) == 0;
 
   for (long long b = b0 + (long long)blockIdx.x * NW + warp; b <= b1; b += (long long)gridDim.x * NW) {
     const long long base_shot = b << QEC_LINW_LGB;
@@ -459,8 +483,10 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     const bool whole = w0 >= 0 && w0 + 8 <= O.n_words;
     uint32_t any0 = 0, any1 = 0, any2 = 0, any3 = 0, any4 = 0, any5 = 0, any6 = 0, any7 = 0;
     uint4 mlo = make_uint4(0u, 0u, 0u, 0u), mhi = mlo;  // running XOR along the lane's chain
+    uint32_t e_next = __ldg(S.rowprog + lane);
     for (int step = 0; step < S.n_steps; ++step) {
-      const uint32_t e = __ldg(S.rowprog + step * 32 + lane);
+      const uint32_t e = e_next;
+      if (step + 1 < S.n_steps) e_next = __ldg(S.rowprog + (step + 1) * 32 + lane);
       if (!(e >> 31)) continue;
       const uint32_t c = e & 0xFFFFu;
       const uint32_t a = acc_s + c * 32u;
@@ -475,8 +501,11 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
       if (BITS) {
         uint32_t *po = O.bits + ((long long)c * O.n_words + w0);
         if (whole && vec_ok) {
-          *reinterpret_cast<uint4 *>(po) = mlo;
-          *reinterpret_cast<uint4 *>(po + 4) = mhi;
+          // one 256-bit store = the row's whole 32-byte sector (two 128-bit stores are two
+          // partial-sector writes, and L2 then fetches the sector from DRAM first)
+          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(po), "r"(mlo.x),
+                       "r"(mlo.y), "r"(mlo.z), "r"(mlo.w), "r"(mhi.x), "r"(mhi.y), "r"(mhi.z), "r"(mhi.w)
+                       : "memory");
         } else {
           const uint32_t v[8] = {mlo.x, mlo.y, mlo.z, mlo.w, mhi.x, mhi.y, mhi.z, mhi.w};
 #pragma unroll
