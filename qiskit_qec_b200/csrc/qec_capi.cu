@@ -1108,9 +1108,14 @@ static int sampler_plan_linear(qec_sampler *s) {
     const bool allow = !(lm && !strcmp(lm, "cta")) && f_lgb == 0 && ((long long)s->L << 8) < (1ll << 30);
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
     rec8 = (maxlen_w <= 7 && c->nc <= 255) ? 1 : 0;
-    const int want_rs = rec8 ? env_int("QEC_B200_LIN_RECSMEM", 0) : 0;
+    // 8-byte records go to shared memory when at least 24 warps still fit beside them
+    // (measured at d=5: 24 warps + records in shared memory 1.59 ms per 1e8 shots, 32 warps +
+    // records in L2 1.65 ms)
+    const int rs_env = rec8 ? env_int("QEC_B200_LIN_RECSMEM", 1) : 0;
+    for (int want_rs = rs_env; want_rs >= 0 && !found; --want_rs)
     for (int wz = (w_env > 0 ? w_env : 32); allow && wz >= (w_env > 0 ? w_env : 24) && !found; --wz) {
       for (int is = 1; is >= 0 && !found; --is) {
+        if (want_rs && !is) continue;
         const size_t need = qec_linw_smem_words(c->nc, wz, s->K1, s->B, (uint32_t)s->L,
                                                 (uint32_t)s->n_classes, s->lgP, is,
                                                 want_rs ? 2u * (uint32_t)F : 0u) * 4 + 16;

@@ -92,24 +92,32 @@ __device__ __forceinline__ uint32_t lin_digit(uint32_t cdf_s, uint32_t r) {
 }
 
 // One thread's share of the accumulator read-out: `n_it` row pieces, `a` / `po` / `tl` walk
-// the accumulator column, the output column and this warp's tally row.
+// the accumulator column, the output column and this warp's tally row.  With fewer than 32
+// word columns (FULL = false) a warp spans several rows that may run out at different times:
+// every lane then makes lane 0's number of trips (the most) and idles through the extra ones,
+// so the shuffles always see the whole warp.
 template <bool TALLY, bool BITS, bool FULL>
 __device__ __forceinline__ uint32_t lin_out_rows(int n_it, uint32_t a, const uint32_t a_step,
                                                  uint32_t *po, const long long po_step, uint32_t tl,
                                                  const uint32_t tl_step, const bool inr,
                                                  const bool head, const uint32_t grp) {
   uint32_t anyv = 0;
+  const int trips = FULL ? n_it : __shfl_sync(0xFFFFFFFFu, n_it, 0);
 #pragma unroll 2
-  for (; n_it > 0; --n_it, a += a_step, po += po_step, tl += tl_step) {
-    const uint32_t v = ld_s(a);
-    st_s(a, 0u);
-    if (BITS && inr) *po = v;
+  for (int it = 0; it < trips; ++it, a += a_step, po += po_step, tl += tl_step) {
+    const bool live = FULL || it < n_it;
+    uint32_t v = 0;
+    if (live) {
+      v = ld_s(a);
+      st_s(a, 0u);
+      if (BITS && inr) *po = v;
+    }
     if (TALLY) {
       anyv |= v;
       int cnt = __popc(v);
       if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
       else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
-      if (head) st_s(tl, ld_s(tl) + (uint32_t)cnt);
+      if (head && live) st_s(tl, ld_s(tl) + (uint32_t)cnt);
     }
   }
   return anyv;
