@@ -842,7 +842,7 @@ struct qec_sampler {
   uint32_t B = 32, K1 = 1;
   std::vector<uint32_t> T1, T2, slop, slloc, cls_acc, cls_off, cdf;
   std::vector<uint16_t> slcls;
-  std::vector<uint8_t> cls_always, codes;
+  std::vector<uint8_t> cls_always, codes, cls_uniform;
   double mean_events = 0;  // expected events per 32-shot word
   QecSamplerDev dev{};
   uint32_t *d_T1 = nullptr, *d_T2 = nullptr, *d_slop = nullptr, *d_slloc = nullptr,
@@ -878,6 +878,7 @@ struct qec_sampler {
     uint16_t *d_sigrec = nullptr;
     std::vector<uint32_t> rowprog;
     uint32_t *d_rowprog = nullptr;
+    bool cls_uniform_all = true;
   } lin;
 };
 
@@ -993,6 +994,7 @@ static int sampler_plan_linear(qec_sampler *s) {
     const uint32_t cls = s->slcls[sl], o = s->cls_off[cls], n = s->cls_off[cls + 1] - o;
     if (fop.size() + n >= (1u << 21)) { ln.why = "more than 2^21 distinct faults"; return 0; }
     ln.info.push_back((uint32_t)fop.size() | (cls << 21) | (s->cls_always[cls] ? (1u << 31) : 0u));
+    ln.cls_uniform_all = ln.cls_uniform_all && s->cls_uniform[cls];
     for (uint32_t d = 0; d < n; ++d) {
       fop.push_back((int32_t)s->slop[sl]);
       fpauli.push_back(s->codes[o + d]);
@@ -1196,6 +1198,11 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
   d.rec2 = rec2; d.rowprog = ln.d_rowprog; d.n_steps = n_steps;
   d.rec8 = rec8; d.rec_in_smem = rec_s;
+  d.uniform_digits = ln.cls_uniform_all ? 1 : 0;
+  {  // Philox round keys: constant-bank operands of the kernels' XORs
+    uint32_t k0 = (uint32_t)s->seed, k1 = (uint32_t)(s->seed >> 32);
+    for (int r = 0; r < 10; ++r) { d.rk[2 * r] = k0; d.rk[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  }
   d.k0 = (uint32_t)s->seed; d.k1 = (uint32_t)(s->seed >> 32);
   ln.ctas = ctas;
   ln.cfg.block = threads;
@@ -1264,9 +1271,20 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
       W += class_weight[j];
     }
     if (!(W > 0)) { delete s; return fail(QEC_ERR_INVALID, "class %d has zero total weight", k); }
+    // equal weights (every model the reference ships): thresholds ceil(2^32 (j+1) / n), so
+    // that "entries <= r" is exactly floor(r * n / 2^32) -- one multiply in the fast kernels
+    bool uniform = true;
+    for (int j = class_off[k]; j < class_off[k + 1]; ++j)
+      uniform = uniform && class_weight[j] == class_weight[class_off[k]];
+    s->cls_uniform.push_back(uniform ? 1 : 0);
     double cum = 0;
     for (int j = class_off[k]; j < class_off[k + 1]; ++j) {
       cum += class_weight[j];
+      if (uniform) {
+        const uint64_t num = (uint64_t)(j - class_off[k] + 1) << 32;
+        const uint64_t th = (num + (uint64_t)n - 1) / (uint64_t)n;
+        s->cdf.push_back(th > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)th);
+      } else
       s->cdf.push_back(fix32(cum / W));
       s->codes.push_back(class_codes[j] & 15);
     }

@@ -121,6 +121,8 @@ struct QecLinDev {
   const uint4 *sigrec;      // [n_faults][1 << rec2] uint16 x 8: length, first 7 (15) clbits of the fault
   int rec2;
   int rec8, rec_in_smem;    // 8-byte records (length + 7 clbits as bytes), optionally in shared memory
+  int uniform_digits;       // every class has equal Pauli weights: digit = floor(r * n / 2^32)
+  uint32_t rk[20];          // Philox round keys (k0, k1 of round 0..9)
   // warp-autonomous variant: read-out program, [n_steps][32 lanes]: clbit row | chain start << 30
   // | valid << 31.  A lane XORs the rows of a chain cumulatively (time-difference basis).
   const uint32_t *rowprog;
@@ -374,6 +376,21 @@ __device__ __forceinline__ QecPhilox qec_philox(uint32_t c0, uint32_t c1, uint32
     const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
     c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
     k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  QecPhilox o;
+  o.c[0] = c0; o.c[1] = c1; o.c[2] = c2; o.c[3] = c3;
+  return o;
+}
+
+// the same with the ten round keys precomputed (kernel parameters: constant-bank operands)
+__device__ __forceinline__ QecPhilox qec_philox_rk(uint32_t c0, uint32_t c1, uint32_t c2,
+                                                   uint32_t c3, const uint32_t (&rk)[20]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ rk[2 * r], n2 = hi0 ^ c3 ^ rk[2 * r + 1];
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
   }
   QecPhilox o;
   o.c[0] = c0; o.c[1] = c1; o.c[2] = c2; o.c[3] = c3;

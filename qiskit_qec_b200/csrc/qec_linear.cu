@@ -148,8 +148,8 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
   const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
   int pos = start - 1;
   for (uint32_t it = 0; pos < end; ++it) {
-    const QecPhilox r = qec_philox(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
-                                   S.k0, S.k1);
+    const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
+                                      S.rk);
     // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
     // next K1 * B slots -- exact by memorylessness)
     uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
@@ -181,7 +181,8 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
     if (ok) {
       const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
       uint32_t d;
-      if (S.lgP == 4u) d = lin_digit<4>(cd, r.c[3]);
+      if (S.uniform_digits) d = __umulhi(r.c[3], m.cnp1[cls] + 1u);  // == the cdf count (host: ceil thresholds)
+      else if (S.lgP == 4u) d = lin_digit<4>(cd, r.c[3]);
       else if (S.lgP == 2u) d = lin_digit<2>(cd, r.c[3]);
       else {
         d = 0;
