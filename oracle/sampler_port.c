@@ -80,45 +80,94 @@ int orc_sample_word(const uint32_t *tab, uint64_t gw, int nv, uint32_t *ev_out, 
 }
 
 /*
+ * Computed geometric gap of draw schemes 1 and 2 (qec_gap_len in qec_device.cuh): u = (r | 1) /
+ * 2^32, gap = floor(C * -log2(u)) clamped to 2^24, -log2(u) = (clz + 1) - log2(f) with f the top
+ * 24 bits of the normalised word and log2(f) a degree-7 polynomial in f - 1.5 evaluated with
+ * fused multiply-adds only (fmaf is exact IEEE: the same bits as the GPU's FFMA; this file is
+ * compiled with -ffp-contract=off so that no other operation is fused).
+ */
+#include <math.h>
+#include <string.h>
+#define GAP_CAP 16777216u
+static uint32_t gap_len(uint32_t r, float C) {
+  static const float k[8] = {0.584962785243988f, 0.9617953896522522f, -0.32063233852386475f,
+                             0.14254532754421234f, -0.07058960944414139f, 0.037311289459466934f,
+                             -0.025123370811343193f, 0.015125359408557415f};
+  const uint32_t x = r | 1u;
+  const int n = __builtin_clz(x);
+  const uint32_t fb = ((x << n) >> 8) + 0x3F000000u;
+  float f;
+  memcpy(&f, &fb, 4);
+  const float z = f + -1.5f;
+  float p = k[7];
+  for (int j = 6; j >= 0; --j) p = fmaf(p, z, k[j]);
+  const float l = (float)(n + 1) + -p;
+  const float t = fminf(C * l, (float)GAP_CAP);
+  const int32_t g = (int32_t)t; /* truncation, as __float2int_rz */
+  return g > 0 ? (uint32_t)g : 0u;
+}
+uint32_t orc_gap_len(uint32_t r, float C) { return gap_len(r, C); }
+
+/*
  * Draw order of the linear-response sampler (qec_linear.cu): batches of 2^lgb shots, slot =
  * sorted location << lgb | shot in batch, the slot space cut into n_streams equal ranges, one
  * Philox stream (counter = batch lo, batch hi, draw index, 0x4C000000 | stream) per range.
- * A draw advances by a * B + b + 1 slots to a candidate fault, or -- when the first-level
- * table is exhausted (a == K1) -- by K1 * B slots without one.  Writes the accepted faults of
- * batch `batch` as triples (sorted location, shot in batch, digit) in stream order; returns
- * their number (may exceed cap).  The same tables as above; tab[7] carries lgb and n_streams.
+ * Scheme 0 (tab[7] bits 2-3): a draw advances by a * B + b + 1 slots to a candidate fault, or
+ * -- when the first-level table is exhausted (a == K1) -- by K1 * B slots without one; words
+ * c0, c1 = gap, c2 = class thinning, c3 = Pauli digit.  Schemes 1 / 2: computed gaps (gap_len),
+ * one candidate per draw (c0 gap, c1 digit, c2 thinning) or two (c0 gap, c1 digit; c2 gap, c3
+ * digit; only when no class needs thinning); a clamped gap advances GAP_CAP slots without a
+ * candidate.  The stream's draws are taken 32 at a time (one warp step): a step starts only
+ * while the position is before the stream's end, but then all of its 32 draws are placed.
+ * Writes the accepted faults of batch `batch` as triples (sorted location, shot in batch,
+ * digit) in stream order; returns their number (may exceed cap).  The same tables as above;
+ * tab[7] carries lgb and n_streams, the gap constant C follows the tables.
  */
 int orc_sample_batch(const uint32_t *tab, uint64_t batch, uint32_t *ev_out, int cap) {
   const uint32_t B = tab[0], K1 = tab[1], ncls = tab[2], L = tab[3], np = tab[4];
   const uint32_t k0 = tab[5], k1 = tab[6];
-  const uint32_t lgb = (tab[7] >> 8) & 255u, ns = tab[7] >> 16;
+  const uint32_t lgb = (tab[7] >> 8) & 255u, ns = tab[7] >> 16, scheme = (tab[7] >> 2) & 3u;
   const uint32_t *T1 = tab + 8, *T2 = T1 + K1, *slop = T2 + B, *slloc = slop + L;
   const uint32_t *slcls = slloc + L, *cls_acc = slcls + L, *cls_always = cls_acc + ncls;
-  const uint32_t *cls_off = cls_always + ncls, *cdf = cls_off + ncls + 1;
-  (void)np;
+  const uint32_t *cls_off = cls_always + ncls, *cdf = cls_off + ncls + 1, *codes = cdf + np;
+  float C;
+  memcpy(&C, codes + np, 4);
   if (!(tab[7] & 2u)) return -1;
   const int64_t n_slots = (int64_t)L << lgb;
   const int64_t slen = (n_slots + ns - 1) / ns;
+  const uint32_t nper = scheme == 2u ? 2u : 1u;
   int n = 0;
   for (uint32_t s = 0; s < ns; ++s) {
     const int64_t start = (int64_t)s * slen;
     const int64_t end = start + slen < n_slots ? start + slen : n_slots;
     int64_t pos = start - 1;
-    for (uint32_t draw = 0; pos < end; ++draw) {
+    for (uint32_t draw = 0;; ++draw) {
+      if ((draw & 31u) == 0u && pos >= end) break; /* a warp step starts only before the end */
       uint32_t c[4] = {(uint32_t)batch, (uint32_t)(batch >> 32), draw, 0x4C000000u | s};
       philox4x32_10(c, k0, k1);
-      const uint32_t a = count_greater(T1, K1, c[0]);
-      if (a == K1) { pos += (int64_t)K1 * B; continue; }
-      pos += (int64_t)a * B + count_greater(T2 + 1, B - 1, c[1]) + 1;
-      if (pos >= end) break;
-      const uint32_t sl = (uint32_t)(pos >> lgb), shot = (uint32_t)(pos & ((1u << lgb) - 1u));
-      const uint32_t cls = slcls[sl];
-      if (!cls_always[cls] && c[2] >= cls_acc[cls]) continue;
-      const uint32_t base = cls_off[cls], npc = cls_off[cls + 1] - base;
-      uint32_t d = 0;
-      while (d + 1 < npc && c[3] >= cdf[base + d]) ++d;
-      if (n < cap) { ev_out[3 * n] = sl; ev_out[3 * n + 1] = shot; ev_out[3 * n + 2] = d; }
-      ++n;
+      for (uint32_t j = 0; j < nper; ++j) {
+        uint32_t rd, rt = c[2];
+        if (scheme == 0u) {
+          const uint32_t a = count_greater(T1, K1, c[0]);
+          if (a == K1) { pos += (int64_t)K1 * B; continue; }
+          pos += (int64_t)a * B + count_greater(T2 + 1, B - 1, c[1]) + 1;
+          rd = c[3];
+        } else {
+          const uint32_t g = gap_len(c[2 * j], C);
+          if (g >= GAP_CAP) { pos += GAP_CAP; continue; }
+          pos += (int64_t)g + 1;
+          rd = c[2 * j + 1];
+        }
+        if (pos >= end) continue;
+        const uint32_t sl = (uint32_t)(pos >> lgb), shot = (uint32_t)(pos & ((1u << lgb) - 1u));
+        const uint32_t cls = slcls[sl];
+        if (!cls_always[cls] && rt >= cls_acc[cls]) continue;
+        const uint32_t base = cls_off[cls], npc = cls_off[cls + 1] - base;
+        uint32_t d = 0;
+        while (d + 1 < npc && rd >= cdf[base + d]) ++d;
+        if (n < cap) { ev_out[3 * n] = sl; ev_out[3 * n + 1] = shot; ev_out[3 * n + 2] = d; }
+        ++n;
+      }
     }
   }
   return n;

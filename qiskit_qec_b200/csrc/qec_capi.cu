@@ -844,6 +844,7 @@ struct qec_sampler {
   std::vector<uint16_t> slcls;
   std::vector<uint8_t> cls_always, codes, cls_uniform;
   double mean_events = 0;  // expected events per 32-shot word
+  double pmax = 0;         // largest class probability in use
   QecSamplerDev dev{};
   uint32_t *d_T1 = nullptr, *d_T2 = nullptr, *d_slop = nullptr, *d_slloc = nullptr,
            *d_cls_acc = nullptr, *d_cls_off = nullptr, *d_cdf = nullptr;
@@ -879,6 +880,8 @@ struct qec_sampler {
     std::vector<uint32_t> rowprog;
     uint32_t *d_rowprog = nullptr;
     bool cls_uniform_all = true;
+    std::vector<uint32_t> info2;
+    uint32_t *d_info2 = nullptr;
   } lin;
 };
 
@@ -990,16 +993,31 @@ static int sampler_plan_linear(qec_sampler *s) {
   std::vector<int32_t> fop;
   std::vector<uint8_t> fpauli;
   ln.info.clear();
+  ln.info2.clear();
+  bool all_always = true;
   for (int sl = 0; sl < s->L; ++sl) {
     const uint32_t cls = s->slcls[sl], o = s->cls_off[cls], n = s->cls_off[cls + 1] - o;
     if (fop.size() + n >= (1u << 21)) { ln.why = "more than 2^21 distinct faults"; return 0; }
     ln.info.push_back((uint32_t)fop.size() | (cls << 21) | (s->cls_always[cls] ? (1u << 31) : 0u));
+    ln.info2.push_back((uint32_t)fop.size());
+    ln.info2.push_back(n);
     ln.cls_uniform_all = ln.cls_uniform_all && s->cls_uniform[cls];
+    all_always = all_always && s->cls_always[cls];
     for (uint32_t d = 0; d < n; ++d) {
       fop.push_back((int32_t)s->slop[sl]);
       fpauli.push_back(s->codes[o + d]);
     }
   }
+  // draw scheme: computed 32-bit gaps (two candidates per Philox call when no class needs
+  // thinning) unless pmax is so small that one 32-bit word no longer resolves single slots
+  int draw = s->pmax >= 0x1p-20 ? (all_always ? 2 : 1) : 0;
+  if (const char *dm = std::getenv("QEC_B200_LIN_DRAW")) {
+    if (!strcmp(dm, "table")) draw = 0;
+    else if (!strcmp(dm, "computed")) draw = all_always ? 2 : 1;
+    else if (!strcmp(dm, "computed1")) draw = 1;
+    else return fail(QEC_ERR_INVALID, "QEC_B200_LIN_DRAW must be table, computed or computed1");
+  }
+  const uint32_t tK1 = draw ? 0u : s->K1, tB = draw ? 0u : s->B;  // gap tables only with scheme 0
   const int64_t F = (int64_t)fop.size();
   path_off.resize(F + 1);
   for (int64_t f = 0; f <= F; ++f) path_off[f] = f;
@@ -1086,7 +1104,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   int lgb = 0, ctas = 0, info_s = 0, sig_s = 0;
   size_t smem = 0;
   auto words = [&](int lg, int is, int ss) {
-    return qec_lin_smem_words(c->nc, lg, T, s->K1, s->B, (uint32_t)s->L, (uint32_t)s->n_classes,
+    return qec_lin_smem_words(c->nc, lg, T, tK1, tB, (uint32_t)s->L, (uint32_t)s->n_classes,
                               s->lgP, (uint32_t)F, n_sig, is, ss) * 4 + 16;
   };
   auto try_cfg = [&](int ct, int lg) {
@@ -1102,7 +1120,7 @@ static int sampler_plan_linear(qec_sampler *s) {
     return true;
   };
   bool found = false;
-  int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0;
+  int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0;
   {
     // warp-autonomous variant (256-shot batches, one warp each) when at least 24 warps'
     // accumulators fit next to the tables: no CTA barriers, row-parallel read-out
@@ -1118,12 +1136,16 @@ static int sampler_plan_linear(qec_sampler *s) {
     for (int wz = (w_env > 0 ? w_env : 32); allow && wz >= (w_env > 0 ? w_env : 24) && !found; --wz) {
       for (int is = 1; is >= 0 && !found; --is) {
         if (want_rs && !is) continue;
-        const size_t need = qec_linw_smem_words(c->nc, wz, s->K1, s->B, (uint32_t)s->L,
+        // lean kernel: scheme 2, equal Pauli weights, records and {first fault, n} in shared memory
+        const int want_fast = want_rs && is && draw == 2 && ln.cls_uniform_all &&
+                              env_int("QEC_B200_LIN_FAST", 1) != 0;
+        const size_t need = qec_linw_smem_words(c->nc, wz, tK1, tB, (uint32_t)s->L,
                                                 (uint32_t)s->n_classes, s->lgP, is,
-                                                want_rs ? 2u * (uint32_t)F : 0u) * 4 + 16;
+                                                (want_rs ? 2u * (uint32_t)F : 0u) +
+                                                    (want_fast ? 2u * (uint32_t)s->L : 0u)) * 4 + 16;
         if (need > di.smem_optin) continue;
         found = true; warp_mode = 1; threads = 32 * wz; ctas = 1; lgb = 8; info_s = is; sig_s = 0;
-        rec_s = want_rs;
+        rec_s = want_rs; fast = want_fast;
         smem = need;
       }
     }
@@ -1162,8 +1184,8 @@ static int sampler_plan_linear(qec_sampler *s) {
       return 0;
     }
     ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
-    if (rec8) {  // bytes: length, 7 clbits
-      uint8_t by[8] = {(uint8_t)len, 0, 0, 0, 0, 0, 0, 0};
+    if (rec8) {  // bytes: validity mask of the entries (2^len - 1), 7 clbits
+      uint8_t by[8] = {(uint8_t)((1u << len) - 1u), 0, 0, 0, 0, 0, 0, 0};
       for (size_t k = 0; k < len; ++k) by[1 + k] = (uint8_t)lists[f][k];
       for (int k = 0; k < 4; ++k) ln.sigrec.push_back((uint16_t)(by[2 * k] | (by[2 * k + 1] << 8)));
     } else {
@@ -1176,7 +1198,8 @@ static int sampler_plan_linear(qec_sampler *s) {
   if (ln.rowprog.empty()) ln.rowprog.push_back(0u);
   if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
-      (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)))
+      (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)) ||
+      (rc = upload(ln.info2, &ln.d_info2)))
     return rc;
   {
     const int e = qec_lin_set_smem_attr(smem);
@@ -1186,9 +1209,16 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.nc = c->nc; d.L = s->L; d.lgb = lgb; d.n_streams = ns;
   d.n_slots = (uint32_t)s->L << lgb;
   d.slen = (d.n_slots + (uint32_t)ns - 1u) / (uint32_t)ns;
-  d.B = s->B; d.K1 = s->K1;
+  d.B = tB; d.K1 = tK1;
   d.gshift = 32;
   while ((1u << (32 - d.gshift)) < 2u * s->B) --d.gshift;
+  d.draw = draw;
+  {
+    const double l2q = std::log2(1.0 - s->pmax);  // -inf when pmax == 1: every slot is a candidate
+    d.gapC = std::isinf(l2q) ? 0.0f : (float)(-1.0 / l2q);
+  }
+  d.info2 = reinterpret_cast<const uint2 *>(ln.d_info2);
+  d.fast = fast;
   d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
   d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
   d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;
@@ -1257,6 +1287,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
     s->loc_p.push_back(p);
   }
   s->mean_events = 32.0 * psum;
+  s->pmax = pmax;
   // classes
   s->cls_off.assign(n_classes + 1, 0);
   for (int k = 0; k < n_classes; ++k) {
@@ -1372,7 +1403,7 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
-                  s->lin.d_sigrec, s->lin.d_rowprog};
+                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1386,9 +1417,12 @@ extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, 
   v.insert(v.end(), {s->B, s->K1, ncls, (uint32_t)s->L, np, (uint32_t)s->seed,
                      (uint32_t)(s->seed >> 32),
                      // bit 0: some fault can occur; bit 1: linear-response draw order (batches
-                     // of 2^lgb shots, n_streams streams each), lgb << 8, n_streams << 16
+                     // of 2^lgb shots, n_streams streams each), lgb << 8, n_streams << 16;
+                     // bits 2-3: draw scheme of the linear sampler (QecLinDev::draw); its gap
+                     // constant follows the tables as one extra word (float bits)
                      (uint32_t)(s->dev.n_slots > 0) |
-                         (s->lin.eligible ? (2u | ((uint32_t)s->lin.dev.lgb << 8) |
+                         (s->lin.eligible ? (2u | ((uint32_t)s->lin.dev.draw << 2) |
+                                                 ((uint32_t)s->lin.dev.lgb << 8) |
                                                  ((uint32_t)s->lin.dev.n_streams << 16))
                                           : 0u)});
   v.insert(v.end(), s->T1.begin(), s->T1.end());
@@ -1401,6 +1435,11 @@ extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, 
   v.insert(v.end(), s->cls_off.begin(), s->cls_off.end());
   v.insert(v.end(), s->cdf.begin(), s->cdf.end());
   for (uint8_t x : s->codes) v.push_back(x);
+  {
+    uint32_t cb = 0;
+    memcpy(&cb, &s->lin.dev.gapC, 4);
+    v.push_back(cb);
+  }
   if (n) *n = (int)v.size();
   if (buf) {
     if (cap < (int)v.size()) return fail(QEC_ERR_LIMIT, "table buffer too small (%zu needed)", v.size());
@@ -1431,7 +1470,8 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
                     " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
-                    (d.sig_in_smem ? " sig=smem" : " sig=global") +
+                    (d.sig_in_smem ? " sig=smem" : " sig=global") + " draw=" + std::to_string(d.draw) +
+                    (d.fast ? " lean" : "") +
                     (d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B"));
     return 0;
   }

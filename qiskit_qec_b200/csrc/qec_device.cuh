@@ -131,7 +131,25 @@ struct QecLinDev {
   int info_in_smem, sig_in_smem;
   int warp_mode;            // 1: k_sample_linw (lgb = 8, one warp per batch)
   uint32_t k0, k1;
+  // draw scheme: 0 = two-level gap tables (64 bits per gap; any p), 1 / 2 = computed gap
+  // (qec_gap_len: 32 bits per gap) with 1 / 2 candidate faults per Philox call (2 when no class
+  // needs thinning).  Results depend on the scheme, never on the launch geometry.
+  int draw;
+  float gapC;               // -1 / log2(1 - pmax)
+  const uint2 *info2;       // [L] {first fault of sl, number of Paulis of sl} (lean warp kernel)
+  int fast;                 // lean warp kernel eligible: draw 2, uniform digits, 8-byte records and info2 in smem
 };
+
+// Computed geometric gap (draw schemes 1 and 2).  u = (r | 1) / 2^32 is uniform on (0, 1);
+// the gap is floor(C * -log2(u)), C = -1 / log2(1 - pmax), so that P(gap >= k) = (1-pmax)^k.
+// -log2(u) = (clz + 1) - log2(f), f in [1, 2) the top 24 bits of the normalised word; log2(f)
+// by a degree-7 minimax polynomial in f - 1.5 (|error| < 2.8e-7) evaluated with IEEE fused
+// multiply-adds only, so that the CPU restatement (oracle/sampler_port.c: fmaf) reproduces every
+// gap bit for bit.  Gaps are clamped to QEC_GAP_CAP: a clamped draw advances the stream by
+// QEC_GAP_CAP slots without a candidate (exact by memorylessness).
+#define QEC_GAP_CAP 16777216u
+#define QEC_GAP_COEFFS {0.584962785243988f, 0.9617953896522522f, -0.32063233852386475f, 0.14254532754421234f, \
+                        -0.07058960944414139f, 0.037311289459466934f, -0.025123370811343193f, 0.015125359408557415f}
 
 // shared-memory words of the warp-autonomous variant (256-shot batches, `warps` warps per CTA)
 static inline __host__ __device__ size_t qec_linw_smem_words(int nc, int warps, uint32_t K1, uint32_t B,
@@ -395,6 +413,21 @@ __device__ __forceinline__ QecPhilox qec_philox_rk(uint32_t c0, uint32_t c1, uin
   QecPhilox o;
   o.c[0] = c0; o.c[1] = c1; o.c[2] = c2; o.c[3] = c3;
   return o;
+}
+
+// gap of one 32-bit draw, clamped to QEC_GAP_CAP (see the comment at QecLinDev)
+__device__ __forceinline__ uint32_t qec_gap_len(uint32_t r, float C) {
+  const float k[8] = QEC_GAP_COEFFS;
+  const uint32_t x = r | 1u;
+  const int n = __clz((int)x);
+  const float f = __uint_as_float(((x << n) >> 8) + 0x3F000000u);
+  const float z = __fadd_rn(f, -1.5f);
+  float p = k[7];
+#pragma unroll
+  for (int j = 6; j >= 0; --j) p = __fmaf_rn(p, z, k[j]);
+  const float l = __fadd_rn((float)(n + 1), -p);
+  const float t = fminf(__fmul_rn(C, l), (float)QEC_GAP_CAP);
+  return (uint32_t)max(__float2int_rz(t), 0);
 }
 
 // number of entries of the non-increasing table t[0..n) that are > r

@@ -129,86 +129,60 @@ struct LinDraw {
   int lgb;
 };
 
-// One fault stream of one batch, walked by one warp: 32 draws per step (lane = draw), a warp
-// prefix sum of the gaps, then every lane resolves its candidate (class thinning, Pauli digit)
-// and XORs the fault's clbit list into the accumulator at shared address acc_s (row pitch
-// dc.bw4 bytes) with shared-memory reductions.
+// One candidate fault at stream position p: range checks, class thinning (word rt), Pauli digit
+// (word rd), then the fault's clbit list is XORed into the accumulator at shared address acc_s
+// (row pitch dc.bw4 bytes) with shared-memory reductions.
 template <bool TALLY>
-__device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m, const LinDraw &dc,
-                                           const int s, const int lane, const uint32_t blo,
-                                           const uint32_t bhi, const uint32_t slo, const uint32_t shi,
-                                           const long long base_shot, const long long w_lo,
-                                           const uint32_t acc_s, const uint32_t cnt_s,
-                                           const QecSampleExport &X) {
+__device__ __forceinline__ void lin_apply(const QecLinDev &S, const LinSmem &m, const LinDraw &dc,
+                                          const int p, const bool has, const uint32_t rd,
+                                          const uint32_t rt, const int end, const uint32_t slo,
+                                          const uint32_t shi, const long long base_shot,
+                                          const long long w_lo, const uint32_t acc_s,
+                                          const uint32_t cnt_s, const QecSampleExport &X) {
   const int lgb = dc.lgb;
-  const uint32_t BATCH = 1u << lgb, P = dc.P, bw4 = dc.bw4, kb = dc.kb;
-  const uint32_t t1_0 = dc.t1_0, t1_1 = dc.t1_1, t1_2 = dc.t1_2;
+  const uint32_t BATCH = 1u << lgb, P = dc.P, bw4 = dc.bw4;
   const uint32_t cdf_s = dc.cdf_s, desc_s = dc.desc_s, list_s = dc.list_s;
-  const int start = (int)((uint32_t)s * S.slen);
-  const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
-  int pos = start - 1;
-  for (uint32_t it = 0; pos < end; ++it) {
-    const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
-                                      S.rk);
-    // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
-    // next K1 * B slots -- exact by memorylessness)
-    uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
-    if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
-    // second-level gap: guide bucket, two unconditional steps, then the (rare) rest of the
-    // scan; T2 carries a 0 sentinel at index B, so the steps need no bound check
-    uint32_t g = m.G[r.c[1] >> S.gshift];
-    g += m.T2[1u + g] > r.c[1];
-    g += m.T2[1u + g] > r.c[1];
-    while (m.T2[1u + g] > r.c[1]) ++g;
-    const bool has = a < S.K1;
-    uint32_t incl = has ? a * S.B + g + 1u : kb;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-      if (lane >= o) incl += t;
+  const uint32_t sl = (uint32_t)p >> lgb, shot = (uint32_t)p & (BATCH - 1u);
+  bool ok = has && p < end && shot >= slo && shot < shi;  // inside the requested range
+  uint32_t inf = 0, cls = 0;
+  if (ok) {
+    inf = m.info[sl];
+    cls = (inf >> 21) & 1023u;
+    ok = (inf >> 31) || rt < m.cacc[cls];  // class thinning
+  }
+  if (ok) {
+    const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
+    uint32_t d;
+    if (S.uniform_digits) d = __umulhi(rd, m.cnp1[cls] + 1u);  // == the cdf count (host: ceil thresholds)
+    else if (S.lgP == 4u) d = lin_digit<4>(cd, rd);
+    else if (S.lgP == 2u) d = lin_digit<2>(cd, rd);
+    else {
+      d = 0;
+      for (uint32_t step = P >> 1; step; step >>= 1)
+        if (ld_s(cd + ((d + step - 1u) << 2)) <= rd) d += step;
     }
-    const int p = pos + (int)incl;
-    pos = __shfl_sync(0xFFFFFFFFu, p, 31);
-    // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
-    const uint32_t sl = (uint32_t)p >> lgb, shot = (uint32_t)p & (BATCH - 1u);
-    bool ok = has && p < end && shot >= slo && shot < shi;  // inside the requested range
-    uint32_t inf = 0, cls = 0;
-    if (ok) {
-      inf = m.info[sl];
-      cls = (inf >> 21) & 1023u;
-      ok = (inf >> 31) || r.c[2] < m.cacc[cls];  // class thinning
-    }
-    if (ok) {
-      const uint32_t cd = cdf_s + (cls << (S.lgP + 2u));
-      uint32_t d;
-      if (S.uniform_digits) d = __umulhi(r.c[3], m.cnp1[cls] + 1u);  // == the cdf count (host: ceil thresholds)
-      else if (S.lgP == 4u) d = lin_digit<4>(cd, r.c[3]);
-      else if (S.lgP == 2u) d = lin_digit<2>(cd, r.c[3]);
-      else {
-        d = 0;
-        for (uint32_t step = P >> 1; step; step >>= 1)
-          if (ld_s(cd + ((d + step - 1u) << 2)) <= r.c[3]) d += step;
-      }
-      d = min(d, m.cnp1[cls]);
-      const uint32_t f = (inf & 0x1FFFFFu) + d;
-      const uint32_t colb = acc_s + ((shot >> 5) << 2);
-      const uint32_t msk = 1u << (shot & 31u);
-      if (S.sig_in_smem) {
-        const uint32_t desc = ld_s(desc_s + (f << 2));
-        uint32_t li = list_s + ((desc & 0x3FFFFFu) << 1);
-        for (uint32_t n = desc >> 22; n; --n, li += 2u) red_xor_s(colb + ld_s16(li) * bw4, msk);
+    d = min(d, m.cnp1[cls]);
+    const uint32_t f = (inf & 0x1FFFFFu) + d;
+    const uint32_t colb = acc_s + ((shot >> 5) << 2);
+    const uint32_t msk = 1u << (shot & 31u);
+    if (S.sig_in_smem) {
+      const uint32_t desc = ld_s(desc_s + (f << 2));
+      uint32_t li = list_s + ((desc & 0x3FFFFFu) << 1);
+      for (uint32_t n = desc >> 22; n; --n, li += 2u) red_xor_s(colb + ld_s16(li) * bw4, msk);
+    } else {
+      if (S.rec8) {
+        // 8-byte record: validity mask of the entries, then up to 7 clbits, one byte each
+        // (circuits with <= 255 clbits)
+        const uint2 q = S.rec_in_smem ? ld_s64(dc.rec_s + (f << 3)) : __ldg(reinterpret_cast<const uint2 *>(S.sigrec) + f);
+#define QEC_RED8(K, E) if (q.x & (1u << (K))) red_xor_s(colb + (E) * bw4, msk)
+        QEC_RED8(0, (q.x >> 8) & 0xFFu); QEC_RED8(1, (q.x >> 16) & 0xFFu); QEC_RED8(2, q.x >> 24);
+        QEC_RED8(3, q.y & 0xFFu); QEC_RED8(4, (q.y >> 8) & 0xFFu);
+        QEC_RED8(5, (q.y >> 16) & 0xFFu); QEC_RED8(6, q.y >> 24);
+#undef QEC_RED8
       } else {
-        // 32-byte record: length, then the first 15 clbits (one or two 128-bit loads per
-        // fault instead of a descriptor and one 16-bit load per clbit)
-        if (S.rec8) {
-          // 8-byte record: length and up to 7 clbits, one byte each (circuits with <= 255 clbits)
-          const uint2 q = S.rec_in_smem ? ld_s64(dc.rec_s + (f << 3)) : __ldg(reinterpret_cast<const uint2 *>(S.sigrec) + f);
-          const uint32_t len = q.x & 0xFFu;
+        // 16 / 32-byte record: length, then the first 7 / 15 clbits (one or two 128-bit loads
+        // per fault instead of a descriptor and one 16-bit load per clbit)
 #define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
-          QEC_RED(0u, (q.x >> 8) & 0xFFu); QEC_RED(1u, (q.x >> 16) & 0xFFu); QEC_RED(2u, q.x >> 24);
-          QEC_RED(3u, q.y & 0xFFu); QEC_RED(4u, (q.y >> 8) & 0xFFu);
-          QEC_RED(5u, (q.y >> 16) & 0xFFu); QEC_RED(6u, q.y >> 24);
-        } else {
         const uint4 *rec = S.sigrec + (f << S.rec2);
         const uint4 q0 = __ldg(rec);
         const uint32_t len = q0.x & 0xFFFFu;
@@ -227,17 +201,78 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
             for (uint32_t n = len - 15u; n; --n, ++li) red_xor_s(colb + (uint32_t)__ldg(li) * bw4, msk);
           }
         }
-        }
 #undef QEC_RED
       }
-      if (TALLY) red_add_s(cnt_s + ((shot >> 1) << 2), 1u << ((shot & 1u) << 4));
-      if (X.cnt) {
-        const long long wr = ((base_shot + shot) >> 5) - w_lo;
-        const uint32_t k = atomicAdd(X.cnt + wr, 1u);
-        if (k < (uint32_t)X.cap)
-          X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
+    }
+    if (TALLY) red_add_s(cnt_s + ((shot >> 1) << 2), 1u << ((shot & 1u) << 4));
+    if (X.cnt) {
+      const long long wr = ((base_shot + shot) >> 5) - w_lo;
+      const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+      if (k < (uint32_t)X.cap)
+        X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
+    }
+  }
+}
+
+// One fault stream of one batch, walked by one warp: 32 Philox calls per step (lane = call),
+// each giving one candidate fault (draw schemes 0 and 1) or two (scheme 2); a warp prefix sum
+// of the gaps places them, then every lane resolves its candidates (lin_apply).
+template <bool TALLY>
+__device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m, const LinDraw &dc,
+                                           const int s, const int lane, const uint32_t blo,
+                                           const uint32_t bhi, const uint32_t slo, const uint32_t shi,
+                                           const long long base_shot, const long long w_lo,
+                                           const uint32_t acc_s, const uint32_t cnt_s,
+                                           const QecSampleExport &X) {
+  const uint32_t kb = dc.kb;
+  const uint32_t t1_0 = dc.t1_0, t1_1 = dc.t1_1, t1_2 = dc.t1_2;
+  const int start = (int)((uint32_t)s * S.slen);
+  const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
+  const int draw = S.draw;
+  int pos = start - 1;
+  for (uint32_t it = 0; pos < end; ++it) {
+    const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
+                                      S.rk);
+    uint32_t len0, len1 = 0u, rd0, rd1 = 0u;
+    bool has0, has1 = false;
+    if (draw == 0) {
+      // first-level gap a = entries of T1 above r0 (a == K1: the table ends, no fault in the
+      // next K1 * B slots -- exact by memorylessness)
+      uint32_t a = (t1_0 > r.c[0]) + (t1_1 > r.c[0]) + (t1_2 > r.c[0]);
+      if (a == 3u) while (a < S.K1 && m.T1[a] > r.c[0]) ++a;
+      // second-level gap: guide bucket, two unconditional steps, then the (rare) rest of the
+      // scan; T2 carries a 0 sentinel at index B, so the steps need no bound check
+      uint32_t g = m.G[r.c[1] >> S.gshift];
+      g += m.T2[1u + g] > r.c[1];
+      g += m.T2[1u + g] > r.c[1];
+      while (m.T2[1u + g] > r.c[1]) ++g;
+      has0 = a < S.K1;
+      len0 = has0 ? a * S.B + g + 1u : kb;
+      rd0 = r.c[3];
+    } else {
+      const uint32_t g0 = qec_gap_len(r.c[0], S.gapC);
+      has0 = g0 < QEC_GAP_CAP;
+      len0 = g0 + (has0 ? 1u : 0u);
+      rd0 = r.c[1];
+      if (draw == 2) {
+        const uint32_t g1 = qec_gap_len(r.c[2], S.gapC);
+        has1 = g1 < QEC_GAP_CAP;
+        len1 = g1 + (has1 ? 1u : 0u);
+        rd1 = r.c[3];
       }
     }
+    uint32_t incl = len0 + len1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int p1 = pos + (int)incl, p0 = p1 - (int)len1;
+    pos = __shfl_sync(0xFFFFFFFFu, p1, 31);
+    // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
+    lin_apply<TALLY>(S, m, dc, p0, has0, rd0, r.c[2], end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    if (draw == 2)
+      lin_apply<TALLY>(S, m, dc, p1, has1, rd1, 0u, end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
   }
 }
 
@@ -388,11 +423,12 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
 // Warp-autonomous variant for circuits with few clbits: batch = 256 shots, one stream, owned by
 // ONE warp with a private accumulator acc[nc][8 words] -- no CTA barrier between drawing and
 // read-out, no accumulator traffic between warps.  Read-out is row-parallel: lane = clbit, a
-// lane moves its row's 32 bytes with two 128-bit loads / stores, sums its popcounts in
-// registers and updates its own tally entry without a warp reduction.
+// lane moves its row's 32 bytes with two 128-bit loads and one 256-bit store, sums its popcounts
+// in registers and updates its own tally entry without a warp reduction.
 // Shared memory: [warp regions: acc nc*8 | cnt 128 | tally nc (padded to 4)] then the tables.
 #define QEC_LINW_LGB 8
 #define QEC_LINW_BW 8u
+#define QEC_LINW_REGSTEPS 8  // read-out programs up to this many steps live in registers
 
 __device__ __forceinline__ uint4 ld_s128(uint32_t addr) {
   uint4 v;
@@ -402,8 +438,125 @@ __device__ __forceinline__ uint4 ld_s128(uint32_t addr) {
 __device__ __forceinline__ void st_s128z(uint32_t addr) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(addr), "r"(0u) : "memory");
 }
+// predicated shared-memory reductions (no branch: the two candidates of a lane interleave)
+__device__ __forceinline__ void red_xor_if(uint32_t cond, uint32_t addr, uint32_t v) {
+  asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.xor.b32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_add_if(uint32_t cond, uint32_t addr, uint32_t v) {
+  asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
+}
 
+// Lean path of the warp variant (draw scheme 2, equal Pauli weights, 8-byte records and
+// {first fault, number of Paulis} per location in shared memory): one candidate, branch-free.
+// A lane without a fault reads location 0's tables and has every reduction predicated off.
+template <bool TALLY>
+__device__ __forceinline__ void linw_apply_fast(const QecLinDev &S, const int p, const bool has,
+                                                const uint32_t rd, const int end, const uint32_t slo,
+                                                const uint32_t nsh, const uint32_t info2_s,
+                                                const uint32_t rec_s, const uint32_t acc_s,
+                                                const uint32_t cnt_s, const long long base_shot,
+                                                const long long w_lo, const QecSampleExport &X) {
+  const uint32_t shot = (uint32_t)p & 255u;
+  const bool ok = has && p < end && (shot - slo) < nsh;
+  const uint32_t sl = ok ? (uint32_t)p >> QEC_LINW_LGB : 0u;
+  const uint2 inf = ld_s64(info2_s + (sl << 3));
+  const uint32_t d = __umulhi(rd, inf.y);
+  const uint2 q = ld_s64(rec_s + ((inf.x + d) << 3));
+  const uint32_t vm = ok ? q.x : 0u;  // bits 0..6: entry k of the record is present
+  const uint32_t colb = acc_s + ((shot >> 3) & 0x1Cu);
+  const uint32_t msk = 1u << (shot & 31u);
+  red_xor_if(vm & 1u, colb + (__byte_perm(q.x, 0u, 0x4441u) << 5), msk);
+  red_xor_if(vm & 2u, colb + (__byte_perm(q.x, 0u, 0x4442u) << 5), msk);
+  red_xor_if(vm & 4u, colb + (__byte_perm(q.x, 0u, 0x4443u) << 5), msk);
+  red_xor_if(vm & 8u, colb + (__byte_perm(q.y, 0u, 0x4440u) << 5), msk);
+  red_xor_if(vm & 16u, colb + (__byte_perm(q.y, 0u, 0x4441u) << 5), msk);
+  red_xor_if(vm & 32u, colb + (__byte_perm(q.y, 0u, 0x4442u) << 5), msk);
+  red_xor_if(vm & 64u, colb + (__byte_perm(q.y, 0u, 0x4443u) << 5), msk);
+  if (TALLY) red_add_if(ok ? 1u : 0u, cnt_s + ((shot << 1) & 0x1FCu), 1u << ((shot & 1u) << 4));
+  if (X.cnt) {
+    if (ok) {
+      const long long wr = ((base_shot + shot) >> 5) - w_lo;
+      const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+      if (k < (uint32_t)X.cap) X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | ((shot & 31u) << 9) | d;
+    }
+  }
+}
+
+template <bool TALLY>
+__device__ __forceinline__ void linw_stream_fast(const QecLinDev &S, const int s, const int lane,
+                                                 const uint32_t blo, const uint32_t bhi,
+                                                 const uint32_t slo, const uint32_t shi,
+                                                 const uint32_t info2_s, const uint32_t rec_s,
+                                                 const uint32_t acc_s, const uint32_t cnt_s,
+                                                 const long long base_shot, const long long w_lo,
+                                                 const QecSampleExport &X) {
+  const int start = (int)((uint32_t)s * S.slen);
+  const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
+  const uint32_t nsh = shi - slo;
+  const float C = S.gapC;
+  int pos = start - 1;
+  for (uint32_t it = 0; pos < end; ++it) {
+    const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
+                                      S.rk);
+    const uint32_t g0 = qec_gap_len(r.c[0], C), g1 = qec_gap_len(r.c[2], C);
+    const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP;
+    const uint32_t len1 = g1 + (has1 ? 1u : 0u);
+    uint32_t incl = g0 + (has0 ? 1u : 0u) + len1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    const int p1 = pos + (int)incl, p0 = p1 - (int)len1;
+    pos = __shfl_sync(0xFFFFFFFFu, p1, 31);
+    linw_apply_fast<TALLY>(S, p0, has0, r.c[1], end, slo, nsh, info2_s, rec_s, acc_s, cnt_s, base_shot, w_lo, X);
+    linw_apply_fast<TALLY>(S, p1, has1, r.c[3], end, slo, nsh, info2_s, rec_s, acc_s, cnt_s, base_shot, w_lo, X);
+  }
+}
+
+// One read-out step of a lane: row e of the accumulator is folded into the running XOR of the
+// lane's chain (time-difference basis), cleared, stored (one 256-bit store = the row's whole
+// 32-byte sector; two 128-bit stores are two partial-sector writes, and L2 then fetches the
+// sector from DRAM first) and counted.
 template <bool TALLY, bool BITS>
+__device__ __forceinline__ void linw_row(const uint32_t e, const uint32_t acc_s, const uint32_t tal_s,
+                                         uint4 &mlo, uint4 &mhi, uint4 &alo, uint4 &ahi,
+                                         const QecOutDev &O, const long long w0, const bool fastst) {
+  if (!(e >> 31)) return;
+  const uint32_t c = e & 0xFFFFu;
+  const uint32_t a = acc_s + c * 32u;
+  const uint4 lo4 = ld_s128(a), hi4 = ld_s128(a + 16u);
+  st_s128z(a);
+  st_s128z(a + 16u);
+  const uint32_t keep = (e & (1u << 30)) ? 0u : 0xFFFFFFFFu;  // a chain starts: drop the running XOR
+  mlo.x = (mlo.x & keep) ^ lo4.x; mlo.y = (mlo.y & keep) ^ lo4.y;
+  mlo.z = (mlo.z & keep) ^ lo4.z; mlo.w = (mlo.w & keep) ^ lo4.w;
+  mhi.x = (mhi.x & keep) ^ hi4.x; mhi.y = (mhi.y & keep) ^ hi4.y;
+  mhi.z = (mhi.z & keep) ^ hi4.z; mhi.w = (mhi.w & keep) ^ hi4.w;
+  if (BITS) {
+    uint32_t *po = O.bits + ((long long)c * O.n_words + w0);
+    if (fastst) {
+      asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(po), "r"(mlo.x),
+                   "r"(mlo.y), "r"(mlo.z), "r"(mlo.w), "r"(mhi.x), "r"(mhi.y), "r"(mhi.z), "r"(mhi.w)
+                   : "memory");
+    } else {
+      const uint32_t v[8] = {mlo.x, mlo.y, mlo.z, mlo.w, mhi.x, mhi.y, mhi.z, mhi.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (w0 + j >= 0 && w0 + j < O.n_words) po[j] = v[j];
+    }
+  }
+  if (TALLY) {
+    alo.x |= mlo.x; alo.y |= mlo.y; alo.z |= mlo.z; alo.w |= mlo.w;
+    ahi.x |= mhi.x; ahi.y |= mhi.y; ahi.z |= mhi.z; ahi.w |= mhi.w;
+    const uint32_t cnt = __popc(mlo.x) + __popc(mlo.y) + __popc(mlo.z) + __popc(mlo.w) +
+                         __popc(mhi.x) + __popc(mhi.y) + __popc(mhi.z) + __popc(mhi.w);
+    const uint32_t ta = tal_s + (c << 2);
+    st_s(ta, ld_s(ta) + cnt);
+  }
+}
+
+template <bool TALLY, bool BITS, bool FAST>
 __global__ void __launch_bounds__(1024, 1)
 k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
               const QecSampleExport X) {
@@ -413,7 +566,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   const uint32_t wwords = (uint32_t)S.nc * QEC_LINW_BW + 128u + ncp;  // words per warp region
   const uint32_t P = 1u << S.lgP;
   LinSmem m;
-  uint32_t *rec_sm = nullptr;
+  uint32_t *rec_sm = nullptr, *info2_sm = nullptr;
   m.acc = qec_lin_smem + (size_t)warp * wwords;
   m.cnt = m.acc + (size_t)S.nc * QEC_LINW_BW;
   m.tally = m.cnt + 128;
@@ -437,6 +590,12 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     m.list = S.siglist;
     if (S.info_in_smem) p += S.L;
     p += (2u - ((uint32_t)(p - qec_lin_smem) & 1u)) & 1u;  // 8-byte aligned
+    if (S.fast) {
+      info2_sm = p;
+      const uint32_t *src = reinterpret_cast<const uint32_t *>(S.info2);
+      for (uint32_t i = tid; i < 2u * (uint32_t)S.L; i += T) p[i] = src[i];
+      p += 2u * (uint32_t)S.L;
+    }
     rec_sm = p;
     if (S.rec_in_smem) {
       const uint32_t *src = reinterpret_cast<const uint32_t *>(S.sigrec);
@@ -444,10 +603,12 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     }
   }
   for (uint32_t i = tid; i < S.K1; i += T) m.T1[i] = S.T1[i];
-  for (uint32_t i = tid; i <= S.B; i += T) m.T2[i] = i < S.B ? S.T2[i] : 0u;
-  for (uint32_t k = tid; k < 2u * S.B; k += T) {
-    const uint32_t rmax = (k << S.gshift) | ((1u << S.gshift) - 1u);
-    m.G[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1u, rmax);
+  if (S.draw == 0) {
+    for (uint32_t i = tid; i <= S.B; i += T) m.T2[i] = i < S.B ? S.T2[i] : 0u;
+    for (uint32_t k = tid; k < 2u * S.B; k += T) {
+      const uint32_t rmax = (k << S.gshift) | ((1u << S.gshift) - 1u);
+      m.G[k] = (uint16_t)qec_count_greater(S.T2 + 1, S.B - 1u, rmax);
+    }
   }
   for (uint32_t c = tid; c < S.n_classes; c += T) {
     m.cacc[c] = S.cls_acc[c];
@@ -463,94 +624,84 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(m.acc);
   const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(m.cnt);
   const uint32_t tal_s = (uint32_t)__cvta_generic_to_shared(m.tally);
+  const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec_sm);
+  const uint32_t info2_s = (uint32_t)__cvta_generic_to_shared(info2_sm);
   LinDraw dc;
-  dc.t1_0 = m.T1[0]; dc.t1_1 = S.K1 > 1 ? m.T1[1] : 0u; dc.t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
+  dc.t1_0 = S.K1 > 0 ? m.T1[0] : 0u; dc.t1_1 = S.K1 > 1 ? m.T1[1] : 0u; dc.t1_2 = S.K1 > 2 ? m.T1[2] : 0u;
   dc.kb = S.K1 * S.B;
   dc.cdf_s = (uint32_t)__cvta_generic_to_shared(m.cdf);
   dc.desc_s = 0u; dc.list_s = 0u;
-  dc.rec_s = (uint32_t)__cvta_generic_to_shared(rec_sm);
+  dc.rec_s = rec_s;
   dc.bw4 = 4u * QEC_LINW_BW;
   dc.P = P;
   dc.lgb = QEC_LINW_LGB;
   unsigned long long nz_shots = 0;
-  uint32_t h0 = 0, h1 = 0, h2 = 0;
+  uint32_t h1 = 0, h2 = 0, hx = 0;  // shots with exactly 1 / exactly 2 / at least 3 faults
   const long long b0 = shot_lo >> QEC_LINW_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LINW_LGB;
   const long long w_lo = shot_lo >> 5;
   const bool vec_ok = ((O.n_words | w_lo) & 7) == 0 && ((size_t)O.bits & 31) == 0;
+  // the lane's read-out program: constant over batches, kept in registers when short
+  const bool regprog = S.n_steps <= QEC_LINW_REGSTEPS;
+  uint32_t prog[QEC_LINW_REGSTEPS];
+#pragma unroll
+  for (int k = 0; k < QEC_LINW_REGSTEPS; ++k)
+    prog[k] = (regprog && k < S.n_steps) ? __ldg(S.rowprog + k * 32 + lane) : 0u;
 
   for (long long b = b0 + (long long)blockIdx.x * NW + warp; b <= b1; b += (long long)gridDim.x * NW) {
     const long long base_shot = b << QEC_LINW_LGB;
     const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
     const uint32_t shi = (uint32_t)min(256ll, shot_lo + n_shots - base_shot);
     const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
-    for (int s = 0; s < S.n_streams; ++s)
-      lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    for (int s = 0; s < S.n_streams; ++s) {
+      if (FAST) linw_stream_fast<TALLY>(S, s, lane, blo, bhi, slo, shi, info2_s, rec_s, acc_s, cnt_s, base_shot, w_lo, X);
+      else lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    }
     __syncwarp();
 
-    // ---- read-out: lane = clbit row
+    // ---- read-out: lane = chain of clbit rows
     const long long w0 = (b << 3) - w_lo;  // first output word of the batch (may be < 0 at the range start)
-    const bool whole = w0 >= 0 && w0 + 8 <= O.n_words;
-    uint32_t any0 = 0, any1 = 0, any2 = 0, any3 = 0, any4 = 0, any5 = 0, any6 = 0, any7 = 0;
-    uint4 mlo = make_uint4(0u, 0u, 0u, 0u), mhi = mlo;  // running XOR along the lane's chain
-    uint32_t e_next = __ldg(S.rowprog + lane);
-    for (int step = 0; step < S.n_steps; ++step) {
-      const uint32_t e = e_next;
-      if (step + 1 < S.n_steps) e_next = __ldg(S.rowprog + (step + 1) * 32 + lane);
-      if (!(e >> 31)) continue;
-      const uint32_t c = e & 0xFFFFu;
-      const uint32_t a = acc_s + c * 32u;
-      const uint4 lo4 = ld_s128(a), hi4 = ld_s128(a + 16u);
-      st_s128z(a);
-      st_s128z(a + 16u);
-      if (e & (1u << 30)) { mlo = lo4; mhi = hi4; }
-      else {
-        mlo.x ^= lo4.x; mlo.y ^= lo4.y; mlo.z ^= lo4.z; mlo.w ^= lo4.w;
-        mhi.x ^= hi4.x; mhi.y ^= hi4.y; mhi.z ^= hi4.z; mhi.w ^= hi4.w;
-      }
-      if (BITS) {
-        uint32_t *po = O.bits + ((long long)c * O.n_words + w0);
-        if (whole && vec_ok) {
-          // one 256-bit store = the row's whole 32-byte sector (two 128-bit stores are two
-          // partial-sector writes, and L2 then fetches the sector from DRAM first)
-          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(po), "r"(mlo.x),
-                       "r"(mlo.y), "r"(mlo.z), "r"(mlo.w), "r"(mhi.x), "r"(mhi.y), "r"(mhi.z), "r"(mhi.w)
-                       : "memory");
-        } else {
-          const uint32_t v[8] = {mlo.x, mlo.y, mlo.z, mlo.w, mhi.x, mhi.y, mhi.z, mhi.w};
+    const bool fastst = w0 >= 0 && w0 + 8 <= O.n_words && vec_ok;
+    uint4 alo = make_uint4(0u, 0u, 0u, 0u), ahi = alo;  // OR of the lane's rows (non-zero shots)
+    uint4 mlo = alo, mhi = alo;                         // running XOR along the lane's chain
+    if (regprog) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (w0 + j >= 0 && w0 + j < O.n_words) po[j] = v[j];
-        }
-      }
-      if (TALLY) {
-        any0 |= mlo.x; any1 |= mlo.y; any2 |= mlo.z; any3 |= mlo.w;
-        any4 |= mhi.x; any5 |= mhi.y; any6 |= mhi.z; any7 |= mhi.w;
-        const uint32_t cnt = __popc(mlo.x) + __popc(mlo.y) + __popc(mlo.z) + __popc(mlo.w) +
-                             __popc(mhi.x) + __popc(mhi.y) + __popc(mhi.z) + __popc(mhi.w);
-        const uint32_t ta = tal_s + (c << 2);
-        st_s(ta, ld_s(ta) + cnt);
+      for (int k = 0; k < QEC_LINW_REGSTEPS; ++k)
+        if (k < S.n_steps) linw_row<TALLY, BITS>(prog[k], acc_s, tal_s, mlo, mhi, alo, ahi, O, w0, fastst);
+    } else {
+      uint32_t e_next = __ldg(S.rowprog + lane);
+      for (int step = 0; step < S.n_steps; ++step) {
+        const uint32_t e = e_next;
+        if (step + 1 < S.n_steps) e_next = __ldg(S.rowprog + (step + 1) * 32 + lane);
+        linw_row<TALLY, BITS>(e, acc_s, tal_s, mlo, mhi, alo, ahi, O, w0, fastst);
       }
     }
     if (TALLY) {
-      uint32_t nzb = __popc(__reduce_or_sync(0xFFFFFFFFu, any0)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any1)) +
-                     __popc(__reduce_or_sync(0xFFFFFFFFu, any2)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any3)) +
-                     __popc(__reduce_or_sync(0xFFFFFFFFu, any4)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any5)) +
-                     __popc(__reduce_or_sync(0xFFFFFFFFu, any6)) + __popc(__reduce_or_sync(0xFFFFFFFFu, any7));
+      const uint32_t nzb =
+          __popc(__reduce_or_sync(0xFFFFFFFFu, alo.x)) + __popc(__reduce_or_sync(0xFFFFFFFFu, alo.y)) +
+          __popc(__reduce_or_sync(0xFFFFFFFFu, alo.z)) + __popc(__reduce_or_sync(0xFFFFFFFFu, alo.w)) +
+          __popc(__reduce_or_sync(0xFFFFFFFFu, ahi.x)) + __popc(__reduce_or_sync(0xFFFFFFFFu, ahi.y)) +
+          __popc(__reduce_or_sync(0xFFFFFFFFu, ahi.z)) + __popc(__reduce_or_sync(0xFFFFFFFFu, ahi.w));
       if (lane == 0) nz_shots += nzb;
-      // faults-per-shot histogram: 128 counter words (two shots each), four per lane
+      // faults-per-shot histogram: 128 counter words (two 16-bit counters each), four per lane.
+      // Shots outside the requested range never receive a fault, and the zero-fault count is
+      // derived at the end, so no range test here.  pk: byte j counts the lane's shots with
+      // min(faults, 3) == j.
+      const uint4 cw = ld_s128(cnt_s + ((uint32_t)lane << 4));
+      st_s128z(cnt_s + ((uint32_t)lane << 4));
+      uint32_t pk = 0;
+#define QEC_CNT(W) pk += (1u << (min((W) & 0xFFFFu, 3u) << 3)) + (1u << (min((W) >> 16, 3u) << 3))
+      QEC_CNT(cw.x); QEC_CNT(cw.y); QEC_CNT(cw.z); QEC_CNT(cw.w);
+#undef QEC_CNT
+      h1 += (pk >> 8) & 0xFFu;
+      h2 += (pk >> 16) & 0xFFu;
+      if (pk >> 24) {  // rare: some shot of this lane carries 3 or more faults
+        hx += pk >> 24;
+        const uint32_t v[4] = {cw.x, cw.y, cw.z, cw.w};
 #pragma unroll
-      for (uint32_t q = 0; q < 4u; ++q) {
-        const uint32_t i = q * 32u + (uint32_t)lane;
-        const uint32_t cw = ld_s(cnt_s + (i << 2));
-        st_s(cnt_s + (i << 2), 0u);
-#pragma unroll
-        for (uint32_t h = 0; h < 2u; ++h) {
-          const uint32_t shot = 2u * i + h, k = (cw >> (16u * h)) & 0xFFFFu;
-          if (shot < slo || shot >= shi) continue;
-          if (k == 0u) ++h0;
-          else if (k == 1u) ++h1;
-          else if (k == 2u) ++h2;
-          else atomicAdd(m.hist + min(k, 63u), 1u);
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t k0 = v[j] & 0xFFFFu, k1 = v[j] >> 16;
+          if (k0 >= 3u) atomicAdd(m.hist + min(k0, 63u), 1u);
+          if (k1 >= 3u) atomicAdd(m.hist + min(k1, 63u), 1u);
         }
       }
     }
@@ -558,11 +709,18 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   }
 
   if (TALLY) {
-    h0 = __reduce_add_sync(0xFFFFFFFFu, h0);
-    h1 = __reduce_add_sync(0xFFFFFFFFu, h1);
-    h2 = __reduce_add_sync(0xFFFFFFFFu, h2);
+    // faults-per-shot histogram: entries 1 and 2 from the registers, >= 3 from shared memory;
+    // entry 0 = shots of the range minus the shots with a fault (64-bit wrap-around adds)
+    unsigned long long t1 = h1, t2 = h2, tx = hx;
+    for (int off = 16; off > 0; off >>= 1) {
+      t1 += __shfl_down_sync(0xFFFFFFFFu, t1, off);
+      t2 += __shfl_down_sync(0xFFFFFFFFu, t2, off);
+      tx += __shfl_down_sync(0xFFFFFFFFu, tx, off);
+    }
     if (lane == 0) {
-      atomicAdd(m.hist + 0, h0); atomicAdd(m.hist + 1, h1); atomicAdd(m.hist + 2, h2);
+      if (t1) atomicAdd(&O.tally[S.nc + 2 + 1], t1);
+      if (t2) atomicAdd(&O.tally[S.nc + 2 + 2], t2);
+      if (t1 + t2 + tx) atomicAdd(&O.tally[S.nc + 2], 0ull - (t1 + t2 + tx));
       if (nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
     }
     __syncthreads();
@@ -573,7 +731,10 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
     }
     for (int c = tid; c < 64; c += T)
       if (m.hist[c]) atomicAdd(&O.tally[S.nc + 2 + c], (unsigned long long)m.hist[c]);
-    if (blockIdx.x == 0 && tid == 0) atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
+    if (blockIdx.x == 0 && tid == 0) {
+      atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
+      atomicAdd(&O.tally[S.nc + 2], (unsigned long long)n_shots);
+    }
   }
 }
 
@@ -586,8 +747,10 @@ int qec_lin_set_smem_attr(size_t smem) {
   if (e != cudaSuccess) return (int)e;
   QEC_SET((k_sample_lin<true, true>)) QEC_SET((k_sample_lin<true, false>))
   QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
-  QEC_SET((k_sample_linw<true, true>)) QEC_SET((k_sample_linw<true, false>))
-  QEC_SET((k_sample_linw<false, true>)) QEC_SET((k_sample_linw<false, false>))
+  QEC_SET((k_sample_linw<true, true, false>)) QEC_SET((k_sample_linw<true, false, false>))
+  QEC_SET((k_sample_linw<false, true, false>)) QEC_SET((k_sample_linw<false, false, false>))
+  QEC_SET((k_sample_linw<true, true, true>)) QEC_SET((k_sample_linw<true, false, true>))
+  QEC_SET((k_sample_linw<false, true, true>)) QEC_SET((k_sample_linw<false, false, true>))
 #undef QEC_SET
   return 0;
 }
@@ -597,11 +760,16 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecSampleExport &X) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
 #define QEC_GO(K) K<<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X)
-  if (S.warp_mode) {
-    if (t && b) QEC_GO((k_sample_linw<true, true>));
-    else if (t) QEC_GO((k_sample_linw<true, false>));
-    else if (b) QEC_GO((k_sample_linw<false, true>));
-    else QEC_GO((k_sample_linw<false, false>));
+  if (S.warp_mode && S.fast) {
+    if (t && b) QEC_GO((k_sample_linw<true, true, true>));
+    else if (t) QEC_GO((k_sample_linw<true, false, true>));
+    else if (b) QEC_GO((k_sample_linw<false, true, true>));
+    else QEC_GO((k_sample_linw<false, false, true>));
+  } else if (S.warp_mode) {
+    if (t && b) QEC_GO((k_sample_linw<true, true, false>));
+    else if (t) QEC_GO((k_sample_linw<true, false, false>));
+    else if (b) QEC_GO((k_sample_linw<false, true, false>));
+    else QEC_GO((k_sample_linw<false, false, false>));
   } else {
     if (t && b) QEC_GO((k_sample_lin<true, true>));
     else if (t) QEC_GO((k_sample_lin<true, false>));
