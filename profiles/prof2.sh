@@ -10,9 +10,9 @@ except Exception as e: print("$name", "ERR", e)
 PY
 }
 run base X=1
-run w16 QEC_B200_LIN_WARPS=16
-run w24 QEC_B200_LIN_WARPS=24
-run nofast QEC_B200_LIN_FAST=0
-run table QEC_B200_LIN_DRAW=table
-ncu --set full --clock-control none --import-source on -k regex:'k_sample_lin' -s 3 -c 1 -f -o gpurun_out/full_lean python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-enum --e2e-steps 1 > gpurun_out/ncu_full_lean.log 2>&1
+run lanes4 QEC_B200_LIN_WARPS=4
+run warp QEC_B200_LIN_MODE=warp
+run lanes6 QEC_B200_LIN_WARPS=6
+
+ncu --set full --clock-control none --import-source on -k regex:'k_sample_l' -s 3 -c 1 -f -o gpurun_out/full_lean python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-enum --e2e-steps 1 > gpurun_out/ncu_full_lean.log 2>&1
 tail -2 gpurun_out/ncu_full_lean.log

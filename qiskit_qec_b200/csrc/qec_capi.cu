@@ -1045,8 +1045,9 @@ static int sampler_plan_linear(qec_sampler *s) {
   bool use_diff = false;
   size_t maxlen_w = 0;  // longest list the warp variant would see
   std::vector<std::vector<uint16_t>> tr((size_t)F);
+  std::vector<int> pred(c->nc, -1), succ(c->nc, -1);
   {
-    std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
+    std::vector<int> last(c->nq, -1);
     for (size_t i = 0; i < c->packed.size(); ++i) {
       const uint32_t g = c->packed[i];
       if ((g & 15u) != QOP_MEASF) continue;
@@ -1119,12 +1120,51 @@ static int sampler_plan_linear(qec_sampler *s) {
     smem = words(lg, info_s, sig_s);
     return true;
   };
+  // read-out passes of the lane-stream variant: four rows per pass, a row never together with
+  // the previous row of its chain.  Entry: row | previous row << 8 (nc + 1 = the zero row: none)
+  // | 1 << 17 if a row follows | 1 << 18 valid
+  std::vector<uint32_t> lanes_prog;
+  if (c->nc <= 254) {
+    const uint32_t none = (uint32_t)c->nc + 1u;
+    std::vector<int> cur;
+    auto flush = [&]() {
+      while (!cur.empty() && cur.size() < 4) cur.push_back(-1);
+      for (int x : cur) {
+        if (x < 0) { lanes_prog.push_back(none | (none << 8)); continue; }
+        const int pr = use_diff ? pred[x] : -1, sc = use_diff ? succ[x] : -1;
+        lanes_prog.push_back((uint32_t)x | ((pr >= 0 ? (uint32_t)pr : none) << 8) | (sc >= 0 ? (1u << 17) : 0u) | (1u << 18));
+      }
+      cur.clear();
+    };
+    for (int cb = 0; cb < c->nc; ++cb) {
+      const int pr = use_diff ? pred[cb] : -1;
+      if (cur.size() == 4 || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
+      cur.push_back(cb);
+    }
+    flush();
+  }
   bool found = false;
-  int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0;
+  int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0, lane_mode = 0;
+  const char *lmode = std::getenv("QEC_B200_LIN_MODE");
   {
+    // lane-stream variant (1024-shot batches, lane = word column, no shared-memory atomics):
+    // draw scheme 2, equal Pauli weights, 8-byte records, at least 4 warps' accumulators
+    const bool want = lmode ? !strcmp(lmode, "lanes") : true;
+    const bool can = draw == 2 && ln.cls_uniform_all && maxlen_w <= 7 && c->nc <= 254 && f_lgb == 0 &&
+                     ((long long)s->L << 10) < (1ll << 30);
+    const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
+    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; --wz) {
+      const size_t need = qec_lanes_smem_words(c->nc, wz, (uint32_t)s->L, (uint32_t)F, (uint32_t)lanes_prog.size()) * 4 + 16;
+      if (need > di.smem_optin) continue;
+      found = true; lane_mode = 1; threads = 32 * wz; ctas = 1; lgb = 10; info_s = 1; sig_s = 0;
+      rec8 = 1; rec_s = 1; smem = need;
+    }
+    if (lmode && !strcmp(lmode, "lanes") && !found) { ln.why = "QEC_B200_LIN_MODE=lanes: not eligible"; return 0; }
+  }
+  if (!found) {
     // warp-autonomous variant (256-shot batches, one warp each) when at least 24 warps'
     // accumulators fit next to the tables: no CTA barriers, row-parallel read-out
-    const char *lm = std::getenv("QEC_B200_LIN_MODE");
+    const char *lm = lmode;
     const bool allow = !(lm && !strcmp(lm, "cta")) && f_lgb == 0 && ((long long)s->L << 8) < (1ll << 30);
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
     rec8 = (maxlen_w <= 7 && c->nc <= 255) ? 1 : 0;
@@ -1163,11 +1203,11 @@ static int sampler_plan_linear(qec_sampler *s) {
   const double mean_batch = psum * (double)(1 << lgb);
   int ns = 64;
   while (ns > 1 && mean_batch / ns < 128.0) ns >>= 1;
-  if (warp_mode) ns = 1;
+  if (warp_mode || lane_mode) ns = 1;
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
-  if (warp_mode && use_diff) lists.swap(tr);
+  if ((warp_mode || lane_mode) && use_diff) lists.swap(tr);
   // descriptor + list (CTA variant with tables in shared memory, overflow of long lists) and
   // fixed-size records: 16 bytes (length + 7 clbits) when no list is longer, else 32 (+15)
   ln.sigdesc.clear();
@@ -1176,7 +1216,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   size_t maxlen = 0;
   for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
   const int rec2 = maxlen > 7 ? 1 : 0;
-  if (rec8 && (maxlen > 7 || !warp_mode)) return fail(QEC_ERR_LOGIC, "linear sampler: record plan out of step");
+  if (rec8 && (maxlen > 7 || !(warp_mode || lane_mode))) return fail(QEC_ERR_LOGIC, "linear sampler: record plan out of step");
   for (int64_t f = 0; f < F; ++f) {
     const size_t len = lists[f].size();
     if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
@@ -1185,7 +1225,9 @@ static int sampler_plan_linear(qec_sampler *s) {
     }
     ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
     if (rec8) {  // bytes: validity mask of the entries (2^len - 1), 7 clbits
-      uint8_t by[8] = {(uint8_t)((1u << len) - 1u), 0, 0, 0, 0, 0, 0, 0};
+      // (lane-stream variant: absent entries name the dummy row nc)
+      const uint8_t pad = lane_mode ? (uint8_t)c->nc : (uint8_t)0;
+      uint8_t by[8] = {(uint8_t)((1u << len) - 1u), pad, pad, pad, pad, pad, pad, pad};
       for (size_t k = 0; k < len; ++k) by[1 + k] = (uint8_t)lists[f][k];
       for (int k = 0; k < 4; ++k) ln.sigrec.push_back((uint16_t)(by[2 * k] | (by[2 * k + 1] << 8)));
     } else {
@@ -1195,6 +1237,10 @@ static int sampler_plan_linear(qec_sampler *s) {
     ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
   }
   ln.siglist.resize((ln.siglist.size() + 2u) & ~(size_t)1u, 0);  // whole 32-bit words, never empty
+  if (lane_mode) {
+    ln.rowprog = lanes_prog;
+    n_steps = (int)(lanes_prog.size() / 4);
+  }
   if (ln.rowprog.empty()) ln.rowprog.push_back(0u);
   if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
@@ -1219,6 +1265,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   }
   d.info2 = reinterpret_cast<const uint2 *>(ln.d_info2);
   d.fast = fast;
+  d.lane_mode = lane_mode;
   d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
   d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
   d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;
@@ -1418,10 +1465,12 @@ extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, 
                      (uint32_t)(s->seed >> 32),
                      // bit 0: some fault can occur; bit 1: linear-response draw order (batches
                      // of 2^lgb shots, n_streams streams each), lgb << 8, n_streams << 16;
-                     // bits 2-3: draw scheme of the linear sampler (QecLinDev::draw); its gap
+                     // bits 2-3: draw scheme of the linear sampler (QecLinDev::draw), bit 4: lane-stream
+                     // order (k_sample_lanes); the gap
                      // constant follows the tables as one extra word (float bits)
                      (uint32_t)(s->dev.n_slots > 0) |
                          (s->lin.eligible ? (2u | ((uint32_t)s->lin.dev.draw << 2) |
+                                                 ((uint32_t)s->lin.dev.lane_mode << 4) |
                                                  ((uint32_t)s->lin.dev.lgb << 8) |
                                                  ((uint32_t)s->lin.dev.n_streams << 16))
                                           : 0u)});
@@ -1459,14 +1508,14 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
     const QecLinDev &d = s->lin.dev;
     QecLaunchCfg cfg = s->lin.cfg;
     long long n_batches = ((shot_lo + n_shots - 1) >> d.lgb) - (shot_lo >> d.lgb) + 1;
-    if (d.warp_mode) n_batches = (n_batches + cfg.block / 32 - 1) / (cfg.block / 32);  // one per warp
+    if (d.warp_mode || d.lane_mode) n_batches = (n_batches + cfg.block / 32 - 1) / (cfg.block / 32);  // one per warp
     if (cfg.grid > n_batches) cfg.grid = (int)n_batches;
     time_begin(s->c, stream);
     qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
     time_end(s->c, stream);
     CU(cudaGetLastError());
     s->last_cap = 0;
-    g_last_kernel = std::string("sample:linear ") + (d.warp_mode ? "warp-batches" : "cta-batches") +
+    g_last_kernel = std::string("sample:linear ") + (d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
                     " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +

@@ -138,7 +138,18 @@ struct QecLinDev {
   float gapC;               // -1 / log2(1 - pmax)
   const uint2 *info2;       // [L] {first fault of sl, number of Paulis of sl} (lean warp kernel)
   int fast;                 // lean warp kernel eligible: draw 2, uniform digits, 8-byte records and info2 in smem
+  // lane-stream variant (k_sample_lanes): lgb = 10, lane = word column, no shared-memory atomics;
+  // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
+  int lane_mode;
 };
+
+// shared-memory words of the lane-stream variant (1024-shot batches, `warps` warps per CTA)
+static inline __host__ __device__ size_t qec_lanes_smem_words(int nc, int warps, uint32_t L, uint32_t n_faults,
+                                                              uint32_t prog_words) {
+  const size_t ncp = ((size_t)nc + 3u) & ~(size_t)3u;
+  const size_t per_warp = ((size_t)nc + 2u) * 32u + ncp;
+  return (size_t)warps * per_warp + 64u + prog_words + 2u * (size_t)L + 2u * (size_t)n_faults;
+}
 
 // Computed geometric gap (draw schemes 1 and 2).  u = (r | 1) / 2^32 is uniform on (0, 1);
 // the gap is floor(C * -log2(u)), C = -1 / log2(1 - pmax), so that P(gap >= k) = (1-pmax)^k.

@@ -738,6 +738,242 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Lane-stream variant: no shared-memory atomics at all.  ncu on k_sample_linw showed the SM's
+// shared-memory atomic unit (about 2 cycles per lane) as the bound: ~700 lane-atomics per 256
+// shots, whatever the instruction count or the occupancy.  Here a warp owns a batch of 1024
+// shots and LANE l OWNS WORD COLUMN l (shots 32 l .. 32 l + 31 of the batch): every lane walks
+// its own fault stream over slot = sorted location * 32 + shot bit (computed gaps, two
+// candidates per Philox call, counter = (batch, call * 32 + lane, 0x4D000000)), and all flips of
+// column l are plain load / xor / store on acc[row][l] -- bank = lane, so neither conflicts nor
+// races.  The price is the imbalance between lanes (a step lasts as long as its busiest lane:
+// ~70 % useful at d=5, p=1e-3).  Faults per shot are counted in six bit-sliced register planes.
+// Read-out moves four rows per pass (8 lanes x 128 bits per row: conflict-free shared loads, one
+// full 128-byte line per row stored); the time-difference basis is undone in place (row ^=
+// previous row of the chain; the host schedules the passes so that a row and its previous row
+// never share one).  Eligible: draw scheme 2, equal Pauli weights, 8-byte
+// records.
+// Shared memory: [warp regions: acc (nc+2)*32 (row nc = dummy target of absent record entries,
+// row nc+1 = always zero, the "previous row" of rows without one) | tally ncp] then hist 64,
+// prog 4 * n_steps (read-out passes), info2 2L, rec 2F.
+#define QEC_LANES_LGB 10
+
+// One candidate of a lane.  Absent record entries (and every entry of a lane without a fault)
+// name the dummy row nc, so the seven load / xor / store triples need no predicate.
+__device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p, const bool ok,
+                                            const uint2 q, const uint32_t d, const uint32_t sl,
+                                            const uint32_t lane_acc, const int lane,
+                                            const long long base_shot, const long long w_lo,
+                                            const QecSampleExport &X) {
+  const uint32_t bit = p & 31u, msk = 1u << bit;
+  const uint32_t a0 = lane_acc + (__byte_perm(q.x, 0u, 0x4441u) << 7);
+  const uint32_t a1 = lane_acc + (__byte_perm(q.x, 0u, 0x4442u) << 7);
+  const uint32_t a2 = lane_acc + (__byte_perm(q.x, 0u, 0x4443u) << 7);
+  const uint32_t a3 = lane_acc + (__byte_perm(q.y, 0u, 0x4440u) << 7);
+  const uint32_t a4 = lane_acc + (__byte_perm(q.y, 0u, 0x4441u) << 7);
+  const uint32_t a5 = lane_acc + (__byte_perm(q.y, 0u, 0x4442u) << 7);
+  const uint32_t a6 = lane_acc + (__byte_perm(q.y, 0u, 0x4443u) << 7);
+  // the rows of one fault are distinct (or the dummy): all loads first, then all stores
+  const uint32_t v0 = ld_s(a0), v1 = ld_s(a1), v2 = ld_s(a2), v3 = ld_s(a3), v4 = ld_s(a4),
+                 v5 = ld_s(a5), v6 = ld_s(a6);
+  st_s(a0, v0 ^ msk); st_s(a1, v1 ^ msk); st_s(a2, v2 ^ msk); st_s(a3, v3 ^ msk);
+  st_s(a4, v4 ^ msk); st_s(a5, v5 ^ msk); st_s(a6, v6 ^ msk);
+  if (X.cnt) {
+    if (ok) {
+      const uint32_t shot = ((uint32_t)lane << 5) | bit;
+      const long long wr = ((base_shot + shot) >> 5) - w_lo;
+      const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+      if (k < (uint32_t)X.cap) X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | (bit << 9) | d;
+    }
+  }
+}
+
+// faults-per-shot counters of a lane's 32 shots: six bit planes, ripple-carry increment of the
+// shots in mask c (the carry rarely leaves plane 1)
+struct LanePlanes {
+  uint32_t p0, p1, p2, p3, p4, p5;
+};
+__device__ __forceinline__ void planes_add(LanePlanes &P, uint32_t c) {
+  uint32_t t = P.p0 & c; P.p0 ^= c; c = t;
+  t = P.p1 & c; P.p1 ^= c; c = t;
+  if (c) {
+    t = P.p2 & c; P.p2 ^= c; c = t;
+    t = P.p3 & c; P.p3 ^= c; c = t;
+    t = P.p4 & c; P.p4 ^= c; c = t;
+    t = P.p5 & c; P.p5 ^= c; c = t;
+    // 63 + 1: stay at 63 (the last histogram bin is ">= 63")
+    P.p0 |= c; P.p1 |= c; P.p2 |= c; P.p3 |= c; P.p4 |= c; P.p5 |= c;
+  }
+}
+
+template <bool TALLY, bool BITS>
+__global__ void __launch_bounds__(512, 1)
+k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
+               const QecSampleExport X) {
+  extern __shared__ __align__(16) uint32_t qec_lin_smem[];
+  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
+  const uint32_t nc = (uint32_t)S.nc, ncp = (nc + 3u) & ~3u;
+  const uint32_t wwords = (nc + 2u) * 32u + ncp;  // words per warp region
+  uint32_t *acc = qec_lin_smem + (size_t)warp * wwords;
+  uint32_t *hist = qec_lin_smem + (size_t)NW * wwords;
+  uint32_t *prog = hist + 64;
+  uint32_t *info2 = prog + 4u * (uint32_t)S.n_steps;
+  uint32_t *rec = info2 + 2u * (uint32_t)S.L;
+  {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(S.info2);
+    for (uint32_t i = tid; i < 2u * (uint32_t)S.L; i += T) info2[i] = src[i];
+    src = reinterpret_cast<const uint32_t *>(S.sigrec);
+    for (uint32_t i = tid; i < 2u * S.n_faults; i += T) rec[i] = src[i];
+    for (uint32_t i = tid; i < 4u * (uint32_t)S.n_steps; i += T) prog[i] = S.rowprog[i];
+    for (uint32_t i = tid; i < (uint32_t)NW * wwords + 64u; i += T) qec_lin_smem[i] = 0u;
+  }
+  __syncthreads();
+
+  const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(acc);
+  const uint32_t lane_acc = acc_s + ((uint32_t)lane << 2);
+  const uint32_t tal_s = acc_s + (((nc + 2u) * 32u) << 2);
+  const uint32_t prog_s = (uint32_t)__cvta_generic_to_shared(prog);
+  const uint32_t info2_s = (uint32_t)__cvta_generic_to_shared(info2);
+  const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec);
+  const uint32_t null_x = nc * 0x01010100u, null_y = nc * 0x01010101u;  // record of a lane without a fault
+  const uint32_t end = (uint32_t)S.L << 5;
+  const float C = S.gapC;
+  unsigned long long nz_shots = 0;
+  uint32_t h1 = 0, h2 = 0, h3 = 0, hx = 0;  // shots with exactly 1 / 2 / 3 / at least 4 faults
+  const long long b0 = shot_lo >> QEC_LANES_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LANES_LGB;
+  const long long w_lo = shot_lo >> 5;
+  const bool vec_ok = ((O.n_words | w_lo) & 3) == 0 && ((size_t)O.bits & 15) == 0;
+  // read-out geometry: 8 lanes x 4 words per row, 4 rows per pass
+  const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
+
+  for (long long b = b0 + (long long)blockIdx.x * NW + warp; b <= b1; b += (long long)gridDim.x * NW) {
+    const long long base_shot = b << QEC_LANES_LGB;
+    const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
+    const uint32_t shi = (uint32_t)min(1024ll, shot_lo + n_shots - base_shot);
+    const uint32_t nsh = shi - slo, lane_sh = ((uint32_t)lane << 5) - slo;
+    const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
+
+    // ---- the lane's fault stream
+    LanePlanes P = {0u, 0u, 0u, 0u, 0u, 0u};
+    uint32_t pos = 0xFFFFFFFFu;  // -1; saturates at `end`
+    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); ++it) {
+      const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+      const uint32_t g0 = qec_gap_len(r.c[0], C), g1 = qec_gap_len(r.c[2], C);
+      const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP;
+      const uint32_t p0 = pos + g0 + (has0 ? 1u : 0u), p1 = p0 + g1 + (has1 ? 1u : 0u);
+      // (pos + 1 <= end: the lane is still inside its stream; p0, p1 < 2^26 + end: no overflow)
+      const bool live = pos + 1u <= end;
+      const bool ok0 = live && has0 && p0 < end && (lane_sh + (p0 & 31u)) < nsh;
+      const bool ok1 = live && has1 && p1 < end && (lane_sh + (p1 & 31u)) < nsh;
+      pos = live ? min(p1, end) : end;
+      const uint32_t sl0 = ok0 ? p0 >> 5 : 0u, sl1 = ok1 ? p1 >> 5 : 0u;
+      const uint2 i0 = ld_s64(info2_s + (sl0 << 3)), i1 = ld_s64(info2_s + (sl1 << 3));
+      const uint32_t d0 = __umulhi(r.c[1], i0.y), d1 = __umulhi(r.c[3], i1.y);
+      uint2 q0 = ld_s64(rec_s + ((i0.x + d0) << 3)), q1 = ld_s64(rec_s + ((i1.x + d1) << 3));
+      if (!ok0) { q0.x = null_x; q0.y = null_y; }
+      if (!ok1) { q1.x = null_x; q1.y = null_y; }
+      lanes_apply(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
+      lanes_apply(S, p1, ok1, q1, d1, sl1, lane_acc, lane, base_shot, w_lo, X);
+      if (TALLY) {
+        planes_add(P, ok0 ? 1u << (p0 & 31u) : 0u);
+        planes_add(P, ok1 ? 1u << (p1 & 31u) : 0u);
+      }
+    }
+    __syncwarp();
+
+    // ---- read-out: four rows per pass, lane = (row of the pass, 4-word piece of the row)
+    const long long w0 = (b << 5) - w_lo;  // first output word of the batch (may be < 0 at the range start)
+    const bool fastst = w0 >= 0 && w0 + 32 <= O.n_words && vec_ok;
+    uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
+    for (uint32_t pass = 0; pass < (uint32_t)S.n_steps; ++pass) {
+      // row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a row
+      // follows in the chain | 1 << 18 if the slot holds a row at all
+      const uint32_t e = ld_s(prog_s + (((pass << 2) + rsub) << 2));
+      const uint32_t rr = e & 0xFFu;
+      const uint32_t a = acc_s + (rr << 7) + (c4 << 2);
+      const uint32_t ap = acc_s + (((e >> 8) & 0xFFu) << 7) + (c4 << 2);
+      uint4 v = ld_s128(a);
+      const uint4 pv = ld_s128(ap);
+      v.x ^= pv.x; v.y ^= pv.y; v.z ^= pv.z; v.w ^= pv.w;
+      st_s128z(ap);
+      {
+        const uint32_t keep = (e & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x & keep), "r"(v.y & keep), "r"(v.z & keep), "r"(v.w & keep) : "memory");
+      }
+      const bool rowok = (e & 0x40000u) != 0u;
+      if (BITS && rowok) {
+        uint32_t *po = O.bits + ((long long)rr * O.n_words + w0 + c4);
+        if (fastst) *reinterpret_cast<uint4 *>(po) = v;
+        else {
+          const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
+        }
+      }
+      if (TALLY) {
+        anyv.x |= v.x; anyv.y |= v.y; anyv.z |= v.z; anyv.w |= v.w;
+        uint32_t cnt = __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
+        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 1);
+        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 2);
+        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 4);
+        if (c4 == 0u && rowok) { const uint32_t ta = tal_s + (rr << 2); st_s(ta, ld_s(ta) + cnt); }
+      }
+    }
+    if (TALLY) {
+      // non-zero shots: OR over the four row groups, then lanes 0..7 hold the batch's 32 words
+      anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 8); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 8);
+      anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 8); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 8);
+      anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 16); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 16);
+      anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 16); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 16);
+      if (lane < 8) nz_shots += __popc(anyv.x) + __popc(anyv.y) + __popc(anyv.z) + __popc(anyv.w);
+      // faults-per-shot histogram from the planes
+      const uint32_t hi = P.p2 | P.p3 | P.p4 | P.p5;
+      h1 += __popc(P.p0 & ~P.p1 & ~hi);
+      h2 += __popc(~P.p0 & P.p1 & ~hi);
+      h3 += __popc(P.p0 & P.p1 & ~hi);
+      hx += __popc(hi);
+      for (uint32_t m = hi; m; m &= m - 1u) {  // rare: shots with four or more faults
+        const uint32_t j = __ffs((int)m) - 1;
+        const uint32_t k = ((P.p0 >> j) & 1u) | (((P.p1 >> j) & 1u) << 1) | (((P.p2 >> j) & 1u) << 2) |
+                           (((P.p3 >> j) & 1u) << 3) | (((P.p4 >> j) & 1u) << 4) | (((P.p5 >> j) & 1u) << 5);
+        atomicAdd(hist + k, 1u);
+      }
+    }
+    __syncwarp();
+  }
+
+  if (TALLY) {
+    unsigned long long t1 = h1, t2 = h2, t3 = h3, tx = hx;
+    for (int off = 16; off > 0; off >>= 1) {
+      t1 += __shfl_down_sync(0xFFFFFFFFu, t1, off);
+      t2 += __shfl_down_sync(0xFFFFFFFFu, t2, off);
+      t3 += __shfl_down_sync(0xFFFFFFFFu, t3, off);
+      tx += __shfl_down_sync(0xFFFFFFFFu, tx, off);
+      nz_shots += __shfl_down_sync(0xFFFFFFFFu, nz_shots, off);
+    }
+    if (lane == 0) {
+      if (t1) atomicAdd(&O.tally[S.nc + 2 + 1], t1);
+      if (t2) atomicAdd(&O.tally[S.nc + 2 + 2], t2);
+      if (t3) atomicAdd(&O.tally[S.nc + 2 + 3], t3);
+      if (t1 + t2 + t3 + tx) atomicAdd(&O.tally[S.nc + 2], 0ull - (t1 + t2 + t3 + tx));
+      if (nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
+    }
+    __syncthreads();
+    for (uint32_t c = tid; c < nc; c += T) {
+      unsigned long long v = 0;
+      for (int k = 0; k < NW; ++k) v += qec_lin_smem[(size_t)k * wwords + (nc + 2u) * 32u + c];
+      if (v) atomicAdd(&O.tally[c], v);
+    }
+    for (int c = tid; c < 64; c += T)
+      if (hist[c]) atomicAdd(&O.tally[S.nc + 2 + c], (unsigned long long)hist[c]);
+    if (blockIdx.x == 0 && tid == 0) {
+      atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
+      atomicAdd(&O.tally[S.nc + 2], (unsigned long long)n_shots);
+    }
+  }
+}
+
 }  // namespace
 
 int qec_lin_set_smem_attr(size_t smem) {
@@ -749,6 +985,8 @@ int qec_lin_set_smem_attr(size_t smem) {
   QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
   QEC_SET((k_sample_linw<true, true, false>)) QEC_SET((k_sample_linw<true, false, false>))
   QEC_SET((k_sample_linw<false, true, false>)) QEC_SET((k_sample_linw<false, false, false>))
+  QEC_SET((k_sample_lanes<true, true>)) QEC_SET((k_sample_lanes<true, false>))
+  QEC_SET((k_sample_lanes<false, true>)) QEC_SET((k_sample_lanes<false, false>))
   QEC_SET((k_sample_linw<true, true, true>)) QEC_SET((k_sample_linw<true, false, true>))
   QEC_SET((k_sample_linw<false, true, true>)) QEC_SET((k_sample_linw<false, false, true>))
 #undef QEC_SET
@@ -760,7 +998,12 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecSampleExport &X) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
 #define QEC_GO(K) K<<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X)
-  if (S.warp_mode && S.fast) {
+  if (S.lane_mode) {
+    if (t && b) QEC_GO((k_sample_lanes<true, true>));
+    else if (t) QEC_GO((k_sample_lanes<true, false>));
+    else if (b) QEC_GO((k_sample_lanes<false, true>));
+    else QEC_GO((k_sample_lanes<false, false>));
+  } else if (S.warp_mode && S.fast) {
     if (t && b) QEC_GO((k_sample_linw<true, true, true>));
     else if (t) QEC_GO((k_sample_linw<true, false, true>));
     else if (b) QEC_GO((k_sample_linw<false, true, true>));
