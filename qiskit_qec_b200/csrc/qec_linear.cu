@@ -760,6 +760,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
 
 // One candidate of a lane.  Absent record entries (and every entry of a lane without a fault)
 // name the dummy row nc, so the seven load / xor / store triples need no predicate.
+template <bool EXPORT>
 __device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p, const bool ok,
                                             const uint2 q, const uint32_t d, const uint32_t sl,
                                             const uint32_t lane_acc, const int lane,
@@ -778,7 +779,7 @@ __device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p
                  v5 = ld_s(a5), v6 = ld_s(a6);
   st_s(a0, v0 ^ msk); st_s(a1, v1 ^ msk); st_s(a2, v2 ^ msk); st_s(a3, v3 ^ msk);
   st_s(a4, v4 ^ msk); st_s(a5, v5 ^ msk); st_s(a6, v6 ^ msk);
-  if (X.cnt) {
+  if (EXPORT) {
     if (ok) {
       const uint32_t shot = ((uint32_t)lane << 5) | bit;
       const long long wr = ((base_shot + shot) >> 5) - w_lo;
@@ -806,7 +807,7 @@ __device__ __forceinline__ void planes_add(LanePlanes &P, uint32_t c) {
   }
 }
 
-template <bool TALLY, bool BITS>
+template <bool TALLY, bool BITS, bool EXPORT>
 __global__ void __launch_bounds__(512, 1)
 k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
                const QecSampleExport X) {
@@ -856,9 +857,12 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
     // ---- the lane's fault stream
     LanePlanes P = {0u, 0u, 0u, 0u, 0u, 0u};
     uint32_t pos = 0xFFFFFFFFu;  // -1; saturates at `end`
+    // (software pipeline: the next call's Philox and gaps do not depend on the position, so they
+    // are computed while this call's candidates wait on shared memory)
+    QecPhilox r = qec_philox_rk(blo, bhi, (uint32_t)lane, 0x4D000000u, S.rk);
+    uint32_t g0 = qec_gap_len(r.c[0], C), g1 = qec_gap_len(r.c[2], C);
     for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); ++it) {
-      const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      const uint32_t g0 = qec_gap_len(r.c[0], C), g1 = qec_gap_len(r.c[2], C);
+      const QecPhilox rn = qec_philox_rk(blo, bhi, (it + 1u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
       const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP;
       const uint32_t p0 = pos + g0 + (has0 ? 1u : 0u), p1 = p0 + g1 + (has1 ? 1u : 0u);
       // (pos + 1 <= end: the lane is still inside its stream; p0, p1 < 2^26 + end: no overflow)
@@ -872,12 +876,14 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
       uint2 q0 = ld_s64(rec_s + ((i0.x + d0) << 3)), q1 = ld_s64(rec_s + ((i1.x + d1) << 3));
       if (!ok0) { q0.x = null_x; q0.y = null_y; }
       if (!ok1) { q1.x = null_x; q1.y = null_y; }
-      lanes_apply(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
-      lanes_apply(S, p1, ok1, q1, d1, sl1, lane_acc, lane, base_shot, w_lo, X);
+      const uint32_t gn0 = qec_gap_len(rn.c[0], C), gn1 = qec_gap_len(rn.c[2], C);
+      lanes_apply<EXPORT>(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
+      lanes_apply<EXPORT>(S, p1, ok1, q1, d1, sl1, lane_acc, lane, base_shot, w_lo, X);
       if (TALLY) {
         planes_add(P, ok0 ? 1u << (p0 & 31u) : 0u);
         planes_add(P, ok1 ? 1u << (p1 & 31u) : 0u);
       }
+      r = rn; g0 = gn0; g1 = gn1;
     }
     __syncwarp();
 
@@ -985,8 +991,10 @@ int qec_lin_set_smem_attr(size_t smem) {
   QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
   QEC_SET((k_sample_linw<true, true, false>)) QEC_SET((k_sample_linw<true, false, false>))
   QEC_SET((k_sample_linw<false, true, false>)) QEC_SET((k_sample_linw<false, false, false>))
-  QEC_SET((k_sample_lanes<true, true>)) QEC_SET((k_sample_lanes<true, false>))
-  QEC_SET((k_sample_lanes<false, true>)) QEC_SET((k_sample_lanes<false, false>))
+  QEC_SET((k_sample_lanes<true, true, false>)) QEC_SET((k_sample_lanes<true, false, false>))
+  QEC_SET((k_sample_lanes<false, true, false>)) QEC_SET((k_sample_lanes<false, false, false>))
+  QEC_SET((k_sample_lanes<true, true, true>)) QEC_SET((k_sample_lanes<true, false, true>))
+  QEC_SET((k_sample_lanes<false, true, true>)) QEC_SET((k_sample_lanes<false, false, true>))
   QEC_SET((k_sample_linw<true, true, true>)) QEC_SET((k_sample_linw<true, false, true>))
   QEC_SET((k_sample_linw<false, true, true>)) QEC_SET((k_sample_linw<false, false, true>))
 #undef QEC_SET
@@ -998,11 +1006,16 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecSampleExport &X) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
 #define QEC_GO(K) K<<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X)
-  if (S.lane_mode) {
-    if (t && b) QEC_GO((k_sample_lanes<true, true>));
-    else if (t) QEC_GO((k_sample_lanes<true, false>));
-    else if (b) QEC_GO((k_sample_lanes<false, true>));
-    else QEC_GO((k_sample_lanes<false, false>));
+  if (S.lane_mode && X.cnt) {
+    if (t && b) QEC_GO((k_sample_lanes<true, true, true>));
+    else if (t) QEC_GO((k_sample_lanes<true, false, true>));
+    else if (b) QEC_GO((k_sample_lanes<false, true, true>));
+    else QEC_GO((k_sample_lanes<false, false, true>));
+  } else if (S.lane_mode) {
+    if (t && b) QEC_GO((k_sample_lanes<true, true, false>));
+    else if (t) QEC_GO((k_sample_lanes<true, false, false>));
+    else if (b) QEC_GO((k_sample_lanes<false, true, false>));
+    else QEC_GO((k_sample_lanes<false, false, false>));
   } else if (S.warp_mode && S.fast) {
     if (t && b) QEC_GO((k_sample_linw<true, true, true>));
     else if (t) QEC_GO((k_sample_linw<true, false, true>));
