@@ -1120,15 +1120,17 @@ static int sampler_plan_linear(qec_sampler *s) {
     smem = words(lg, info_s, sig_s);
     return true;
   };
-  // read-out passes of the lane-stream variant: four rows per pass, a row never together with
-  // the previous row of its chain.  Entry: row | previous row << 8 (nc + 1 = the zero row: none)
-  // | 1 << 17 if a row follows | 1 << 18 valid
+  // read-out passes of the lane-stream variant: four rows per pass, four passes per trip of the
+  // kernel's loop (QEC_LANES_UNROLL), all of a trip's rows loaded before any is stored: a row is
+  // never in one trip with the previous row of its chain.  Entry: row | previous row << 8
+  // (nc + 1 = the zero row: none) | 1 << 17 if a row follows | 1 << 18 valid
   std::vector<uint32_t> lanes_prog;
   if (c->nc <= 254) {
     const uint32_t none = (uint32_t)c->nc + 1u;
+    const size_t trip = 16;
     std::vector<int> cur;
     auto flush = [&]() {
-      while (!cur.empty() && cur.size() < 4) cur.push_back(-1);
+      while (!cur.empty() && cur.size() < trip) cur.push_back(-1);
       for (int x : cur) {
         if (x < 0) { lanes_prog.push_back(none | (none << 8)); continue; }
         const int pr = use_diff ? pred[x] : -1, sc = use_diff ? succ[x] : -1;
@@ -1138,7 +1140,7 @@ static int sampler_plan_linear(qec_sampler *s) {
     };
     for (int cb = 0; cb < c->nc; ++cb) {
       const int pr = use_diff ? pred[cb] : -1;
-      if (cur.size() == 4 || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
+      if (cur.size() == trip || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
       cur.push_back(cb);
     }
     flush();

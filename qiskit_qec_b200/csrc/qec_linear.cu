@@ -757,6 +757,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
 // row nc+1 = always zero, the "previous row" of rows without one) | tally ncp] then hist 64,
 // prog 4 * n_steps (read-out passes), info2 2L, rec 2F.
 #define QEC_LANES_LGB 10
+#define QEC_LANES_UNROLL 4  // read-out passes per trip (the host pads the schedule: qec_capi.cu)
 
 // One candidate of a lane.  Absent record entries (and every entry of a lane without a fault)
 // name the dummy row nc, so the seven load / xor / store triples need no predicate.
@@ -857,33 +858,51 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
     // ---- the lane's fault stream
     LanePlanes P = {0u, 0u, 0u, 0u, 0u, 0u};
     uint32_t pos = 0xFFFFFFFFu;  // -1; saturates at `end`
-    // (software pipeline: the next call's Philox and gaps do not depend on the position, so they
-    // are computed while this call's candidates wait on shared memory)
-    QecPhilox r = qec_philox_rk(blo, bhi, (uint32_t)lane, 0x4D000000u, S.rk);
-    uint32_t g0 = qec_gap_len(r.c[0], C), g1 = qec_gap_len(r.c[2], C);
-    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); ++it) {
-      const QecPhilox rn = qec_philox_rk(blo, bhi, (it + 1u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP;
+    // Two Philox calls (four candidates) per trip, software-pipelined: the next trip's Philox
+    // and gaps do not depend on the position, so they are computed while this trip's candidates
+    // wait on shared memory (four independent dependency chains per warp instead of two).
+    QecPhilox ra = qec_philox_rk(blo, bhi, (uint32_t)lane, 0x4D000000u, S.rk);
+    QecPhilox rb = qec_philox_rk(blo, bhi, 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+    uint32_t g0 = qec_gap_len(ra.c[0], C), g1 = qec_gap_len(ra.c[2], C);
+    uint32_t g2 = qec_gap_len(rb.c[0], C), g3 = qec_gap_len(rb.c[2], C);
+    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); it += 2u) {
+      const QecPhilox na = qec_philox_rk(blo, bhi, (it + 2u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+      const QecPhilox nb = qec_philox_rk(blo, bhi, (it + 3u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+      const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP, has2 = g2 < QEC_GAP_CAP, has3 = g3 < QEC_GAP_CAP;
       const uint32_t p0 = pos + g0 + (has0 ? 1u : 0u), p1 = p0 + g1 + (has1 ? 1u : 0u);
-      // (pos + 1 <= end: the lane is still inside its stream; p0, p1 < 2^26 + end: no overflow)
+      const uint32_t p2 = p1 + g2 + (has2 ? 1u : 0u), p3 = p2 + g3 + (has3 ? 1u : 0u);
+      // (pos + 1 <= end: the lane is still inside its stream; positions stay below 2^27 + end)
       const bool live = pos + 1u <= end;
       const bool ok0 = live && has0 && p0 < end && (lane_sh + (p0 & 31u)) < nsh;
       const bool ok1 = live && has1 && p1 < end && (lane_sh + (p1 & 31u)) < nsh;
-      pos = live ? min(p1, end) : end;
+      const bool ok2 = live && has2 && p2 < end && (lane_sh + (p2 & 31u)) < nsh;
+      const bool ok3 = live && has3 && p3 < end && (lane_sh + (p3 & 31u)) < nsh;
+      pos = live ? min(p3, end) : end;
       const uint32_t sl0 = ok0 ? p0 >> 5 : 0u, sl1 = ok1 ? p1 >> 5 : 0u;
+      const uint32_t sl2 = ok2 ? p2 >> 5 : 0u, sl3 = ok3 ? p3 >> 5 : 0u;
       const uint2 i0 = ld_s64(info2_s + (sl0 << 3)), i1 = ld_s64(info2_s + (sl1 << 3));
-      const uint32_t d0 = __umulhi(r.c[1], i0.y), d1 = __umulhi(r.c[3], i1.y);
+      const uint2 i2 = ld_s64(info2_s + (sl2 << 3)), i3 = ld_s64(info2_s + (sl3 << 3));
+      const uint32_t d0 = __umulhi(ra.c[1], i0.y), d1 = __umulhi(ra.c[3], i1.y);
+      const uint32_t d2 = __umulhi(rb.c[1], i2.y), d3 = __umulhi(rb.c[3], i3.y);
       uint2 q0 = ld_s64(rec_s + ((i0.x + d0) << 3)), q1 = ld_s64(rec_s + ((i1.x + d1) << 3));
+      uint2 q2 = ld_s64(rec_s + ((i2.x + d2) << 3)), q3 = ld_s64(rec_s + ((i3.x + d3) << 3));
       if (!ok0) { q0.x = null_x; q0.y = null_y; }
       if (!ok1) { q1.x = null_x; q1.y = null_y; }
-      const uint32_t gn0 = qec_gap_len(rn.c[0], C), gn1 = qec_gap_len(rn.c[2], C);
+      if (!ok2) { q2.x = null_x; q2.y = null_y; }
+      if (!ok3) { q3.x = null_x; q3.y = null_y; }
+      const uint32_t n0 = qec_gap_len(na.c[0], C), n1 = qec_gap_len(na.c[2], C);
+      const uint32_t n2 = qec_gap_len(nb.c[0], C), n3 = qec_gap_len(nb.c[2], C);
       lanes_apply<EXPORT>(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
       lanes_apply<EXPORT>(S, p1, ok1, q1, d1, sl1, lane_acc, lane, base_shot, w_lo, X);
+      lanes_apply<EXPORT>(S, p2, ok2, q2, d2, sl2, lane_acc, lane, base_shot, w_lo, X);
+      lanes_apply<EXPORT>(S, p3, ok3, q3, d3, sl3, lane_acc, lane, base_shot, w_lo, X);
       if (TALLY) {
         planes_add(P, ok0 ? 1u << (p0 & 31u) : 0u);
         planes_add(P, ok1 ? 1u << (p1 & 31u) : 0u);
+        planes_add(P, ok2 ? 1u << (p2 & 31u) : 0u);
+        planes_add(P, ok3 ? 1u << (p3 & 31u) : 0u);
       }
-      r = rn; g0 = gn0; g1 = gn1;
+      ra = na; rb = nb; g0 = n0; g1 = n1; g2 = n2; g3 = n3;
     }
     __syncwarp();
 
@@ -891,39 +910,59 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
     const long long w0 = (b << 5) - w_lo;  // first output word of the batch (may be < 0 at the range start)
     const bool fastst = w0 >= 0 && w0 + 32 <= O.n_words && vec_ok;
     uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
-    for (uint32_t pass = 0; pass < (uint32_t)S.n_steps; ++pass) {
-      // row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a row
-      // follows in the chain | 1 << 18 if the slot holds a row at all
-      const uint32_t e = ld_s(prog_s + (((pass << 2) + rsub) << 2));
-      const uint32_t rr = e & 0xFFu;
-      const uint32_t a = acc_s + (rr << 7) + (c4 << 2);
-      const uint32_t ap = acc_s + (((e >> 8) & 0xFFu) << 7) + (c4 << 2);
-      uint4 v = ld_s128(a);
-      const uint4 pv = ld_s128(ap);
-      v.x ^= pv.x; v.y ^= pv.y; v.z ^= pv.z; v.w ^= pv.w;
-      st_s128z(ap);
-      {
-        const uint32_t keep = (e & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
-        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x & keep), "r"(v.y & keep), "r"(v.z & keep), "r"(v.w & keep) : "memory");
-      }
-      const bool rowok = (e & 0x40000u) != 0u;
-      if (BITS && rowok) {
-        uint32_t *po = O.bits + ((long long)rr * O.n_words + w0 + c4);
-        if (fastst) *reinterpret_cast<uint4 *>(po) = v;
-        else {
-          const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+    // (QEC_LANES_UNROLL passes per trip, all shared-memory loads first: the host schedules the
+    // passes so that no row of a trip has its previous row inside the same trip)
+    for (uint32_t pass = 0; pass < (uint32_t)S.n_steps; pass += QEC_LANES_UNROLL) {
+      // entry: row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a
+      // row follows in the chain | 1 << 18 if the slot holds a row at all
+      uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL], ap[QEC_LANES_UNROLL];
+      uint4 v[QEC_LANES_UNROLL], pv[QEC_LANES_UNROLL];
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(prog_s + ((((pass + u) << 2) + rsub) << 2));
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
+        a[u] = acc_s + ((e[u] & 0xFFu) << 7) + (c4 << 2);
+        ap[u] = acc_s + (((e[u] >> 8) & 0xFFu) << 7) + (c4 << 2);
+        v[u] = ld_s128(a[u]);
+        pv[u] = ld_s128(ap[u]);
+      }
+      uint32_t cpk[QEC_LANES_UNROLL / 2];
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
+        v[u].x ^= pv[u].x; v[u].y ^= pv[u].y; v[u].z ^= pv[u].z; v[u].w ^= pv[u].w;
+        st_s128z(ap[u]);
+        const uint32_t keep = (e[u] & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a[u]), "r"(v[u].x & keep), "r"(v[u].y & keep), "r"(v[u].z & keep), "r"(v[u].w & keep) : "memory");
+        const bool rowok = (e[u] & 0x40000u) != 0u;
+        if (BITS && rowok) {
+          uint32_t *po = O.bits + ((long long)(e[u] & 0xFFu) * O.n_words + w0 + c4);
+          if (fastst) *reinterpret_cast<uint4 *>(po) = v[u];
+          else {
+            const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
+          }
+        }
+        if (TALLY) {
+          anyv.x |= v[u].x; anyv.y |= v[u].y; anyv.z |= v[u].z; anyv.w |= v[u].w;
+          const uint32_t cnt = __popc(v[u].x) + __popc(v[u].y) + __popc(v[u].z) + __popc(v[u].w);
+          if (u & 1) cpk[u >> 1] |= cnt << 16; else cpk[u >> 1] = cnt;  // two rows' counts per register
         }
       }
       if (TALLY) {
-        anyv.x |= v.x; anyv.y |= v.y; anyv.z |= v.z; anyv.w |= v.w;
-        uint32_t cnt = __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);
-        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 1);
-        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 2);
-        cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, 4);
-        if (c4 == 0u && rowok) { const uint32_t ta = tal_s + (rr << 2); st_s(ta, ld_s(ta) + cnt); }
+#pragma unroll
+        for (int h = 0; h < QEC_LANES_UNROLL / 2; ++h) {
+          uint32_t c = cpk[h];  // (8-lane sums stay below 2^16: at most 1024 per row)
+          c += __shfl_xor_sync(0xFFFFFFFFu, c, 1);
+          c += __shfl_xor_sync(0xFFFFFFFFu, c, 2);
+          c += __shfl_xor_sync(0xFFFFFFFFu, c, 4);
+          if (c4 == 0u) {
+            // (invalid slots name the zero row, whose tally entry does not exist: skip them)
+            if (e[2 * h] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c & 0xFFFFu)); }
+            if (e[2 * h + 1] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h + 1] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c >> 16)); }
+          }
+        }
       }
     }
     if (TALLY) {
