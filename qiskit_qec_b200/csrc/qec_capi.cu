@@ -1155,7 +1155,10 @@ static int sampler_plan_linear(qec_sampler *s) {
     const bool can = draw == 2 && ln.cls_uniform_all && maxlen_w <= 7 && c->nc <= 254 && f_lgb == 0 &&
                      ((long long)s->L << 10) < (1ll << 30);
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
-    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; --wz) {
+    // (whole multiples of the four warp schedulers: batches are dealt to the warps statically, and
+    // a scheduler with one warp more than the others would finish last -- 9 warps measured
+    // slower than 8)
+    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; wz -= (w_env > 0 ? 1 : 4)) {
       const size_t need = qec_lanes_smem_words(c->nc, wz, (uint32_t)s->L, (uint32_t)F, (uint32_t)lanes_prog.size()) * 4 + 16;
       if (need > di.smem_optin) continue;
       found = true; lane_mode = 1; threads = 32 * wz; ctas = 1; lgb = 10; info_s = 1; sig_s = 0;

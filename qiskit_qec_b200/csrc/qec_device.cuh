@@ -148,7 +148,7 @@ static inline __host__ __device__ size_t qec_lanes_smem_words(int nc, int warps,
                                                               uint32_t prog_words) {
   const size_t ncp = ((size_t)nc + 3u) & ~(size_t)3u;
   const size_t per_warp = ((size_t)nc + 2u) * 32u + ncp;
-  return (size_t)warps * per_warp + 64u + prog_words + 2u * (size_t)L + 2u * (size_t)n_faults;
+  return (size_t)warps * per_warp + 64u + prog_words + (((size_t)L + 1u) & ~(size_t)1u) + 2u * (size_t)n_faults;
 }
 
 // Computed geometric gap (draw schemes 1 and 2).  u = (r | 1) / 2^32 is uniform on (0, 1);

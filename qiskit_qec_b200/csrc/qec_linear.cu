@@ -755,7 +755,7 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
 // records.
 // Shared memory: [warp regions: acc (nc+2)*32 (row nc = dummy target of absent record entries,
 // row nc+1 = always zero, the "previous row" of rows without one) | tally ncp] then hist 64,
-// prog 4 * n_steps (read-out passes), info2 2L, rec 2F.
+// prog 4 * n_steps (read-out passes), info L (first fault | number of Paulis << 21), rec 2F.
 #define QEC_LANES_LGB 10
 #define QEC_LANES_UNROLL 4  // read-out passes per trip (the host pads the schedule: qec_capi.cu)
 
@@ -820,11 +820,11 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   uint32_t *hist = qec_lin_smem + (size_t)NW * wwords;
   uint32_t *prog = hist + 64;
   uint32_t *info2 = prog + 4u * (uint32_t)S.n_steps;
-  uint32_t *rec = info2 + 2u * (uint32_t)S.L;
+  uint32_t *rec = info2 + (((uint32_t)S.L + 1u) & ~1u);
   {
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(S.info2);
-    for (uint32_t i = tid; i < 2u * (uint32_t)S.L; i += T) info2[i] = src[i];
-    src = reinterpret_cast<const uint32_t *>(S.sigrec);
+    // one word per location: first fault | number of Paulis << 21
+    for (uint32_t i = tid; i < (uint32_t)S.L; i += T) info2[i] = S.info2[i].x | (S.info2[i].y << 21);
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(S.sigrec);
     for (uint32_t i = tid; i < 2u * S.n_faults; i += T) rec[i] = src[i];
     for (uint32_t i = tid; i < 4u * (uint32_t)S.n_steps; i += T) prog[i] = S.rowprog[i];
     for (uint32_t i = tid; i < (uint32_t)NW * wwords + 64u; i += T) qec_lin_smem[i] = 0u;
@@ -880,12 +880,12 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
       pos = live ? min(p3, end) : end;
       const uint32_t sl0 = ok0 ? p0 >> 5 : 0u, sl1 = ok1 ? p1 >> 5 : 0u;
       const uint32_t sl2 = ok2 ? p2 >> 5 : 0u, sl3 = ok3 ? p3 >> 5 : 0u;
-      const uint2 i0 = ld_s64(info2_s + (sl0 << 3)), i1 = ld_s64(info2_s + (sl1 << 3));
-      const uint2 i2 = ld_s64(info2_s + (sl2 << 3)), i3 = ld_s64(info2_s + (sl3 << 3));
-      const uint32_t d0 = __umulhi(ra.c[1], i0.y), d1 = __umulhi(ra.c[3], i1.y);
-      const uint32_t d2 = __umulhi(rb.c[1], i2.y), d3 = __umulhi(rb.c[3], i3.y);
-      uint2 q0 = ld_s64(rec_s + ((i0.x + d0) << 3)), q1 = ld_s64(rec_s + ((i1.x + d1) << 3));
-      uint2 q2 = ld_s64(rec_s + ((i2.x + d2) << 3)), q3 = ld_s64(rec_s + ((i3.x + d3) << 3));
+      const uint32_t i0 = ld_s(info2_s + (sl0 << 2)), i1 = ld_s(info2_s + (sl1 << 2));
+      const uint32_t i2 = ld_s(info2_s + (sl2 << 2)), i3 = ld_s(info2_s + (sl3 << 2));
+      const uint32_t d0 = __umulhi(ra.c[1], i0 >> 21), d1 = __umulhi(ra.c[3], i1 >> 21);
+      const uint32_t d2 = __umulhi(rb.c[1], i2 >> 21), d3 = __umulhi(rb.c[3], i3 >> 21);
+      uint2 q0 = ld_s64(rec_s + (((i0 & 0x1FFFFFu) + d0) << 3)), q1 = ld_s64(rec_s + (((i1 & 0x1FFFFFu) + d1) << 3));
+      uint2 q2 = ld_s64(rec_s + (((i2 & 0x1FFFFFu) + d2) << 3)), q3 = ld_s64(rec_s + (((i3 & 0x1FFFFFu) + d3) << 3));
       if (!ok0) { q0.x = null_x; q0.y = null_y; }
       if (!ok1) { q1.x = null_x; q1.y = null_y; }
       if (!ok2) { q2.x = null_x; q2.y = null_y; }

@@ -64,6 +64,26 @@ def test_order2_outcomes_are_xors_of_order1_outcomes(capi, name):
     ("rep", 0.05, 20_000, 0), ("surf3", 0.01, 30_000, 4096 * 3 + 32 * 5), ("surf3x", 0.3, 6_000, 32),
     ("surf5", 1e-3, 40_000, 8192 - 64), ("arc", 2e-3, 20_000, 0), ("surf7", 5e-3, 9_000, 0)])
 def test_linear_sampler_equals_explicit_propagation(capi, port, name, p, n_shots, lo):
+    _check_sampler_against_port_and_oracle(capi, port, name, p, n_shots, lo)
+
+
+@pytest.mark.parametrize("mode,draw,kernel", [
+    ("lanes", None, "lane-streams"), ("warp", None, "warp-batches"), ("warp", "table", "draw=0"),
+    ("warp", "computed1", "draw=1"), ("cta", None, "cta-batches"), ("cta", "table", "draw=0")])
+@pytest.mark.parametrize("name,p,n_shots,lo", [("surf3", 0.01, 20_000, 4096 + 32 * 3), ("rep", 0.05, 9_000, 0),
+                                               ("surf5", 2e-3, 12_000, 1024 * 5 - 96)])
+def test_linear_sampler_every_kernel_and_draw_scheme(capi, port, monkeypatch, mode, draw, kernel, name, p, n_shots, lo):
+    """The three kernels (lane streams / warp batches / CTA batches) and the three draw schemes
+    (gap tables, computed gaps with one or two candidates per Philox call), each against the CPU
+    restatement of its draw order and against explicit propagation."""
+    monkeypatch.setenv("QEC_B200_LIN_MODE", mode)
+    if draw:
+        monkeypatch.setenv("QEC_B200_LIN_DRAW", draw)
+    _check_sampler_against_port_and_oracle(capi, port, name, p, n_shots, lo)
+    assert kernel in capi.last_kernel(), capi.last_kernel()
+
+
+def _check_sampler_against_port_and_oracle(capi, port, name, p, n_shots, lo):
     circ = _circuit(name)
     model = standard_depolarizing_model(p)
     idx, labels, lw, lp = sampler_inputs(circ, model)

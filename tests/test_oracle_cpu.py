@@ -154,3 +154,30 @@ def test_philox_known_answers():
     assert port.philox([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
     assert port.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
         [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_computed_gap_is_geometric():
+    """The sampler's computed gap (oracle/sampler_port.c gap_len == qec_gap_len on the device):
+    known answers, clamping, and P(gap >= k) = (1 - p)^k over a regular sweep of the 32-bit
+    draw (2^22 points, so the empirical tail is exact to ~2^-22 plus the polynomial's error)."""
+    import ctypes as C
+    from oracle import port
+    lib = port.lib()
+    lib.orc_gap_len.restype = C.c_uint32
+    lib.orc_gap_len.argtypes = [C.c_uint32, C.c_float]
+    for p in (1e-3, 0.05, 0.5):
+        c = np.float32(-1.0 / np.log2(1.0 - p))
+        r = (np.arange(1 << 22, dtype=np.uint64) << 10).astype(np.uint32) | np.uint32(0x155)
+        g = np.array([lib.orc_gap_len(int(x), c) for x in r[::64]], dtype=np.int64)
+        # exact answer from double arithmetic; the float path may differ by one slot at a boundary
+        u = ((r[::64] | 1).astype(np.float64)) / 2.0 ** 32
+        want = np.floor(np.log(u) / np.log1p(-p))
+        assert np.abs(g - want).max() <= 1 and (g != want).mean() < 2e-3
+        ks = np.array([0, 1, 2, 5, 10, 100, 1000])
+        tail = np.array([(g >= k).mean() for k in ks])
+        assert np.allclose(tail, (1 - p) ** ks, atol=4 * np.sqrt(0.25 / len(g)))
+    assert lib.orc_gap_len(0xFFFFFFFF, np.float32(692.8)) == 0           # u ~ 1: no gap
+    assert lib.orc_gap_len(0, np.float32(6.9e8)) == 1 << 24               # clamped
+    assert lib.orc_gap_len(0x30000000, np.float32(1.0)) == 2              # u = 3/16: -log2 u = 2.415
+    assert lib.orc_gap_len(0x30000000, np.float32(10.0)) == 24
+    assert lib.orc_gap_len(12345, np.float32(0.0)) == 0                   # p = 1: every slot
