@@ -759,15 +759,16 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
 #define QEC_LANES_LGB 10
 #define QEC_LANES_UNROLL 4  // read-out passes per trip (the host pads the schedule: qec_capi.cu)
 
-// One candidate of a lane.  Absent record entries (and every entry of a lane without a fault)
-// name the dummy row nc, so the seven load / xor / store triples need no predicate.
+// One candidate of a lane.  Absent record entries name the dummy row nc and a lane without a
+// fault XORs a zero mask (into whatever rows location 0's record names), so the seven load /
+// xor / store triples need no predicate.
 template <bool EXPORT>
 __device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p, const bool ok,
                                             const uint2 q, const uint32_t d, const uint32_t sl,
                                             const uint32_t lane_acc, const int lane,
                                             const long long base_shot, const long long w_lo,
                                             const QecSampleExport &X) {
-  const uint32_t bit = p & 31u, msk = 1u << bit;
+  const uint32_t bit = p & 31u, msk = ok ? 1u << bit : 0u;
   const uint32_t a0 = lane_acc + (__byte_perm(q.x, 0u, 0x4441u) << 7);
   const uint32_t a1 = lane_acc + (__byte_perm(q.x, 0u, 0x4442u) << 7);
   const uint32_t a2 = lane_acc + (__byte_perm(q.x, 0u, 0x4443u) << 7);
@@ -837,7 +838,6 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   const uint32_t prog_s = (uint32_t)__cvta_generic_to_shared(prog);
   const uint32_t info2_s = (uint32_t)__cvta_generic_to_shared(info2);
   const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec);
-  const uint32_t null_x = nc * 0x01010100u, null_y = nc * 0x01010101u;  // record of a lane without a fault
   const uint32_t end = (uint32_t)S.L << 5;
   const float C = S.gapC;
   unsigned long long nz_shots = 0;
@@ -884,12 +884,8 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
       const uint32_t i2 = ld_s(info2_s + (sl2 << 2)), i3 = ld_s(info2_s + (sl3 << 2));
       const uint32_t d0 = __umulhi(ra.c[1], i0 >> 21), d1 = __umulhi(ra.c[3], i1 >> 21);
       const uint32_t d2 = __umulhi(rb.c[1], i2 >> 21), d3 = __umulhi(rb.c[3], i3 >> 21);
-      uint2 q0 = ld_s64(rec_s + (((i0 & 0x1FFFFFu) + d0) << 3)), q1 = ld_s64(rec_s + (((i1 & 0x1FFFFFu) + d1) << 3));
-      uint2 q2 = ld_s64(rec_s + (((i2 & 0x1FFFFFu) + d2) << 3)), q3 = ld_s64(rec_s + (((i3 & 0x1FFFFFu) + d3) << 3));
-      if (!ok0) { q0.x = null_x; q0.y = null_y; }
-      if (!ok1) { q1.x = null_x; q1.y = null_y; }
-      if (!ok2) { q2.x = null_x; q2.y = null_y; }
-      if (!ok3) { q3.x = null_x; q3.y = null_y; }
+      const uint2 q0 = ld_s64(rec_s + (((i0 & 0x1FFFFFu) + d0) << 3)), q1 = ld_s64(rec_s + (((i1 & 0x1FFFFFu) + d1) << 3));
+      const uint2 q2 = ld_s64(rec_s + (((i2 & 0x1FFFFFu) + d2) << 3)), q3 = ld_s64(rec_s + (((i3 & 0x1FFFFFu) + d3) << 3));
       const uint32_t n0 = qec_gap_len(na.c[0], C), n1 = qec_gap_len(na.c[2], C);
       const uint32_t n2 = qec_gap_len(nb.c[0], C), n3 = qec_gap_len(nb.c[2], C);
       lanes_apply<EXPORT>(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
