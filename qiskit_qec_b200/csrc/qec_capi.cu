@@ -879,6 +879,7 @@ struct qec_sampler {
     uint16_t *d_sigrec = nullptr;
     std::vector<uint32_t> rowprog;
     uint32_t *d_rowprog = nullptr;
+    uint32_t *d_batch_ctr = nullptr;  // lane-stream kernel: next batch of the launch (dynamic assignment)
     bool cls_uniform_all = true;
     std::vector<uint32_t> info2;
     uint32_t *d_info2 = nullptr;
@@ -1155,10 +1156,9 @@ static int sampler_plan_linear(qec_sampler *s) {
     const bool can = draw == 2 && ln.cls_uniform_all && maxlen_w <= 7 && c->nc <= 254 && f_lgb == 0 &&
                      ((long long)s->L << 10) < (1ll << 30);
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
-    // (whole multiples of the four warp schedulers: batches are dealt to the warps statically, and
-    // a scheduler with one warp more than the others would finish last -- 9 warps measured
-    // slower than 8)
-    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; wz -= (w_env > 0 ? 1 : 4)) {
+    // (the kernel hands out batches dynamically, so the warp count need not be a multiple of the
+    // four schedulers: with static dealing 9 warps were slower than 8)
+    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; --wz) {
       const size_t need = qec_lanes_smem_words(c->nc, wz, (uint32_t)s->L, (uint32_t)F, (uint32_t)lanes_prog.size()) * 4 + 16;
       if (need > di.smem_optin) continue;
       found = true; lane_mode = 1; threads = 32 * wz; ctas = 1; lgb = 10; info_s = 1; sig_s = 0;
@@ -1279,6 +1279,10 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.n_faults = (uint32_t)F; d.n_sig = n_sig;
   d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
   d.rec2 = rec2; d.rowprog = ln.d_rowprog; d.n_steps = n_steps;
+  if (lane_mode) {
+    if (cudaMalloc(&ln.d_batch_ctr, 4) != cudaSuccess) return fail(QEC_ERR_CUDA, "cudaMalloc failed");
+    d.batch_ctr = ln.d_batch_ctr;
+  }
   d.rec8 = rec8; d.rec_in_smem = rec_s;
   d.uniform_digits = ln.cls_uniform_all ? 1 : 0;
   {  // Philox round keys: constant-bank operands of the kernels' XORs
@@ -1455,7 +1459,7 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
-                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2};
+                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1515,6 +1519,7 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
     long long n_batches = ((shot_lo + n_shots - 1) >> d.lgb) - (shot_lo >> d.lgb) + 1;
     if (d.warp_mode || d.lane_mode) n_batches = (n_batches + cfg.block / 32 - 1) / (cfg.block / 32);  // one per warp
     if (cfg.grid > n_batches) cfg.grid = (int)n_batches;
+    if (d.lane_mode) CU(cudaMemsetAsync(d.batch_ctr, 0, 4, stream));
     time_begin(s->c, stream);
     qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
     time_end(s->c, stream);

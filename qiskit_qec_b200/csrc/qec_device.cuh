@@ -141,6 +141,7 @@ struct QecLinDev {
   // lane-stream variant (k_sample_lanes): lgb = 10, lane = word column, no shared-memory atomics;
   // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
   int lane_mode;
+  uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
 };
 
 // shared-memory words of the lane-stream variant (1024-shot batches, `warps` warps per CTA)

@@ -848,7 +848,13 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   // read-out geometry: 8 lanes x 4 words per row, 4 rows per pass
   const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
 
-  for (long long b = b0 + (long long)blockIdx.x * NW + warp; b <= b1; b += (long long)gridDim.x * NW) {
+  // batches are handed out dynamically (one atomic per 1024 shots): results depend only on the
+  // batch index, and warps that share a scheduler with more neighbours simply take fewer
+  for (;;) {
+    uint32_t kb = 0;
+    if (lane == 0) kb = atomicAdd(S.batch_ctr, 1u);
+    const long long b = b0 + (long long)__shfl_sync(0xFFFFFFFFu, kb, 0);
+    if (b > b1) break;
     const long long base_shot = b << QEC_LANES_LGB;
     const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
     const uint32_t shi = (uint32_t)min(1024ll, shot_lo + n_shots - base_shot);
