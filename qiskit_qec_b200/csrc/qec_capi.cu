@@ -522,7 +522,17 @@ struct qec_enumerator {
   int jit_tab_in_smem = 0;
   DevBuf redo_list;                    // lane words the specialised kernel deferred
   unsigned int *d_redo_count = nullptr;
+  // linear-response path (k_enum_lanes): per-fault signature records, read-out schedule
+  struct Lin {
+    bool eligible = false;
+    std::string why;
+    QecEnumLinDev dev{};
+    QecLaunchCfg cfg{};
+    uint32_t *d_rowprog = nullptr, *d_rec = nullptr, *d_ctr = nullptr;
+  } lin;
 };
+
+static int enum_plan_linear(qec_enumerator *e);
 
 // Can this enumerator run on the specialised kernel?  (the frame must fit the register file,
 // the location list must be in strictly increasing op order so that the mask events of a lane
@@ -638,6 +648,10 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
       return rc;
     }
     enum_plan_jit(e);
+    if ((rc = enum_plan_linear(e))) {
+      qec_enumerator_destroy(e);
+      return rc;
+    }
     if (e->jit.eligible) {
       const size_t words = (size_t)e->jit.grid * e->jit.threads * 5 * (32 * order + 2);
       if ((rc = upload(e->tile, &e->d_tile)) || (rc = e->jit_scratch.ensure(words * 4))) {
@@ -650,6 +664,129 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
     e->dev.poff = e->d_poff; e->dev.pcode = e->d_pcode; e->dev.lop = e->d_lop;
   }
   *out = e;
+  return 0;
+}
+
+// Linear-response enumerator (k_enum_lanes): the signature of every single fault (one frame
+// propagation each, on the GPU, through qec_propagate_batch), as 8-byte records in the
+// time-difference basis when that shortens them, plus the read-out schedule -- the same tables
+// as the lane-stream sampler's.  Used when they fit (nc <= 254, at most 7 entries per fault, at
+// least 4 warps' accumulators) and the circuit is long enough for the gate stream to cost more
+// than the signatures (QEC_B200_ENUM=linear|frame forces the choice).
+static int enum_plan_linear(qec_enumerator *e) {
+  qec_enumerator::Lin &ln = e->lin;
+  qec_circuit *c = e->c;
+  const char *mode = std::getenv("QEC_B200_ENUM");
+  if (mode && !strcmp(mode, "frame")) { ln.why = "QEC_B200_ENUM=frame"; return 0; }
+  const bool forced = mode && !strcmp(mode, "linear");
+  if (mode && !forced) return fail(QEC_ERR_INVALID, "QEC_B200_ENUM must be linear or frame");
+  if (e->order < 1 || e->order > QEC_KERNEL_MAX_ORDER) { ln.why = "order beyond the kernel's"; return 0; }
+  if (c->nc > 254 || c->nc < 1) { ln.why = "more than 254 clbits"; return 0; }
+  if (!forced && c->packed.size() < (size_t)env_int("QEC_B200_ENUM_LINEAR_MIN_OPS", 400)) {
+    ln.why = "short circuit: frame propagation is cheaper";
+    return 0;
+  }
+  const int64_t F = (int64_t)e->pcode.size();
+  if (F < 1 || F >= (1 << 21)) { ln.why = "fault count out of range"; return 0; }
+  // single-fault paths in (location, digit) order = fault index poff[l] + d
+  std::vector<int64_t> path_off((size_t)F + 1);
+  std::vector<int32_t> fop((size_t)F);
+  for (int64_t f = 0; f <= F; ++f) path_off[f] = f;
+  for (int l = 0; l < e->L; ++l)
+    for (uint32_t d = 0; d < e->npaul[l]; ++d) fop[e->poff[l] + d] = (int32_t)e->lop[l];
+  const int64_t FW = (F + 31) / 32;
+  std::vector<uint32_t> bits((size_t)c->nc * FW);
+  int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), e->pcode.data(), bits.data(), nullptr);
+  if (rc) return rc;
+  std::vector<std::vector<uint16_t>> lists((size_t)F), tr((size_t)F);
+  for (int cb = 0; cb < c->nc; ++cb)
+    for (int64_t fw = 0; fw < FW; ++fw)
+      for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u)
+        lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
+  // time-difference basis: clbit c -> c ^ pred(c), pred = the previous final measurement of the
+  // same qubit (see sampler_plan_linear)
+  std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
+  for (size_t i = 0; i < c->packed.size(); ++i) {
+    const uint32_t g = c->packed[i];
+    if ((g & 15u) != QOP_MEASF) continue;
+    const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
+    if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
+    last[q] = cb;
+  }
+  size_t raw_total = 0, tr_total = 0;
+  {
+    std::vector<uint8_t> mark(c->nc, 0);
+    for (int64_t f = 0; f < F; ++f) {
+      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
+      for (uint16_t cb : lists[f]) {
+        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
+        const int sc = succ[cb];
+        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
+      }
+      std::sort(tr[f].begin(), tr[f].end());
+      raw_total += lists[f].size();
+      tr_total += tr[f].size();
+    }
+  }
+  const bool use_diff = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
+  if (use_diff) lists.swap(tr);
+  size_t maxlen = 0;
+  for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
+  if (maxlen > 7) { ln.why = "a fault flips more than 7 entries"; return 0; }
+  std::vector<uint32_t> rec((size_t)2 * F);
+  for (int64_t f = 0; f < F; ++f) {
+    uint8_t by[8];
+    by[0] = (uint8_t)((1u << lists[f].size()) - 1u);
+    for (int k = 0; k < 7; ++k) by[1 + k] = k < (int)lists[f].size() ? (uint8_t)lists[f][k] : (uint8_t)c->nc;
+    memcpy(&rec[2 * f], by, 8);
+  }
+  // read-out schedule (as in sampler_plan_linear: four rows per pass, 16 per trip, a row never in
+  // one trip with the previous row of its chain)
+  std::vector<uint32_t> prog;
+  {
+    const uint32_t none = (uint32_t)c->nc + 1u;
+    const size_t trip = 16;
+    std::vector<int> cur;
+    auto flush = [&]() {
+      while (!cur.empty() && cur.size() < trip) cur.push_back(-1);
+      for (int x : cur) {
+        if (x < 0) { prog.push_back(none | (none << 8)); continue; }
+        const int pr = use_diff ? pred[x] : -1, sc = use_diff ? succ[x] : -1;
+        prog.push_back((uint32_t)x | ((pr >= 0 ? (uint32_t)pr : none) << 8) | (sc >= 0 ? (1u << 17) : 0u) | (1u << 18));
+      }
+      cur.clear();
+    };
+    for (int cb = 0; cb < c->nc; ++cb) {
+      const int pr = use_diff ? pred[cb] : -1;
+      if (cur.size() == trip || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
+      cur.push_back(cb);
+    }
+    flush();
+  }
+  const DevInfo &di = *c->info;
+  const int w_env = env_int("QEC_B200_ENUM_WARPS", 0);
+  int warps = 0;
+  size_t smem = 0;
+  for (int wz = (w_env > 0 ? w_env : 16); wz >= (w_env > 0 ? w_env : 4); --wz) {
+    const size_t need = qec_enum_lanes_smem_words(c->nc, wz, (uint32_t)F, (uint32_t)prog.size()) * 4 + 16;
+    if (need > di.smem_optin) continue;
+    warps = wz; smem = need;
+    break;
+  }
+  if (!warps) { ln.why = "accumulators and records do not fit in shared memory"; return 0; }
+  if ((rc = upload(prog, &ln.d_rowprog)) || (rc = upload(rec, &ln.d_rec))) return rc;
+  CU(cudaMalloc((void **)&ln.d_ctr, 4));
+  {
+    const int er = qec_enum_lanes_set_smem_attr(smem);
+    if (er) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)er));
+  }
+  ln.dev.nc = c->nc; ln.dev.n_steps = (int)(prog.size() / 4);
+  ln.dev.rowprog = ln.d_rowprog;
+  ln.dev.sigrec = reinterpret_cast<const uint2 *>(ln.d_rec);
+  ln.dev.n_faults = (uint32_t)F;
+  ln.dev.batch_ctr = ln.d_ctr;
+  ln.cfg.block = 32 * warps; ln.cfg.grid = di.sms; ln.cfg.smem = smem;
+  ln.eligible = true;
   return 0;
 }
 
@@ -666,6 +803,9 @@ extern "C" void qec_enumerator_destroy(qec_enumerator *e) {
   e->jit_scratch.release();
   e->redo_list.release();
   if (e->d_redo_count) cudaFree(e->d_redo_count);
+  if (e->lin.d_rowprog) cudaFree(e->lin.d_rowprog);
+  if (e->lin.d_rec) cudaFree(e->lin.d_rec);
+  if (e->lin.d_ctr) cudaFree(e->lin.d_ctr);
   e->jit.release();
   delete e;
 }
@@ -735,6 +875,20 @@ static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bi
   O.frame = nullptr;
   O.tally = (unsigned long long *)d_tally;
   O.n_words = (hi - lo + 31) / 32;
+  if (e->lin.eligible) {
+    QecLaunchCfg cfg = e->lin.cfg;
+    const long long n_batches = (hi - lo + 1023) / 1024;
+    const long long per = (n_batches + cfg.block / 32 - 1) / (cfg.block / 32);
+    if (cfg.grid > per) cfg.grid = (int)per;
+    CU(cudaMemsetAsync(e->lin.dev.batch_ctr, 0, 4, stream));
+    time_begin(e->c, stream);
+    qec_launch_enum_lanes(cfg, stream, O, e->dev, e->lin.dev, lo, hi);
+    time_end(e->c, stream);
+    CU(cudaGetLastError());
+    g_last_kernel = "enumerate:linear lane-words order=" + std::to_string(e->order) + " T=" +
+                    std::to_string(cfg.block) + " smem=" + std::to_string(cfg.smem);
+    return 0;
+  }
   if (e->jit.eligible) {
     JitVariant *v = jit_get(e->c, e->jit, 1, e->order, d_tally != nullptr, d_bits != nullptr);
     if (v->ok) {

@@ -144,6 +144,23 @@ struct QecLinDev {
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
 };
 
+// Linear-response enumerator (k_enum_lanes in qec_linear.cu): outcome(path) = XOR of the
+// signatures of its faults (the locations of a path are distinct, so no op carries two faults).
+// Same lane-owned accumulator and read-out as the lane-stream sampler: a warp owns 1024
+// consecutive paths, lane l the 32 paths of word l.
+struct QecEnumLinDev {
+  int nc, n_steps;          // read-out passes (rowprog: [n_steps][4], see QecLinDev)
+  const uint32_t *rowprog;
+  const uint2 *sigrec;      // [n_faults] 8-byte records: fault = poff[location] + digit
+  uint32_t n_faults;
+  uint32_t *batch_ctr;      // batches handed out so far in this launch (zeroed per launch)
+};
+static inline __host__ __device__ size_t qec_enum_lanes_smem_words(int nc, int warps, uint32_t n_faults,
+                                                                   uint32_t prog_words) {
+  const size_t ncp = ((size_t)nc + 3u) & ~(size_t)3u;
+  return (size_t)warps * (((size_t)nc + 2u) * 32u + ncp) + prog_words + 2u * (size_t)n_faults;
+}
+
 // shared-memory words of the lane-stream variant (1024-shot batches, `warps` warps per CTA)
 static inline __host__ __device__ size_t qec_lanes_smem_words(int nc, int warps, uint32_t L, uint32_t n_faults,
                                                               uint32_t prog_words) {

@@ -26,6 +26,10 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecLinDev &S, long long shot_lo, long long n_shots,
                            const QecSampleExport &X);
 int qec_lin_set_smem_attr(size_t smem);
+// linear-response enumerator (qec_linear.cu); order 1..QEC_KERNEL_MAX_ORDER
+void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
+                           const QecEnumDev &E, const QecEnumLinDev &EL, long long lo, long long hi);
+int qec_enum_lanes_set_smem_attr(size_t smem);
 void qec_launch_outcome_hist(cudaStream_t stream, const uint32_t *bits, int nc, long long n_paths,
                              unsigned long long *keys, unsigned long long *counts,
                              long long table_cap);

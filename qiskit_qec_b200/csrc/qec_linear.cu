@@ -791,6 +791,85 @@ __device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p
   }
 }
 
+// Read-out of a lane-owned accumulator acc[row][32 word columns] (batch = 32 output words
+// starting at word w0): four rows per pass (8 lanes x 128 bits per row: conflict-free shared
+// loads, one full 128-byte line per row stored), QEC_LANES_UNROLL passes per trip with all
+// shared-memory loads first (the host schedules the passes so that no row of a trip has its
+// previous row inside the same trip); the time-difference basis is undone in place and every row
+// is left zero.  Per-row ones are added to the warp's tally row; returns this lane's share of the
+// batch's non-zero outcomes (lanes 0..7 carry it).
+template <bool TALLY, bool BITS>
+__device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
+                                                  const uint32_t prog_s, const uint32_t n_steps,
+                                                  const long long w0, const bool vec_ok, const int lane) {
+  const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
+  const bool fastst = w0 >= 0 && w0 + 32 <= O.n_words && vec_ok;
+  uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
+  for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
+    // entry: row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a
+    // row follows in the chain | 1 << 18 if the slot holds a row at all
+    uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL], ap[QEC_LANES_UNROLL];
+    uint4 v[QEC_LANES_UNROLL], pv[QEC_LANES_UNROLL];
+#pragma unroll
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(prog_s + ((((pass + u) << 2) + rsub) << 2));
+#pragma unroll
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
+      a[u] = acc_s + ((e[u] & 0xFFu) << 7) + (c4 << 2);
+      ap[u] = acc_s + (((e[u] >> 8) & 0xFFu) << 7) + (c4 << 2);
+      v[u] = ld_s128(a[u]);
+      pv[u] = ld_s128(ap[u]);
+    }
+    uint32_t cpk[QEC_LANES_UNROLL / 2];
+#pragma unroll
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
+      v[u].x ^= pv[u].x; v[u].y ^= pv[u].y; v[u].z ^= pv[u].z; v[u].w ^= pv[u].w;
+      st_s128z(ap[u]);
+      const uint32_t keep = (e[u] & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
+      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a[u]), "r"(v[u].x & keep), "r"(v[u].y & keep), "r"(v[u].z & keep), "r"(v[u].w & keep) : "memory");
+      const bool rowok = (e[u] & 0x40000u) != 0u;
+      if (BITS && rowok) {
+        uint32_t *po = O.bits + ((long long)(e[u] & 0xFFu) * O.n_words + w0 + c4);
+        if (fastst) *reinterpret_cast<uint4 *>(po) = v[u];
+        else {
+          const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
+        }
+      }
+      if (TALLY) {
+        anyv.x |= v[u].x; anyv.y |= v[u].y; anyv.z |= v[u].z; anyv.w |= v[u].w;
+        const uint32_t cnt = __popc(v[u].x) + __popc(v[u].y) + __popc(v[u].z) + __popc(v[u].w);
+        if (u & 1) cpk[u >> 1] |= cnt << 16; else cpk[u >> 1] = cnt;  // two rows' counts per register
+      }
+    }
+    if (TALLY) {
+#pragma unroll
+      for (int h = 0; h < QEC_LANES_UNROLL / 2; ++h) {
+        uint32_t c = cpk[h];  // (8-lane sums stay below 2^16: at most 1024 per row)
+        c += __shfl_xor_sync(0xFFFFFFFFu, c, 1);
+        c += __shfl_xor_sync(0xFFFFFFFFu, c, 2);
+        c += __shfl_xor_sync(0xFFFFFFFFu, c, 4);
+        if (c4 == 0u) {
+          // (invalid slots name the zero row, whose tally entry does not exist: skip them)
+          if (e[2 * h] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c & 0xFFFFu)); }
+          if (e[2 * h + 1] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h + 1] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c >> 16)); }
+        }
+      }
+    }
+  }
+  uint32_t nz = 0;
+  if (TALLY) {
+    // non-zero outcomes: OR over the four row groups, then lanes 0..7 hold the batch's 32 words
+    anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 8); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 8);
+    anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 8); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 8);
+    anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 16); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 16);
+    anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 16); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 16);
+    if (lane < 8) nz = __popc(anyv.x) + __popc(anyv.y) + __popc(anyv.z) + __popc(anyv.w);
+  }
+  return nz;
+}
+
 // faults-per-shot counters of a lane's 32 shots: six bit planes, ripple-carry increment of the
 // shots in mask c (the carry rarely leaves plane 1)
 struct LanePlanes {
@@ -845,8 +924,6 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   const long long b0 = shot_lo >> QEC_LANES_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LANES_LGB;
   const long long w_lo = shot_lo >> 5;
   const bool vec_ok = ((O.n_words | w_lo) & 3) == 0 && ((size_t)O.bits & 15) == 0;
-  // read-out geometry: 8 lanes x 4 words per row, 4 rows per pass
-  const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
 
   // batches are handed out dynamically (one atomic per 1024 shots): results depend only on the
   // batch index, and warps that share a scheduler with more neighbours simply take fewer
@@ -908,72 +985,11 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
     }
     __syncwarp();
 
-    // ---- read-out: four rows per pass, lane = (row of the pass, 4-word piece of the row)
+    // ---- read-out (lanes_readout): four rows per pass, lane = (row of the pass, 4-word piece)
     const long long w0 = (b << 5) - w_lo;  // first output word of the batch (may be < 0 at the range start)
-    const bool fastst = w0 >= 0 && w0 + 32 <= O.n_words && vec_ok;
-    uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
-    // (QEC_LANES_UNROLL passes per trip, all shared-memory loads first: the host schedules the
-    // passes so that no row of a trip has its previous row inside the same trip)
-    for (uint32_t pass = 0; pass < (uint32_t)S.n_steps; pass += QEC_LANES_UNROLL) {
-      // entry: row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a
-      // row follows in the chain | 1 << 18 if the slot holds a row at all
-      uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL], ap[QEC_LANES_UNROLL];
-      uint4 v[QEC_LANES_UNROLL], pv[QEC_LANES_UNROLL];
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(prog_s + ((((pass + u) << 2) + rsub) << 2));
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-        a[u] = acc_s + ((e[u] & 0xFFu) << 7) + (c4 << 2);
-        ap[u] = acc_s + (((e[u] >> 8) & 0xFFu) << 7) + (c4 << 2);
-        v[u] = ld_s128(a[u]);
-        pv[u] = ld_s128(ap[u]);
-      }
-      uint32_t cpk[QEC_LANES_UNROLL / 2];
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-        v[u].x ^= pv[u].x; v[u].y ^= pv[u].y; v[u].z ^= pv[u].z; v[u].w ^= pv[u].w;
-        st_s128z(ap[u]);
-        const uint32_t keep = (e[u] & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
-        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a[u]), "r"(v[u].x & keep), "r"(v[u].y & keep), "r"(v[u].z & keep), "r"(v[u].w & keep) : "memory");
-        const bool rowok = (e[u] & 0x40000u) != 0u;
-        if (BITS && rowok) {
-          uint32_t *po = O.bits + ((long long)(e[u] & 0xFFu) * O.n_words + w0 + c4);
-          if (fastst) *reinterpret_cast<uint4 *>(po) = v[u];
-          else {
-            const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
-          }
-        }
-        if (TALLY) {
-          anyv.x |= v[u].x; anyv.y |= v[u].y; anyv.z |= v[u].z; anyv.w |= v[u].w;
-          const uint32_t cnt = __popc(v[u].x) + __popc(v[u].y) + __popc(v[u].z) + __popc(v[u].w);
-          if (u & 1) cpk[u >> 1] |= cnt << 16; else cpk[u >> 1] = cnt;  // two rows' counts per register
-        }
-      }
-      if (TALLY) {
-#pragma unroll
-        for (int h = 0; h < QEC_LANES_UNROLL / 2; ++h) {
-          uint32_t c = cpk[h];  // (8-lane sums stay below 2^16: at most 1024 per row)
-          c += __shfl_xor_sync(0xFFFFFFFFu, c, 1);
-          c += __shfl_xor_sync(0xFFFFFFFFu, c, 2);
-          c += __shfl_xor_sync(0xFFFFFFFFu, c, 4);
-          if (c4 == 0u) {
-            // (invalid slots name the zero row, whose tally entry does not exist: skip them)
-            if (e[2 * h] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c & 0xFFFFu)); }
-            if (e[2 * h + 1] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h + 1] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c >> 16)); }
-          }
-        }
-      }
-    }
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)S.n_steps, w0, vec_ok, lane);
     if (TALLY) {
-      // non-zero shots: OR over the four row groups, then lanes 0..7 hold the batch's 32 words
-      anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 8); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 8);
-      anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 8); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 8);
-      anyv.x |= __shfl_xor_sync(0xFFFFFFFFu, anyv.x, 16); anyv.y |= __shfl_xor_sync(0xFFFFFFFFu, anyv.y, 16);
-      anyv.z |= __shfl_xor_sync(0xFFFFFFFFu, anyv.z, 16); anyv.w |= __shfl_xor_sync(0xFFFFFFFFu, anyv.w, 16);
-      if (lane < 8) nz_shots += __popc(anyv.x) + __popc(anyv.y) + __popc(anyv.z) + __popc(anyv.w);
+      nz_shots += nzb;
       // faults-per-shot histogram from the planes
       const uint32_t hi = P.p2 | P.p3 | P.p4 | P.p5;
       h1 += __popc(P.p0 & ~P.p1 & ~hi);
@@ -1018,6 +1034,94 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
       atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
       atomicAdd(&O.tally[S.nc + 2], (unsigned long long)n_shots);
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Linear-response enumerator: the paths of FaultEnumerator::enumerate (reference
+// faultenumerator.cpp:71-111) have distinct locations, so outcome(path) = XOR of the signatures
+// of its K faults -- no gate stream.  A warp owns 1024 consecutive paths, lane l the 32 paths of
+// output word l: it unranks its first path once (enum_unrank) and steps through the other 31
+// (enum_next), XORing each fault's 8-byte record into its own accumulator column with plain
+// load / xor / store (bank = lane), exactly as the lane-stream sampler does; all lanes have the
+// same 32 paths of work, so there is no imbalance.  Read-out: lanes_readout.
+// Shared memory: [warp regions: acc (nc+2)*32 | tally ncp] then prog 4 * n_steps, rec 2F.
+template <int K, bool TALLY, bool BITS>
+__global__ void __launch_bounds__(512, 1)
+k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, const long long lo, const long long hi) {
+  extern __shared__ __align__(16) uint32_t qec_lin_smem[];
+  const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
+  const uint32_t nc = (uint32_t)EL.nc, ncp = (nc + 3u) & ~3u;
+  const uint32_t wwords = (nc + 2u) * 32u + ncp;
+  uint32_t *acc = qec_lin_smem + (size_t)warp * wwords;
+  uint32_t *prog = qec_lin_smem + (size_t)NW * wwords;
+  uint32_t *rec = prog + 4u * (uint32_t)EL.n_steps;
+  {
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(EL.sigrec);
+    for (uint32_t i = tid; i < 2u * EL.n_faults; i += T) rec[i] = src[i];
+    for (uint32_t i = tid; i < 4u * (uint32_t)EL.n_steps; i += T) prog[i] = EL.rowprog[i];
+    for (uint32_t i = tid; i < (uint32_t)NW * wwords; i += T) qec_lin_smem[i] = 0u;
+  }
+  __syncthreads();
+  const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(acc);
+  const uint32_t lane_acc = acc_s + ((uint32_t)lane << 2);
+  const uint32_t tal_s = acc_s + (((nc + 2u) * 32u) << 2);
+  const uint32_t prog_s = (uint32_t)__cvta_generic_to_shared(prog);
+  const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec);
+  const bool vec_ok = (O.n_words & 3) == 0 && ((size_t)O.bits & 15) == 0;
+  const long long n_paths = hi - lo;
+  const long long n_batches = (n_paths + 1023) >> 10;
+  unsigned long long nz_paths = 0;
+
+  for (;;) {
+    uint32_t kb = 0;
+    if (lane == 0) kb = atomicAdd(EL.batch_ctr, 1u);
+    const long long b = (long long)__shfl_sync(0xFFFFFFFFu, kb, 0);
+    if (b >= n_batches) break;
+    const long long first = (b << 10) + ((long long)lane << 5);  // relative to lo
+    const int nv = (int)max(0ll, min(32ll, n_paths - first));
+    if (nv > 0) {
+      EnumState<K> st;
+      enum_unrank<K>(E, (unsigned long long)(lo + first), st);
+      for (int i = 0; i < nv; ++i) {
+        const uint32_t msk = 1u << i;
+        uint2 q[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) q[j] = ld_s64(rec_s + ((st.pb[j] + st.dig[j]) << 3));
+        if (i + 1 < nv) enum_next<K>(E, st);
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          // (two faults of a path may flip the same row: one record at a time, loads first)
+          const uint32_t a0 = lane_acc + (__byte_perm(q[j].x, 0u, 0x4441u) << 7);
+          const uint32_t a1 = lane_acc + (__byte_perm(q[j].x, 0u, 0x4442u) << 7);
+          const uint32_t a2 = lane_acc + (__byte_perm(q[j].x, 0u, 0x4443u) << 7);
+          const uint32_t a3 = lane_acc + (__byte_perm(q[j].y, 0u, 0x4440u) << 7);
+          const uint32_t a4 = lane_acc + (__byte_perm(q[j].y, 0u, 0x4441u) << 7);
+          const uint32_t a5 = lane_acc + (__byte_perm(q[j].y, 0u, 0x4442u) << 7);
+          const uint32_t a6 = lane_acc + (__byte_perm(q[j].y, 0u, 0x4443u) << 7);
+          const uint32_t v0 = ld_s(a0), v1 = ld_s(a1), v2 = ld_s(a2), v3 = ld_s(a3), v4 = ld_s(a4),
+                         v5 = ld_s(a5), v6 = ld_s(a6);
+          st_s(a0, v0 ^ msk); st_s(a1, v1 ^ msk); st_s(a2, v2 ^ msk); st_s(a3, v3 ^ msk);
+          st_s(a4, v4 ^ msk); st_s(a5, v5 ^ msk); st_s(a6, v6 ^ msk);
+        }
+      }
+    }
+    __syncwarp();
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)EL.n_steps, b << 5, vec_ok, lane);
+    if (TALLY) nz_paths += nzb;
+    __syncwarp();
+  }
+
+  if (TALLY) {
+    for (int off = 16; off > 0; off >>= 1) nz_paths += __shfl_down_sync(0xFFFFFFFFu, nz_paths, off);
+    if (lane == 0 && nz_paths) atomicAdd(&O.tally[nc], nz_paths);
+    __syncthreads();
+    for (uint32_t c = tid; c < nc; c += T) {
+      unsigned long long v = 0;
+      for (int k = 0; k < NW; ++k) v += qec_lin_smem[(size_t)k * wwords + (nc + 2u) * 32u + c];
+      if (v) atomicAdd(&O.tally[c], v);
+    }
+    if (blockIdx.x == 0 && tid == 0) atomicAdd(&O.tally[nc + 1], (unsigned long long)n_paths);
   }
 }
 
@@ -1072,6 +1176,36 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
     else if (t) QEC_GO((k_sample_lin<true, false>));
     else if (b) QEC_GO((k_sample_lin<false, true>));
     else QEC_GO((k_sample_lin<false, false>));
+  }
+#undef QEC_GO
+}
+
+int qec_enum_lanes_set_smem_attr(size_t smem) {
+  const int s = (int)smem;
+  cudaError_t e;
+#define QEC_SET(fn) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, s); \
+  if (e != cudaSuccess) return (int)e;
+#define QEC_SETK(K) QEC_SET((k_enum_lanes<K, true, true>)) QEC_SET((k_enum_lanes<K, true, false>)) \
+  QEC_SET((k_enum_lanes<K, false, true>)) QEC_SET((k_enum_lanes<K, false, false>))
+  QEC_SETK(1) QEC_SETK(2) QEC_SETK(3) QEC_SETK(4)
+#undef QEC_SETK
+#undef QEC_SET
+  return 0;
+}
+
+void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
+                           const QecEnumDev &E, const QecEnumLinDev &EL, long long lo, long long hi) {
+  const bool t = O.tally != nullptr, b = O.bits != nullptr;
+#define QEC_GO(K) \
+  if (t && b) k_enum_lanes<K, true, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else if (t) k_enum_lanes<K, true, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else if (b) k_enum_lanes<K, false, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else k_enum_lanes<K, false, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi);
+  switch (E.order) {
+    case 1: QEC_GO(1) break;
+    case 2: QEC_GO(2) break;
+    case 3: QEC_GO(3) break;
+    default: QEC_GO(4) break;
   }
 #undef QEC_GO
 }

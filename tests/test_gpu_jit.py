@@ -23,14 +23,19 @@ class jit_env:
         self.value = value
 
     def __enter__(self):
+        # (these tests are about the frame-propagation kernels: keep the linear-response
+        # enumerator, the default for long circuits, out of the way)
         self.old = os.environ.get("QEC_B200_JIT")
+        self.old_enum = os.environ.get("QEC_B200_ENUM")
         os.environ["QEC_B200_JIT"] = self.value
+        os.environ["QEC_B200_ENUM"] = "frame"
 
     def __exit__(self, *a):
-        if self.old is None:
-            os.environ.pop("QEC_B200_JIT", None)
-        else:
-            os.environ["QEC_B200_JIT"] = self.old
+        for key, old in (("QEC_B200_JIT", self.old), ("QEC_B200_ENUM", self.old_enum)):
+            if old is None:
+                os.environ.pop(key, None)
+            else:
+                os.environ[key] = old
 
 
 def _circuit(name):

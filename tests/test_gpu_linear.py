@@ -226,3 +226,35 @@ def test_frame_mode_switch(capi, monkeypatch):
     sm.sample(0, 4096)
     assert "sample:linear" not in capi.last_kernel()
     assert not int(sm.tables()[7]) & 2
+
+
+@pytest.mark.parametrize("name,order", [("rep", 1), ("rep", 2), ("rep", 3), ("surf3", 1), ("surf3", 2),
+                                        ("surf3x", 2), ("arc", 2), ("arc", 3), ("surf5", 1), ("surf5", 2)])
+def test_linear_enumerator_equals_frame_enumerator(capi, monkeypatch, name, order):
+    """k_enum_lanes (outcome = XOR of the faults' signatures) against the frame-propagation
+    enumerators, bit for bit: whole enumerations when small, else windows cut anywhere (unaligned
+    starts, ragged ends, the last paths), bits and tallies."""
+    circ = _circuit(name)
+    idx, labels, paulis = noise_inputs(circ, standard_depolarizing_model())
+    monkeypatch.setenv("QEC_B200_ENUM", "linear")
+    gl = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    el = make_enumerator(capi, gl, order, idx, paulis)
+    monkeypatch.setenv("QEC_B200_ENUM", "frame")
+    gf = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    ef = make_enumerator(capi, gf, order, idx, paulis)
+    n = el.num_paths()
+    assert n == ef.num_paths()
+    rng = np.random.default_rng(3)
+    ranges = [(0, min(n, 70_000)), (max(0, n - 33_333), n), (0, 1), (n - 1, n)]
+    ranges += [(int(lo), int(min(n, lo + rng.integers(1, 5000)))) for lo in rng.integers(0, n, size=6)]
+    for lo, hi in ranges:
+        bl, tl = el.range(lo, hi, want_tally=True)
+        assert "enumerate:linear" in capi.last_kernel(), capi.last_kernel()
+        _, tl2 = el.range(lo, hi, want_bits=False, want_tally=True)
+        bl3, _ = el.range(lo, hi)
+        bf, tf = ef.range(lo, hi, want_tally=True)
+        assert "enumerate:linear" not in capi.last_kernel()
+        assert np.array_equal(bl, bf), f"bits differ on [{lo}, {hi})"
+        assert np.array_equal(bl3, bf)
+        assert np.array_equal(tl, tf), f"tallies differ on [{lo}, {hi})"
+        assert np.array_equal(tl2, tf)
