@@ -764,11 +764,13 @@ static int enum_plan_linear(qec_enumerator *e) {
     flush();
   }
   const DevInfo &di = *c->info;
+  const int e32 = e->total < (1ll << 32) ? 1 : 0;
   const int w_env = env_int("QEC_B200_ENUM_WARPS", 0);
   int warps = 0;
   size_t smem = 0;
   for (int wz = (w_env > 0 ? w_env : 16); wz >= (w_env > 0 ? w_env : 4); --wz) {
-    const size_t need = qec_enum_lanes_smem_words(c->nc, wz, (uint32_t)F, (uint32_t)prog.size()) * 4 + 16;
+    const size_t need = qec_enum_lanes_smem_words(c->nc, wz, (uint32_t)F, (uint32_t)prog.size(), (uint32_t)e->L,
+                                                  e->order, e32) * 4 + 16;
     if (need > di.smem_optin) continue;
     warps = wz; smem = need;
     break;
@@ -785,6 +787,7 @@ static int enum_plan_linear(qec_enumerator *e) {
   ln.dev.sigrec = reinterpret_cast<const uint2 *>(ln.d_rec);
   ln.dev.n_faults = (uint32_t)F;
   ln.dev.batch_ctr = ln.d_ctr;
+  ln.dev.e32 = e32;
   ln.cfg.block = 32 * warps; ln.cfg.grid = di.sms; ln.cfg.smem = smem;
   ln.eligible = true;
   return 0;

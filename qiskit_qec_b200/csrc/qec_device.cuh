@@ -154,11 +154,14 @@ struct QecEnumLinDev {
   const uint2 *sigrec;      // [n_faults] 8-byte records: fault = poff[location] + digit
   uint32_t n_faults;
   uint32_t *batch_ctr;      // batches handed out so far in this launch (zeroed per launch)
+  int e32;                  // fewer than 2^32 paths: suffix-sum tables as 32-bit words in shared memory
 };
 static inline __host__ __device__ size_t qec_enum_lanes_smem_words(int nc, int warps, uint32_t n_faults,
-                                                                   uint32_t prog_words) {
+                                                                   uint32_t prog_words, uint32_t L, int order,
+                                                                   int e32) {
   const size_t ncp = ((size_t)nc + 3u) & ~(size_t)3u;
-  return (size_t)warps * (((size_t)nc + 2u) * 32u + ncp) + prog_words + 2u * (size_t)n_faults;
+  return (size_t)warps * (((size_t)nc + 2u) * 32u + ncp) + prog_words + L +
+         (e32 ? (size_t)order * ((size_t)L + 2u) : 0u) + 2u + 2u * (size_t)n_faults;
 }
 
 // shared-memory words of the lane-stream variant (1024-shot batches, `warps` warps per CTA)

@@ -759,6 +759,20 @@ k_sample_linw(const QecOutDev O, const QecLinDev S, const long long shot_lo, con
 #define QEC_LANES_LGB 10
 #define QEC_LANES_UNROLL 4  // read-out passes per trip (the host pads the schedule: qec_capi.cu)
 
+// record table -> shared memory, 128 bits per thread and trip (device allocations are 256-byte
+// aligned; the shared copy is 8-byte aligned: two 64-bit stores)
+__device__ __forceinline__ void lin_copy_records(uint32_t *dst, const uint2 *src_rec, uint32_t n_faults, int tid, int T) {
+  const uint4 *src = reinterpret_cast<const uint4 *>(src_rec);
+  const uint32_t n4 = n_faults >> 1;  // two records per 128-bit load
+  uint2 *d2 = reinterpret_cast<uint2 *>(dst);
+  for (uint32_t i = tid; i < n4; i += T) {
+    const uint4 v = __ldg(src + i);
+    d2[2 * i] = make_uint2(v.x, v.y);
+    d2[2 * i + 1] = make_uint2(v.z, v.w);
+  }
+  if ((n_faults & 1u) && tid == 0) d2[n_faults - 1] = src_rec[n_faults - 1];
+}
+
 // One candidate of a lane.  Absent record entries name the dummy row nc and a lane without a
 // fault XORs a zero mask (into whatever rows location 0's record names), so the seven load /
 // xor / store triples need no predicate.
@@ -803,7 +817,8 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
                                                   const uint32_t prog_s, const uint32_t n_steps,
                                                   const long long w0, const bool vec_ok, const int lane) {
   const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
-  const bool fastst = w0 >= 0 && w0 + 32 <= O.n_words && vec_ok;
+  const bool whole = w0 >= 0 && w0 + 32 <= O.n_words;  // the batch's 32 words all exist
+  const bool fastst = whole && vec_ok;
   uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
   for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
     // entry: row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a
@@ -830,7 +845,9 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
       if (BITS && rowok) {
         uint32_t *po = O.bits + ((long long)(e[u] & 0xFFu) * O.n_words + w0 + c4);
         if (fastst) *reinterpret_cast<uint4 *>(po) = v[u];
-        else {
+        else if (whole) {  // rows not 16-byte aligned (n_words not a multiple of 4)
+          po[0] = v[u].x; po[1] = v[u].y; po[2] = v[u].z; po[3] = v[u].w;
+        } else {
           const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -904,8 +921,7 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   {
     // one word per location: first fault | number of Paulis << 21
     for (uint32_t i = tid; i < (uint32_t)S.L; i += T) info2[i] = S.info2[i].x | (S.info2[i].y << 21);
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(S.sigrec);
-    for (uint32_t i = tid; i < 2u * S.n_faults; i += T) rec[i] = src[i];
+    lin_copy_records(rec, reinterpret_cast<const uint2 *>(S.sigrec), S.n_faults, tid, T);
     for (uint32_t i = tid; i < 4u * (uint32_t)S.n_steps; i += T) prog[i] = S.rowprog[i];
     for (uint32_t i = tid; i < (uint32_t)NW * wwords + 64u; i += T) qec_lin_smem[i] = 0u;
   }
@@ -1046,20 +1062,96 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
 // load / xor / store (bank = lane), exactly as the lane-stream sampler does; all lanes have the
 // same 32 paths of work, so there is no imbalance.  Read-out: lanes_readout.
 // Shared memory: [warp regions: acc (nc+2)*32 | tally ncp] then prog 4 * n_steps, rec 2F.
-template <int K, bool TALLY, bool BITS>
+// Path stepping of the linear enumerator with its tables in shared memory (the device-memory
+// versions in qec_device.cuh put three dependent global loads into every change of location):
+// linfo[l] = first fault of location l | number of Paulis << 21; Es = the suffix-sum tables
+// E[1..K][0..L+1] as 32-bit words when the enumeration has fewer than 2^32 paths (E32), else
+// the 64-bit tables stay in device memory.
+template <int K>
+struct LinEnumState {
+  uint32_t loc[K], dig[K], np[K], pb[K];
+};
+template <int K>
+__device__ __forceinline__ void lin_enum_load(const uint32_t linfo_s, LinEnumState<K> &s, int j) {
+  const uint32_t w = ld_s(linfo_s + (s.loc[j] << 2));
+  s.pb[j] = w & 0x1FFFFFu;
+  s.np[j] = w >> 21;
+}
+template <int K>
+__device__ __forceinline__ void lin_enum_next(const uint32_t linfo_s, const uint32_t L, LinEnumState<K> &s) {
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    if (++s.dig[j] < s.np[j]) return;
+    s.dig[j] = 0;
+  }
+  int i = K - 1;
+  while (i >= 0 && s.loc[i] >= L - K + i) --i;
+  if (i < 0) return;  // past the last path: the caller never uses the state again
+  const uint32_t base = s.loc[i] + 1;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    if (j >= i) {
+      s.loc[j] = base + (uint32_t)(j - i);
+      lin_enum_load<K>(linfo_s, s, j);
+    }
+  }
+}
+template <int K, bool E32>
+__device__ __forceinline__ void lin_enum_unrank(const QecEnumDev &E, const uint32_t es_s, const uint32_t linfo_s,
+                                                unsigned long long r, LinEnumState<K> &s) {
+  const uint32_t L2 = (uint32_t)E.L + 2u;
+  uint32_t mult = 1, start = 0;
+#pragma unroll
+  for (int j = 0; j < K; ++j) {
+    // level K - j of the tables; Es holds levels 1..K
+    const uint32_t lvl_s = es_s + (((uint32_t)(K - j - 1) * L2) << 2);
+    const unsigned long long *Em = E.E + (size_t)(K - j) * L2;
+    auto at = [&](uint32_t l) -> unsigned long long {
+      return E32 ? (unsigned long long)ld_s(lvl_s + (l << 2)) : Em[l];
+    };
+    const unsigned long long u = E32 ? (unsigned long long)((uint32_t)r / mult) : qec_div_u64_u32(r, mult);
+    const unsigned long long e0 = at(start);
+    const unsigned long long thr = e0 - u;  // >= 1
+    uint32_t lo = start, hi = (uint32_t)E.L;  // largest l in [start, L] with Em[l] >= thr
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (at(mid) >= thr) lo = mid; else hi = mid;
+    }
+    r -= (unsigned long long)mult * (e0 - at(lo));
+    s.loc[j] = lo;
+    lin_enum_load<K>(linfo_s, s, j);
+    mult *= s.np[j];
+    start = lo + 1;
+  }
+  uint32_t rr = (uint32_t)r;  // index inside the subset's product
+#pragma unroll
+  for (int j = K - 1; j >= 0; --j) {
+    const uint32_t q = rr / s.np[j];
+    s.dig[j] = rr - q * s.np[j];
+    rr = q;
+  }
+}
+
+template <int K, bool TALLY, bool BITS, bool E32>
 __global__ void __launch_bounds__(512, 1)
 k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, const long long lo, const long long hi) {
   extern __shared__ __align__(16) uint32_t qec_lin_smem[];
   const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
   const uint32_t nc = (uint32_t)EL.nc, ncp = (nc + 3u) & ~3u;
   const uint32_t wwords = (nc + 2u) * 32u + ncp;
+  const uint32_t L = (uint32_t)E.L, L2 = L + 2u;
   uint32_t *acc = qec_lin_smem + (size_t)warp * wwords;
   uint32_t *prog = qec_lin_smem + (size_t)NW * wwords;
-  uint32_t *rec = prog + 4u * (uint32_t)EL.n_steps;
+  uint32_t *linfo = prog + 4u * (uint32_t)EL.n_steps;
+  uint32_t *es = linfo + L;
+  uint32_t *rec = es + (E32 ? (uint32_t)K * L2 : 0u);
+  rec += (uint32_t)(rec - qec_lin_smem) & 1u;  // 8-byte aligned
   {
-    const uint32_t *src = reinterpret_cast<const uint32_t *>(EL.sigrec);
-    for (uint32_t i = tid; i < 2u * EL.n_faults; i += T) rec[i] = src[i];
+    lin_copy_records(rec, EL.sigrec, EL.n_faults, tid, T);
     for (uint32_t i = tid; i < 4u * (uint32_t)EL.n_steps; i += T) prog[i] = EL.rowprog[i];
+    for (uint32_t i = tid; i < L; i += T) linfo[i] = E.poff[i] | (E.npaul[i] << 21);
+    if (E32)
+      for (uint32_t i = tid; i < (uint32_t)K * L2; i += T) es[i] = (uint32_t)E.E[L2 + i];  // levels 1..K
     for (uint32_t i = tid; i < (uint32_t)NW * wwords; i += T) qec_lin_smem[i] = 0u;
   }
   __syncthreads();
@@ -1067,6 +1159,8 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
   const uint32_t lane_acc = acc_s + ((uint32_t)lane << 2);
   const uint32_t tal_s = acc_s + (((nc + 2u) * 32u) << 2);
   const uint32_t prog_s = (uint32_t)__cvta_generic_to_shared(prog);
+  const uint32_t linfo_s = (uint32_t)__cvta_generic_to_shared(linfo);
+  const uint32_t es_s = (uint32_t)__cvta_generic_to_shared(es);
   const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec);
   const bool vec_ok = (O.n_words & 3) == 0 && ((size_t)O.bits & 15) == 0;
   const long long n_paths = hi - lo;
@@ -1081,14 +1175,14 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
     const long long first = (b << 10) + ((long long)lane << 5);  // relative to lo
     const int nv = (int)max(0ll, min(32ll, n_paths - first));
     if (nv > 0) {
-      EnumState<K> st;
-      enum_unrank<K>(E, (unsigned long long)(lo + first), st);
+      LinEnumState<K> st;
+      lin_enum_unrank<K, E32>(E, es_s, linfo_s, (unsigned long long)(lo + first), st);
       for (int i = 0; i < nv; ++i) {
         const uint32_t msk = 1u << i;
         uint2 q[K];
 #pragma unroll
         for (int j = 0; j < K; ++j) q[j] = ld_s64(rec_s + ((st.pb[j] + st.dig[j]) << 3));
-        if (i + 1 < nv) enum_next<K>(E, st);
+        lin_enum_next<K>(linfo_s, L, st);
 #pragma unroll
         for (int j = 0; j < K; ++j) {
           // (two faults of a path may flip the same row: one record at a time, loads first)
@@ -1185,8 +1279,10 @@ int qec_enum_lanes_set_smem_attr(size_t smem) {
   cudaError_t e;
 #define QEC_SET(fn) e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, s); \
   if (e != cudaSuccess) return (int)e;
-#define QEC_SETK(K) QEC_SET((k_enum_lanes<K, true, true>)) QEC_SET((k_enum_lanes<K, true, false>)) \
-  QEC_SET((k_enum_lanes<K, false, true>)) QEC_SET((k_enum_lanes<K, false, false>))
+#define QEC_SETK(K) QEC_SET((k_enum_lanes<K, true, true, true>)) QEC_SET((k_enum_lanes<K, true, false, true>)) \
+  QEC_SET((k_enum_lanes<K, false, true, true>)) QEC_SET((k_enum_lanes<K, false, false, true>)) \
+  QEC_SET((k_enum_lanes<K, true, true, false>)) QEC_SET((k_enum_lanes<K, true, false, false>)) \
+  QEC_SET((k_enum_lanes<K, false, true, false>)) QEC_SET((k_enum_lanes<K, false, false, false>))
   QEC_SETK(1) QEC_SETK(2) QEC_SETK(3) QEC_SETK(4)
 #undef QEC_SETK
 #undef QEC_SET
@@ -1196,11 +1292,12 @@ int qec_enum_lanes_set_smem_attr(size_t smem) {
 void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
                            const QecEnumDev &E, const QecEnumLinDev &EL, long long lo, long long hi) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
-#define QEC_GO(K) \
-  if (t && b) k_enum_lanes<K, true, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
-  else if (t) k_enum_lanes<K, true, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
-  else if (b) k_enum_lanes<K, false, true><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
-  else k_enum_lanes<K, false, false><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi);
+#define QEC_GO2(K, E32) \
+  if (t && b) k_enum_lanes<K, true, true, E32><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else if (t) k_enum_lanes<K, true, false, E32><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else if (b) k_enum_lanes<K, false, true, E32><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi); \
+  else k_enum_lanes<K, false, false, E32><<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, E, EL, lo, hi);
+#define QEC_GO(K) if (EL.e32) { QEC_GO2(K, true) } else { QEC_GO2(K, false) }
   switch (E.order) {
     case 1: QEC_GO(1) break;
     case 2: QEC_GO(2) break;
@@ -1208,4 +1305,5 @@ void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
     default: QEC_GO(4) break;
   }
 #undef QEC_GO
+#undef QEC_GO2
 }
