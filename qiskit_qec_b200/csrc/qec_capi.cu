@@ -670,9 +670,8 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
 // Linear-response enumerator (k_enum_lanes): the signature of every single fault (one frame
 // propagation each, on the GPU, through qec_propagate_batch), as 8-byte records in the
 // time-difference basis when that shortens them, plus the read-out schedule -- the same tables
-// as the lane-stream sampler's.  Used when they fit (nc <= 254, at most 7 entries per fault, at
-// least 4 warps' accumulators) and the circuit is long enough for the gate stream to cost more
-// than the signatures (QEC_B200_ENUM=linear|frame forces the choice).
+// as the lane-stream sampler's.  Used whenever they fit (nc <= 254, at most 7 entries per fault,
+// at least 4 warps' accumulators); QEC_B200_ENUM=linear|frame forces the choice.
 static int enum_plan_linear(qec_enumerator *e) {
   qec_enumerator::Lin &ln = e->lin;
   qec_circuit *c = e->c;
@@ -682,8 +681,10 @@ static int enum_plan_linear(qec_enumerator *e) {
   if (mode && !forced) return fail(QEC_ERR_INVALID, "QEC_B200_ENUM must be linear or frame");
   if (e->order < 1 || e->order > QEC_KERNEL_MAX_ORDER) { ln.why = "order beyond the kernel's"; return 0; }
   if (c->nc > 254 || c->nc < 1) { ln.why = "more than 254 clbits"; return 0; }
-  if (!forced && c->packed.size() < (size_t)env_int("QEC_B200_ENUM_LINEAR_MIN_OPS", 400)) {
-    ln.why = "short circuit: frame propagation is cheaper";
+  // (measured faster than the frame kernels on every BASELINE enumeration, the 15-op repetition
+  // code included; the knob remains for experiments)
+  if (!forced && c->packed.size() < (size_t)env_int("QEC_B200_ENUM_LINEAR_MIN_OPS", 0)) {
+    ln.why = "short circuit: QEC_B200_ENUM_LINEAR_MIN_OPS";
     return 0;
   }
   const int64_t F = (int64_t)e->pcode.size();
