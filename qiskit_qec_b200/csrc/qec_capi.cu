@@ -729,7 +729,11 @@ static int enum_plan_linear(qec_enumerator *e) {
       tr_total += tr[f].size();
     }
   }
-  const bool use_diff = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
+  // (the read-out schedule walks the rows in clbit order: a previous row must have the smaller
+  // index, which holds whenever clbits are allocated in time order)
+  bool ordered = true;
+  for (int cb = 0; cb < c->nc; ++cb) ordered = ordered && pred[cb] < cb;
+  const bool use_diff = ordered && tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
   if (use_diff) lists.swap(tr);
   size_t maxlen = 0;
   for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
@@ -1038,6 +1042,8 @@ struct qec_sampler {
     std::vector<uint32_t> rowprog;
     uint32_t *d_rowprog = nullptr;
     uint32_t *d_batch_ctr = nullptr;  // lane-stream kernel: next batch of the launch (dynamic assignment)
+    std::vector<uint32_t> lvl_prog, lvl_off;  // CTA variant: undo of the time-difference basis
+    uint32_t *d_lvl_prog = nullptr, *d_lvl_off = nullptr;
     bool cls_uniform_all = true;
     std::vector<uint32_t> info2;
     uint32_t *d_info2 = nullptr;
@@ -1227,7 +1233,11 @@ static int sampler_plan_linear(qec_sampler *s) {
       raw_total += lists[f].size();
       tr_total += tr[f].size();
     }
-    use_diff = tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
+    // (the lane-stream and CTA read-outs walk the rows in clbit order: a previous row must have
+    // the smaller index, which holds whenever clbits are allocated in time order)
+    bool ordered = true;
+    for (int cb = 0; cb < c->nc; ++cb) ordered = ordered && pred[cb] < cb;
+    use_diff = ordered && tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
     const bool use = use_diff;
     for (int64_t f = 0; f < F; ++f) maxlen_w = std::max(maxlen_w, use ? tr[f].size() : lists[f].size());
     // chains -> 32 lanes, longest first onto the least loaded lane
@@ -1370,7 +1380,24 @@ static int sampler_plan_linear(qec_sampler *s) {
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
-  if ((warp_mode || lane_mode) && use_diff) lists.swap(tr);
+  // the CTA variant takes the shorter lists too (fewer shared-memory atomics per fault) and
+  // undoes the basis level by level before its read-out
+  const bool cta_diff = !warp_mode && !lane_mode && use_diff && env_int("QEC_B200_LIN_CTADIFF", 1) != 0;
+  if ((warp_mode || lane_mode || cta_diff) && use_diff) lists.swap(tr);
+  ln.lvl_prog.clear();
+  ln.lvl_off.assign(1, 0u);
+  if (cta_diff) {
+    std::vector<int> depth(c->nc, 0);
+    int maxd = 0;
+    for (int cb = 0; cb < c->nc; ++cb)  // (pred[cb] < cb: an earlier measurement)
+      if (pred[cb] >= 0) { depth[cb] = depth[pred[cb]] + 1; maxd = std::max(maxd, depth[cb]); }
+    for (int dlev = 1; dlev <= maxd; ++dlev) {
+      for (int cb = 0; cb < c->nc; ++cb)
+        if (depth[cb] == dlev) ln.lvl_prog.push_back((uint32_t)cb | ((uint32_t)pred[cb] << 16));
+      ln.lvl_off.push_back((uint32_t)ln.lvl_prog.size());
+    }
+  }
+  if (ln.lvl_prog.empty()) ln.lvl_prog.push_back(0u);
   // descriptor + list (CTA variant with tables in shared memory, overflow of long lists) and
   // fixed-size records: 16 bytes (length + 7 clbits) when no list is longer, else 32 (+15)
   ln.sigdesc.clear();
@@ -1408,7 +1435,8 @@ static int sampler_plan_linear(qec_sampler *s) {
   if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
       (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)) ||
-      (rc = upload(ln.info2, &ln.d_info2)))
+      (rc = upload(ln.info2, &ln.d_info2)) || (rc = upload(ln.lvl_prog, &ln.d_lvl_prog)) ||
+      (rc = upload(ln.lvl_off, &ln.d_lvl_off)))
     return rc;
   {
     const int e = qec_lin_set_smem_attr(smem);
@@ -1429,6 +1457,8 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.info2 = reinterpret_cast<const uint2 *>(ln.d_info2);
   d.fast = fast;
   d.lane_mode = lane_mode;
+  d.lvl_prog = ln.d_lvl_prog; d.lvl_off = ln.d_lvl_off;
+  d.n_lvl = (int)ln.lvl_off.size() - 1;
   d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
   d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
   d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;
@@ -1617,7 +1647,8 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
-                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr};
+                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr,
+                  s->lin.d_lvl_prog, s->lin.d_lvl_off};
   for (void *p : ptrs) if (p) cudaFree(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1689,7 +1720,8 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
                     (d.sig_in_smem ? " sig=smem" : " sig=global") + " draw=" + std::to_string(d.draw) +
                     (d.fast ? " lean" : "") +
-                    (d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B"));
+                    (d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B")) +
+                    (d.n_lvl > 0 ? " diff-basis" : "");
     return 0;
   }
   if (s->jit.eligible && !X.cnt) {

@@ -142,6 +142,11 @@ struct QecLinDev {
   // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
   int lane_mode;
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
+  // CTA variant with signatures in the time-difference basis: rows with a previous row, grouped by
+  // their depth in the chain (lvl_off[n_lvl + 1] into lvl_prog; entry = row | previous row << 16);
+  // the CTA undoes the basis level by level before the read-out.  n_lvl = 0: raw signatures.
+  const uint32_t *lvl_prog, *lvl_off;
+  int n_lvl;
 };
 
 // Linear-response enumerator (k_enum_lanes in qec_linear.cu): outcome(path) = XOR of the

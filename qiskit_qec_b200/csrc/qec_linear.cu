@@ -9,12 +9,19 @@
 // p = 1e-3 carries ~0.8 faults, each flipping a handful of clbits, against ~760 gates per shot
 // for explicit propagation: this kernel never touches the gate list.
 //
-// One CTA owns a batch of 2^lgb shots: a bit-sliced accumulator acc[nc][batch / 32] in shared
-// memory (the layout of the packed output).  Warps walk the batch's fault streams -- 32
-// geometric gaps per step, one warp prefix sum, every lane ends up with one fault -- and XOR
-// the fault's clbit list into the accumulator with shared-memory atomics.  After a CTA barrier
-// all threads stream the accumulator out (coalesced 128-byte rows), count ones per clbit, and
-// clear it for the next batch.
+// Kernels in this file (all share the signature tables built by qec_capi.cu):
+//   k_sample_lanes  lane-stream sampler (default where it fits): a warp owns 1024 shots, lane l
+//                   owns word column l and walks its own fault stream; plain load/xor/store on
+//                   acc[row][l], no shared-memory atomics (the atomic unit bounded the two
+//                   variants below at ~2 cycles per lane)
+//   k_sample_linw   warp variant: one warp per 256-shot batch, one stream, warp prefix sum of
+//                   the gaps, red.shared.xor into the warp's accumulator
+//   k_sample_lin    CTA variant for circuits with many clbits (d=11): one CTA per batch of 2^lgb
+//                   shots, streams dealt to its warps, CTA barrier, column-wise read-out
+//   k_enum_lanes    the same idea for FaultEnumerator: outcome(path) = XOR of the signatures of
+//                   its faults; lane l owns the 32 paths of output word l
+// Draw schemes (QecLinDev::draw): computed 32-bit geometric gaps (qec_gap_len), two candidates
+// per Philox call when no class needs thinning; two-level gap tables for very small p.
 #include <cuda_runtime.h>
 #include "qec_kernels.cuh"
 
@@ -349,6 +356,17 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     for (int s = warp; s < S.n_streams; s += NW)
       lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
     __syncthreads();
+
+    // ---- signatures in the time-difference basis: row ^= previous row of its chain, one chain
+    // depth at a time (the previous row is final when its own depth is done)
+    for (int lv = 0; lv < S.n_lvl; ++lv) {
+      const uint32_t o0 = __ldg(S.lvl_off + lv) << lgw, o1 = __ldg(S.lvl_off + lv + 1) << lgw;
+      for (uint32_t i = o0 + (uint32_t)tid; i < o1; i += (uint32_t)T) {
+        const uint32_t e = __ldg(S.lvl_prog + (i >> lgw)), wcol = i & (BW - 1u);
+        m.acc[((e & 0xFFFFu) << lgw) + wcol] ^= m.acc[((e >> 16) << lgw) + wcol];
+      }
+      __syncthreads();
+    }
 
     // ---- stream the accumulator out: thread -> fixed word column wb, clbits c0, c0 + T/BW, ...
     {
