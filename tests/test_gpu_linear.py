@@ -258,3 +258,52 @@ def test_linear_enumerator_equals_frame_enumerator(capi, monkeypatch, name, orde
         assert np.array_equal(bl3, bf)
         assert np.array_equal(tl, tf), f"tallies differ on [{lo}, {hi})"
         assert np.array_equal(tl2, tf)
+
+
+def test_linear_kernels_on_random_circuits_with_clbits_out_of_time_order(capi, port, monkeypatch):
+    """Random gate streams measure qubits repeatedly into arbitrary clbits (overwrites, clbits not
+    in time order, never-measured clbits): the linear kernels must fall back to raw signatures
+    where their read-out schedules need ordered chains, and still agree with explicit propagation
+    (enumerator: frame kernels; sampler: port + oracle replay inside the kernels' own checks)."""
+    from helpers import random_circuit
+    rng = np.random.default_rng(11)
+    model = standard_depolarizing_model(0.02)
+    for trial in range(4):
+        circ = random_circuit(rng, nq=6, nc=9, n_ops=70)
+        idx, labels, paulis = noise_inputs(circ, model)
+        if len(idx) < 3:
+            continue
+        for order in (1, 2):
+            monkeypatch.setenv("QEC_B200_ENUM", "linear")
+            gl = capi.Circuit(circ.nq, circ.nc, circ.ops)
+            el = make_enumerator(capi, gl, order, idx, paulis)
+            monkeypatch.setenv("QEC_B200_ENUM", "frame")
+            gf = capi.Circuit(circ.nq, circ.nc, circ.ops)
+            ef = make_enumerator(capi, gf, order, idx, paulis)
+            n = min(el.num_paths(), 50_000)
+            bl, tl = el.range(0, n, want_tally=True)
+            assert "enumerate:linear" in capi.last_kernel()
+            bf, tf = ef.range(0, n, want_tally=True)
+            assert np.array_equal(bl, bf) and np.array_equal(tl, tf), f"trial {trial} order {order}"
+        monkeypatch.delenv("QEC_B200_ENUM")
+        _, _, lw, lp = sampler_inputs(circ, model)
+        for mode in ("lanes", "warp", "cta"):
+            monkeypatch.setenv("QEC_B200_LIN_MODE", mode)
+            g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+            sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=trial)
+            n_shots = 6_000
+            bits, tally, cnt, ev = sm.sample(0, n_shots, want_tally=True, fault_cap=96)
+            assert "sample:linear" in capi.last_kernel()
+            tab = sm.tables()
+            paths = [([], []) for _ in range(n_shots)]
+            for w in range((n_shots + 31) // 32):
+                want_ev = port.sample_word(tab, w, min(32, n_shots - 32 * w))
+                assert np.array_equal(ev[w, :cnt[w]], want_ev)
+                for e in want_ev:
+                    loc, bit, dig = int(e) >> 14, (int(e) >> 9) & 31, int(e) & 511
+                    paths[32 * w + bit][0].append(idx[loc])
+                    paths[32 * w + bit][1].append(paulis[loc][dig])
+            want = port.propagate_batch(circ.nq, circ.nc, circ.ops, paths)
+            assert np.array_equal(capi.unpack_bits(bits, n_shots), want), f"trial {trial} mode {mode}"
+            assert np.array_equal(tally[:circ.nc], want.sum(axis=0).astype(np.uint64))
+        monkeypatch.delenv("QEC_B200_LIN_MODE")
