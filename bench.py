@@ -263,13 +263,25 @@ def run_ours(args):
         g2.close()
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_step(0)  # two untimed steps: the first touches (pins) every page of the host buffers
-    e2e_step(0)
+    # untimed steps until the step time settles (at most 10): on a fresh box the first passes over
+    # the 1.8 GB pinned host buffer run 3-6x slower (the VM's memory is backed lazily), and which
+    # pass is the last slow one varies from run to run
+    prev, e2e_warm = None, []
+    for _ in range(10):
+        ts = time.perf_counter()
+        e2e_step(0)
+        e2e_warm.append(time.perf_counter() - ts)
+        if prev is not None and len(e2e_warm) >= 3 and abs(e2e_warm[-1] - prev) <= 0.1 * prev:
+            break
+        prev = e2e_warm[-1]
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
+    e2e_times = []
     for i in range(e2e_steps):
+        ts = time.perf_counter()
         e2e_step(1 + i)
+        e2e_times.append(time.perf_counter() - ts)
     t1 = time.perf_counter()
     t = torch.tensor([t1 - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -372,7 +384,8 @@ def run_ours(args):
                                      "kernel obtains the same outcomes without executing them"},
             "e2e": {"value": e2e_value, "unit": "shots/s", "h2d_bytes_per_step": tab_bytes,
                     "d2h_bytes_per_step": int(host_bits.numel() * 4 + host_tally.numel() * 8),
-                    "steps": e2e_steps,
+                    "steps": e2e_steps, "ms_per_step": [round(x * 1e3, 2) for x in e2e_times],
+                    "warmup_ms": [round(x * 1e3, 1) for x in e2e_warm],
                     "call": "qec_circuit_create + qec_sampler_create + qec_sampler_sample (host "
                             "pointers, pinned) + destroy"},
             "gpu_launches": args.steps, "clocks": clk, "cpu_baseline": cpu_baseline,
