@@ -88,20 +88,44 @@ static int dev_info(int device, DevInfo **out) {
   return 0;
 }
 
+// Device allocations come from the device's stream-ordered pool (cudaMallocAsync on the legacy
+// default stream, pool never trimmed): creating and destroying a sampler per call -- the
+// end-to-end pattern of bench.py and of the reference's drivers -- then costs no cudaMalloc /
+// cudaFree round trips (each cudaFree is a device-wide synchronisation).  Every destroy entry
+// point synchronises the device once before it frees, so that work on non-blocking streams cannot
+// outlive its tables.
+static cudaError_t qec_dev_alloc(void **p, size_t bytes) {
+  static thread_local int pool_ready_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (pool_ready_dev != dev) {
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+    pool_ready_dev = dev;
+  }
+  return cudaMallocAsync(p, bytes ? bytes : 1, (cudaStream_t)0);
+}
+template <class T>
+static cudaError_t qec_dev_alloc(T **p, size_t bytes) { return qec_dev_alloc((void **)p, bytes); }
+static cudaError_t qec_dev_free(void *p) { return p ? cudaFreeAsync(p, (cudaStream_t)0) : cudaSuccess; }
+
 struct DevBuf {  // growable device buffer
   void *p = nullptr;
   size_t cap = 0;
   int ensure(size_t bytes) {
     if (bytes <= cap) return 0;
-    if (p) cudaFree(p);
+    if (p) { cudaDeviceSynchronize(); qec_dev_free(p); }
     p = nullptr;
     cap = 0;
-    CU(cudaMalloc(&p, bytes));
+    CU(qec_dev_alloc(&p, bytes));
     cap = bytes;
     return 0;
   }
   void release() {
-    if (p) cudaFree(p);
+    if (p) qec_dev_free(p);
     p = nullptr;
     cap = 0;
   }
@@ -111,7 +135,7 @@ template <class T>
 static int upload(const std::vector<T> &v, T **out) {
   *out = nullptr;
   const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
-  CU(cudaMalloc((void **)out, bytes));
+  CU(qec_dev_alloc((void **)out, bytes));
   if (!v.empty()) CU(cudaMemcpy(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
   return 0;
 }
@@ -280,7 +304,8 @@ extern "C" int qec_circuit_create(int device, int nq, int nc, int n_ops, const i
 extern "C" void qec_circuit_destroy(qec_circuit *c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  if (c->d_ops) cudaFree(c->d_ops);
+  cudaDeviceSynchronize();  // (see qec_dev_alloc: frees are stream-ordered)
+  if (c->d_ops) qec_dev_free(c->d_ops);
   c->out_bits.release(); c->out_frame.release(); c->tally.release();
   c->ev_off.release(); c->ev.release();
   for (int i = 0; i < 2; ++i) {
@@ -782,7 +807,7 @@ static int enum_plan_linear(qec_enumerator *e) {
   }
   if (!warps) { ln.why = "accumulators and records do not fit in shared memory"; return 0; }
   if ((rc = upload(prog, &ln.d_rowprog)) || (rc = upload(rec, &ln.d_rec))) return rc;
-  CU(cudaMalloc((void **)&ln.d_ctr, 4));
+  CU(qec_dev_alloc((void **)&ln.d_ctr, 4));
   {
     const int er = qec_enum_lanes_set_smem_attr(smem);
     if (er) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)er));
@@ -801,19 +826,20 @@ static int enum_plan_linear(qec_enumerator *e) {
 extern "C" void qec_enumerator_destroy(qec_enumerator *e) {
   if (!e) return;
   cudaSetDevice(e->c->device);
-  if (e->d_E) cudaFree(e->d_E);
-  if (e->d_npaul) cudaFree(e->d_npaul);
-  if (e->d_poff) cudaFree(e->d_poff);
-  if (e->d_lop) cudaFree(e->d_lop);
-  if (e->d_pcode) cudaFree(e->d_pcode);
-  if (e->d_tile) cudaFree(e->d_tile);
+  cudaDeviceSynchronize();  // (see qec_dev_alloc: frees are stream-ordered)
+  if (e->d_E) qec_dev_free(e->d_E);
+  if (e->d_npaul) qec_dev_free(e->d_npaul);
+  if (e->d_poff) qec_dev_free(e->d_poff);
+  if (e->d_lop) qec_dev_free(e->d_lop);
+  if (e->d_pcode) qec_dev_free(e->d_pcode);
+  if (e->d_tile) qec_dev_free(e->d_tile);
   e->scratch.release();
   e->jit_scratch.release();
   e->redo_list.release();
-  if (e->d_redo_count) cudaFree(e->d_redo_count);
-  if (e->lin.d_rowprog) cudaFree(e->lin.d_rowprog);
-  if (e->lin.d_rec) cudaFree(e->lin.d_rec);
-  if (e->lin.d_ctr) cudaFree(e->lin.d_ctr);
+  if (e->d_redo_count) qec_dev_free(e->d_redo_count);
+  if (e->lin.d_rowprog) qec_dev_free(e->lin.d_rowprog);
+  if (e->lin.d_rec) qec_dev_free(e->lin.d_rec);
+  if (e->lin.d_ctr) qec_dev_free(e->lin.d_ctr);
   e->jit.release();
   delete e;
 }
@@ -910,7 +936,7 @@ static int enum_launch(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *d_bi
       int max_seg = max_seg_env > 0 ? max_seg_env : (1 << 30);
       int rc2 = e->redo_list.ensure((size_t)std::max<int64_t>(O.n_words, 1) * 8);
       if (rc2) return rc2;
-      if (!e->d_redo_count) CU(cudaMalloc((void **)&e->d_redo_count, 4));
+      if (!e->d_redo_count) CU(qec_dev_alloc((void **)&e->d_redo_count, 4));
       CU(cudaMemsetAsync(e->d_redo_count, 0, 4, stream));
       long long *redo = (long long *)e->redo_list.p;
       void *args[] = {&O, &e->dev, &lo_, &hi_, &scr, &e->jit_tab_in_smem, &max_seg, &redo,
@@ -1124,7 +1150,7 @@ static int sampler_plan_jit(qec_sampler *s) {
   pl.grid = c->info->sms * pl.min_blocks;
   s->jit_capw = capw;
   s->jit_cap = capw / 2;
-  if (s->d_seg_end) { cudaFree(s->d_seg_end); s->d_seg_end = nullptr; }
+  if (s->d_seg_end) { qec_dev_free(s->d_seg_end); s->d_seg_end = nullptr; }
   int rc = upload(s->seg_end, &s->d_seg_end);
   if (rc) return rc;
   s->dev.n_seg = pl.segments;
@@ -1468,7 +1494,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.info_in_smem = info_s; d.sig_in_smem = sig_s; d.warp_mode = warp_mode;
   d.rec2 = rec2; d.rowprog = ln.d_rowprog; d.n_steps = n_steps;
   if (lane_mode) {
-    if (cudaMalloc(&ln.d_batch_ctr, 4) != cudaSuccess) return fail(QEC_ERR_CUDA, "cudaMalloc failed");
+    if (qec_dev_alloc(&ln.d_batch_ctr, 4) != cudaSuccess) return fail(QEC_ERR_CUDA, "cudaMalloc failed");
     d.batch_ctr = ln.d_batch_ctr;
   }
   d.rec8 = rec8; d.rec_in_smem = rec_s;
@@ -1617,7 +1643,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
     qec_sampler_destroy(s);
     return rc;
   }
-  if (cudaMalloc((void **)&s->d_flag, 4) != cudaSuccess || cudaMemset(s->d_flag, 0, 4) != cudaSuccess) {
+  if (qec_dev_alloc((void **)&s->d_flag, 4) != cudaSuccess || cudaMemset(s->d_flag, 0, 4) != cudaSuccess) {
     qec_sampler_destroy(s);
     return fail(QEC_ERR_CUDA, "cudaMalloc failed");
   }
@@ -1644,12 +1670,13 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
 extern "C" void qec_sampler_destroy(qec_sampler *s) {
   if (!s) return;
   cudaSetDevice(s->c->device);
+  cudaDeviceSynchronize();  // (see qec_dev_alloc: frees are stream-ordered)
   void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
                   s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr,
                   s->lin.d_lvl_prog, s->lin.d_lvl_off};
-  for (void *p : ptrs) if (p) cudaFree(p);
+  for (void *p : ptrs) if (p) qec_dev_free(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
   delete s;
@@ -1897,7 +1924,7 @@ extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_
   if (rc) return rc;
   CU(cudaSetDevice(device));
   uint32_t *sink = nullptr;
-  CU(cudaMalloc((void **)&sink, 4));
+  CU(qec_dev_alloc((void **)&sink, 4));
   const int grid = d->sms * 8, block = 256;
   int iters = 2000;
   double best = 0;
@@ -1912,7 +1939,7 @@ extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_
     if (t > 0) best = std::max(best, ops / (t * 1e-3));
     if (pass == 0 && t > 0) iters = (int)std::max(2000.0, std::min(4e6, iters * (ms / t)));
   }
-  cudaFree(sink);
+  qec_dev_free(sink);
   int khz = 0;
   cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device);
   if (lane_ops_per_s) *lane_ops_per_s = best;
@@ -1923,10 +1950,10 @@ extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_
 #define DEV_ENTER(device) { DevInfo *d__; int rc__ = dev_info(device, &d__); if (rc__) return rc__; CU(cudaSetDevice(device)); }
 extern "C" int qec_dev_alloc(int device, size_t bytes, void **out) {
   DEV_ENTER(device);
-  CU(cudaMalloc(out, bytes ? bytes : 1));
+  CU(qec_dev_alloc(out, bytes ? bytes : 1));
   return 0;
 }
-extern "C" int qec_dev_free(int device, void *p) { DEV_ENTER(device); CU(cudaFree(p)); return 0; }
+extern "C" int qec_dev_free(int device, void *p) { DEV_ENTER(device); CU(qec_dev_free(p)); return 0; }
 extern "C" int qec_dev_memset(int device, void *p, int value, size_t bytes, void *stream) {
   DEV_ENTER(device);
   CU(cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
