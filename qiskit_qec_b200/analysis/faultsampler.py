@@ -7,6 +7,8 @@ from the reference's mt19937 stream; the distribution does not (tests hold it to
 
 from __future__ import annotations
 
+import numpy as np
+
 from qiskit_qec_b200.analysis.errorpropagator import ErrorPropagator
 from qiskit_qec_b200.analysis.extensions import C_FAULT_SAMPLER
 from qiskit_qec_b200.analysis.faultenumerator import _with_separators
@@ -71,3 +73,38 @@ class FaultSampler:
     def sample_packed(self, n: int, want_bits: bool = True, want_tally: bool = False):
         """Packed outcomes uint32[nc][ceil(n/32)] and/or tallies of ``n`` fresh shots."""
         return self.faultsamp.sample_packed(n, want_bits, want_tally)
+
+    def sample_counts(self, shots: int = 4000):
+        """Counts dictionary in standard Qiskit form for ``shots`` fresh shots: keys are the
+        outcome bitstrings with the LAST clbit first and a space between classical registers,
+        values their multiplicities -- the format of the reference's
+        ``get_counts_via_stim`` (``utils/stim_tools.py:234-283``) and what every decoder of the
+        reference consumes (``decoders/decoding_graph.py:165-209``).  Outcomes are FLIPS
+        relative to the noiseless run (the propagator's semantics): they equal the stim /
+        Aer absolute outcomes when the noiseless outcome is all zero (base circuit "0").
+        The shots are sampled and packed on the GPU; distinct outcomes are counted on the host
+        from the packed bits."""
+        if shots <= 0:
+            return {}
+        packed, _ = self.faultsamp.sample_packed(int(shots), True, False)
+        return counts_from_packed(np.asarray(packed), int(shots), self.reg_sizes)
+
+
+def counts_from_packed(packed: np.ndarray, n: int, reg_sizes) -> dict:
+    """{bitstring: count} from packed outcomes uint32[nc][ceil(n/32)] (bit b of word w of row c
+    = clbit c of shot 32 w + b).  Strings list clbit nc-1 first, registers (declaration order
+    ``reg_sizes``) separated by a space."""
+    nc = packed.shape[0]
+    if sum(reg_sizes) != nc:
+        raise ValueError("register sizes do not add up to the number of clbits")
+    bits = np.unpackbits(np.ascontiguousarray(packed).view(np.uint8).reshape(nc, -1), axis=1,
+                         bitorder="little")[:, :n]            # [clbit][shot]
+    rows = np.packbits(bits[::-1].T, axis=1)                   # per shot, clbit nc-1 first
+    uniq, cnt = np.unique(rows, axis=0, return_counts=True)
+    cuts = set(np.cumsum(list(reg_sizes)[::-1])[:-1].tolist())  # after these many chars: a space
+    out = {}
+    for u, k in zip(uniq, cnt):
+        chars = np.unpackbits(u)[:nc]
+        s = "".join((" " if i in cuts else "") + ("1" if b else "0") for i, b in enumerate(chars))
+        out[s] = int(k)
+    return out

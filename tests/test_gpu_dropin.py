@@ -241,3 +241,26 @@ def test_driver_classes(ext):
     for k, pk in enumerate([0.64, 0.32, 0.04]):
         assert abs(counts[k] - pk) < 5 * np.sqrt(pk * (1 - pk) / n)
     assert fs.sample_one()[0] == -1
+
+
+def test_sample_counts_qiskit_format(ext):
+    """FaultSampler.sample_counts: the counts dictionary of the reference's
+    get_counts_via_stim (utils/stim_tools.py:234-283) -- last clbit first, registers separated --
+    with frequencies that match the closed form on a circuit small enough to write it down."""
+    from qiskit_qec_b200.analysis import FaultSampler
+    from qiskit_qec_b200.circuits import EncodedCircuit
+    from qiskit_qec_b200.noise import PauliNoiseModel
+    qc = EncodedCircuit(2, 3, creg_sizes=[1, 2])
+    qc.h(0); qc.cx(0, 1); qc.measure(0, 0); qc.measure(1, 1); qc.measure(1, 2)
+    model = PauliNoiseModel()
+    model.add_operation("cx", {"ix": 1, "xi": 1, "xx": 1})
+    model.set_error_probability("cx", 0.3)
+    fs = FaultSampler(qc, model, sim_seed=11)
+    n = 200_000
+    counts = fs.sample_counts(n)
+    assert sum(counts.values()) == n
+    # flips: ix -> clbits 1, 2; xi -> clbit 0; xx -> all; key = "c2c1 c0"
+    assert set(counts) == {"00 0", "11 0", "00 1", "11 1"}
+    for key, p in (("00 0", 0.7), ("11 0", 0.1), ("00 1", 0.1), ("11 1", 0.1)):
+        assert abs(counts[key] / n - p) < 5 * np.sqrt(p * (1 - p) / n), key
+    assert fs.sample_counts(0) == {}

@@ -1,5 +1,6 @@
 """CPU checks of the host-side mirror: circuit emitters, noise model, location tagging."""
 
+import numpy as np
 import pytest
 
 from qiskit_qec_b200.circuits import (arc_circuit, heavy_hex_27_arc_layout,
@@ -74,3 +75,32 @@ def test_location_tagging():
     m.add_operation("measure", {"x": 1})
     idx, labels = tag_fault_locations(c.labels, m)
     assert len(idx) == 145 and set(labels) == {"measure"}
+
+
+def test_counts_from_packed_matches_qiskit_format():
+    """Counts adaptor (reference utils/stim_tools.py:266-277 format): last clbit first, a space
+    where the register changes, multiplicities of identical outcomes."""
+    from qiskit_qec_b200.analysis.faultsampler import counts_from_packed
+    rng = np.random.default_rng(5)
+    nc, n, regs = 7, 75, [2, 2, 3]
+    outcomes = (rng.random((n, nc)) < 0.3).astype(np.uint8)
+    outcomes[10] = outcomes[3]
+    packed = np.zeros((nc, (n + 31) // 32), dtype=np.uint32)
+    for s in range(n):
+        for c in range(nc):
+            if outcomes[s, c]:
+                packed[c, s // 32] |= np.uint32(1 << (s % 32))
+    want = {}
+    for s in range(n):
+        key, prev = "", None
+        reg_of = [r for r, size in enumerate(regs) for _ in range(size)]
+        for c in range(nc - 1, -1, -1):
+            if prev is not None and reg_of[c] != prev:
+                key += " "
+            key += str(int(outcomes[s, c]))
+            prev = reg_of[c]
+        want[key] = want.get(key, 0) + 1
+    assert counts_from_packed(packed, n, regs) == want
+    assert sum(counts_from_packed(packed, n, [nc]).values()) == n
+    with pytest.raises(ValueError):
+        counts_from_packed(packed, n, [3, 3])
