@@ -390,6 +390,7 @@ def run_ours(args):
                             "pointers, pinned) + destroy"},
             "gpu_launches": args.steps, "clocks": clk, "cpu_baseline": cpu_baseline,
             "enumerator": enum, "kernel_ms_per_launch": kern_ms,
+            "step_ms": [round(x, 4) for x in step_ms],
         }
         print(json.dumps(line))
     if world > 1:
