@@ -127,14 +127,24 @@ int qec_enumerator_range_dev(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t
  * Location l belongs to class (label) loc_class[l] in [0, n_classes); class k fails with
  * probability class_p[k] per shot and then draws digit d with probability proportional to
  * class_weight[class_off[k] + d]; digit d injects class_codes[class_off[k] + d].
- * RNG: Philox4x32-10 keyed by `seed`, counter = (global 32-shot word index, draw index);
- * results depend only on (seed, global shot id), never on grid shape or GPU count.
+ * RNG: Philox4x32-10 keyed by `seed`; the counter is built from the global shot position (a
+ * 32-shot word or a batch of shots) and a draw index, so that results never depend on the grid
+ * shape, on how a shot range is cut into calls or on the GPU count: 1 GPU == N GPUs bit for bit.
+ * They DO depend on the sampler's kernel variant and draw scheme (frame / linear lane-streams /
+ * warp / cta; gap tables or computed gaps), which the library picks from the circuit and the
+ * noise model (clbit count, equal Pauli weights, pmax) and which the QEC_B200_SAMPLER /
+ * QEC_B200_LIN_* environment variables can force: the same (seed, shot id) gives different --
+ * equally distributed -- faults under a different variant.  qec_sampler_variant() names the
+ * variant in use so that a caller can record or pin it.
  * Every probability is realised to within 2^-31 absolute (32-bit fixed point tables). */
 int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op, const int32_t *loc_class,
                        int n_classes, const double *class_p, const int32_t *class_off,
                        const uint8_t *class_codes, const double *class_weight, uint64_t seed,
                        qec_sampler **out);
 void qec_sampler_destroy(qec_sampler *s);
+/* kernel variant and draw scheme this sampler uses (see above), e.g.
+ * "linear lane-streams draw=2"; the string lives as long as the sampler */
+const char *qec_sampler_variant(const qec_sampler *s);
 /* shots [shot_lo, shot_lo + n_shots); shot_lo must be a multiple of 32.
  * out_bits host uint32[nc][ceil(n/32)] (may be NULL); tally host (may be NULL; overwritten);
  * fault export (all three NULL or all non-NULL): fault_cnt host uint32[ceil(n/32)] = events
@@ -156,11 +166,38 @@ int qec_sampler_check(qec_sampler *s);
 int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, int *n);
 
 /* ---- K4: full-outcome histogram over a packed outcome buffer --------------------------
- * Counts distinct outcomes of n paths held bit-sliced on the device of `c`.
- * Open-addressed table of `table_cap` (power of two) 64-bit outcome hashes + counts. */
+ * (new: the reference returns per-shot tuples only; this is the device-side form of the counts
+ * dictionary its consumers build, reference utils/stim_tools.py:234-283,
+ * decoders/decoding_graph.py:165-209.)
+ * Counts distinct outcomes of n_paths paths held bit-sliced on the device of `c` (row stride
+ * n_words >= ceil(n_paths/32)).  Open-addressed table of `table_cap` (power of two) slots:
+ *   d_keys   uint64[table_cap]  64-bit hash of the outcome (0 = empty slot; zero the table first)
+ *   d_counts uint64[table_cap]  multiplicity (accumulated: several calls may share one table)
+ *   d_rows   uint32[table_cap][ceil(nc/32)] (may be NULL) the outcome itself, bit c%32 of word
+ *            c/32 = clbit c, written by the thread that claims the slot
+ *   d_status uint64[3] (may be NULL, accumulated): slots claimed, paths dropped because the
+ *            table was full, paths with the all-zero outcome (counted here, NOT in the table)
+ * Two distinct outcomes with equal 64-bit hashes would share a slot (probability about
+ * n_distinct^2 / 2^65; 3e-6 for 1e7 distinct outcomes). */
+int qec_outcome_histogram_rows_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                   int64_t n_words, uint64_t *d_keys, uint64_t *d_counts,
+                                   uint32_t *d_rows, int64_t table_cap, uint64_t *d_status,
+                                   void *stream);
+/* the same without rows / status, row stride ceil(n_paths/32); the all-zero outcome is then
+ * not reported anywhere */
 int qec_outcome_histogram_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
                               uint64_t *d_keys, uint64_t *d_counts, int64_t table_cap,
                               void *stream);
+/* FaultSampler -> {outcome: multiplicity} with host buffers: shots [shot_lo, shot_lo + n_shots)
+ * are drawn and histogrammed on the device chunk by chunk; only the distinct outcomes cross
+ * PCIe.  out_counts uint64[max_out], out_rows uint32[max_out][ceil(nc/32)] (order arbitrary);
+ * *n_out = distinct non-zero outcomes, *n_zero = shots with the all-zero outcome; tally as in
+ * qec_sampler_sample (may be NULL).  QEC_ERR_LIMIT if the table (table_cap slots, power of two)
+ * or the output arrays are too small: *n_out then holds the number found so far / needed.
+ * max_out = 0 only counts (n_out, n_zero). */
+int qec_sampler_counts(qec_sampler *s, int64_t shot_lo, int64_t n_shots, int64_t table_cap,
+                       int64_t max_out, uint64_t *out_counts, uint32_t *out_rows, int64_t *n_out,
+                       uint64_t *n_zero, uint64_t *tally);
 
 /* ---- device memory helpers (so a ctypes/cgo caller needs no CUDA binding) ------------- */
 int qec_dev_alloc(int device, size_t bytes, void **out);

@@ -30,8 +30,8 @@ SYMBOLS = [
     "qec_enumerator_unrank", "qec_enumerator_subset_rank", "qec_enumerator_range",
     "qec_enumerator_range_dev",
     "qec_sampler_create", "qec_sampler_destroy", "qec_sampler_sample", "qec_sampler_sample_dev",
-    "qec_sampler_check", "qec_sampler_tables",
-    "qec_outcome_histogram_dev",
+    "qec_sampler_check", "qec_sampler_tables", "qec_sampler_variant", "qec_sampler_counts",
+    "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
     "qec_last_kernel", "qec_jit_compile_to_file",
@@ -302,12 +302,73 @@ class Sampler:
     def check(self):
         _check(lib().qec_sampler_check(self._h))
 
+    def variant(self) -> str:
+        """kernel variant and draw scheme (results are reproducible per variant)"""
+        lib().qec_sampler_variant.restype = C.c_char_p
+        return lib().qec_sampler_variant(self._h).decode()
+
+    def counts(self, shot_lo: int, n_shots: int, table_cap: int = 0, want_tally: bool = False):
+        """K4 on the hot path: (rows uint32[n][ceil(nc/32)], counts uint64[n], n_zero, tally) of
+        the distinct NON-ZERO outcomes of the shots, histogrammed on the device; ``n_zero`` is
+        the multiplicity of the all-zero outcome."""
+        nc = self.circuit.nc
+        rw = (nc + 31) // 32
+        if table_cap <= 0:
+            table_cap = 1 << 16
+            while table_cap < 2 * min(n_shots, 1 << 26):
+                table_cap <<= 1
+        tally = np.zeros(tally_len(nc), dtype=np.uint64) if want_tally else None
+        max_out = min(n_shots, table_cap)
+        n_out, n_zero = C.c_int64(), C.c_uint64()
+        # first pass sizes the output (distinct outcomes are usually far fewer than shots)
+        probe = min(max_out, 1 << 16)
+        while True:
+            cnt = np.zeros(max(probe, 1), dtype=np.uint64)
+            rows = np.zeros((max(probe, 1), rw), dtype=np.uint32)
+            rc = lib().qec_sampler_counts(self._h, C.c_int64(shot_lo), C.c_int64(n_shots),
+                                          C.c_int64(table_cap), C.c_int64(probe), _p(cnt), _p(rows),
+                                          C.byref(n_out), C.byref(n_zero), _p(tally))
+            if rc == QEC_ERR_LIMIT and n_out.value > probe and probe < max_out:
+                probe = min(max_out, max(n_out.value, 2 * probe))  # deterministic RNG: re-run
+                continue
+            _check(rc)
+            n = n_out.value
+            return rows[:n], cnt[:n], int(n_zero.value), tally
+
 
 def outcome_histogram_dev(circuit: Circuit, d_bits: int, n_paths: int, d_keys: int, d_counts: int,
-                          table_cap: int, stream: int = 0):
-    _check(lib().qec_outcome_histogram_dev(circuit._h, C.c_void_p(d_bits), C.c_int64(n_paths),
-                                           C.c_void_p(d_keys), C.c_void_p(d_counts),
-                                           C.c_int64(table_cap), C.c_void_p(stream or None)))
+                          table_cap: int, stream: int = 0, d_rows: int = 0, d_status: int = 0,
+                          n_words: int = 0):
+    """K4 over a device buffer (raw device addresses).  keys / counts / status are accumulated:
+    zero them first."""
+    _check(lib().qec_outcome_histogram_rows_dev(
+        circuit._h, C.c_void_p(d_bits), C.c_int64(n_paths), C.c_int64(n_words or (n_paths + 31) // 32),
+        C.c_void_p(d_keys), C.c_void_p(d_counts), C.c_void_p(d_rows or None), C.c_int64(table_cap),
+        C.c_void_p(d_status or None), C.c_void_p(stream or None)))
+
+
+def outcome_hash(rows: np.ndarray) -> np.ndarray:
+    """The 64-bit key K4 gives an outcome (rows uint32[n][ceil(nc/32)]), for checking tables
+    against numpy: mix64 folds of the 32-clbit tiles (csrc/qec_kernels.cu qec_mix64)."""
+    h = np.full(len(rows), 0x243F6A8885A308D3, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        for j in range(rows.shape[1]):
+            h ^= rows[:, j].astype(np.uint64)
+            h *= np.uint64(0x9E3779B97F4A7C15)
+            h ^= h >> np.uint64(29)
+        h ^= h >> np.uint64(32)
+    h[h == 0] = 1
+    return h
+
+
+def pack_rows(packed: np.ndarray, n: int) -> np.ndarray:
+    """bit-sliced uint32[nc][n_words] -> row-packed uint32[n][ceil(nc/32)] (K4's outcome rows)"""
+    nc = packed.shape[0]
+    b = unpack_bits(packed, n)                                     # [n][nc]
+    rw = (nc + 31) // 32
+    pad = np.zeros((n, rw * 32), dtype=np.uint8)
+    pad[:, :nc] = b
+    return np.packbits(pad, axis=1, bitorder="little").view(np.uint32).reshape(n, rw)
 
 
 def unpack_bits(packed: np.ndarray, n: int) -> np.ndarray:

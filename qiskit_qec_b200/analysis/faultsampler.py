@@ -82,18 +82,42 @@ class FaultSampler:
         reference consumes (``decoders/decoding_graph.py:165-209``).  Outcomes are FLIPS
         relative to the noiseless run (the propagator's semantics): they equal the stim /
         Aer absolute outcomes when the noiseless outcome is all zero (base circuit "0").
-        The shots are sampled and packed on the GPU; distinct outcomes are counted on the host
-        from the packed bits."""
+        Sampling AND counting run on the GPU (K4, the hashed outcome table of
+        ``qec_sampler_counts``): only the distinct outcomes cross PCIe; the host formats strings."""
         if shots <= 0:
             return {}
-        packed, _ = self.faultsamp.sample_packed(int(shots), True, False)
-        return counts_from_packed(np.asarray(packed), int(shots), self.reg_sizes)
+        rows, counts, n_zero = self.faultsamp.sample_counts(int(shots))
+        return counts_from_rows(np.asarray(rows), np.asarray(counts), int(n_zero),
+                                self.circuit.nc, self.reg_sizes)
+
+
+def _format_key(chars, cuts) -> str:
+    return "".join((" " if i in cuts else "") + ("1" if b else "0") for i, b in enumerate(chars))
+
+
+def counts_from_rows(rows: np.ndarray, counts: np.ndarray, n_zero: int, nc: int, reg_sizes) -> dict:
+    """{bitstring: count} from K4's table: ``rows`` uint32[k][ceil(nc/32)] (bit c % 32 of word
+    c / 32 = clbit c) with multiplicities ``counts``, plus ``n_zero`` all-zero outcomes.  Strings
+    list clbit nc-1 first, registers (declaration order ``reg_sizes``) separated by a space."""
+    if sum(reg_sizes) != nc:
+        raise ValueError("register sizes do not add up to the number of clbits")
+    cuts = set(np.cumsum(list(reg_sizes)[::-1])[:-1].tolist())  # after these many chars: a space
+    out = {}
+    if n_zero:
+        out[_format_key(np.zeros(nc, dtype=np.uint8), cuts)] = int(n_zero)
+    if len(rows):
+        bits = np.unpackbits(np.ascontiguousarray(rows).view(np.uint8), axis=1, bitorder="little")[:, :nc]
+        for chars, k in zip(bits[:, ::-1], counts):
+            s = _format_key(chars, cuts)
+            out[s] = out.get(s, 0) + int(k)
+    return out
 
 
 def counts_from_packed(packed: np.ndarray, n: int, reg_sizes) -> dict:
     """{bitstring: count} from packed outcomes uint32[nc][ceil(n/32)] (bit b of word w of row c
-    = clbit c of shot 32 w + b).  Strings list clbit nc-1 first, registers (declaration order
-    ``reg_sizes``) separated by a space."""
+    = clbit c of shot 32 w + b), counted on the host with numpy: the CHECKER of
+    :func:`counts_from_rows` in the tests and a convenience for outcome buffers that are already
+    on the host."""
     nc = packed.shape[0]
     if sum(reg_sizes) != nc:
         raise ValueError("register sizes do not add up to the number of clbits")
@@ -101,10 +125,5 @@ def counts_from_packed(packed: np.ndarray, n: int, reg_sizes) -> dict:
                          bitorder="little")[:, :n]            # [clbit][shot]
     rows = np.packbits(bits[::-1].T, axis=1)                   # per shot, clbit nc-1 first
     uniq, cnt = np.unique(rows, axis=0, return_counts=True)
-    cuts = set(np.cumsum(list(reg_sizes)[::-1])[:-1].tolist())  # after these many chars: a space
-    out = {}
-    for u, k in zip(uniq, cnt):
-        chars = np.unpackbits(u)[:nc]
-        s = "".join((" " if i in cuts else "") + ("1" if b else "0") for i, b in enumerate(chars))
-        out[s] = int(k)
-    return out
+    cuts = set(np.cumsum(list(reg_sizes)[::-1])[:-1].tolist())
+    return {_format_key(np.unpackbits(u)[:nc], cuts): int(k) for u, k in zip(uniq, cnt)}

@@ -429,6 +429,40 @@ class FaultSampler {
     return py::make_tuple(want_bits ? py::object(bits) : py::none(),
                           want_tally ? py::object(tally) : py::none());
   }
+  // bulk API: {outcome: multiplicity} of `n` fresh shots, histogrammed on the device (K4);
+  // returns (rows uint32[k][ceil(nc/32)], counts uint64[k], n_zero): the k distinct non-zero
+  // outcomes, row-packed (bit c % 32 of word c / 32 = clbit c), and the all-zero multiplicity
+  py::tuple sample_counts(int64_t n) {
+    const int64_t nw = (std::max<int64_t>(n, 0) + 31) / 32;
+    const int rw = (nc_ + 31) / 32;
+    int64_t cap = 1 << 16;
+    while (cap < 2 * std::min<int64_t>(std::max<int64_t>(n, 1), (int64_t)1 << 26)) cap <<= 1;
+    int64_t room = std::min<int64_t>(std::max<int64_t>(n, 1), 1 << 16), n_out = 0;
+    uint64_t n_zero = 0;
+    std::vector<uint64_t> cnt;
+    std::vector<uint32_t> rows;
+    for (;;) {
+      cnt.assign((size_t)room, 0);
+      rows.assign((size_t)room * rw, 0);
+      int rc;
+      {
+        py::gil_scoped_release nogil;
+        rc = qec_sampler_counts(h_, cursor_, n, cap, room, cnt.data(), rows.data(), &n_out, &n_zero, nullptr);
+      }
+      if (rc == QEC_ERR_LIMIT && n_out > room) { room = std::max(n_out, 2 * room); continue; }  // same seed, same shots
+      check(rc);
+      break;
+    }
+    cursor_ += nw * 32;
+    py::array_t<uint32_t> r({(py::ssize_t)n_out, (py::ssize_t)rw});
+    py::array_t<uint64_t> c((py::ssize_t)n_out);
+    if (n_out) {
+      memcpy(r.mutable_data(), rows.data(), (size_t)n_out * rw * 4);
+      memcpy(c.mutable_data(), cnt.data(), (size_t)n_out * 8);
+    }
+    return py::make_tuple(r, c, (uint64_t)n_zero);
+  }
+  std::string variant() const { return qec_sampler_variant(h_); }
   int64_t get_cursor() const { return cursor_; }
   void set_cursor(int64_t c) {
     if (c < 0 || (c & 31)) throw std::invalid_argument("cursor must be a non-negative multiple of 32");
@@ -659,6 +693,8 @@ PYBIND11_MODULE(_c_analysis, module) {
       .def("sample", &FaultSampler::sample)
       .def("sample_packed", &FaultSampler::sample_packed, py::arg("n"), py::arg("want_bits") = true,
            py::arg("want_tally") = false)
+      .def("sample_counts", &FaultSampler::sample_counts, py::arg("n"))
+      .def("variant", &FaultSampler::variant)
       .def("get_cursor", &FaultSampler::get_cursor)
       .def("set_cursor", &FaultSampler::set_cursor);
 

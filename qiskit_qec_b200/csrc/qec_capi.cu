@@ -714,6 +714,18 @@ static int enum_plan_linear(qec_enumerator *e) {
   }
   const int64_t F = (int64_t)e->pcode.size();
   if (F < 1 || F >= (1 << 21)) { ln.why = "fault count out of range"; return 0; }
+  {
+    // outcome = XOR of signatures needs every op to carry at most one fault of a path.  Two
+    // locations on one op break that: the reference's `fail[icomb[j]] = j` keeps only the LAST
+    // one (errorpropagator.cpp:265-267), which the frame kernels reproduce.
+    std::vector<uint32_t> ops(e->lop);
+    std::sort(ops.begin(), ops.end());
+    if (std::adjacent_find(ops.begin(), ops.end()) != ops.end()) {
+      if (forced) return fail(QEC_ERR_INVALID, "QEC_B200_ENUM=linear: two fault locations share one op");
+      ln.why = "two fault locations share one op (last-duplicate-wins needs the frame kernels)";
+      return 0;
+    }
+  }
   // single-fault paths in (location, digit) order = fault index poff[l] + d
   std::vector<int64_t> path_off((size_t)F + 1);
   std::vector<int32_t> fop((size_t)F);
@@ -1052,6 +1064,7 @@ struct qec_sampler {
   std::vector<uint32_t> slinf;
   uint32_t *d_slinf = nullptr;
   int last_cap = 0;  // event capacity of the kernel that served the latest launches
+  std::string variant;  // qec_sampler_variant()
   // linear-response path (qec_linear.cu): the default when the circuit is eligible
   struct Lin {
     bool eligible = false;
@@ -1175,6 +1188,12 @@ static int sampler_plan_linear(qec_sampler *s) {
   const char *mode = std::getenv("QEC_B200_SAMPLER");
   if (mode && !strcmp(mode, "frame")) { ln.why = "QEC_B200_SAMPLER=frame"; return 0; }
   if (s->dev.n_slots <= 0) { ln.why = "no fault can occur"; return 0; }
+  for (int i = 1; i < s->L; ++i)
+    if (s->slop[i] == s->slop[i - 1]) {
+      // (see enum_plan_linear: the reference keeps only the last fault of an op)
+      ln.why = "two fault locations share one op (last-duplicate-wins needs the frame kernels)";
+      return 0;
+    }
   if (s->L >= 65536 || s->n_classes > 1024 || c->nc > 65535 || c->nc < 1) {
     ln.why = "too many locations / classes / clbits for the packed tables";
     return 0;
@@ -1682,6 +1701,22 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   delete s;
 }
 
+extern "C" const char *qec_sampler_variant(const qec_sampler *s) {
+  if (!s) return "";
+  qec_sampler *m = const_cast<qec_sampler *>(s);
+  if (s->lin.eligible) {
+    const QecLinDev &d = s->lin.dev;
+    m->variant = std::string("linear ") + (d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
+                 " batch=" + std::to_string(1 << d.lgb) + " streams=" + std::to_string(d.n_streams) +
+                 " draw=" + std::to_string(d.draw);
+  } else if (s->jit.eligible) {
+    m->variant = "frame specialised segments=" + std::to_string(s->jit.segments);
+  } else {
+    m->variant = "frame table-driven";
+  }
+  return s->variant.c_str();
+}
+
 extern "C" int qec_sampler_tables(const qec_sampler *s, uint32_t *buf, int cap, int *n) {
   if (!s) return fail(QEC_ERR_INVALID, "null sampler");
   std::vector<uint32_t> v;
@@ -1904,17 +1939,115 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
 }
 
 // ---- K4 + helpers --------------------------------------------------------------------------------
-extern "C" int qec_outcome_histogram_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
-                                         uint64_t *d_keys, uint64_t *d_counts, int64_t table_cap,
-                                         void *stream) {
+extern "C" int qec_outcome_histogram_rows_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                              int64_t n_words, uint64_t *d_keys, uint64_t *d_counts,
+                                              uint32_t *d_rows, int64_t table_cap, uint64_t *d_status,
+                                              void *stream) {
   if (!c || !d_bits || !d_keys || !d_counts) return fail(QEC_ERR_INVALID, "null pointer");
   if (table_cap <= 0 || (table_cap & (table_cap - 1)))
     return fail(QEC_ERR_INVALID, "table_cap must be a power of two");
   if (n_paths <= 0) return 0;
+  if (n_words < (n_paths + 31) / 32) return fail(QEC_ERR_INVALID, "row stride shorter than the paths");
   CU(cudaSetDevice(c->device));
-  qec_launch_outcome_hist((cudaStream_t)stream, d_bits, c->nc, n_paths, (unsigned long long *)d_keys,
-                          (unsigned long long *)d_counts, table_cap);
+  qec_launch_outcome_hist((cudaStream_t)stream, d_bits, c->nc, n_paths, n_words,
+                          (unsigned long long *)d_keys, (unsigned long long *)d_counts, d_rows,
+                          table_cap, (unsigned long long *)d_status);
   CU(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int qec_outcome_histogram_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                         uint64_t *d_keys, uint64_t *d_counts, int64_t table_cap,
+                                         void *stream) {
+  return qec_outcome_histogram_rows_dev(c, d_bits, n_paths, (n_paths + 31) / 32, d_keys, d_counts,
+                                        nullptr, table_cap, nullptr, stream);
+}
+
+// FaultSampler -> outcome counts, all on the device: the shots are drawn chunk by chunk into a
+// device buffer, every chunk is folded into one hashed outcome table (K4), and only the occupied
+// slots (count + the outcome row) cross PCIe.  This is the compact form of
+// qec_sampler_sample for callers that want `{outcome: multiplicity}` (the reference's
+// get_counts_via_stim contract, utils/stim_tools.py:234-283).
+extern "C" int qec_sampler_counts(qec_sampler *s, int64_t shot_lo, int64_t n_shots, int64_t table_cap,
+                                  int64_t max_out, uint64_t *out_counts, uint32_t *out_rows,
+                                  int64_t *n_out, uint64_t *n_zero, uint64_t *tally) {
+  int rc = sample_args(s, shot_lo, n_shots);
+  if (rc) return rc;
+  if (!n_out || !n_zero || (max_out > 0 && (!out_counts || !out_rows)))
+    return fail(QEC_ERR_INVALID, "null pointer");
+  if (table_cap <= 0 || (table_cap & (table_cap - 1)))
+    return fail(QEC_ERR_INVALID, "table_cap must be a power of two");
+  qec_circuit *c = s->c;
+  *n_out = 0; *n_zero = 0;
+  const size_t tl = QEC_TALLY_LEN(c->nc);
+  if (tally) memset(tally, 0, tl * 8);
+  if (n_shots == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int rw = (c->nc + 31) / 32;
+  const int64_t n_words = (n_shots + 31) / 32;
+  const int64_t cw = pipe_chunk_words(c, n_words);
+  DevBuf keys, counts, rows, status, okeys, ocounts, orows;
+  auto cleanup = [&]() { keys.release(); counts.release(); rows.release(); status.release();
+                         okeys.release(); ocounts.release(); orows.release(); };
+  if ((rc = keys.ensure((size_t)table_cap * 8)) || (rc = counts.ensure((size_t)table_cap * 8)) ||
+      (rc = rows.ensure((size_t)table_cap * rw * 4)) || (rc = status.ensure(5 * 8)) ||
+      (rc = c->pipe_buf[0].ensure((size_t)c->nc * cw * 4)) || (tally && (rc = c->tally.ensure(tl * 8)))) {
+    cleanup();
+    return rc;
+  }
+  cudaStream_t st = 0;
+  cudaMemsetAsync(keys.p, 0, (size_t)table_cap * 8, st);
+  cudaMemsetAsync(counts.p, 0, (size_t)table_cap * 8, st);
+  cudaMemsetAsync(status.p, 0, 5 * 8, st);
+  if (tally) cudaMemsetAsync(c->tally.p, 0, tl * 8, st);
+  QecSampleExport X{nullptr, nullptr, 0};
+  for (int64_t w0 = 0; w0 < n_words; w0 += cw) {
+    const int64_t words = std::min(cw, n_words - w0);
+    const int64_t shots = std::min<int64_t>(n_shots - 32 * w0, 32 * words);
+    rc = sample_launch(s, shot_lo + 32 * w0, shots, (uint32_t *)c->pipe_buf[0].p,
+                       tally ? (uint64_t *)c->tally.p : nullptr, X, st);
+    if (rc) { cleanup(); return rc; }
+    qec_launch_outcome_hist(st, (const uint32_t *)c->pipe_buf[0].p, c->nc, shots, (shots + 31) / 32,
+                            (unsigned long long *)keys.p, (unsigned long long *)counts.p,
+                            (uint32_t *)rows.p, table_cap, (unsigned long long *)status.p);
+  }
+  uint64_t stat[5] = {0, 0, 0, 0, 0};
+  if (cudaMemcpyAsync(stat, status.p, 3 * 8, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess) {
+    cleanup();
+    return fail(QEC_ERR_CUDA, "CUDA error in the outcome histogram: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  if ((rc = sampler_check(s))) { cleanup(); return rc; }
+  *n_zero = stat[2];
+  *n_out = (int64_t)stat[0];
+  if (stat[1]) {
+    cleanup();
+    return fail(QEC_ERR_LIMIT, "outcome table full: %llu shots dropped (table_cap %lld)",
+                (unsigned long long)stat[1], (long long)table_cap);
+  }
+  if (tally) cudaMemcpyAsync(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost, st);
+  if ((int64_t)stat[0] > max_out) {
+    cudaStreamSynchronize(st);
+    cleanup();
+    return max_out > 0 ? fail(QEC_ERR_LIMIT, "%llu distinct outcomes, room for %lld",
+                              (unsigned long long)stat[0], (long long)max_out) : 0;
+  }
+  if (stat[0]) {
+    const size_t n = (size_t)stat[0];
+    if ((rc = okeys.ensure(n * 8)) || (rc = ocounts.ensure(n * 8)) || (rc = orows.ensure(n * rw * 4))) {
+      cleanup();
+      return rc;
+    }
+    unsigned long long *d_n = (unsigned long long *)status.p + 4;
+    qec_launch_hist_compact(st, (const unsigned long long *)keys.p, (const unsigned long long *)counts.p,
+                            (const uint32_t *)rows.p, table_cap, rw, (unsigned long long *)okeys.p,
+                            (unsigned long long *)ocounts.p, (uint32_t *)orows.p, d_n);
+    cudaMemcpyAsync(out_counts, ocounts.p, n * 8, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(out_rows, orows.p, n * rw * 4, cudaMemcpyDeviceToHost, st);
+  }
+  const cudaError_t e = cudaStreamSynchronize(st);
+  cleanup();
+  if (e != cudaSuccess) return fail(QEC_ERR_CUDA, "CUDA error %s in qec_sampler_counts", cudaGetErrorString(e));
   return 0;
 }
 
@@ -1935,7 +2068,7 @@ extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_
     CU(cudaEventSynchronize(d->ev1));
     float t = 0;
     CU(cudaEventElapsedTime(&t, d->ev0, d->ev1));
-    const double ops = (double)grid * block * (double)iters * 16.0 * 8.0;
+    const double ops = (double)grid * block * (double)iters * (double)QEC_INT_PEAK_OPS_PER_TRIP;
     if (t > 0) best = std::max(best, ops / (t * 1e-3));
     if (pass == 0 && t > 0) iters = (int)std::max(2000.0, std::min(4e6, iters * (ms / t)));
   }

@@ -231,16 +231,24 @@ __device__ __forceinline__ unsigned long long qec_mix64(unsigned long long h, ui
   return h;
 }
 
+// rows (may be null): uint32[table_cap][ceil(nc/32)], the outcome itself (bit c % 32 of word c / 32
+// = clbit c), written once by the thread that claims the slot; status[0] = slots claimed,
+// status[1] = paths dropped because the table was full, status[2] = paths with the all-zero
+// outcome (counted apart: at small p it is by far the hottest key, and it never enters the table).
 __global__ void __launch_bounds__(256)
 k_outcome_hist(const uint32_t *__restrict__ bits, const int nc, const long long n_paths,
-               unsigned long long *__restrict__ keys, unsigned long long *__restrict__ counts,
-               const long long table_cap) {
-  const long long n_words = (n_paths + 31) / 32;
+               const long long n_words, unsigned long long *__restrict__ keys,
+               unsigned long long *__restrict__ counts, uint32_t *__restrict__ rows,
+               const long long table_cap, unsigned long long *__restrict__ status) {
   const unsigned lane = threadIdx.x & 31u;
   const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long n_warps = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long w = warp; w < n_words; w += n_warps) {
+  const int rw = (nc + 31) / 32;
+  const long long used_words = (n_paths + 31) / 32;
+  unsigned long long zeros = 0, dropped = 0, claimed = 0;
+  for (long long w = warp; w < used_words; w += n_warps) {
     unsigned long long h = 0x243F6A8885A308D3ull;
+    uint32_t anyv = 0;
     for (int c0 = 0; c0 < nc; c0 += 32) {
       const int c = c0 + (int)lane;
       const uint32_t row = (c < nc) ? bits[(long long)c * n_words + w] : 0u;
@@ -250,41 +258,96 @@ k_outcome_hist(const uint32_t *__restrict__ bits, const int nc, const long long 
         const uint32_t col = __ballot_sync(0xFFFFFFFFu, (row >> b) & 1u);
         if ((int)lane == b) mine = col;
       }
+      anyv |= mine;
       h = qec_mix64(h, mine);
     }
     h ^= h >> 32;
     if (h == 0) h = 1;  // 0 marks an empty slot
-    if (32 * w + lane < n_paths) {
+    const bool valid = 32 * w + lane < n_paths;
+    long long won = -1;  // slot this lane claimed (its outcome row still has to be written)
+    if (valid && anyv == 0u) ++zeros;
+    else if (valid) {
       unsigned long long slot = h & (unsigned long long)(table_cap - 1);
-      for (long long probe = 0; probe < table_cap; ++probe) {
+      long long probe = 0;
+      for (; probe < table_cap; ++probe) {
         const unsigned long long prev = atomicCAS(&keys[slot], 0ull, h);
         if (prev == 0ull || prev == h) {
           atomicAdd(&counts[slot], 1ull);
+          if (prev == 0ull) { won = (long long)slot; ++claimed; }
           break;
         }
         slot = (slot + 1) & (unsigned long long)(table_cap - 1);
       }
+      if (probe == table_cap) ++dropped;
     }
+    if (rows && __any_sync(0xFFFFFFFFu, won >= 0)) {
+      // second transpose, only when some lane of the word claimed a new slot (rare once the
+      // table holds the common outcomes): winners store their outcome row
+      for (int c0 = 0; c0 < nc; c0 += 32) {
+        const int c = c0 + (int)lane;
+        const uint32_t row = (c < nc) ? bits[(long long)c * n_words + w] : 0u;
+        uint32_t mine = 0;
+#pragma unroll
+        for (int b = 0; b < 32; ++b) {
+          const uint32_t col = __ballot_sync(0xFFFFFFFFu, (row >> b) & 1u);
+          if ((int)lane == b) mine = col;
+        }
+        if (won >= 0) rows[won * rw + (c0 >> 5)] = mine;
+      }
+    }
+  }
+  if (status) {
+    zeros = __reduce_add_sync(0xFFFFFFFFu, (unsigned)zeros);  // (< 2^32 per warp: 32 paths per trip)
+    if (claimed) atomicAdd(&status[0], claimed);
+    if (dropped) atomicAdd(&status[1], dropped);
+    if (lane == 0 && zeros) atomicAdd(&status[2], zeros);
+  }
+}
+
+// Occupied slots of the table -> dense arrays (order arbitrary): out_counts[i], out_rows[i][rw],
+// out_keys[i]; *n_out counts them.
+__global__ void __launch_bounds__(256)
+k_hist_compact(const unsigned long long *__restrict__ keys, const unsigned long long *__restrict__ counts,
+               const uint32_t *__restrict__ rows, const long long table_cap, const int rw,
+               unsigned long long *__restrict__ out_keys, unsigned long long *__restrict__ out_counts,
+               uint32_t *__restrict__ out_rows, unsigned long long *__restrict__ n_out) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < table_cap;
+       i += (long long)gridDim.x * blockDim.x) {
+    const unsigned long long k = keys[i];
+    if (!k) continue;
+    const unsigned long long o = atomicAdd(n_out, 1ull);
+    out_keys[o] = k;
+    out_counts[o] = counts[i];
+    if (rows) for (int j = 0; j < rw; ++j) out_rows[o * rw + j] = rows[i * rw + j];
   }
 }
 
 // ------------------------------------------------------------------------------------------
-// Integer-pipe roofline denominator: 8 independent LOP3 chains per thread, no memory.
+// Integer-pipe roofline denominator: 8 independent LOP3 chains per thread, no memory.  Every
+// chain step is ONE `lop3.b32` written as inline PTX (asm volatile), so that the ops counted by
+// qec_measure_int_peak are the LOP3 instructions the SM executes: ptxas neither merges nor
+// splits them (round 1 wrote the chains in C and ptxas re-associated 128 counted ops into ~190
+// executed ones).  QEC_INT_PEAK_OPS_PER_TRIP is the count per loop trip and per thread;
+// profiles/r02/sass_k_int_peak.txt holds the SASS of the loop.
+#define QEC_LOP3(d, a, b, c, lut) asm volatile("lop3.b32 %0, %1, %2, %3, " #lut ";" : "=r"(d) : "r"(a), "r"(b), "r"(c))
 __global__ void __launch_bounds__(256) k_int_peak(const int iters, uint32_t *__restrict__ sink) {
   uint32_t a0 = threadIdx.x, a1 = a0 * 3u + 1u, a2 = a0 * 5u + 2u, a3 = a0 * 7u + 3u;
   uint32_t a4 = a0 ^ 0x55u, a5 = a0 ^ 0xAAu, a6 = a0 + 11u, a7 = a0 + 13u;
   const uint32_t k0 = blockIdx.x * 0x9E3779B9u + 1u, k1 = ~k0;
   for (int i = 0; i < iters; ++i) {
 #pragma unroll
-    for (int u = 0; u < 16; ++u) {
-      // each statement is one 3-input logic op (LOP3) on an independent chain
-      a0 = (a0 & k0) ^ a1; a1 = (a1 | k1) ^ a2; a2 = (a2 & k0) ^ a3; a3 = (a3 | k1) ^ a4;
-      a4 = (a4 & k0) ^ a5; a5 = (a5 | k1) ^ a6; a6 = (a6 & k0) ^ a7; a7 = (a7 | k1) ^ a0;
+    for (int u = 0; u < QEC_INT_PEAK_UNROLL; ++u) {
+      // 0x6A = (a & b) ^ c, 0x1E = (a | b) ^ c: one three-input logic op per chain per step
+      QEC_LOP3(a0, a0, k0, a1, 0x6A); QEC_LOP3(a1, a1, k1, a2, 0x1E);
+      QEC_LOP3(a2, a2, k0, a3, 0x6A); QEC_LOP3(a3, a3, k1, a4, 0x1E);
+      QEC_LOP3(a4, a4, k0, a5, 0x6A); QEC_LOP3(a5, a5, k1, a6, 0x1E);
+      QEC_LOP3(a6, a6, k0, a7, 0x6A); QEC_LOP3(a7, a7, k1, a0, 0x1E);
     }
   }
   const uint32_t r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
   if (r == 0x12345678u) sink[0] = r;  // practically never: keeps the chains live
 }
+#undef QEC_LOP3
 
 }  // namespace
 
@@ -340,13 +403,25 @@ void qec_launch_sample(const QecLaunchCfg &cfg, cudaStream_t stream, const QecCi
 }
 
 void qec_launch_outcome_hist(cudaStream_t stream, const uint32_t *bits, int nc, long long n_paths,
-                             unsigned long long *keys, unsigned long long *counts,
-                             long long table_cap) {
-  const long long n_words = (n_paths + 31) / 32;
-  long long blocks = (n_words * 32 + 255) / 256;
+                             long long n_words, unsigned long long *keys, unsigned long long *counts,
+                             uint32_t *rows, long long table_cap, unsigned long long *status) {
+  const long long used = (n_paths + 31) / 32;
+  long long blocks = (used * 32 + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
-  k_outcome_hist<<<(int)blocks, 256, 0, stream>>>(bits, nc, n_paths, keys, counts, table_cap);
+  k_outcome_hist<<<(int)blocks, 256, 0, stream>>>(bits, nc, n_paths, n_words, keys, counts, rows,
+                                                    table_cap, status);
+}
+
+void qec_launch_hist_compact(cudaStream_t stream, const unsigned long long *keys,
+                             const unsigned long long *counts, const uint32_t *rows,
+                             long long table_cap, int rw, unsigned long long *out_keys,
+                             unsigned long long *out_counts, uint32_t *out_rows,
+                             unsigned long long *n_out) {
+  long long blocks = (table_cap + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  k_hist_compact<<<(int)blocks, 256, 0, stream>>>(keys, counts, rows, table_cap, rw, out_keys,
+                                                    out_counts, out_rows, n_out);
 }
 
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink) {

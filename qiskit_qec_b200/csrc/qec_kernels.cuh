@@ -4,6 +4,9 @@
 #include "qec_device.cuh"
 
 #define QEC_KERNEL_MAX_ORDER 4
+// k_int_peak: unrolled chain steps per loop trip x 8 chains = LOP3 executed per trip and thread
+#define QEC_INT_PEAK_UNROLL 16
+#define QEC_INT_PEAK_OPS_PER_TRIP (QEC_INT_PEAK_UNROLL * 8)
 
 struct QecLaunchCfg {
   int grid, block;
@@ -31,8 +34,13 @@ void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecEnumDev &E, const QecEnumLinDev &EL, long long lo, long long hi);
 int qec_enum_lanes_set_smem_attr(size_t smem);
 void qec_launch_outcome_hist(cudaStream_t stream, const uint32_t *bits, int nc, long long n_paths,
-                             unsigned long long *keys, unsigned long long *counts,
-                             long long table_cap);
+                             long long n_words, unsigned long long *keys, unsigned long long *counts,
+                             uint32_t *rows, long long table_cap, unsigned long long *status);
+void qec_launch_hist_compact(cudaStream_t stream, const unsigned long long *keys,
+                             const unsigned long long *counts, const uint32_t *rows,
+                             long long table_cap, int rw, unsigned long long *out_keys,
+                             unsigned long long *out_counts, uint32_t *out_rows,
+                             unsigned long long *n_out);
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink);
 size_t qec_kernel_smem_bytes(int kind, int nq, int nc, int T, uint32_t B, uint32_t K1);
 int qec_kernel_set_smem_attr(int kind, int order, size_t smem);

@@ -892,6 +892,8 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
         }
       }
     }
+    // rows kept for the next row of their chain are read by OTHER lanes in a later trip
+    __syncwarp();
   }
   uint32_t nz = 0;
   if (TALLY) {

@@ -264,3 +264,53 @@ def test_sample_counts_qiskit_format(ext):
     for key, p in (("00 0", 0.7), ("11 0", 0.1), ("00 1", 0.1), ("11 1", 0.1)):
         assert abs(counts[key] / n - p) < 5 * np.sqrt(p * (1 - p) / n), key
     assert fs.sample_counts(0) == {}
+
+
+def test_drivers_fed_by_a_quantum_circuit_shaped_object(ext, monkeypatch):
+    """FaultEnumerator / FaultSampler / CErrorPropagator constructed from a
+    qiskit-shaped circuit (stub ``qiskit.converters.circuit_to_dag`` with duck-typed DAG nodes:
+    qiskit itself is not installed here), through ``lower()``'s QuantumCircuit branch: the 13
+    fault paths of reference test_faultenumerator.py:50-84 with its two classical registers (" "
+    separators in generate() only) and its ``IGate(label="special")``."""
+    import sys
+    import types
+    from test_widened_cpu import _Circuit, _Dag
+    from qiskit_qec_b200.analysis import CErrorPropagator, FaultEnumerator, FaultSampler
+    qiskit = types.ModuleType("qiskit")
+    conv = types.ModuleType("qiskit.converters")
+    conv.circuit_to_dag = _Dag
+    qiskit.converters = conv
+    monkeypatch.setitem(sys.modules, "qiskit", qiskit)
+    monkeypatch.setitem(sys.modules, "qiskit.converters", conv)
+    # topological order qiskit gives the reference's circuit: h, cx01, id(special), cx12, m0, m1, m2
+    qc = _Circuit(3, [2, 1])
+    qc.add("h", [0]); qc.add("cx", [0, 1]); qc.add("id", [0], label="special"); qc.add("cx", [1, 2])
+    qc.add("measure", [0], [0]); qc.add("measure", [1], [1]); qc.add("measure", [2], [2])
+    pnm = PauliNoiseModel()
+    pnm.add_operation("h", {"x": 1, "y": 1, "z": 1})
+    pnm.add_operation("cx", {"ix": 1, "xi": 1, "xx": 1})
+    pnm.add_operation("special", {"y": 1})
+    pnm.add_operation("measure", {"x": 1})
+    flat = [(0, ["h"], ["x"], [1, 1, 1]), (1, ["h"], ["y"], [1, 1, 1]), (2, ["h"], ["z"], [0, 0, 0]),
+            (3, ["cx"], ["ix"], [0, 1, 1]), (4, ["cx"], ["xi"], [1, 0, 0]), (5, ["cx"], ["xx"], [1, 1, 1]),
+            (6, ["special"], ["y"], [1, 0, 0]), (7, ["cx"], ["ix"], [0, 0, 1]), (8, ["cx"], ["xi"], [0, 1, 0]),
+            (9, ["cx"], ["xx"], [0, 1, 1]), (10, ["measure"], ["x"], [1, 0, 0]),
+            (11, ["measure"], ["x"], [0, 1, 0]), (12, ["measure"], ["x"], [0, 0, 1])]
+    fe = FaultEnumerator(qc, order=1, method="propagator", model=pnm, sim_seed=0)
+    sep = [(i, l, e, [o[0], o[1], " ", o[2]]) for i, l, e, o in flat]
+    assert list(fe.generate()) == sep
+    assert [x for b in fe.generate_blocks(3) for x in b] == flat
+    ep = CErrorPropagator()
+    ep.load_circuit(qc)
+    assert ep.propagate_faults([0], ["x"]) == [1, 1, 1] and ep.propagate_faults([1], ["ix"]) == [0, 1, 1]
+    pnm.set_error_probability("h", 0.2)
+    pnm.set_error_probability("cx", 0.1)
+    pnm.set_error_probability("special", 0.0)
+    pnm.set_error_probability("measure", 0.0)
+    fs = FaultSampler(qc, pnm, sim_seed=9)
+    n = 50_000
+    block = fs.sample(n)
+    k = np.bincount([len(x[1]) for x in block], minlength=4)[:4] / n
+    for j, pj in enumerate([0.8 * 0.81, 0.2 * 0.81 + 0.8 * 0.18, 0.8 * 0.01 + 0.2 * 0.18, 0.2 * 0.01]):
+        assert abs(k[j] - pj) < 5 * np.sqrt(pj * (1 - pj) / n), j
+    assert fs.sample_one()[3][2] == " "
