@@ -177,6 +177,40 @@ static inline __host__ __device__ size_t qec_lanes_smem_words(int nc, int warps,
   return (size_t)warps * per_warp + 64u + prog_words + (((size_t)L + 1u) & ~(size_t)1u) + 2u * (size_t)n_faults;
 }
 
+// Half-word lane-stream sampler (k_sample_lanes16 in qec_lanes16.cu): the lane-stream idea with
+// 16 shots per lane, so that the accumulator of a warp is half the size and twice the warps fit
+// an SM.  A warp owns a batch of 512 shots, lane l the shots 16 l .. 16 l + 15.  The accumulator
+// is acc[word-row][lane] (uint32): a word-row packs TWO clbit rows, row A in the low and row B in
+// the high half-word; the host pairs whole chains of the time-difference basis (A_k, B_k = k-th
+// rows of two chains), so that "previous row of the chain" is the previous word-row for both
+// halves.  Fault records are deduplicated 16-byte entries of seven 16-bit byte offsets
+// (word-row * 128 + 2 * half; absent = the dummy word-row) that the lanes apply with 16-bit
+// shared-memory loads and stores at their own column (bank = lane: no conflicts, no atomics).
+struct QecLanes16Dev {
+  int nc, L;
+  uint32_t n_faults, n_rec, n_wrows;  // word-rows in use (the dummy and the zero word-row follow)
+  int n_steps;                         // read-out passes of four word-rows (multiple of 4)
+  // tables, each padded to a multiple of 16 bytes (bulk-copied into shared memory)
+  const uint32_t *info;     // [L] first fault of sorted location | number of Paulis << 21
+  const uint16_t *recidx;   // [n_faults] record of fault (sorted location, digit)
+  const uint4 *rec;         // [n_rec] eight uint16: 7 offsets, spare
+  const uint32_t *prog;     // [4 n_steps][2] {word-row | previous << 8 | has next << 17 | valid << 18,
+                            //                 clbit of row A | clbit of row B << 16 (0xFFFF: none)}
+  const uint32_t *slloc;    // [L] original location index (fault export)
+  uint32_t info_bytes, recidx_bytes, rec_bytes, prog_bytes;
+  uint32_t rk[20];          // Philox round keys
+  float gapC;
+  int noclamp;              // no 32-bit draw reaches QEC_GAP_CAP slots: skip the clamp test
+  uint32_t *batch_ctr;      // batches handed out so far in this launch (zeroed per launch)
+};
+static inline __host__ __device__ size_t qec_lanes16_smem_bytes(int nc, int warps, uint32_t n_wrows,
+                                                                uint32_t info_bytes, uint32_t recidx_bytes,
+                                                                uint32_t rec_bytes, uint32_t prog_bytes) {
+  const size_t ncp = ((size_t)nc + 3u) & ~(size_t)3u;
+  return (size_t)warps * ((size_t)n_wrows + 2u) * 128u + (ncp + 64u) * 4u + info_bytes + recidx_bytes +
+         rec_bytes + prog_bytes;
+}
+
 // Computed geometric gap (draw schemes 1 and 2).  u = (r | 1) / 2^32 is uniform on (0, 1);
 // the gap is floor(C * -log2(u)), C = -1 / log2(1 - pmax), so that P(gap >= k) = (1-pmax)^k.
 // -log2(u) = (clz + 1) - log2(f), f in [1, 2) the top 24 bits of the normalised word; log2(f)
