@@ -138,22 +138,26 @@ int orc_sample_batch(const uint32_t *tab, uint64_t batch, uint32_t *ev_out, int 
   const uint32_t nper = scheme == 2u ? 2u : 1u;
   int n = 0;
   if (tab[7] & 16u) {
-    /* lane-stream order (k_sample_lanes): batch = 1024 shots, lane l owns shots 32 l .. 32 l + 31
-     * and walks its own stream over slot = sorted location * 32 + shot bit; Philox counter =
-     * (batch lo, batch hi, call * 32 + lane, 0x4D000000), scheme 2 (two candidates per call, no
-     * thinning).  Faults are written lane by lane, each lane's in stream order. */
-    const int64_t lend = (int64_t)L * 32;
+    /* lane-stream order (k_sample_lanes: lgb = 10, k_sample_lanes16: lgb = 9): batch = 2^lgb
+     * shots, lane l owns the 2^(lgb-5) shots spl * l .. spl * l + spl - 1 and walks its own stream
+     * over slot = sorted location * spl + shot bit; Philox counter = (batch lo, batch hi,
+     * call * 32 + lane, 0x4D000000 for 32 shots per lane / 0x4E000000 for 16), scheme 2 (two
+     * candidates per call, no thinning).  Faults are written lane by lane, each lane's in stream
+     * order. */
+    const uint32_t lgs = lgb - 5u, spl = 1u << lgs;
+    const uint32_t tag = lgb == 10u ? 0x4D000000u : 0x4E000000u;
+    const int64_t lend = (int64_t)L << lgs;
     for (uint32_t lane = 0; lane < 32u; ++lane) {
       int64_t pos = -1;
       for (uint32_t call = 0; pos < lend; ++call) {
-        uint32_t c[4] = {(uint32_t)batch, (uint32_t)(batch >> 32), call * 32u + lane, 0x4D000000u};
+        uint32_t c[4] = {(uint32_t)batch, (uint32_t)(batch >> 32), call * 32u + lane, tag};
         philox4x32_10(c, k0, k1);
         for (uint32_t j = 0; j < 2u && pos < lend; ++j) {
           const uint32_t g = gap_len(c[2 * j], C);
           if (g >= GAP_CAP) { pos += GAP_CAP; continue; }
           pos += (int64_t)g + 1;
           if (pos >= lend) break;
-          const uint32_t sl = (uint32_t)(pos >> 5), shot = lane * 32u + (uint32_t)(pos & 31);
+          const uint32_t sl = (uint32_t)(pos >> lgs), shot = lane * spl + (uint32_t)(pos & (spl - 1u));
           const uint32_t cls = slcls[sl], base = cls_off[cls], npc = cls_off[cls + 1] - base;
           uint32_t d = 0;
           while (d + 1 < npc && c[2 * j + 1] >= cdf[base + d]) ++d;

@@ -1086,8 +1086,17 @@ struct qec_sampler {
     bool cls_uniform_all = true;
     std::vector<uint32_t> info2;
     uint32_t *d_info2 = nullptr;
+    // half-word lane-stream kernel (qec_lanes16.cu)
+    bool l16 = false;
+    QecLanes16Dev l16dev{};
+    uint32_t *d16_info = nullptr, *d16_prog = nullptr;
+    uint16_t *d16_recidx = nullptr, *d16_rec = nullptr;
   } lin;
 };
+
+static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<uint16_t>> &lists,
+                                const std::vector<int> &pred, const std::vector<int> &succ,
+                                bool use_diff, bool forced);
 
 static int sampler_plan_jit(qec_sampler *s) {
   JitPlan &pl = s->jit;
@@ -1363,6 +1372,22 @@ static int sampler_plan_linear(qec_sampler *s) {
   int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0, lane_mode = 0;
   const char *lmode = std::getenv("QEC_B200_LIN_MODE");
   {
+    // half-word lane-stream variant (512-shot batches, 16 shots per lane, twice the warps): the
+    // default where it fits; QEC_B200_LIN_MODE=lanes keeps the 32-shot lanes below
+    const bool want16 = lmode ? !strcmp(lmode, "lanes16") : true;
+    const bool can16 = draw == 2 && ln.cls_uniform_all && maxlen_w <= 7 && f_lgb == 0 &&
+                       ((long long)s->L << 9) < (1ll << 30);
+    if (want16 && can16) {
+      rc = sampler_plan_lanes16(s, use_diff ? tr : lists, pred, succ, use_diff, lmode != nullptr);
+      if (rc) return rc;
+      if (ln.l16) {
+        found = true; lane_mode = 1; threads = ln.cfg.block; ctas = 1; lgb = 9; info_s = 1; sig_s = 0;
+        rec8 = 0; rec_s = 1; smem = ln.cfg.smem;
+      }
+    }
+    if (lmode && !strcmp(lmode, "lanes16") && !ln.l16) { ln.why = "QEC_B200_LIN_MODE=lanes16: not eligible"; return 0; }
+  }
+  if (!found) {
     // lane-stream variant (1024-shot batches, lane = word column, no shared-memory atomics):
     // draw scheme 2, equal Pauli weights, 8-byte records, at least 4 warps' accumulators
     const bool want = lmode ? !strcmp(lmode, "lanes") : true;
@@ -1527,7 +1552,134 @@ static int sampler_plan_linear(qec_sampler *s) {
   ln.cfg.block = threads;
   ln.cfg.grid = di.sms * ctas;
   ln.cfg.smem = smem;
+  if (ln.l16) {
+    ln.l16dev.slloc = s->d_slloc;
+    memcpy(ln.l16dev.rk, d.rk, sizeof d.rk);
+    ln.l16dev.gapC = d.gapC;
+    // the largest value of -log2(u) is 32: no gap reaches the clamp when 32.5 C stays below it
+    ln.l16dev.noclamp = (double)d.gapC * 32.5 < (double)QEC_GAP_CAP ? 1 : 0;
+    ln.l16dev.batch_ctr = d.batch_ctr;
+  }
   ln.eligible = true;
+  return 0;
+}
+
+// Tables of the half-word lane-stream kernel (QecLanes16Dev): chains of the time-difference basis
+// paired into word-rows, deduplicated 16-byte offset records, the read-out program.
+static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<uint16_t>> &lists,
+                                const std::vector<int> &pred, const std::vector<int> &succ,
+                                bool use_diff, bool forced) {
+  qec_sampler::Lin &ln = s->lin;
+  qec_circuit *c = s->c;
+  const DevInfo &di = *c->info;
+  (void)forced;
+  const int nc = c->nc;
+  // chains (single rows when the raw basis is in use), longest first, paired two by two
+  std::vector<std::vector<int>> chains;
+  for (int cb = 0; cb < nc; ++cb) {
+    if (use_diff && pred[cb] >= 0) continue;
+    chains.emplace_back();
+    for (int x = cb; x >= 0; x = use_diff ? succ[x] : -1) chains.back().push_back(x);
+  }
+  std::stable_sort(chains.begin(), chains.end(),
+                   [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
+  struct WRow { int rowA, rowB, prev; bool next; };
+  std::vector<WRow> wrows;
+  std::vector<uint32_t> off_of(nc, 0u);  // byte offset of clbit row inside a warp's accumulator
+  for (size_t j = 0; j < chains.size(); j += 2) {
+    const std::vector<int> &A = chains[j];
+    const std::vector<int> *B = j + 1 < chains.size() ? &chains[j + 1] : nullptr;
+    for (size_t k = 0; k < A.size(); ++k) {
+      const int w = (int)wrows.size();
+      const int rb = (B && k < B->size()) ? (*B)[k] : -1;
+      wrows.push_back({A[k], rb, k > 0 ? w - 1 : -1, k + 1 < A.size()});
+      off_of[A[k]] = (uint32_t)w * 128u;
+      if (rb >= 0) off_of[rb] = (uint32_t)w * 128u + 2u;
+    }
+  }
+  const uint32_t n_wrows = (uint32_t)wrows.size();
+  if (n_wrows + 2u > 256u) return 0;  // (word-row index is one byte of the read-out program)
+  const uint32_t dummy = n_wrows, zero = n_wrows + 1u;
+  // records: seven offsets + spare, deduplicated
+  const size_t F = lists.size();
+  std::vector<uint16_t> rec, recidx(F);
+  {
+    std::vector<std::pair<std::vector<uint16_t>, uint32_t>> keyed(F);
+    for (size_t f = 0; f < F; ++f) {
+      std::vector<uint16_t> r(8, (uint16_t)(dummy * 128u));
+      if (lists[f].size() > 7) return 0;
+      for (size_t k = 0; k < lists[f].size(); ++k) r[k] = (uint16_t)off_of[lists[f][k]];
+      r[7] = (uint16_t)lists[f].size();
+      keyed[f] = {r, (uint32_t)f};
+    }
+    std::sort(keyed.begin(), keyed.end());
+    uint32_t id = 0;
+    for (size_t i = 0; i < F; ++i) {
+      if (i == 0 || keyed[i].first != keyed[i - 1].first) {
+        id = (uint32_t)(rec.size() / 8);
+        rec.insert(rec.end(), keyed[i].first.begin(), keyed[i].first.end());
+      }
+      recidx[keyed[i].second] = (uint16_t)id;
+    }
+    if (rec.size() / 8 > 65535) return 0;
+  }
+  // read-out program: word-rows in order, 16 per trip, never with their previous word-row
+  std::vector<uint32_t> prog;
+  {
+    const size_t trip = 16;
+    std::vector<int> cur;
+    auto flush = [&]() {
+      while (!cur.empty() && cur.size() < trip) cur.push_back(-1);
+      for (int x : cur) {
+        if (x < 0) { prog.push_back(zero | (zero << 8)); prog.push_back(0xFFFF0000u); continue; }
+        const WRow &w = wrows[x];
+        prog.push_back((uint32_t)x | ((w.prev >= 0 ? (uint32_t)w.prev : zero) << 8) | (w.next ? (1u << 17) : 0u) | (1u << 18));
+        prog.push_back((uint32_t)w.rowA | ((w.rowB >= 0 ? (uint32_t)w.rowB : 0xFFFFu) << 16));
+      }
+      cur.clear();
+    };
+    for (int x = 0; x < (int)n_wrows; ++x) {
+      const int pr = wrows[x].prev;
+      if (cur.size() == trip || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
+      cur.push_back(x);
+    }
+    flush();
+  }
+  std::vector<uint32_t> info((size_t)s->L);
+  for (int sl = 0; sl < s->L; ++sl) info[sl] = ln.info2[2 * sl] | (ln.info2[2 * sl + 1] << 21);
+  auto pad16 = [](size_t bytes) { return (uint32_t)((bytes + 15u) & ~(size_t)15u); };
+  const uint32_t info_b = pad16(info.size() * 4), ridx_b = pad16(recidx.size() * 2);
+  const uint32_t rec_b = pad16(rec.size() * 2), prog_b = pad16(prog.size() * 4);
+  info.resize(info_b / 4, 0u);
+  recidx.resize(ridx_b / 2, 0);
+  prog.resize(prog_b / 4, 0u);
+  const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
+  int warps = 0;
+  size_t smem = 0;
+  for (int wz = (w_env > 0 ? w_env : 16); wz >= (w_env > 0 ? w_env : 4); --wz) {
+    const size_t need = qec_lanes16_smem_bytes(nc, wz, n_wrows, info_b, ridx_b, rec_b, prog_b) + 128;
+    if (need > di.smem_optin) continue;
+    warps = wz; smem = need;
+    break;
+  }
+  if (!warps || warps > 16) return 0;
+  int rc;
+  if ((rc = upload(info, &ln.d16_info)) || (rc = upload(prog, &ln.d16_prog)) ||
+      (rc = upload(recidx, &ln.d16_recidx)) || (rc = upload(rec, &ln.d16_rec)))
+    return rc;
+  {
+    const int e = qec_lanes16_set_smem_attr(smem);
+    if (e) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)e));
+  }
+  QecLanes16Dev &d = ln.l16dev;
+  d.nc = nc; d.L = s->L; d.n_faults = (uint32_t)F; d.n_rec = (uint32_t)(rec.size() / 8);
+  d.n_wrows = n_wrows; d.n_steps = (int)(prog.size() / 8);
+  d.info = ln.d16_info; d.recidx = ln.d16_recidx; d.rec = reinterpret_cast<const uint4 *>(ln.d16_rec);
+  d.prog = ln.d16_prog;
+  d.info_bytes = info_b; d.recidx_bytes = ridx_b; d.rec_bytes = rec_b; d.prog_bytes = prog_b;
+  ln.cfg.block = 32 * warps;
+  ln.cfg.smem = smem;
+  ln.l16 = true;
   return 0;
 }
 
@@ -1694,7 +1846,8 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
                   s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
                   s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
                   s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr,
-                  s->lin.d_lvl_prog, s->lin.d_lvl_off};
+                  s->lin.d_lvl_prog, s->lin.d_lvl_off, s->lin.d16_info, s->lin.d16_prog,
+                  s->lin.d16_recidx, s->lin.d16_rec};
   for (void *p : ptrs) if (p) qec_dev_free(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -1706,7 +1859,7 @@ extern "C" const char *qec_sampler_variant(const qec_sampler *s) {
   qec_sampler *m = const_cast<qec_sampler *>(s);
   if (s->lin.eligible) {
     const QecLinDev &d = s->lin.dev;
-    m->variant = std::string("linear ") + (d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
+    m->variant = std::string("linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
                  " batch=" + std::to_string(1 << d.lgb) + " streams=" + std::to_string(d.n_streams) +
                  " draw=" + std::to_string(d.draw);
   } else if (s->jit.eligible) {
@@ -1772,17 +1925,19 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
     if (cfg.grid > n_batches) cfg.grid = (int)n_batches;
     if (d.lane_mode) CU(cudaMemsetAsync(d.batch_ctr, 0, 4, stream));
     time_begin(s->c, stream);
-    qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
+    if (s->lin.l16) qec_launch_sample_lanes16(cfg, stream, O, s->lin.l16dev, shot_lo, n_shots, X);
+    else qec_launch_sample_lin(cfg, stream, O, d, shot_lo, n_shots, X);
     time_end(s->c, stream);
     CU(cudaGetLastError());
     s->last_cap = 0;
-    g_last_kernel = std::string("sample:linear ") + (d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
+    g_last_kernel = std::string("sample:linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
                     " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +
                     (d.sig_in_smem ? " sig=smem" : " sig=global") + " draw=" + std::to_string(d.draw) +
                     (d.fast ? " lean" : "") +
-                    (d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B")) +
+                    (s->lin.l16 ? " rec=16B-offsets/smem x" + std::to_string(s->lin.l16dev.n_rec) + " wrows=" + std::to_string(s->lin.l16dev.n_wrows)
+                     : d.rec8 ? (d.rec_in_smem ? " rec=8B/smem" : " rec=8B") : (d.rec2 ? " rec=32B" : " rec=16B")) +
                     (d.n_lvl > 0 ? " diff-basis" : "");
     return 0;
   }
@@ -1917,6 +2072,17 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
   if (exp) {
     CU(cudaMemcpy(fault_cnt, s->xcnt.p, (size_t)n_words * 4, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(fault_ev, s->xev.p, (size_t)n_words * fault_cap * 4, cudaMemcpyDeviceToHost));
+    if (s->lin.eligible && s->lin.l16) {
+      // the two lanes of a 32-shot word filled its row from the two ends: count = even lane's |
+      // odd lane's << 16; close the gap (when the row overflowed, only the total is reported)
+      for (int64_t w = 0; w < n_words; ++w) {
+        const uint32_t lo = fault_cnt[w] & 0xFFFFu, hi = fault_cnt[w] >> 16;
+        uint32_t *e = fault_ev + (size_t)w * fault_cap;
+        if (lo + hi <= (uint32_t)fault_cap)
+          for (uint32_t k = 0; k < hi; ++k) e[lo + k] = e[fault_cap - 1 - k];
+        fault_cnt[w] = lo + hi;
+      }
+    }
     uint32_t mx = 0;
     for (int64_t w = 0; w < n_words; ++w) mx = std::max(mx, fault_cnt[w]);
     if (fault_cap_needed) *fault_cap_needed = (int)mx;

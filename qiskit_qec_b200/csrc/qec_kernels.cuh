@@ -29,6 +29,11 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecLinDev &S, long long shot_lo, long long n_shots,
                            const QecSampleExport &X);
 int qec_lin_set_smem_attr(size_t smem);
+// half-word lane-stream sampler (qec_lanes16.cu)
+void qec_launch_sample_lanes16(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
+                               const QecLanes16Dev &S, long long shot_lo, long long n_shots,
+                               const QecSampleExport &X);
+int qec_lanes16_set_smem_attr(size_t smem);
 // linear-response enumerator (qec_linear.cu); order 1..QEC_KERNEL_MAX_ORDER
 void qec_launch_enum_lanes(const QecLaunchCfg &cfg, cudaStream_t stream, const QecOutDev &O,
                            const QecEnumDev &E, const QecEnumLinDev &EL, long long lo, long long hi);

@@ -68,12 +68,13 @@ def test_linear_sampler_equals_explicit_propagation(capi, port, name, p, n_shots
 
 
 @pytest.mark.parametrize("mode,draw,kernel", [
-    ("lanes", None, "lane-streams"), ("warp", None, "warp-batches"), ("warp", "table", "draw=0"),
+    ("lanes16", None, "lane16-streams"), ("lanes", None, "lane-streams"), ("warp", None, "warp-batches"),
+    ("warp", "table", "draw=0"),
     ("warp", "computed1", "draw=1"), ("cta", None, "cta-batches"), ("cta", "table", "draw=0")])
 @pytest.mark.parametrize("name,p,n_shots,lo", [("surf3", 0.01, 20_000, 4096 + 32 * 3), ("rep", 0.05, 9_000, 0),
                                                ("surf5", 2e-3, 12_000, 1024 * 5 - 96)])
 def test_linear_sampler_every_kernel_and_draw_scheme(capi, port, monkeypatch, mode, draw, kernel, name, p, n_shots, lo):
-    """The three kernels (lane streams / warp batches / CTA batches) and the three draw schemes
+    """The four kernels (16- and 32-shot lane streams / warp batches / CTA batches) and the three draw schemes
     (gap tables, computed gaps with one or two candidates per Philox call), each against the CPU
     restatement of its draw order and against explicit propagation."""
     monkeypatch.setenv("QEC_B200_LIN_MODE", mode)
@@ -287,7 +288,7 @@ def test_linear_kernels_on_random_circuits_with_clbits_out_of_time_order(capi, p
             assert np.array_equal(bl, bf) and np.array_equal(tl, tf), f"trial {trial} order {order}"
         monkeypatch.delenv("QEC_B200_ENUM")
         _, _, lw, lp = sampler_inputs(circ, model)
-        for mode in ("lanes", "warp", "cta"):
+        for mode in ("lanes16", "lanes", "warp", "cta"):
             monkeypatch.setenv("QEC_B200_LIN_MODE", mode)
             g = capi.Circuit(circ.nq, circ.nc, circ.ops)
             sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=trial)
