@@ -31,6 +31,7 @@ SYMBOLS = [
     "qec_enumerator_range_dev",
     "qec_sampler_create", "qec_sampler_destroy", "qec_sampler_sample", "qec_sampler_sample_dev",
     "qec_sampler_check", "qec_sampler_tables", "qec_sampler_variant", "qec_sampler_counts",
+    "qec_sampler_sample_events",
     "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
@@ -301,6 +302,29 @@ class Sampler:
 
     def check(self):
         _check(lib().qec_sampler_check(self._h))
+
+    def sample_events(self, shot_lo: int, n_shots: int, want_tally: bool = False, pinned=None):
+        """Compact form: (word_cnt uint16[ceil(n/32)], events uint32[n_events], tally).  ``pinned``
+        may hold preallocated (word_cnt, events) arrays (e.g. pinned host memory) to fill."""
+        nw = (max(n_shots, 0) + 31) // 32
+        tally = np.zeros(tally_len(self.circuit.nc), dtype=np.uint64) if want_tally else None
+        if pinned is not None:
+            cnt, ev = pinned
+        else:
+            cnt = np.zeros(nw, dtype=np.uint16)
+            ev = np.zeros(max(1024, int(1.2 * n_shots) + 4096), dtype=np.uint32)
+        n_ev = C.c_int64()
+        for _ in range(6):
+            rc = lib().qec_sampler_sample_events(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(cnt),
+                                                 _p(ev), C.c_int64(len(ev)), C.byref(n_ev), _p(tally))
+            if rc == QEC_ERR_OVERFLOW:
+                continue                       # deterministic RNG: re-run with the raised capacity
+            if rc == QEC_ERR_LIMIT and pinned is None and n_ev.value > len(ev):
+                ev = np.zeros(int(n_ev.value * max(1.0, nw * 32 / max(1, n_shots)) * 2) + 4096, dtype=np.uint32)
+                continue
+            break
+        _check(rc)
+        return cnt[:nw], ev[:n_ev.value], tally
 
     def variant(self) -> str:
         """kernel variant and draw scheme (results are reproducible per variant)"""

@@ -462,6 +462,36 @@ class FaultSampler {
     }
     return py::make_tuple(r, c, (uint64_t)n_zero);
   }
+  // bulk API, compact form: (word_cnt uint16[ceil(n/32)], events uint32[n_events], tally or None)
+  // of `n` fresh shots: the sampled faults (location << 14 | shot bit << 9 | digit), the words'
+  // events back to back -- see qec_sampler_sample_events
+  py::tuple sample_events(int64_t n, bool want_tally) {
+    const int64_t nw = (std::max<int64_t>(n, 0) + 31) / 32;
+    py::array_t<uint16_t> cnt((py::ssize_t)nw);
+    py::array_t<uint64_t> tally((py::ssize_t)QEC_TALLY_LEN(nc_));
+    std::vector<uint32_t> ev((size_t)std::max<int64_t>(1024, n + n / 4 + 4096));
+    int64_t n_ev = 0;
+    for (int attempt = 0;; ++attempt) {
+      int rc;
+      {
+        uint16_t *pc = cnt.mutable_data();
+        uint64_t *pt = want_tally ? tally.mutable_data() : nullptr;
+        py::gil_scoped_release nogil;
+        rc = qec_sampler_sample_events(h_, cursor_, n, pc, ev.data(), (int64_t)ev.size(), &n_ev, pt);
+      }
+      if (rc == QEC_ERR_OVERFLOW && attempt < 6) continue;  // same seed, same shots
+      if (rc == QEC_ERR_LIMIT && n_ev > (int64_t)ev.size() && attempt < 6) {
+        ev.resize((size_t)(2 * n_ev * std::max<int64_t>(1, nw * 32 / std::max<int64_t>(1, n)) + 4096));
+        continue;
+      }
+      check(rc);
+      break;
+    }
+    cursor_ += nw * 32;
+    py::array_t<uint32_t> e((py::ssize_t)n_ev);
+    if (n_ev) memcpy(e.mutable_data(), ev.data(), (size_t)n_ev * 4);
+    return py::make_tuple(cnt, e, want_tally ? py::object(tally) : py::none());
+  }
   std::string variant() const { return qec_sampler_variant(h_); }
   int64_t get_cursor() const { return cursor_; }
   void set_cursor(int64_t c) {
@@ -694,6 +724,7 @@ PYBIND11_MODULE(_c_analysis, module) {
       .def("sample_packed", &FaultSampler::sample_packed, py::arg("n"), py::arg("want_bits") = true,
            py::arg("want_tally") = false)
       .def("sample_counts", &FaultSampler::sample_counts, py::arg("n"))
+      .def("sample_events", &FaultSampler::sample_events, py::arg("n"), py::arg("want_tally") = false)
       .def("variant", &FaultSampler::variant)
       .def("get_cursor", &FaultSampler::get_cursor)
       .def("set_cursor", &FaultSampler::set_cursor);

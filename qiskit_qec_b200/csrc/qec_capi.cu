@@ -1065,6 +1065,7 @@ struct qec_sampler {
   uint32_t *d_slinf = nullptr;
   int last_cap = 0;  // event capacity of the kernel that served the latest launches
   std::string variant;  // qec_sampler_variant()
+  int ev_cap_hint = 0;  // qec_sampler_sample_events: event-row capacity learnt from an overflow
   // linear-response path (qec_linear.cu): the default when the circuit is eligible
   struct Lin {
     bool eligible = false;
@@ -1372,9 +1373,13 @@ static int sampler_plan_linear(qec_sampler *s) {
   int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0, lane_mode = 0;
   const char *lmode = std::getenv("QEC_B200_LIN_MODE");
   {
-    // half-word lane-stream variant (512-shot batches, 16 shots per lane, twice the warps): the
-    // default where it fits; QEC_B200_LIN_MODE=lanes keeps the 32-shot lanes below
-    const bool want16 = lmode ? !strcmp(lmode, "lanes16") : true;
+    // half-word lane-stream variant (512-shot batches, 16 shots per lane, two clbit rows per
+    // accumulator word): serves circuits with 255..~500 clbits, whose accumulators the 32-shot
+    // lanes below cannot hold.  Measured at d=5 (profiles/r02): 16 warps per SM instead of 9 and
+    // issue slots 70 % busy instead of 56 %, but 1.44x the instructions per shot (shorter lane
+    // streams are less balanced, the read-out un-interleaves two rows per word): 1.17 ms against
+    // 1.03 ms per 1e8 shots -- so the 32-shot lanes stay the default where they fit.
+    const bool want16 = lmode ? !strcmp(lmode, "lanes16") : c->nc > 254;
     const bool can16 = draw == 2 && ln.cls_uniform_all && maxlen_w <= 7 && f_lgb == 0 &&
                        ((long long)s->L << 9) < (1ll << 30);
     if (want16 && can16) {
@@ -1527,6 +1532,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.info2 = reinterpret_cast<const uint2 *>(ln.d_info2);
   d.fast = fast;
   d.lane_mode = lane_mode;
+  d.lanes_np = env_int("QEC_B200_LANES_NP", 2);  // (results do not depend on it: the lane's stream is sequential)
   d.lvl_prog = ln.d_lvl_prog; d.lvl_off = ln.d_lvl_off;
   d.n_lvl = (int)ln.lvl_off.size() - 1;
   d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
@@ -1583,19 +1589,51 @@ static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<ui
   }
   std::stable_sort(chains.begin(), chains.end(),
                    [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
-  struct WRow { int rowA, rowB, prev; bool next; };
+  // Two chains may share word-rows (A_k and B_k in one word) only if no single fault flips A_k
+  // and B_k together for any k: the kernel loads all words of a fault before it stores any.
+  // Greedy matching on that conflict relation; a chain without a partner keeps its words alone.
+  const size_t F0 = lists.size();
+  std::vector<int> chain_of(nc, -1), step_of(nc, 0);
+  for (size_t j = 0; j < chains.size(); ++j)
+    for (size_t k = 0; k < chains[j].size(); ++k) { chain_of[chains[j][k]] = (int)j; step_of[chains[j][k]] = (int)k; }
+  std::vector<std::vector<uint8_t>> conflict(chains.size(), std::vector<uint8_t>(chains.size(), 0));
+  for (size_t f = 0; f < F0; ++f)
+    for (size_t x = 0; x < lists[f].size(); ++x)
+      for (size_t y = x + 1; y < lists[f].size(); ++y) {
+        const int r1 = lists[f][x], r2 = lists[f][y];
+        if (step_of[r1] == step_of[r2]) conflict[chain_of[r1]][chain_of[r2]] = conflict[chain_of[r2]][chain_of[r1]] = 1;
+      }
+  struct WRow { int rowA, rowB, prev; bool nextA, nextB; };
   std::vector<WRow> wrows;
-  std::vector<uint32_t> off_of(nc, 0u);  // byte offset of clbit row inside a warp's accumulator
-  for (size_t j = 0; j < chains.size(); j += 2) {
-    const std::vector<int> &A = chains[j];
-    const std::vector<int> *B = j + 1 < chains.size() ? &chains[j + 1] : nullptr;
-    for (size_t k = 0; k < A.size(); ++k) {
-      const int w = (int)wrows.size();
-      const int rb = (B && k < B->size()) ? (*B)[k] : -1;
-      wrows.push_back({A[k], rb, k > 0 ? w - 1 : -1, k + 1 < A.size()});
-      off_of[A[k]] = (uint32_t)w * 128u;
-      if (rb >= 0) off_of[rb] = (uint32_t)w * 128u + 2u;
+  std::vector<uint32_t> off_of(nc, 0u);  // record entry of a clbit row: word-row * 128 | half * 16
+  std::vector<std::pair<int, int>> pairs;  // (chain A, chain B or -1), |A| >= |B|
+  {
+    std::vector<uint8_t> used(chains.size(), 0);
+    for (size_t j = 0; j < chains.size(); ++j) {
+      if (used[j]) continue;
+      used[j] = 1;
+      int partner = -1;
+      for (size_t j2 = j + 1; j2 < chains.size(); ++j2)
+        if (!used[j2] && !conflict[j][j2]) { used[j2] = 1; partner = (int)j2; break; }
+      pairs.emplace_back((int)j, partner);
     }
+  }
+  // word-rows in step-major order (step k of every pair, then step k + 1): the previous word-row
+  // of a chain is then a whole "generation" back, and the read-out trips fill up
+  {
+    std::vector<int> last(pairs.size(), -1);
+    for (size_t k = 0; !chains.empty() && k < chains[0].size(); ++k)
+      for (size_t pi = 0; pi < pairs.size(); ++pi) {
+        const std::vector<int> &A = chains[pairs[pi].first];
+        if (k >= A.size()) continue;
+        const std::vector<int> *B = pairs[pi].second >= 0 ? &chains[pairs[pi].second] : nullptr;
+        const int w = (int)wrows.size();
+        const int rb = (B && k < B->size()) ? (*B)[k] : -1;
+        wrows.push_back({A[k], rb, last[pi], k + 1 < A.size(), B && k + 1 < B->size()});
+        last[pi] = w;
+        off_of[A[k]] = (uint32_t)w * 128u;
+        if (rb >= 0) off_of[rb] = (uint32_t)w * 128u + 16u;
+      }
   }
   const uint32_t n_wrows = (uint32_t)wrows.size();
   if (n_wrows + 2u > 256u) return 0;  // (word-row index is one byte of the read-out program)
@@ -1633,7 +1671,8 @@ static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<ui
       for (int x : cur) {
         if (x < 0) { prog.push_back(zero | (zero << 8)); prog.push_back(0xFFFF0000u); continue; }
         const WRow &w = wrows[x];
-        prog.push_back((uint32_t)x | ((w.prev >= 0 ? (uint32_t)w.prev : zero) << 8) | (w.next ? (1u << 17) : 0u) | (1u << 18));
+        prog.push_back((uint32_t)x | ((w.prev >= 0 ? (uint32_t)w.prev : zero) << 8) | (w.nextA ? (1u << 17) : 0u) |
+                       (1u << 18) | (w.nextB ? (1u << 19) : 0u));
         prog.push_back((uint32_t)w.rowA | ((w.rowB >= 0 ? (uint32_t)w.rowB : 0xFFFFu) << 16));
       }
       cur.clear();
@@ -2078,8 +2117,10 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
       for (int64_t w = 0; w < n_words; ++w) {
         const uint32_t lo = fault_cnt[w] & 0xFFFFu, hi = fault_cnt[w] >> 16;
         uint32_t *e = fault_ev + (size_t)w * fault_cap;
-        if (lo + hi <= (uint32_t)fault_cap)
-          for (uint32_t k = 0; k < hi; ++k) e[lo + k] = e[fault_cap - 1 - k];
+        if (lo + hi <= (uint32_t)fault_cap) {  // (source and target may overlap: through a copy)
+          std::vector<uint32_t> back(e + fault_cap - hi, e + fault_cap);
+          for (uint32_t k = 0; k < hi; ++k) e[lo + k] = back[hi - 1 - k];
+        }
         fault_cnt[w] = lo + hi;
       }
     }
@@ -2101,6 +2142,123 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
       }
     }
   }
+  return 0;
+}
+
+// ---- compact sampler output: the faults themselves ------------------------------------------------
+// What the reference's sample() returns per shot is (labels, errors, outcome).  At p = 1e-3 a shot
+// carries 0.76 faults: its fault list (4 bytes per fault) is six times smaller than its packed
+// outcome row (nc / 8 bytes), and it is lossless -- labels and errors ARE the list, and the
+// outcome is the XOR of the faults' signatures (or one qec_propagate_batch call).  This entry
+// point moves only that across PCIe: per 32-shot word a 16-bit count, and one dense pool of
+// events (location << 14 | shot bit << 9 | digit; a word's events are contiguous, words in
+// order), compacted on the device from the kernels' fixed-capacity export rows, plus the tallies.
+extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                         uint16_t *word_cnt, uint32_t *events, int64_t events_cap,
+                                         int64_t *n_events, uint64_t *tally) {
+  int rc = sample_args(s, shot_lo, n_shots);
+  if (rc) return rc;
+  if (!word_cnt || !events || !n_events) return fail(QEC_ERR_INVALID, "null pointer");
+  qec_circuit *c = s->c;
+  const size_t tl = QEC_TALLY_LEN(c->nc);
+  *n_events = 0;
+  if (tally) memset(tally, 0, tl * 8);
+  if (n_shots == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const int64_t n_words = (n_shots + 31) / 32;
+  const double mu = std::max(s->mean_events, 1.0);
+  int cap = std::max(s->ev_cap_hint, ((int)std::ceil(mu + 8.0 * std::sqrt(mu) + 16.0) + 7) / 8 * 8);
+  if (cap > 65535) return fail(QEC_ERR_LIMIT, "more than 65535 events per 32-shot word");
+  const bool two_ended = s->lin.eligible && s->lin.l16;
+  // chunk: at most 128 MB of export rows per buffer
+  int64_t cw = std::max<int64_t>(((int64_t)128 << 20) / ((int64_t)cap * 4) / 1024 * 1024, 1024);
+  cw = std::min(cw, (n_words + 1023) / 1024 * 1024);
+  struct Buf { DevBuf cnt, ev, sums, ocnt, oev, misc; } buf[2];
+  cudaStream_t st[2];
+  cudaEvent_t kdone[2], tdone[2];
+  unsigned long long *h_total = nullptr;
+  if (cudaMallocHost((void **)&h_total, 4 * 8) != cudaSuccess) return fail(QEC_ERR_CUDA, "cudaMallocHost failed");
+  auto cleanup = [&]() {
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 2; ++i) {
+      buf[i].cnt.release(); buf[i].ev.release(); buf[i].sums.release(); buf[i].ocnt.release();
+      buf[i].oev.release(); buf[i].misc.release();
+      cudaEventDestroy(kdone[i]); cudaEventDestroy(tdone[i]);
+    }
+    cudaFreeHost(h_total);
+  };
+  for (int i = 0; i < 2; ++i) {
+    if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    st[i] = c->pipe_stream[i];
+    cudaEventCreateWithFlags(&kdone[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&tdone[i], cudaEventDisableTiming);
+  }
+  // event pool of a chunk: mean + 6 sigma of its total (checked below)
+  const double chunk_mu = mu * (double)cw;
+  const size_t pool = (size_t)(chunk_mu + 6.0 * std::sqrt(chunk_mu) + 4096.0);
+  for (int i = 0; i < 2; ++i) {
+    if ((rc = buf[i].cnt.ensure((size_t)cw * 4)) || (rc = buf[i].ev.ensure((size_t)cw * cap * 4)) ||
+        (rc = buf[i].sums.ensure((size_t)(cw / 1024 + 1) * 4)) || (rc = buf[i].ocnt.ensure((size_t)cw * 2)) ||
+        (rc = buf[i].oev.ensure(pool * 4)) || (rc = buf[i].misc.ensure(16))) {
+      cleanup();
+      return rc;
+    }
+  }
+  if (tally) {
+    if ((rc = c->tally.ensure(tl * 8))) { cleanup(); return rc; }
+    cudaMemsetAsync(c->tally.p, 0, tl * 8, 0);
+  }
+  cudaStreamSynchronize(0);
+  uint64_t *d_tally = tally ? (uint64_t *)c->tally.p : nullptr;
+  const int64_t n_chunks = (n_words + cw - 1) / cw;
+  auto launch = [&](int64_t k) -> int {
+    const int i = (int)(k & 1);
+    const int64_t w0 = k * cw, words = std::min(cw, n_words - w0);
+    const int64_t shots = std::min<int64_t>(n_shots - 32 * w0, 32 * words);
+    if (k > 0) cudaStreamWaitEvent(st[i], kdone[i ^ 1], 0);  // kernels of successive chunks share scratch
+    cudaMemsetAsync(buf[i].cnt.p, 0, (size_t)words * 4, st[i]);
+    cudaMemsetAsync(buf[i].misc.p, 0, 16, st[i]);
+    QecSampleExport X{(uint32_t *)buf[i].cnt.p, (uint32_t *)buf[i].ev.p, cap};
+    const int r = sample_launch(s, shot_lo + 32 * w0, shots, nullptr, d_tally, X, st[i]);
+    if (r) return r;
+    qec_launch_event_compact(st[i], (const uint32_t *)buf[i].cnt.p, (const uint32_t *)buf[i].ev.p, words,
+                             two_ended ? 1 : 0, cap, (uint32_t *)buf[i].sums.p, (uint32_t *)buf[i].misc.p + 2,
+                             (unsigned long long *)buf[i].misc.p, (uint16_t *)buf[i].ocnt.p, (uint32_t *)buf[i].oev.p,
+                             (unsigned long long)pool);
+    cudaEventRecord(kdone[i], st[i]);
+    cudaMemcpyAsync(h_total + 2 * i, buf[i].misc.p, 16, cudaMemcpyDeviceToHost, st[i]);
+    cudaEventRecord(tdone[i], st[i]);
+    return 0;
+  };
+  if ((rc = launch(0))) { cleanup(); return rc; }
+  int64_t run = 0;
+  int err = 0;
+  for (int64_t k = 0; k < n_chunks && !err; ++k) {
+    const int i = (int)(k & 1);
+    if (k + 1 < n_chunks && (rc = launch(k + 1))) { err = rc; break; }
+    if (cudaEventSynchronize(tdone[i]) != cudaSuccess) { err = QEC_ERR_CUDA; break; }
+    const int64_t total = (int64_t)h_total[2 * i];
+    const uint32_t worst = (uint32_t)(h_total[2 * i + 1] & 0xFFFFFFFFu);
+    const int64_t w0 = k * cw, words = std::min(cw, n_words - w0);
+    if (worst > (uint32_t)cap || (size_t)total > pool) {  // (astronomically rare with the sizing above)
+      s->ev_cap_hint = std::max<int>(2 * cap, (int)worst + 8);
+      err = QEC_ERR_OVERFLOW;
+      break;
+    }
+    if (run + total > events_cap) { *n_events = run + total; err = QEC_ERR_LIMIT; break; }
+    cudaMemcpyAsync(events + run, buf[i].oev.p, (size_t)total * 4, cudaMemcpyDeviceToHost, st[i]);
+    cudaMemcpyAsync(word_cnt + w0, buf[i].ocnt.p, (size_t)words * 2, cudaMemcpyDeviceToHost, st[i]);
+    run += total;
+  }
+  const cudaError_t e0 = cudaStreamSynchronize(st[0]), e1 = cudaStreamSynchronize(st[1]);
+  if (!err && tally) cudaMemcpy(tally, c->tally.p, tl * 8, cudaMemcpyDeviceToHost);
+  cleanup();
+  if (err == QEC_ERR_OVERFLOW) return fail(QEC_ERR_OVERFLOW, "event rows overflowed; re-run (capacity has been raised)");
+  if (err == QEC_ERR_LIMIT) return fail(QEC_ERR_LIMIT, "event pool too small: more than %lld events", (long long)events_cap);
+  if (err) return err == QEC_ERR_CUDA ? fail(QEC_ERR_CUDA, "CUDA error in qec_sampler_sample_events") : err;
+  if (e0 != cudaSuccess || e1 != cudaSuccess) return fail(QEC_ERR_CUDA, "CUDA error %s", cudaGetErrorString(e0 != cudaSuccess ? e0 : e1));
+  if ((rc = sampler_check(s))) return rc;
+  *n_events = run;
   return 0;
 }
 

@@ -141,6 +141,7 @@ struct QecLinDev {
   // lane-stream variant (k_sample_lanes): lgb = 10, lane = word column, no shared-memory atomics;
   // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
   int lane_mode;
+  int lanes_np;             // Philox calls (two candidates each) per loop trip of the lane-stream kernel: 2, 3 or 4
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
   // CTA variant with signatures in the time-difference basis: rows with a previous row, grouped by
   // their depth in the chain (lvl_off[n_lvl + 1] into lvl_prog; entry = row | previous row << 16);
@@ -194,7 +195,7 @@ struct QecLanes16Dev {
   const uint32_t *info;     // [L] first fault of sorted location | number of Paulis << 21
   const uint16_t *recidx;   // [n_faults] record of fault (sorted location, digit)
   const uint4 *rec;         // [n_rec] eight uint16: 7 offsets, spare
-  const uint32_t *prog;     // [4 n_steps][2] {word-row | previous << 8 | has next << 17 | valid << 18,
+  const uint32_t *prog;     // [4 n_steps][2] {word-row | previous << 8 | row A has next << 17 | valid << 18 | row B has next << 19,
                             //                 clbit of row A | clbit of row B << 16 (0xFFFF: none)}
   const uint32_t *slloc;    // [L] original location index (fault export)
   uint32_t info_bytes, recidx_bytes, rec_bytes, prog_bytes;

@@ -323,6 +323,113 @@ k_hist_compact(const unsigned long long *__restrict__ keys, const unsigned long 
 }
 
 // ------------------------------------------------------------------------------------------
+// Compaction of the sampler's fault export: per 32-shot word a fixed-capacity event row
+// ev[w][cap] and a count (two_ended: the half-word lane-stream kernel fills a row from both
+// ends, count = front | back << 16) -> one dense pool, the words' events back to back, plus a
+// 16-bit count per word.  Three small launches per chunk: block sums, scan of the block sums,
+// copy.  A block covers 1024 words.
+#define QEC_EVC_T 256
+#define QEC_EVC_WPB 1024
+__device__ __forceinline__ uint32_t evc_total(uint32_t c, int two_ended) {
+  return two_ended ? (c & 0xFFFFu) + (c >> 16) : c;
+}
+__global__ void __launch_bounds__(QEC_EVC_T)
+k_ev_block_sums(const uint32_t *__restrict__ cnt, const long long n_words, const int two_ended, const int cap,
+                uint32_t *__restrict__ block_sums, uint32_t *__restrict__ overflow) {
+  __shared__ uint32_t part[QEC_EVC_T / 32];
+  const long long w0 = (long long)blockIdx.x * QEC_EVC_WPB;
+  uint32_t sum = 0, mx = 0;
+  for (int j = threadIdx.x; j < QEC_EVC_WPB; j += QEC_EVC_T) {
+    const long long w = w0 + j;
+    const uint32_t t = w < n_words ? evc_total(cnt[w], two_ended) : 0u;
+    sum += t;
+    mx = max(mx, t);
+  }
+  sum = __reduce_add_sync(0xFFFFFFFFu, sum);
+  mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+  if ((threadIdx.x & 31) == 0) {
+    part[threadIdx.x >> 5] = sum;
+    if (mx > (uint32_t)cap) atomicMax(overflow, mx);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int k = 0; k < QEC_EVC_T / 32; ++k) t += part[k];
+    block_sums[blockIdx.x] = t;
+  }
+}
+// one block: exclusive scan of the block sums in place, grand total out
+__global__ void __launch_bounds__(1024)
+k_ev_scan_blocks(uint32_t *__restrict__ block_sums, const int n_blocks, unsigned long long *__restrict__ total) {
+  __shared__ unsigned long long warp_tot[32];
+  __shared__ unsigned long long carry;
+  if (threadIdx.x == 0) carry = 0ull;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n_blocks; base += 1024) {
+    const int i = base + (int)threadIdx.x;
+    const unsigned long long v = i < n_blocks ? block_sums[i] : 0u;
+    unsigned long long incl = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if ((int)lane >= o) incl += t;
+    }
+    if (lane == 31u) warp_tot[warp] = incl;
+    __syncthreads();
+    unsigned long long before = carry;
+    for (unsigned k = 0; k < warp; ++k) before += warp_tot[k];
+    if (i < n_blocks) block_sums[i] = (uint32_t)(before + incl - v);  // (chunk totals stay below 2^32)
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = before + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+__global__ void __launch_bounds__(QEC_EVC_T)
+k_ev_compact(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ ev, const long long n_words,
+             const int two_ended, const int cap, const uint32_t *__restrict__ block_off,
+             uint16_t *__restrict__ out_cnt, uint32_t *__restrict__ out_ev, const unsigned long long pool_cap) {
+  __shared__ uint32_t warp_tot[QEC_EVC_T / 32];
+  const long long w0 = (long long)blockIdx.x * QEC_EVC_WPB;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t run = block_off[blockIdx.x];
+  // thread t owns words w0 + 4 t .. w0 + 4 t + 3 (consecutive words, consecutive pool ranges)
+  uint32_t c[4], tot[4], mine = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const long long w = w0 + 4 * (long long)threadIdx.x + j;
+    c[j] = w < n_words ? cnt[w] : 0u;
+    tot[j] = min(evc_total(c[j], two_ended), (uint32_t)cap);
+    mine += tot[j];
+  }
+  uint32_t incl = mine;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  if (lane == 31u) warp_tot[warp] = incl;
+  __syncthreads();
+  for (unsigned k = 0; k < warp; ++k) run += warp_tot[k];
+  uint32_t o = run + incl - mine;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const long long w = w0 + 4 * (long long)threadIdx.x + j;
+    if (w >= n_words) break;
+    out_cnt[w] = (uint16_t)tot[j];
+    if ((unsigned long long)o + tot[j] > pool_cap) break;  // (the host sees total > pool and re-runs)
+    const uint32_t *row = ev + w * cap;
+    if (two_ended) {
+      const uint32_t lo = min(c[j] & 0xFFFFu, tot[j]), hi = tot[j] - lo;
+      for (uint32_t k = 0; k < lo; ++k) out_ev[o + k] = row[k];
+      for (uint32_t k = 0; k < hi; ++k) out_ev[o + lo + k] = row[cap - 1 - k];
+    } else {
+      for (uint32_t k = 0; k < tot[j]; ++k) out_ev[o + k] = row[k];
+    }
+    o += tot[j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Integer-pipe roofline denominator: 8 independent LOP3 chains per thread, no memory.  Every
 // chain step is ONE `lop3.b32` written as inline PTX (asm volatile), so that the ops counted by
 // qec_measure_int_peak are the LOP3 instructions the SM executes: ptxas neither merges nor
@@ -422,6 +529,17 @@ void qec_launch_hist_compact(cudaStream_t stream, const unsigned long long *keys
   if (blocks > 148 * 8) blocks = 148 * 8;
   k_hist_compact<<<(int)blocks, 256, 0, stream>>>(keys, counts, rows, table_cap, rw, out_keys,
                                                     out_counts, out_rows, n_out);
+}
+
+void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const uint32_t *ev, long long n_words,
+                              int two_ended, int cap, uint32_t *block_sums, uint32_t *overflow,
+                              unsigned long long *total, uint16_t *out_cnt, uint32_t *out_ev,
+                              unsigned long long pool_cap) {
+  const int n_blocks = (int)((n_words + QEC_EVC_WPB - 1) / QEC_EVC_WPB);
+  if (n_blocks < 1) return;
+  k_ev_block_sums<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, n_words, two_ended, cap, block_sums, overflow);
+  k_ev_scan_blocks<<<1, 1024, 0, stream>>>(block_sums, n_blocks, total);
+  k_ev_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, ev, n_words, two_ended, cap, block_sums, out_cnt, out_ev, pool_cap);
 }
 
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink) {

@@ -46,6 +46,11 @@ void qec_launch_hist_compact(cudaStream_t stream, const unsigned long long *keys
                              long long table_cap, int rw, unsigned long long *out_keys,
                              unsigned long long *out_counts, uint32_t *out_rows,
                              unsigned long long *n_out);
+// sampler fault export: fixed-capacity event rows -> dense pool (block_sums: one word per 1024 lane words)
+void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const uint32_t *ev, long long n_words,
+                              int two_ended, int cap, uint32_t *block_sums, uint32_t *overflow,
+                              unsigned long long *total, uint16_t *out_cnt, uint32_t *out_ev,
+                              unsigned long long pool_cap);
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink);
 size_t qec_kernel_smem_bytes(int kind, int nq, int nc, int T, uint32_t B, uint32_t K1);
 int qec_kernel_set_smem_attr(int kind, int order, size_t smem);

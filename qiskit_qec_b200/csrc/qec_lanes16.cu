@@ -10,8 +10,9 @@
 // d=5, 16 warps per SM.  What changes with it:
 //   * batch = 512 shots per warp; lane stream over slot = sorted location * 16 + shot bit,
 //     Philox counter = (batch lo, batch hi, call * 32 + lane, 0x4E000000);
-//   * records are 16-bit byte offsets applied with ld/st.shared.u16 (both halves of a word
-//     belong to the same lane: still bank = lane);
+//   * records are 16-bit entries (word-row * 128 | half * 16) applied with 32-bit load / xor /
+//     store, the shot mask shifted into the entry's half (both halves of a word belong to the
+//     same lane: still bank = lane); the host pairs only rows that no fault flips together;
 //   * the read-out un-interleaves the two rows of a word-row with byte permutes and stores 64
 //     bytes per clbit row and batch (two full sectors);
 //   * per-clbit tallies are one CTA-wide row updated with red.shared.add by one lane per row;
@@ -45,6 +46,9 @@ __device__ __forceinline__ uint4 l16_ld128(uint32_t addr) {
 __device__ __forceinline__ void l16_st128(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
+__device__ __forceinline__ void l16_st(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t l16_ldh(uint32_t addr) {
   uint32_t v;
   asm volatile("{ .reg .u16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(addr) : "memory");
@@ -57,18 +61,32 @@ __device__ __forceinline__ void l16_red_add(uint32_t addr, uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
-// One candidate of a lane: seven 16-bit load / xor / store triples at the record's offsets in
-// the lane's own column (absent entries name the dummy word-row; a lane without a fault XORs a
-// zero mask).  The (row, half) targets of one fault are distinct: all loads first.
+// One candidate of a lane: seven load / xor / store triples on the lane's own column.  A record
+// entry is 16 bits: word-row * 128 | half * 16 -- bits 15..7 address the word-row, and the low five
+// bits ARE the shift that moves the shot mask into the entry's half-word (0 or 16: a wrapping
+// shift reads exactly those bits), so there is no half test.  32-bit accesses on purpose: with
+// ld/st.shared.u16 the same kernel ran 3.6x slower (sub-word shared-memory stores; measured,
+// profiles/r02).  Absent entries name the dummy word-row; a lane without a fault XORs a zero mask.
+// All loads come first, so two entries of one fault must never share a word: the host pairs only
+// rows that no single fault flips together (sampler_plan_lanes16).
+__device__ __forceinline__ uint32_t l16_shl_wrap(uint32_t v, uint32_t n) {
+  uint32_t r;
+  asm("shf.l.wrap.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(0u), "r"(v), "r"(n));
+  return r;
+}
 __device__ __forceinline__ void l16_apply(const uint4 q, const uint32_t msk, const uint32_t lane_acc) {
-  const uint32_t a0 = lane_acc + (q.x & 0xFFFFu), a1 = lane_acc + (q.x >> 16);
-  const uint32_t a2 = lane_acc + (q.y & 0xFFFFu), a3 = lane_acc + (q.y >> 16);
-  const uint32_t a4 = lane_acc + (q.z & 0xFFFFu), a5 = lane_acc + (q.z >> 16);
-  const uint32_t a6 = lane_acc + (q.w & 0xFFFFu);
-  const uint32_t v0 = l16_ldh(a0), v1 = l16_ldh(a1), v2 = l16_ldh(a2), v3 = l16_ldh(a3),
-                 v4 = l16_ldh(a4), v5 = l16_ldh(a5), v6 = l16_ldh(a6);
-  l16_sth(a0, v0 ^ msk); l16_sth(a1, v1 ^ msk); l16_sth(a2, v2 ^ msk); l16_sth(a3, v3 ^ msk);
-  l16_sth(a4, v4 ^ msk); l16_sth(a5, v5 ^ msk); l16_sth(a6, v6 ^ msk);
+  // fields: q.x lo, q.x hi, q.y lo, q.y hi, q.z lo, q.z hi, q.w lo (q.w hi: number of entries)
+  const uint32_t f1 = q.x >> 16, f3 = q.y >> 16, f5 = q.z >> 16;
+  const uint32_t a0 = lane_acc + (q.x & 0xFF80u), a1 = lane_acc + (f1 & 0xFF80u);
+  const uint32_t a2 = lane_acc + (q.y & 0xFF80u), a3 = lane_acc + (f3 & 0xFF80u);
+  const uint32_t a4 = lane_acc + (q.z & 0xFF80u), a5 = lane_acc + (f5 & 0xFF80u);
+  const uint32_t a6 = lane_acc + (q.w & 0xFF80u);
+  const uint32_t v0 = l16_ld(a0), v1 = l16_ld(a1), v2 = l16_ld(a2), v3 = l16_ld(a3),
+                 v4 = l16_ld(a4), v5 = l16_ld(a5), v6 = l16_ld(a6);
+  l16_st(a0, v0 ^ l16_shl_wrap(msk, q.x)); l16_st(a1, v1 ^ l16_shl_wrap(msk, f1));
+  l16_st(a2, v2 ^ l16_shl_wrap(msk, q.y)); l16_st(a3, v3 ^ l16_shl_wrap(msk, f3));
+  l16_st(a4, v4 ^ l16_shl_wrap(msk, q.z)); l16_st(a5, v5 ^ l16_shl_wrap(msk, f5));
+  l16_st(a6, v6 ^ l16_shl_wrap(msk, q.w));
 }
 
 struct L16Planes {  // faults-per-shot counters of a lane's 16 shots, six bit planes
@@ -187,7 +205,8 @@ __device__ __forceinline__ uint32_t l16_readout(const QecOutDev &O, const uint32
     for (int u = 0; u < QEC_L16_UNROLL; ++u) {
       v[u].x ^= pv[u].x; v[u].y ^= pv[u].y; v[u].z ^= pv[u].z; v[u].w ^= pv[u].w;
       l16_st128(ap[u], 0u, 0u, 0u, 0u);
-      const uint32_t keep = (e[u].x & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next word-row of the chains needs this one
+      // the next word-row of the chains needs this one: per half (chain B may end before chain A)
+      const uint32_t keep = ((e[u].x & 0x20000u) ? 0x0000FFFFu : 0u) | ((e[u].x & 0x80000u) ? 0xFFFF0000u : 0u);
       l16_st128(a[u], v[u].x & keep, v[u].y & keep, v[u].z & keep, v[u].w & keep);
       const uint32_t A01 = __byte_perm(v[u].x, v[u].y, 0x5410u), A23 = __byte_perm(v[u].z, v[u].w, 0x5410u);
       const uint32_t B01 = __byte_perm(v[u].x, v[u].y, 0x7632u), B23 = __byte_perm(v[u].z, v[u].w, 0x7632u);
@@ -224,7 +243,7 @@ __device__ __forceinline__ uint32_t l16_readout(const QecOutDev &O, const uint32
         if (k == 0u && (e[u].x & 0x40000u)) {
           const uint32_t rowA = e[u].y & 0xFFFFu, rowB = e[u].y >> 16;
           if (c & 0xFFFFu) l16_red_add(tal_s + (rowA << 2), c & 0xFFFFu);
-          if (c >> 16) l16_red_add(tal_s + (rowB << 2), c >> 16);  // (row B absent: its half stays 0)
+          if ((c >> 16) && rowB != 0xFFFFu) l16_red_add(tal_s + (rowB << 2), c >> 16);
         }
       }
     }

@@ -794,12 +794,7 @@ __device__ __forceinline__ void lin_copy_records(uint32_t *dst, const uint2 *src
 // One candidate of a lane.  Absent record entries name the dummy row nc and a lane without a
 // fault XORs a zero mask (into whatever rows location 0's record names), so the seven load /
 // xor / store triples need no predicate.
-template <bool EXPORT>
-__device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p, const bool ok,
-                                            const uint2 q, const uint32_t d, const uint32_t sl,
-                                            const uint32_t lane_acc, const int lane,
-                                            const long long base_shot, const long long w_lo,
-                                            const QecSampleExport &X) {
+__device__ __forceinline__ void lanes_apply(const uint32_t p, const bool ok, const uint2 q, const uint32_t lane_acc) {
   const uint32_t bit = p & 31u, msk = ok ? 1u << bit : 0u;
   const uint32_t a0 = lane_acc + (__byte_perm(q.x, 0u, 0x4441u) << 7);
   const uint32_t a1 = lane_acc + (__byte_perm(q.x, 0u, 0x4442u) << 7);
@@ -813,14 +808,6 @@ __device__ __forceinline__ void lanes_apply(const QecLinDev &S, const uint32_t p
                  v5 = ld_s(a5), v6 = ld_s(a6);
   st_s(a0, v0 ^ msk); st_s(a1, v1 ^ msk); st_s(a2, v2 ^ msk); st_s(a3, v3 ^ msk);
   st_s(a4, v4 ^ msk); st_s(a5, v5 ^ msk); st_s(a6, v6 ^ msk);
-  if (EXPORT) {
-    if (ok) {
-      const uint32_t shot = ((uint32_t)lane << 5) | bit;
-      const long long wr = ((base_shot + shot) >> 5) - w_lo;
-      const uint32_t k = atomicAdd(X.cnt + wr, 1u);
-      if (k < (uint32_t)X.cap) X.ev[wr * X.cap + k] = (S.slloc[sl] << 14) | (bit << 9) | d;
-    }
-  }
 }
 
 // Read-out of a lane-owned accumulator acc[row][32 word columns] (batch = 32 output words
@@ -925,7 +912,7 @@ __device__ __forceinline__ void planes_add(LanePlanes &P, uint32_t c) {
   }
 }
 
-template <bool TALLY, bool BITS, bool EXPORT>
+template <bool TALLY, bool BITS, bool EXPORT, int NP>
 __global__ void __launch_bounds__(512, 1)
 k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
                const QecSampleExport X) {
@@ -955,6 +942,8 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   const uint32_t rec_s = (uint32_t)__cvta_generic_to_shared(rec);
   const uint32_t end = (uint32_t)S.L << 5;
   const float C = S.gapC;
+  // no 32-bit draw reaches the clamp when 32.5 C stays below it (-log2 u <= 32): skip the test
+  const bool g_noclamp = C * 32.5f < (float)QEC_GAP_CAP;
   unsigned long long nz_shots = 0;
   uint32_t h1 = 0, h2 = 0, h3 = 0, hx = 0;  // shots with exactly 1 / 2 / 3 / at least 4 faults
   const long long b0 = shot_lo >> QEC_LANES_LGB, b1 = (shot_lo + n_shots - 1) >> QEC_LANES_LGB;
@@ -972,53 +961,81 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
     const uint32_t slo = shot_lo > base_shot ? (uint32_t)(shot_lo - base_shot) : 0u;
     const uint32_t shi = (uint32_t)min(1024ll, shot_lo + n_shots - base_shot);
     const uint32_t nsh = shi - slo, lane_sh = ((uint32_t)lane << 5) - slo;
+    const bool full = nsh == 1024u;  // every shot of the batch is inside the requested range
     const uint32_t blo = (uint32_t)b, bhi = (uint32_t)((unsigned long long)b >> 32);
 
     // ---- the lane's fault stream
     LanePlanes P = {0u, 0u, 0u, 0u, 0u, 0u};
     uint32_t pos = 0xFFFFFFFFu;  // -1; saturates at `end`
-    // Two Philox calls (four candidates) per trip, software-pipelined: the next trip's Philox
-    // and gaps do not depend on the position, so they are computed while this trip's candidates
-    // wait on shared memory (four independent dependency chains per warp instead of two).
-    QecPhilox ra = qec_philox_rk(blo, bhi, (uint32_t)lane, 0x4D000000u, S.rk);
-    QecPhilox rb = qec_philox_rk(blo, bhi, 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-    uint32_t g0 = qec_gap_len(ra.c[0], C), g1 = qec_gap_len(ra.c[2], C);
-    uint32_t g2 = qec_gap_len(rb.c[0], C), g3 = qec_gap_len(rb.c[2], C);
-    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); it += 2u) {
-      const QecPhilox na = qec_philox_rk(blo, bhi, (it + 2u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      const QecPhilox nb = qec_philox_rk(blo, bhi, (it + 3u) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      const bool has0 = g0 < QEC_GAP_CAP, has1 = g1 < QEC_GAP_CAP, has2 = g2 < QEC_GAP_CAP, has3 = g3 < QEC_GAP_CAP;
-      const uint32_t p0 = pos + g0 + (has0 ? 1u : 0u), p1 = p0 + g1 + (has1 ? 1u : 0u);
-      const uint32_t p2 = p1 + g2 + (has2 ? 1u : 0u), p3 = p2 + g3 + (has3 ? 1u : 0u);
+    uint32_t xk = 0;
+    const long long xw = (b << 5) + lane - w_lo;  // the lane's word in the export arrays
+    const bool xin = EXPORT && xw >= 0 && xw < O.n_words;
+    uint32_t *xrow = EXPORT ? X.ev + (xin ? xw : 0) * X.cap : nullptr;
+    // NP Philox calls (2 NP candidates) per trip, software-pipelined: the next trip's Philox and
+    // gaps do not depend on the position, so they are computed while this trip's candidates wait
+    // on shared memory (2 NP independent dependency chains per warp).
+    QecPhilox rr[NP];
+    uint32_t gg[2 * NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) {
+      rr[c] = qec_philox_rk(blo, bhi, (uint32_t)c * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+      gg[2 * c] = qec_gap_len(rr[c].c[0], C);
+      gg[2 * c + 1] = qec_gap_len(rr[c].c[2], C);
+    }
+    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); it += NP) {
+      QecPhilox nr[NP];
+#pragma unroll
+      for (int c = 0; c < NP; ++c)
+        nr[c] = qec_philox_rk(blo, bhi, (it + NP + (uint32_t)c) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
       // (pos + 1 <= end: the lane is still inside its stream; positions stay below 2^27 + end)
       const bool live = pos + 1u <= end;
-      const bool ok0 = live && has0 && p0 < end && (lane_sh + (p0 & 31u)) < nsh;
-      const bool ok1 = live && has1 && p1 < end && (lane_sh + (p1 & 31u)) < nsh;
-      const bool ok2 = live && has2 && p2 < end && (lane_sh + (p2 & 31u)) < nsh;
-      const bool ok3 = live && has3 && p3 < end && (lane_sh + (p3 & 31u)) < nsh;
-      pos = live ? min(p3, end) : end;
-      const uint32_t sl0 = ok0 ? p0 >> 5 : 0u, sl1 = ok1 ? p1 >> 5 : 0u;
-      const uint32_t sl2 = ok2 ? p2 >> 5 : 0u, sl3 = ok3 ? p3 >> 5 : 0u;
-      const uint32_t i0 = ld_s(info2_s + (sl0 << 2)), i1 = ld_s(info2_s + (sl1 << 2));
-      const uint32_t i2 = ld_s(info2_s + (sl2 << 2)), i3 = ld_s(info2_s + (sl3 << 2));
-      const uint32_t d0 = __umulhi(ra.c[1], i0 >> 21), d1 = __umulhi(ra.c[3], i1 >> 21);
-      const uint32_t d2 = __umulhi(rb.c[1], i2 >> 21), d3 = __umulhi(rb.c[3], i3 >> 21);
-      const uint2 q0 = ld_s64(rec_s + (((i0 & 0x1FFFFFu) + d0) << 3)), q1 = ld_s64(rec_s + (((i1 & 0x1FFFFFu) + d1) << 3));
-      const uint2 q2 = ld_s64(rec_s + (((i2 & 0x1FFFFFu) + d2) << 3)), q3 = ld_s64(rec_s + (((i3 & 0x1FFFFFu) + d3) << 3));
-      const uint32_t n0 = qec_gap_len(na.c[0], C), n1 = qec_gap_len(na.c[2], C);
-      const uint32_t n2 = qec_gap_len(nb.c[0], C), n3 = qec_gap_len(nb.c[2], C);
-      lanes_apply<EXPORT>(S, p0, ok0, q0, d0, sl0, lane_acc, lane, base_shot, w_lo, X);
-      lanes_apply<EXPORT>(S, p1, ok1, q1, d1, sl1, lane_acc, lane, base_shot, w_lo, X);
-      lanes_apply<EXPORT>(S, p2, ok2, q2, d2, sl2, lane_acc, lane, base_shot, w_lo, X);
-      lanes_apply<EXPORT>(S, p3, ok3, q3, d3, sl3, lane_acc, lane, base_shot, w_lo, X);
-      if (TALLY) {
-        planes_add(P, ok0 ? 1u << (p0 & 31u) : 0u);
-        planes_add(P, ok1 ? 1u << (p1 & 31u) : 0u);
-        planes_add(P, ok2 ? 1u << (p2 & 31u) : 0u);
-        planes_add(P, ok3 ? 1u << (p3 & 31u) : 0u);
+      uint32_t pp[2 * NP], sl[2 * NP], dd[2 * NP];
+      bool ok[2 * NP];
+      uint2 qq[2 * NP];
+      uint32_t run = pos;
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) {
+        const bool has = g_noclamp || gg[j] < QEC_GAP_CAP;
+        run += gg[j] + (has ? 1u : 0u);
+        pp[j] = run;
+        ok[j] = live && has && run < end && (full || (lane_sh + (run & 31u)) < nsh);
+        sl[j] = ok[j] ? run >> 5 : 0u;
       }
-      ra = na; rb = nb; g0 = n0; g1 = n1; g2 = n2; g3 = n3;
+      pos = live ? min(run, end) : end;
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) {
+        const uint32_t inf = ld_s(info2_s + (sl[j] << 2));
+        dd[j] = __umulhi(rr[j >> 1].c[(j & 1) * 2 + 1], inf >> 21);
+        qq[j] = ld_s64(rec_s + (((inf & 0x1FFFFFu) + dd[j]) << 3));
+      }
+      uint32_t ng[2 * NP];
+#pragma unroll
+      for (int c = 0; c < NP; ++c) {
+        ng[2 * c] = qec_gap_len(nr[c].c[0], C);
+        ng[2 * c + 1] = qec_gap_len(nr[c].c[2], C);
+      }
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) lanes_apply(pp[j], ok[j], qq[j], lane_acc);
+      if (EXPORT) {
+        // the lane owns its 32-shot word: events go to the word's row in stream order, the count
+        // stays in a register (no atomics)
+#pragma unroll
+        for (int j = 0; j < 2 * NP; ++j)
+          if (ok[j]) {
+            if (xk < (uint32_t)X.cap) xrow[xk] = (S.slloc[sl[j]] << 14) | ((pp[j] & 31u) << 9) | dd[j];
+            ++xk;
+          }
+      }
+      if (TALLY) {
+#pragma unroll
+        for (int j = 0; j < 2 * NP; ++j) planes_add(P, ok[j] ? 1u << (pp[j] & 31u) : 0u);
+      }
+#pragma unroll
+      for (int c = 0; c < NP; ++c) rr[c] = nr[c];
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) gg[j] = ng[j];
     }
+    if (EXPORT && xin) X.cnt[xw] = xk;
     __syncwarp();
 
     // ---- read-out (lanes_readout): four rows per pass, lane = (row of the pass, 4-word piece)
@@ -1250,10 +1267,12 @@ int qec_lin_set_smem_attr(size_t smem) {
   QEC_SET((k_sample_lin<false, true>)) QEC_SET((k_sample_lin<false, false>))
   QEC_SET((k_sample_linw<true, true, false>)) QEC_SET((k_sample_linw<true, false, false>))
   QEC_SET((k_sample_linw<false, true, false>)) QEC_SET((k_sample_linw<false, false, false>))
-  QEC_SET((k_sample_lanes<true, true, false>)) QEC_SET((k_sample_lanes<true, false, false>))
-  QEC_SET((k_sample_lanes<false, true, false>)) QEC_SET((k_sample_lanes<false, false, false>))
-  QEC_SET((k_sample_lanes<true, true, true>)) QEC_SET((k_sample_lanes<true, false, true>))
-  QEC_SET((k_sample_lanes<false, true, true>)) QEC_SET((k_sample_lanes<false, false, true>))
+#define QEC_SETL(NP) QEC_SET((k_sample_lanes<true, true, false, NP>)) QEC_SET((k_sample_lanes<true, false, false, NP>)) \
+  QEC_SET((k_sample_lanes<false, true, false, NP>)) QEC_SET((k_sample_lanes<false, false, false, NP>)) \
+  QEC_SET((k_sample_lanes<true, true, true, NP>)) QEC_SET((k_sample_lanes<true, false, true, NP>)) \
+  QEC_SET((k_sample_lanes<false, true, true, NP>)) QEC_SET((k_sample_lanes<false, false, true, NP>))
+  QEC_SETL(2) QEC_SETL(3) QEC_SETL(4)
+#undef QEC_SETL
   QEC_SET((k_sample_linw<true, true, true>)) QEC_SET((k_sample_linw<true, false, true>))
   QEC_SET((k_sample_linw<false, true, true>)) QEC_SET((k_sample_linw<false, false, true>))
 #undef QEC_SET
@@ -1265,16 +1284,22 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
                            const QecSampleExport &X) {
   const bool t = O.tally != nullptr, b = O.bits != nullptr;
 #define QEC_GO(K) K<<<cfg.grid, cfg.block, cfg.smem, stream>>>(O, S, shot_lo, n_shots, X)
-  if (S.lane_mode && X.cnt) {
-    if (t && b) QEC_GO((k_sample_lanes<true, true, true>));
-    else if (t) QEC_GO((k_sample_lanes<true, false, true>));
-    else if (b) QEC_GO((k_sample_lanes<false, true, true>));
-    else QEC_GO((k_sample_lanes<false, false, true>));
-  } else if (S.lane_mode) {
-    if (t && b) QEC_GO((k_sample_lanes<true, true, false>));
-    else if (t) QEC_GO((k_sample_lanes<true, false, false>));
-    else if (b) QEC_GO((k_sample_lanes<false, true, false>));
-    else QEC_GO((k_sample_lanes<false, false, false>));
+  if (S.lane_mode) {
+    const bool x = X.cnt != nullptr;
+#define QEC_GOL(NP)                                                          \
+  if (x) {                                                                   \
+    if (t && b) QEC_GO((k_sample_lanes<true, true, true, NP>));              \
+    else if (t) QEC_GO((k_sample_lanes<true, false, true, NP>));             \
+    else if (b) QEC_GO((k_sample_lanes<false, true, true, NP>));             \
+    else QEC_GO((k_sample_lanes<false, false, true, NP>));                   \
+  } else {                                                                   \
+    if (t && b) QEC_GO((k_sample_lanes<true, true, false, NP>));             \
+    else if (t) QEC_GO((k_sample_lanes<true, false, false, NP>));            \
+    else if (b) QEC_GO((k_sample_lanes<false, true, false, NP>));            \
+    else QEC_GO((k_sample_lanes<false, false, false, NP>));                  \
+  }
+    if (S.lanes_np == 3) { QEC_GOL(3) } else if (S.lanes_np == 4) { QEC_GOL(4) } else { QEC_GOL(2) }
+#undef QEC_GOL
   } else if (S.warp_mode && S.fast) {
     if (t && b) QEC_GO((k_sample_linw<true, true, true>));
     else if (t) QEC_GO((k_sample_linw<true, false, true>));

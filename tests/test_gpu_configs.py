@@ -274,3 +274,47 @@ def test_duplicate_location_ops_keep_the_reference_rule(capi, ref):
     for s, f in enumerate(_decode(cnt, ev, n)):
         want = ep.propagate([idx[l] for l, _ in f], [lw[labels[l]][dd][0] for l, dd in f])
         assert got[s].tolist() == want, f"shot {s} faults {f}"
+
+
+# ------------------------------------------------------------------- compact output (events)
+@pytest.mark.parametrize("d,T,p,n_shots,lo,mode", [
+    (3, 3, 0.01, 50_001, 0, None), (5, 5, 1e-3, 700_000, 4096 * 3 + 64, None),
+    (5, 5, 2e-3, 100_000, 32, "lanes16"), (5, 5, 2e-3, 40_000, 0, "warp"), (11, 3, 1e-3, 20_000, 0, None)])
+def test_compact_events_equal_the_fault_export(capi, monkeypatch, d, T, p, n_shots, lo, mode):
+    """qec_sampler_sample_events (fault lists compacted on the device, ~3 B/shot over PCIe) holds
+    exactly the faults of the dense call's export, word by word; tallies are the dense call's; and
+    the outcome of every shot is the XOR of its faults' order-1 outcomes (what makes the compact
+    form lossless), checked against the dense bits."""
+    if mode:
+        monkeypatch.setenv("QEC_B200_LIN_MODE", mode)
+    circ = surface_code_circuit(d, T)
+    model = standard_depolarizing_model(p)
+    idx, labels, lw, lp = sampler_inputs(circ, model)
+    _, _, paulis = noise_inputs(circ, model)
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=31)
+    n_small = min(n_shots, 60_000)
+    bits, tally, cnt, ev = sm.sample(lo, n_small, want_tally=True, fault_cap=8)
+    wc, events, tally_c = sm.sample_events(lo, n_small, want_tally=True)
+    assert np.array_equal(tally_c, tally)
+    assert np.array_equal(wc.astype(np.uint32), cnt)
+    off = np.concatenate([[0], np.cumsum(wc.astype(np.int64))])
+    assert off[-1] == len(events)
+    first = np.cumsum([0] + [len(pl) for pl in paulis])
+    en = make_enumerator(capi, g, 1, idx, paulis)
+    sig = capi.unpack_bits(en.range(0, en.num_paths())[0], en.num_paths())   # order-1 outcomes
+    got = capi.unpack_bits(bits, n_small)
+    want = np.zeros_like(got)
+    for w in range(len(wc)):
+        e = np.sort(events[off[w]:off[w + 1]])
+        assert np.array_equal(e, np.sort(ev[w, :cnt[w]])), f"word {w}"
+        for x in e:
+            loc, bit, dig = int(x) >> 14, (int(x) >> 9) & 31, int(x) & 511
+            want[32 * w + bit] ^= sig[first[loc] + dig]
+    assert np.array_equal(got, want)
+    # the full size: counts add up, tallies agree with a tallies-only dense call
+    wc, events, tally_c = sm.sample_events(lo, n_shots, want_tally=True)
+    _, tally_d, _, _ = sm.sample(lo, n_shots, want_bits=False, want_tally=True)
+    assert int(wc.astype(np.int64).sum()) == len(events) and np.array_equal(tally_c, tally_d)
+    k = np.arange(64, dtype=np.uint64)
+    assert int((tally_c[circ.nc + 2:] * k).sum()) == len(events) or int(tally_c[circ.nc + 2 + 63]) > 0

@@ -13,9 +13,11 @@ from bench import make_inputs  # noqa: E402
 from qiskit_qec_b200 import _capi  # noqa: E402
 
 
-def run(mode, warps, n_shots=100_000_000, tally=True, bits=True, reps=5, d=5, T=5):
-    for k in ("QEC_B200_LIN_MODE", "QEC_B200_LIN_WARPS"):
+def run(mode, warps, n_shots=100_000_000, tally=True, bits=True, reps=5, d=5, T=5, np_=0):
+    for k in ("QEC_B200_LIN_MODE", "QEC_B200_LIN_WARPS", "QEC_B200_LANES_NP"):
         os.environ.pop(k, None)
+    if np_:
+        os.environ["QEC_B200_LANES_NP"] = str(np_)
     if mode:
         os.environ["QEC_B200_LIN_MODE"] = mode
     if warps:
@@ -44,7 +46,7 @@ def run(mode, warps, n_shots=100_000_000, tally=True, bits=True, reps=5, d=5, T=
         torch.cuda.synchronize()
         times.append(_capi.last_kernel_ms(0))
     ms = min(times[2:])
-    print(f"mode={mode} warps={warps} bits={int(bits)} tally={int(tally)} d={d}: {ms:.4f} ms "
+    print(f"mode={mode} warps={warps} np={np_} bits={int(bits)} tally={int(tally)} d={d}: {ms:.4f} ms "
           f"({n_shots / ms * 1e3:.3e} shots/s, {n_shots * circ.nc / 8 / ms / 1e6:.0f} GB/s)  {_capi.last_kernel()}",
           flush=True)
     sm.close(); g.close()
@@ -54,7 +56,11 @@ if __name__ == "__main__":
     if len(sys.argv) > 1:
         for spec in sys.argv[1:]:
             m, _, w = spec.partition(":")
-            run(m or None, int(w) if w else 0)
+            w, _, npx = w.partition("/")
+            npx, _, dt = npx.partition("@")     # mode:warps/np@d,T
+            dd, tt = (int(x) for x in dt.split(",")) if dt else (5, 5)
+            run(m or None, int(w) if w else 0, np_=int(npx) if npx else 0, d=dd, T=tt,
+                n_shots=100_000_000 if dd <= 5 else 20_000_000)
     else:
         run("lanes", 0)
         for w in (8, 10, 12, 14, 15, 16):
