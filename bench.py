@@ -68,6 +68,20 @@ def reference_rate(n_procs: int, shots_per_proc: int, d=5, T=5, seed0=0):
     return total / max(r[1] for r in res), total, wall
 
 
+def reference_enum_rate(n_paths: int = 100_000, d=5, T=5):
+    """faults/s of the UNMODIFIED reference _CFaultEnumerator.enumerate (order 2) on ONE host core
+    (the reference as shipped is single-threaded), over the first n_paths paths."""
+    from oracle import ref
+    R = ref.module()
+    circ, model, idx, labels, types = make_inputs(d, T)
+    fe = R._CFaultEnumerator(2, circ.nq, circ.nc, circ.ops, idx, labels, [types[lab] for lab in labels])
+    t0 = time.perf_counter()
+    n = 0
+    while n < n_paths and not fe.done():
+        n += len(fe.enumerate(10000))
+    return n / (time.perf_counter() - t0), n
+
+
 def host_cores() -> int:
     try:
         return len(os.sched_getaffinity(0))
@@ -82,7 +96,8 @@ def run_reference(args):
     from oracle import ref
     cores = host_cores()
     config = {"workload": "FaultSampler d=5 T=5 surface code, p=1e-3 circuit-level noise "
-                          "(BASELINE configs[1]); bounded sample per step"}
+                          "(BASELINE configs[1]); bounded sample per step",
+              "host_cores_used": cores}
     if not ref.available():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built"}))
         return
@@ -95,13 +110,24 @@ def run_reference(args):
         rates.append(r)
     wall = time.perf_counter() - t0
     value = statistics.median(rates)
+    # the reference as shipped: one process, one core; and its enumerator
+    one_shots = max(per_proc // 2, 1000)
+    one_core, _, _ = reference_rate(1, one_shots, seed0=77)
+    enum_rate, enum_n = reference_enum_rate(100_000)
     line = {"metric": METRIC, "value": value, "unit": "shots/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
             "data": "synthetic", "impl": "reference", "config": config,
             "cpu_baseline": {"value": value, "unit": "shots/s", "cores": cores, "kind": "reference",
                              "sample": f"{cores} processes x {per_proc} shots per step through "
-                                       "reference _CFaultSampler.sample (oracle/_ref)"},
+                                       "reference _CFaultSampler.sample (oracle/_ref)",
+                             "one_core": {"value": one_core, "unit": "shots/s", "cores": 1,
+                                          "sample": f"1 process x {one_shots} shots: the reference as "
+                                                    "shipped (single-threaded)"},
+                             "enumerator_one_core": {
+                                 "value": enum_rate, "unit": "faults/s", "cores": 1,
+                                 "sample": f"first {enum_n} order-2 paths of d=5 T=5 through reference "
+                                           "_CFaultEnumerator.enumerate"}},
             "e2e": {"value": value, "unit": "shots/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -247,83 +273,198 @@ def run_ours(args):
     # kernel-only launch time of the dominant kernel (k_sample), CUDA events inside the library
     kern_ms = statistics.mean(step_ms)
 
-    # end to end through the host-pointer C ABI call: circuit + tables uploaded from host
-    # memory, kernel, packed outcomes and tallies copied back to pinned host memory
-    host_bits = torch.empty((nc, n_words), dtype=torch.int32, pin_memory=True)
+    # ---- end to end: the public calls with HOST buffers, copies inside the timed region
+    import numpy as np
     host_tally = torch.empty(_capi.tally_len(nc), dtype=torch.int64, pin_memory=True)
     tab_bytes = int(sm.tables().nbytes) + 4 * len(circ.ops)
     del bits
     torch.cuda.empty_cache()
 
-    def e2e_step(i):
+    def settle(fn, max_iter=12):
+        """untimed passes until three in a row are within 5 % of each other AND below 1.5x the
+        best seen: on a fresh box the first passes over a newly pinned buffer run 3-6x slower,
+        and two equally slow passes must not end the warm-up"""
+        seen = []
+        for _ in range(max_iter):
+            ts = time.perf_counter()
+            fn(0)
+            seen.append(time.perf_counter() - ts)
+            last = seen[-3:]
+            if len(seen) >= 3 and max(last) <= 1.05 * min(last) and max(last) <= 1.5 * min(seen):
+                break
+        return seen
+
+    def timed_e2e(fn, steps):
+        warm = settle(fn)
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        times = []
+        for i in range(steps):
+            ts = time.perf_counter()
+            fn(1 + i)
+            times.append(time.perf_counter() - ts)
+        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return world * n_shots * steps / float(t.item()), times, warm
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    # (1) compact call -- the headline: the sampled faults of every shot + tallies.  Lossless:
+    # labels and errors ARE the list, the outcome is the XOR of the faults' signatures; about
+    # 3.2 B/shot cross PCIe instead of 18.1
+    ev_pin = torch.empty(int(n_shots * max(1.2 * len(idx) * P_NOISE, 0.05)) + 65536,
+                         dtype=torch.int32, pin_memory=True)
+    wc_pin = torch.empty(n_words, dtype=torch.int16, pin_memory=True)
+    pinned = (wc_pin.numpy().view(np.uint16), ev_pin.numpy().view(np.uint32))
+    ev_bytes = [0]
+
+    def e2e_compact(i):
         g2, s2 = new_sampler()
-        s2.sample_host_ptr(((rank * 1_000_003 + 500_000 + i) * n_words) * 32, n_shots,
+        wc, ev, tl = s2.sample_events(((rank * 1_000_003 + 500_000 + i) * n_words) * 32, n_shots,
+                                      want_tally=True, pinned=pinned)
+        ev_bytes[0] = int(ev.nbytes + wc.nbytes + tl.nbytes)
+        assert int(tl[nc + 1]) == n_shots
+        s2.close()
+        g2.close()
+
+    e2e_value, e2e_times, e2e_warm = timed_e2e(e2e_compact, e2e_steps)
+    compact_kernel = _capi.last_kernel()
+    del ev_pin, wc_pin, pinned
+
+    # (2) dense call: packed outcome bits of every shot (18.1 B/shot) + tallies, pinned memory
+    host_bits = torch.empty((nc, n_words), dtype=torch.int32, pin_memory=True)
+
+    def e2e_dense(i):
+        g2, s2 = new_sampler()
+        s2.sample_host_ptr(((rank * 1_000_003 + 700_000 + i) * n_words) * 32, n_shots,
                            host_bits.data_ptr(), host_tally.data_ptr())
         s2.close()
         g2.close()
 
-    e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    # untimed steps until the step time settles (at most 10): on a fresh box the first passes over
-    # the 1.8 GB pinned host buffer run 3-6x slower (the VM's memory is backed lazily), and which
-    # pass is the last slow one varies from run to run
-    prev, e2e_warm = None, []
-    for _ in range(10):
-        ts = time.perf_counter()
-        e2e_step(0)
-        e2e_warm.append(time.perf_counter() - ts)
-        if prev is not None and len(e2e_warm) >= 3 and abs(e2e_warm[-1] - prev) <= 0.1 * prev:
-            break
-        prev = e2e_warm[-1]
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    e2e_times = []
-    for i in range(e2e_steps):
-        ts = time.perf_counter()
-        e2e_step(1 + i)
-        e2e_times.append(time.perf_counter() - ts)
-    t1 = time.perf_counter()
-    t = torch.tensor([t1 - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * n_shots * e2e_steps / float(t.item())
+    dense_value, dense_times, dense_warm = timed_e2e(e2e_dense, e2e_steps)
     assert int(host_tally[nc + 1].item()) == n_shots
+    dense_bytes = int(host_bits.numel() * 4 + host_tally.numel() * 8)
+    del host_bits
+
+    # (3) the literal plug-in call of the reference's API: _CFaultSampler(...).sample(N) -> N
+    # Python tuples (index, labels, errors, outcome list); building the objects dominates
+    plugin = None
+    if rank == 0 and args.plugin_shots > 0:
+        from qiskit_qec_b200.analysis.extensions import _CFaultSampler
+        lw = {lab: [(p, model.get_pauli_weight(lab, p)) for p in types[lab]] for lab in set(labels)}
+        lp = {lab: model.get_error_probability(lab) for lab in set(labels)}
+        fs = _CFaultSampler(circ.nq, nc, circ.ops, idx, labels, lw, lp, 5)
+        fs.sample(10_000)
+        ts = time.perf_counter()
+        blk = fs.sample(args.plugin_shots)
+        dt = time.perf_counter() - ts
+        assert len(blk) == args.plugin_shots and blk[0][0] == -1 and len(blk[0][3]) == nc
+        plugin = {"value": args.plugin_shots / dt, "unit": "shots/s", "shots": args.plugin_shots,
+                  "ms": 1e3 * dt,
+                  "call": "_c_analysis._CFaultSampler(...).sample(N): the reference's own signature "
+                          "and return type (list of N tuples); GPU sampling + host tuple building"}
+        del blk, fs
     clk = clocks.stop() if rank == 0 else None
 
-    # secondary metric: FaultEnumerator order 2 on the same circuit (BASELINE configs[2]),
-    # index range sharded evenly across ranks, outcomes + tallies on device
+    # secondary metric: FaultEnumerator order 2 on the same circuit (BASELINE configs[2]), index
+    # range sharded evenly across ranks, outcomes + tallies on device.  The tally all-reduce of a
+    # step runs on a side stream under the next step's kernel, as the sampler's does (round 1 ran
+    # it on the main stream: 60 us of launch + NCCL latency against 36 us of kernel at 8 GPUs)
+    paulis = [types[lab] for lab in labels]
     enum = None
     if not args.no_enum:
-        paulis = [types[lab] for lab in labels]
+        reps = 8
         en = _capi.Enumerator(g, 2, idx, [[_capi.pauli_code(p) for p in pl] for pl in paulis])
         total = en.num_paths()
         lo, hi = shard_range(total, rank, world)
         ebits = torch.empty((nc, (hi - lo + 31) // 32), dtype=torch.int32, device=dev)
+        etal = [torch.zeros(_capi.tally_len(nc), dtype=torch.int64, device=dev) for _ in range(reps + 3)]
 
-        def estep():
-            tally.zero_()
-            en.range_dev(lo, hi, ebits.data_ptr(), tally.data_ptr(), stream)
-            allreduce_tally(tally)
+        def estep(i):
+            en.range_dev(lo, hi, ebits.data_ptr(), etal[i].data_ptr(), stream)
+            if side is not None:
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    allreduce_tally(etal[i])
 
-        for _ in range(3):
-            estep()
+        for i in range(3):
+            estep(i)
+        if side is not None:
+            main.wait_stream(side)
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 5
         e0.record()
-        for _ in range(reps):
-            estep()
+        for i in range(reps):
+            estep(3 + i)
+        if side is not None:
+            main.wait_stream(side)  # the timed region covers every all-reduce
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ems = float(t.item()) / reps
-        assert int(tally[nc + 1].item()) == total
+        assert int(etal[-1][nc + 1].item()) == total
         enum = {"metric": "FaultEnumerator order-2 faults/s", "value": total / (ems * 1e-3),
                 "unit": "faults/s", "paths": total, "ms": ems, "scaling": "strong",
                 "workload": "order=2 exhaustive, SurfaceCodeCircuit d=5 T=5 (BASELINE configs[2])",
-                "kernel": _capi.last_kernel()}
+                "kernel": _capi.last_kernel(),
+                "hbm_frac": (total * nc / 8.0 / (ems * 1e-3) / 1e9 / peaks_hbm()) if world == 1 else None}
+        en.close()
+        del ebits
+
+    # the gate-stream (frame-propagation) kernels the north star names: the same workloads under
+    # QEC_B200_SAMPLER=frame / QEC_B200_ENUM=frame.  These EXECUTE the W_bit/32 lane-ops per shot,
+    # so their integer-pipe roofline fraction is a real one (filled in below, against k_int_peak)
+    frame = None
+    if rank == 0 and world == 1 and not args.no_frame:
+        os.environ["QEC_B200_SAMPLER"] = "frame"
+        os.environ["QEC_B200_ENUM"] = "frame"
+        try:
+            fshots = min(n_shots, args.frame_shots)
+            fwords = (fshots + 31) // 32
+            gf, sf = new_sampler(seed=1)
+            fbits = torch.empty((nc, fwords), dtype=torch.int32, device=dev)
+            ftal = torch.zeros(_capi.tally_len(nc), dtype=torch.int64, device=dev)
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            for i in range(3):
+                sf.sample_dev(i * fwords * 32, fshots, fbits.data_ptr(), ftal.data_ptr(), stream)
+            torch.cuda.synchronize()
+            sf.check()
+            f0.record()
+            for i in range(5):
+                sf.sample_dev((3 + i) * fwords * 32, fshots, fbits.data_ptr(), ftal.data_ptr(), stream)
+            f1.record()
+            torch.cuda.synchronize()
+            sf.check()
+            fms, fkern = f0.elapsed_time(f1) / 5, _capi.last_kernel()
+            sf.close()
+            del fbits
+            en_f = _capi.Enumerator(gf, 2, idx, [[_capi.pauli_code(p) for p in pl] for pl in paulis])
+            tot_f = en_f.num_paths()
+            ebf = torch.empty((nc, (tot_f + 31) // 32), dtype=torch.int32, device=dev)
+            for _ in range(2):
+                en_f.range_dev(0, tot_f, ebf.data_ptr(), ftal.data_ptr(), stream)
+            torch.cuda.synchronize()
+            f0.record()
+            for _ in range(5):
+                en_f.range_dev(0, tot_f, ebf.data_ptr(), ftal.data_ptr(), stream)
+            f1.record()
+            torch.cuda.synchronize()
+            frame = {"sampler": {"value": fshots / (fms * 1e-3), "unit": "shots/s", "units": fshots,
+                                 "ms": fms, "kernel": fkern},
+                     "enumerator": {"value": tot_f / (f0.elapsed_time(f1) / 5 * 1e-3), "unit": "faults/s",
+                                    "units": tot_f, "ms": f0.elapsed_time(f1) / 5,
+                                    "kernel": _capi.last_kernel()}}
+            en_f.close()
+            gf.close()
+            del ebf
+        finally:
+            os.environ.pop("QEC_B200_SAMPLER", None)
+            os.environ.pop("QEC_B200_ENUM", None)
 
     # CPU baseline (rank 0, N=1 only): the unmodified reference in a child process, after
     # the GPU measurements so that its worker processes cannot disturb them
@@ -333,31 +474,35 @@ def run_ours(args):
             out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference",
                                   "--steps", "1", "--warmup", "0", "--ref-shots",
                                   str(args.ref_shots)], capture_output=True, text=True,
-                                 timeout=600).stdout.strip().splitlines()
+                                 timeout=900).stdout.strip().splitlines()
             ref = json.loads(out[-1]) if out else {}
             cpu_baseline = ref.get("cpu_baseline")
         except (subprocess.SubprocessError, ValueError, OSError):
             cpu_baseline = None
 
     if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except OSError:
-            pass
-        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback"
+        hbm_peak, peak_src = peaks_hbm(), peaks_src()
         int_peak, clk_mhz = _capi.measure_int_peak(local, 40.0)
-        traffic = None
-        try:  # dram bytes per shot of the dominant kernel, from the committed ncu --set full capture
-            cap = json.load(open(os.path.join(ROOT, "profiles", "r01", "ncu_dominant_kernel.json")))
-            traffic = float(cap["dram_bytes_per_shot"]) * n_shots
+        # dram bytes per shot of the dominant kernel, from this round's committed ncu --set full
+        # capture -- used only when that capture is of the kernel variant that just ran, so that a
+        # changed kernel cannot silently inherit a stale figure (smaller 12)
+        traffic, traffic_src = None, None
+        try:
+            cap = json.load(open(os.path.join(ROOT, "profiles", "r02", "ncu_dominant_kernel.json")))
+            if cap.get("variant_key") and cap["variant_key"] in sampler_kernel:
+                traffic = float(cap["dram_bytes_per_shot"]) * n_shots
+                traffic_src = ("profiles/r02/ncu_dominant_kernel.json: dram read+write bytes per shot x "
+                               "shots per launch, capture of the same kernel variant")
         except (OSError, ValueError, KeyError):
             pass
-        bytes_per_launch = n_shots * nc / 8.0
-        achieved = bytes_per_launch / (kern_ms * 1e-3) / 1e9
-        ops_per_launch = n_shots * w_bit / 32.0
-        int_ach = ops_per_launch / (kern_ms * 1e-3)
+        achieved = n_shots * nc / 8.0 / (kern_ms * 1e-3) / 1e9
+        lane_ops = w_bit / 32.0
+        if frame:
+            for k in ("sampler", "enumerator"):
+                ach = frame[k]["units"] * lane_ops / (frame[k]["ms"] * 1e-3)
+                frame[k]["int_roofline"] = {"bound": "int32-alu", "achieved": ach, "peak": int_peak,
+                                            "unit": "lane-ops/s", "frac": ach / int_peak,
+                                            "lane_ops_per_unit": lane_ops}
         line = {
             "metric": METRIC, "value": value, "unit": "shots/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
@@ -367,34 +512,57 @@ def run_ours(args):
                                    "T=5, p=1e-3 circuit-level noise (BASELINE configs[1]); packed "
                                    "outcomes + tallies written per step",
                        "l2": "output per step (1.81 GB at 1e8 shots) is larger than L2; no reuse",
-                       "timing": "CUDA events on the launching stream, max over ranks"},
+                       "timing": "CUDA events on the launching stream, max over ranks",
+                       "host_cores": cores},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak, "traffic": traffic,
-                         "traffic_source": "profiles/r01/ncu_dominant_kernel.json (dram read+write "
-                                           "bytes per shot x shots per launch)",
-                         "kernel": sampler_kernel,
-                         "peak_source": peak_src,
-                         "algorithmic_bytes_per_shot": nc / 8.0},
-            "int_roofline": {"bound": "int32-alu", "achieved": int_ach, "peak": int_peak,
-                             "unit": "lane-ops/s", "frac": int_ach / int_peak,
-                             "lane_ops_per_shot": w_bit / 32.0,
-                             "peak_source": "k_int_peak LOP3 microbenchmark, same run",
-                             "note": "lane-ops of explicit frame propagation (the reference's "
-                                     "algorithm) delivered per second; the linear-response "
-                                     "kernel obtains the same outcomes without executing them"},
+                         "traffic_source": traffic_src, "kernel": sampler_kernel,
+                         "peak_source": peak_src, "algorithmic_bytes_per_shot": nc / 8.0},
+            "int_peak": {"value": int_peak, "unit": "lane-ops/s", "sm_clock_mhz": clk_mhz,
+                         "source": "k_int_peak: 8 independent chains of inline-PTX lop3.b32 per thread, "
+                                   "counted ops == executed LOP3 (profiles/r02/sass_k_int_peak.txt), "
+                                   "measured in this run",
+                         "note": "the integer-pipe roofline applies to the gate-stream kernels "
+                                 "(frame.*.int_roofline); the default linear-response kernels do not "
+                                 "execute the gate stream and are judged on the HBM roofline only"},
             "e2e": {"value": e2e_value, "unit": "shots/s", "h2d_bytes_per_step": tab_bytes,
-                    "d2h_bytes_per_step": int(host_bits.numel() * 4 + host_tally.numel() * 8),
-                    "steps": e2e_steps, "ms_per_step": [round(x * 1e3, 2) for x in e2e_times],
+                    "d2h_bytes_per_step": ev_bytes[0], "steps": e2e_steps,
+                    "ms_per_step": [round(x * 1e3, 2) for x in e2e_times],
                     "warmup_ms": [round(x * 1e3, 1) for x in e2e_warm],
-                    "call": "qec_circuit_create + qec_sampler_create + qec_sampler_sample (host "
-                            "pointers, pinned) + destroy"},
+                    "call": "qec_circuit_create + qec_sampler_create + qec_sampler_sample_events "
+                            "(pinned host buffers: per-word counts + the sampled faults of every shot "
+                            "+ tallies) + destroy; lossless compact form of the shots",
+                    "kernel": compact_kernel},
+            "e2e_dense": {"value": dense_value, "unit": "shots/s", "h2d_bytes_per_step": tab_bytes,
+                          "d2h_bytes_per_step": dense_bytes,
+                          "ms_per_step": [round(x * 1e3, 2) for x in dense_times],
+                          "warmup_ms": [round(x * 1e3, 1) for x in dense_warm],
+                          "call": "qec_circuit_create + qec_sampler_create + qec_sampler_sample (host "
+                                  "pointers, pinned: packed outcome bits of every shot + tallies) + destroy"},
+            "e2e_plugin": plugin,
             "gpu_launches": args.steps, "clocks": clk, "cpu_baseline": cpu_baseline,
-            "enumerator": enum, "kernel_ms_per_launch": kern_ms,
+            "enumerator": enum, "frame": frame, "kernel_ms_per_launch": kern_ms,
             "step_ms": [round(x, 4) for x in step_ms],
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        return {}
+
+
+def peaks_hbm() -> float:
+    # fallback: the B200 HBM figure of /opt/skills/guides/B200_PROFILING.md
+    return float(_peaks().get("hbm_gbs", 6650.0))
+
+
+def peaks_src() -> str:
+    return "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in _peaks() else "fallback (B200_PROFILING.md)"
 
 
 def main():
@@ -407,6 +575,11 @@ def main():
     ap.add_argument("--ref-shots", type=int, default=40_000,
                     help="reference shots per host process per step (bounded CPU sample)")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--plugin-shots", type=int, default=1_000_000,
+                    help="shots of the literal _CFaultSampler.sample(N) call (0: skip)")
+    ap.add_argument("--frame-shots", type=int, default=50_000_000,
+                    help="shots per launch of the gate-stream (frame) sampler sub-record")
+    ap.add_argument("--no-frame", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-enum", action="store_true")
     args = ap.parse_args()

@@ -380,9 +380,12 @@ class FaultSampler {
   ~FaultSampler() { if (h_) qec_sampler_destroy(h_); }
 
   // blocksize fresh shots; successive calls continue with new global shot ids (the cursor
-  // moves in whole 32-shot words), so blocks never repeat -- like the reference's RNG stream
-  std::vector<FaultPath> sample(int blocksize) {
-    std::vector<FaultPath> block;
+  // moves in whole 32-shot words), so blocks never repeat -- like the reference's RNG stream.
+  // Returns the reference's list of (-1, labels, errors, outcome) tuples, built straight with the
+  // CPython API: a 1e6-shot block is 1e6 tuples + 3e6 lists, and going through
+  // std::vector<FaultPath> and pybind's casters built every one of them twice.
+  py::list sample(int blocksize) {
+    py::list block;
     if (blocksize <= 0) return block;
     const int64_t n = blocksize, nw = (n + 31) / 32;
     std::vector<uint32_t> bits((size_t)nc_ * nw + 1), cnt((size_t)nw), ev;
@@ -399,19 +402,53 @@ class FaultSampler {
       break;
     }
     cursor_ += nw * 32;
-    std::vector<std::vector<std::string>> labs((size_t)n), errs((size_t)n);
-    for (int64_t w = 0; w < nw; ++w)
-      for (uint32_t k = 0; k < cnt[w]; ++k) {
-        const uint32_t e = ev[(size_t)w * cap + k];
-        const uint32_t loc = e >> 14, bit = (e >> 9) & 31u, dig = e & 511u;
-        const int64_t s = 32 * w + bit;
-        labs[s].push_back(labels_[loc]);
-        errs[s].push_back(class_paulis_[loc_cls_[loc]][dig]);
+    if (py_labels_.empty()) {  // Python strings of the labels / Paulis, made once
+      for (const auto &l : labels_) py_labels_.push_back(py::str(l));
+      for (const auto &cp : class_paulis_) {
+        py_paulis_.emplace_back();
+        for (const auto &ps : cp) py_paulis_.back().push_back(py::str(ps));
       }
-    block.reserve((size_t)n);
-    for (int64_t s = 0; s < n; ++s)
-      block.emplace_back(-1L, std::move(labs[s]), std::move(errs[s]), unpack_path(bits, nc_, nw, s));
-    return block;
+    }
+    PyObject *zero = PyLong_FromLong(0), *one = PyLong_FromLong(1), *minus = PyLong_FromLong(-1);
+    PyObject *out = PyList_New((Py_ssize_t)n);
+    std::vector<uint32_t> col((size_t)nc_), sorted;
+    for (int64_t w = 0; w < nw; ++w) {
+      for (int c = 0; c < nc_; ++c) col[c] = bits[(size_t)c * nw + w];
+      // the word's events by shot (stable: inside a shot they stay in location order)
+      sorted.assign(ev.begin() + (size_t)w * cap, ev.begin() + (size_t)w * cap + cnt[w]);
+      std::stable_sort(sorted.begin(), sorted.end(),
+                       [](uint32_t a, uint32_t b) { return ((a >> 9) & 31u) < ((b >> 9) & 31u); });
+      size_t k = 0;
+      const int nv = (int)std::min<int64_t>(32, n - 32 * w);
+      for (int bit = 0; bit < nv; ++bit) {
+        size_t k1 = k;
+        while (k1 < sorted.size() && ((sorted[k1] >> 9) & 31u) == (uint32_t)bit) ++k1;
+        PyObject *labs = PyList_New((Py_ssize_t)(k1 - k)), *errs = PyList_New((Py_ssize_t)(k1 - k));
+        for (size_t j = k; j < k1; ++j) {
+          const uint32_t loc = sorted[j] >> 14, dig = sorted[j] & 511u;
+          PyObject *l = py_labels_[loc].ptr(), *e = py_paulis_[loc_cls_[loc]][dig].ptr();
+          Py_INCREF(l); Py_INCREF(e);
+          PyList_SET_ITEM(labs, (Py_ssize_t)(j - k), l);
+          PyList_SET_ITEM(errs, (Py_ssize_t)(j - k), e);
+        }
+        k = k1;
+        PyObject *oc = PyList_New((Py_ssize_t)nc_);
+        for (int c = 0; c < nc_; ++c) {
+          PyObject *v = ((col[c] >> bit) & 1u) ? one : zero;
+          Py_INCREF(v);
+          PyList_SET_ITEM(oc, (Py_ssize_t)c, v);
+        }
+        PyObject *t = PyTuple_New(4);
+        Py_INCREF(minus);
+        PyTuple_SET_ITEM(t, 0, minus);
+        PyTuple_SET_ITEM(t, 1, labs);
+        PyTuple_SET_ITEM(t, 2, errs);
+        PyTuple_SET_ITEM(t, 3, oc);
+        PyList_SET_ITEM(out, (Py_ssize_t)(32 * w + bit), t);
+      }
+    }
+    Py_DECREF(zero); Py_DECREF(one); Py_DECREF(minus);
+    return py::reinterpret_steal<py::list>(out);
   }
 
   // bulk API: packed outcomes + tallies of `n` fresh shots
@@ -509,6 +546,8 @@ class FaultSampler {
   qec_sampler *h_ = nullptr;
   int64_t cursor_ = 0;
   int cap_ = 64;
+  std::vector<py::str> py_labels_;
+  std::vector<std::vector<py::str>> py_paulis_;
 };
 
 // ---------------------------------------------------------------------------------------------
