@@ -212,6 +212,29 @@ int qec_sampler_counts(qec_sampler *s, int64_t shot_lo, int64_t n_shots, int64_t
                        int64_t max_out, uint64_t *out_counts, uint32_t *out_rows, int64_t *n_out,
                        uint64_t *n_zero, uint64_t *tally);
 
+/* ---- K4 without any allocation ---------------------------------------------------------
+ * (no counterpart in the reference: added for callers
+ * that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it.)
+ * The outcome histogram of qec_outcome_histogram_rows_dev with its hash table in a fixed device
+ * array inside the library instead of caller memory: this call allocates and frees nothing.
+ * Limits: circuits of at most 256 clbits; at most 65536 distinct non-zero outcomes per call
+ * (fewer in practice: open addressing slows as the table fills; outcomes that find no slot
+ * are counted in status[1], never silently lost); at most 2^40 paths.  Beyond the clbit or path
+ * limit the call fails with QEC_ERR_LIMIT.  The array (3 MiB) is held by every GPU that loads
+ * the library until the process exits.
+ * d_bits: packed outcomes on the device of `c` (row stride n_words >= ceil(n_paths/32)).
+ * Outputs (device pointers, overwritten): d_out_counts uint64[max_out], d_out_rows
+ * uint32[max_out][ceil(nc/32)] -- the distinct non-zero outcomes, order arbitrary;
+ * d_out_status uint64[4] = {distinct non-zero outcomes found, paths dropped because the table
+ * was full, paths with the all-zero outcome, entries written = min(found, max_out)}.
+ * Asynchronous on `stream`.  ALL calls on one GPU share the array, whatever the circuit or
+ * stream: calls that overlap on the GPU race.  Serialise them (one stream, or events).  The
+ * first call on each device looks up the array's address; make it before any graph capture. */
+int qec_outcome_counts_noalloc_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                   int64_t n_words, uint64_t *d_out_counts, uint32_t *d_out_rows,
+                                   int64_t max_out, uint64_t *d_out_status, void *stream);
+
 /* ---- device memory helpers (so a ctypes/cgo caller needs no CUDA binding) ------------- */
 int qec_dev_alloc(int device, size_t bytes, void **out);
 int qec_dev_free(int device, void *p);

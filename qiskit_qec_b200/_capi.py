@@ -32,7 +32,7 @@ SYMBOLS = [
     "qec_sampler_create", "qec_sampler_destroy", "qec_sampler_sample", "qec_sampler_sample_dev",
     "qec_sampler_check", "qec_sampler_tables", "qec_sampler_variant", "qec_sampler_counts",
     "qec_sampler_sample_events",
-    "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev",
+    "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev", "qec_outcome_counts_noalloc_dev",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
     "qec_last_kernel", "qec_jit_compile_to_file",
@@ -369,6 +369,15 @@ def outcome_histogram_dev(circuit: Circuit, d_bits: int, n_paths: int, d_keys: i
         circuit._h, C.c_void_p(d_bits), C.c_int64(n_paths), C.c_int64(n_words or (n_paths + 31) // 32),
         C.c_void_p(d_keys), C.c_void_p(d_counts), C.c_void_p(d_rows or None), C.c_int64(table_cap),
         C.c_void_p(d_status or None), C.c_void_p(stream or None)))
+
+
+def outcome_counts_noalloc_dev(circuit: Circuit, d_bits: int, n_paths: int, n_words: int, d_out_counts: int,
+                               d_out_rows: int, max_out: int, d_out_status: int, stream: int = 0):
+    """K4 with its hash table in the library's fixed device array: allocates nothing (raw device
+    addresses in and out; see include/qec_b200.h for the limits and the sharing rule)."""
+    _check(lib().qec_outcome_counts_noalloc_dev(
+        circuit._h, C.c_void_p(d_bits), C.c_int64(n_paths), C.c_int64(n_words), C.c_void_p(d_out_counts or None),
+        C.c_void_p(d_out_rows or None), C.c_int64(max_out), C.c_void_p(d_out_status), C.c_void_p(stream or None)))
 
 
 def outcome_hash(rows: np.ndarray) -> np.ndarray:

@@ -2477,3 +2477,103 @@ extern "C" int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t 
   }
   return 0;
 }
+
+// ---- K4 without any allocation --------------------------------------------------------------------
+// qec_outcome_counts_noalloc_dev: the outcome histogram of qec_outcome_histogram_rows_dev for
+// callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  No counterpart in the reference.
+// The hash table -- the scratch memory of K4 -- is the file-scope device array below,
+// of a fixed size: every GPU that loads the library holds its 3 MiB until the process exits.
+//   layout (uint64 units): status[8] | keys[CAP] | counts[CAP] | rows[CAP][ROW_WORDS] (uint32)
+// In host code the array's NAME is a host-side stand-in, not a device address: its address is
+// looked up once per device with cudaGetSymbolAddress (noalloc_scratch_ptr) and that pointer is
+// what the kernels in qec_kernels.cu receive; device code in this file names the array directly.
+// Every call shares the array: the part that must start at zero is cleared on the caller's
+// stream at the start of each call, and calls that overlap on one GPU race.
+#define QEC_NOALLOC_TABLE_SLOTS 65536
+#define QEC_NOALLOC_MAX_CLBITS 256
+#define QEC_NOALLOC_ROW_WORDS (QEC_NOALLOC_MAX_CLBITS / 32)
+#define QEC_NOALLOC_STATUS_U64 8
+#define QEC_NOALLOC_SCRATCH_U64 \
+  (QEC_NOALLOC_STATUS_U64 + (size_t)QEC_NOALLOC_TABLE_SLOTS * (2 + QEC_NOALLOC_ROW_WORDS / 2))
+static __device__ __align__(256) unsigned long long qec_noalloc_scratch[QEC_NOALLOC_SCRATCH_U64];
+
+// occupied slots of the scratch table -> the caller's dense arrays, never past max_out entries
+// (the existing compaction, k_hist_compact, trusts a count its host caller read back first; this
+// entry point is asynchronous and cannot)
+__global__ void __launch_bounds__(256)
+k_noalloc_compact(const int rw, unsigned long long *__restrict__ out_counts,
+                  uint32_t *__restrict__ out_rows, const long long max_out) {
+  unsigned long long *status = qec_noalloc_scratch;
+  const unsigned long long *keys = qec_noalloc_scratch + QEC_NOALLOC_STATUS_U64;
+  const unsigned long long *counts = keys + QEC_NOALLOC_TABLE_SLOTS;
+  const uint32_t *rows = reinterpret_cast<const uint32_t *>(counts + QEC_NOALLOC_TABLE_SLOTS);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < QEC_NOALLOC_TABLE_SLOTS;
+       i += (long long)gridDim.x * blockDim.x) {
+    if (!keys[i]) continue;
+    const unsigned long long o = atomicAdd(&status[4], 1ull);
+    if ((long long)o >= max_out) continue;
+    out_counts[o] = counts[i];
+    for (int j = 0; j < rw; ++j) out_rows[o * rw + j] = rows[i * rw + j];
+  }
+}
+// status of the call -> the caller's uint64[4] (overwritten): distinct non-zero outcomes, paths
+// dropped because the table was full, all-zero outcomes, entries written
+__global__ void k_noalloc_status(unsigned long long *__restrict__ out_status, const long long max_out) {
+  const unsigned long long *status = qec_noalloc_scratch;
+  out_status[0] = status[0];
+  out_status[1] = status[1];
+  out_status[2] = status[2];
+  out_status[3] = status[4] < (unsigned long long)max_out ? status[4] : (unsigned long long)max_out;
+}
+
+// device address of the scratch array on `device` (which must be current), looked up once
+static int noalloc_scratch_ptr(int device, unsigned long long **out) {
+  static unsigned long long *ptr[64];
+  static bool have[64];
+  if (device < 0 || device >= 64) return fail(QEC_ERR_CUDA, "bad device index %d", device);
+  if (!have[device]) {
+    unsigned long long *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&p, qec_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(QEC_ERR_CUDA, "cudaGetSymbolAddress(qec_noalloc_scratch) failed on device %d: %s", device,
+                  cudaGetErrorString(e));
+    ptr[device] = p;
+    have[device] = true;
+  }
+  *out = ptr[device];
+  return 0;
+}
+
+extern "C" int qec_outcome_counts_noalloc_dev(qec_circuit *c, const uint32_t *d_bits, int64_t n_paths,
+                                              int64_t n_words, uint64_t *d_out_counts, uint32_t *d_out_rows,
+                                              int64_t max_out, uint64_t *d_out_status, void *stream) {
+  if (!c || !d_bits || !d_out_status) return fail(QEC_ERR_INVALID, "null pointer");
+  if (max_out < 0 || (max_out > 0 && (!d_out_counts || !d_out_rows)))
+    return fail(QEC_ERR_INVALID, "max_out > 0 needs d_out_counts and d_out_rows");
+  if (c->nc < 1 || c->nc > QEC_NOALLOC_MAX_CLBITS)
+    return fail(QEC_ERR_LIMIT, "qec_outcome_counts_noalloc_dev serves at most %d clbits (circuit has %d): its "
+                "scratch table is a fixed device array; use qec_outcome_histogram_rows_dev with your own table",
+                QEC_NOALLOC_MAX_CLBITS, c->nc);
+  if (n_paths < 0) return fail(QEC_ERR_INVALID, "negative path count");
+  if (n_paths > ((int64_t)1 << 40))
+    return fail(QEC_ERR_LIMIT, "qec_outcome_counts_noalloc_dev serves at most 2^40 paths per call");
+  if (n_words < (n_paths + 31) / 32) return fail(QEC_ERR_INVALID, "row stride shorter than the paths");
+  CU(cudaSetDevice(c->device));
+  unsigned long long *scr = nullptr;
+  int rc = noalloc_scratch_ptr(c->device, &scr);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long *keys = scr + QEC_NOALLOC_STATUS_U64, *counts = keys + QEC_NOALLOC_TABLE_SLOTS;
+  uint32_t *rows = reinterpret_cast<uint32_t *>(counts + QEC_NOALLOC_TABLE_SLOTS);
+  // the last call's status, keys and counts go; rows are written when a slot is claimed
+  CU(cudaMemsetAsync(scr, 0, (QEC_NOALLOC_STATUS_U64 + (size_t)2 * QEC_NOALLOC_TABLE_SLOTS) * 8, st));
+  if (n_paths > 0)
+    qec_launch_outcome_hist(st, d_bits, c->nc, n_paths, n_words, keys, counts, rows, QEC_NOALLOC_TABLE_SLOTS, scr);
+  k_noalloc_compact<<<QEC_NOALLOC_TABLE_SLOTS / 256, 256, 0, st>>>((c->nc + 31) / 32,
+                                                                    (unsigned long long *)d_out_counts,
+                                                                    d_out_rows, max_out);
+  k_noalloc_status<<<1, 1, 0, st>>>((unsigned long long *)d_out_status, max_out);
+  CU(cudaGetLastError());
+  return 0;
+}
