@@ -318,3 +318,44 @@ def test_compact_events_equal_the_fault_export(capi, monkeypatch, d, T, p, n_sho
     assert int(wc.astype(np.int64).sum()) == len(events) and np.array_equal(tally_c, tally_d)
     k = np.arange(64, dtype=np.uint64)
     assert int((tally_c[circ.nc + 2:] * k).sum()) == len(events) or int(tally_c[circ.nc + 2 + 63]) > 0
+
+
+# ------------------------------------------------------------------------- 8(f2): heavy-hexagon
+@pytest.mark.parametrize("kw", [dict(), dict(num_initialize=1, idle_before_measure=True),
+                                dict(num_initialize=0, group_meas=True, blocks=2)])
+def test_hhc_labelled_idles_order1_stream_vs_reference(capi, ref, kw):
+    """HHC circuit with its labelled idles as separate noise channels (idm / idbm<k> / idinit /
+    plain id): the whole order-1 stream -- index, labels, errors, outcomes -- against the reference
+    enumerator; an order-2 window too."""
+    from qiskit_qec_b200.hhc import hhc_circuit
+    from qiskit_qec_b200.noise import PauliNoiseModel
+    circ = hhc_circuit(d=3, **kw)
+    model = PauliNoiseModel()
+    model.add_operation("cx", {p: 1 for p in ["ix", "iy", "iz", "xi", "xx", "xy", "xz", "yi", "yx", "yy", "yz",
+                                               "zi", "zx", "zy", "zz"]})
+    model.add_operation("h", {"x": 1, "y": 1, "z": 1})
+    model.add_operation("id", {"x": 1, "y": 1, "z": 1})
+    model.add_operation("idm", {"x": 1, "y": 2, "z": 1})
+    model.add_operation("idinit", {"x": 1})
+    model.add_operation("reset", {"x": 1})
+    model.add_operation("measure", {"x": 1})
+    for lab in sorted(set(circ.labels)):
+        if lab.startswith("idbm"):
+            model.add_operation(lab, {"x": 1, "z": 1})
+    idx, labels, paulis = noise_inputs(circ, model)
+    assert "idm" in labels or kw.get("group_meas")
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    for order, limit in ((1, None), (2, 30_000)):
+        fe = ref._CFaultEnumerator(order, circ.nq, circ.nc, circ.ops, idx, labels, paulis)
+        want = []
+        while not fe.done() and (limit is None or len(want) < limit):
+            want += fe.enumerate(10_000)
+        en = make_enumerator(capi, g, order, idx, paulis)
+        n = len(want) if limit else en.num_paths()
+        assert n == len(want)
+        bits, _ = en.range(0, n)
+        assert np.array_equal(capi.unpack_bits(bits, n), ref_outcome_matrix(want))
+        for r in range(0, n, max(1, n // 200)):
+            locs, digs = en.unrank(r)
+            assert want[r][0] == r and want[r][1] == [labels[l] for l in locs]
+            assert want[r][2] == [paulis[l][dd] for l, dd in zip(locs, digs)]
