@@ -212,6 +212,44 @@ int qec_sampler_counts(qec_sampler *s, int64_t shot_lo, int64_t n_shots, int64_t
                        int64_t max_out, uint64_t *out_counts, uint32_t *out_rows, int64_t *n_out,
                        uint64_t *n_zero, uint64_t *tally);
 
+/* ---- several GPUs, one process ---------------------------------------------------------
+ * (new: the reference is single-threaded and single-device, reference faultsampler.cpp:52,
+ * faultenumerator.cpp:82)  A multi handle owns one circuit + sampler /
+ * enumerator on each of `devices[n_dev]`.  A call cuts its shot / path range into n_dev
+ * contiguous pieces of whole 32-unit lane words; there is no data-path exchange, only the
+ * tallies are summed.  Results are those of ONE GPU, bit for bit (the Philox counters are
+ * functions of the global shot position; path indices are global).
+ *   *_sample / *_range: host buffers as in the single-GPU calls (out_bits host
+ *     uint32[nc][ceil(n/32)] or NULL, tally host or NULL), one host thread per device.
+ *   *_tally_dev: tallies only, all devices launched asynchronously, then device devices[0]
+ *     sums its peers' tallies read over NVLink peer mappings (no collective launch; falls back
+ *     to per-device copies where no peer mapping exists); *elapsed_ms (may be NULL) = device
+ *     time from before the first kernel to after the reduce.
+ * Creation arguments: those of qec_circuit_create + qec_sampler_create / qec_enumerator_create. */
+typedef struct qec_multi_sampler qec_multi_sampler;
+typedef struct qec_multi_enumerator qec_multi_enumerator;
+int qec_multi_sampler_create(int n_dev, const int *devices, int nq, int nc, int n_ops,
+                             const int32_t *row_off, const int32_t *row_data, int L,
+                             const int32_t *loc_op, const int32_t *loc_class, int n_classes,
+                             const double *class_p, const int32_t *class_off,
+                             const uint8_t *class_codes, const double *class_weight, uint64_t seed,
+                             qec_multi_sampler **out);
+void qec_multi_sampler_destroy(qec_multi_sampler *ms);
+int qec_multi_sampler_sample(qec_multi_sampler *ms, int64_t shot_lo, int64_t n_shots,
+                             uint32_t *out_bits, uint64_t *tally);
+int qec_multi_sampler_tally_dev(qec_multi_sampler *ms, int64_t shot_lo, int64_t n_shots,
+                                uint64_t *tally, float *elapsed_ms);
+int qec_multi_enumerator_create(int n_dev, const int *devices, int nq, int nc, int n_ops,
+                                const int32_t *row_off, const int32_t *row_data, int order, int L,
+                                const int32_t *loc_op, const int32_t *pauli_off,
+                                const uint8_t *pauli_codes, qec_multi_enumerator **out);
+void qec_multi_enumerator_destroy(qec_multi_enumerator *me);
+int qec_multi_enumerator_num_paths(const qec_multi_enumerator *me, int64_t *n);
+int qec_multi_enumerator_range(qec_multi_enumerator *me, int64_t lo, int64_t hi, uint32_t *out_bits,
+                               uint64_t *tally);
+int qec_multi_enumerator_tally_dev(qec_multi_enumerator *me, int64_t lo, int64_t hi, uint64_t *tally,
+                                   float *elapsed_ms);
+
 /* ---- K4 without any allocation ---------------------------------------------------------
  * (no counterpart in the reference: added for callers
  * that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses

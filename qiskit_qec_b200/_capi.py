@@ -32,6 +32,9 @@ SYMBOLS = [
     "qec_sampler_create", "qec_sampler_destroy", "qec_sampler_sample", "qec_sampler_sample_dev",
     "qec_sampler_check", "qec_sampler_tables", "qec_sampler_variant", "qec_sampler_counts",
     "qec_sampler_sample_events",
+    "qec_multi_sampler_create", "qec_multi_sampler_destroy", "qec_multi_sampler_sample",
+    "qec_multi_sampler_tally_dev", "qec_multi_enumerator_create", "qec_multi_enumerator_destroy",
+    "qec_multi_enumerator_num_paths", "qec_multi_enumerator_range", "qec_multi_enumerator_tally_dev",
     "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev", "qec_outcome_counts_noalloc_dev",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
@@ -358,6 +361,104 @@ class Sampler:
             _check(rc)
             n = n_out.value
             return rows[:n], cnt[:n], int(n_zero.value), tally
+
+
+class _Multi:
+    """common part of the multi-GPU handles: one process, several devices (include/qec_b200.h)"""
+
+    _destroy = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            getattr(lib(), self._destroy)(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _out(self, n, want_bits, want_tally):
+        nw = (max(n, 0) + 31) // 32
+        out = np.zeros((self.nc, nw), dtype=np.uint32) if want_bits else None
+        tally = np.zeros(tally_len(self.nc), dtype=np.uint64) if want_tally else None
+        return out, tally
+
+
+class MultiSampler(_Multi):
+    """``qec_multi_sampler``: FaultSampler on several GPUs of one box; results are one GPU's."""
+
+    _destroy = "qec_multi_sampler_destroy"
+
+    def __init__(self, devices, nq, nc, encoded_circ, loc_op, loc_class, class_p, class_codes, class_weights,
+                 seed: int):
+        self.nc, self.devices = int(nc), [int(d) for d in devices]
+        lib().qec_multi_sampler_destroy.restype = None
+        lib().qec_multi_sampler_destroy.argtypes = [C.c_void_p]
+        roff, rdata = rows_to_csr(encoded_circ)
+        loc_op, loc_class = _i32(loc_op), _i32(loc_class)
+        off = np.zeros(len(class_p) + 1, dtype=np.int32)
+        for i, codes in enumerate(class_codes):
+            off[i + 1] = off[i] + len(codes)
+        codes = np.fromiter((c for cs in class_codes for c in cs), dtype=np.uint8, count=int(off[-1]))
+        w = np.fromiter((x for ws in class_weights for x in ws), dtype=np.float64, count=int(off[-1]))
+        p = np.ascontiguousarray(class_p, dtype=np.float64)
+        devs = _i32(self.devices)
+        h = C.c_void_p()
+        _check(lib().qec_multi_sampler_create(
+            C.c_int(len(devs)), _p(devs), C.c_int(nq), C.c_int(nc), C.c_int(len(encoded_circ)), _p(roff),
+            _p(rdata), C.c_int(len(loc_op)), _p(loc_op), _p(loc_class), C.c_int(len(class_p)), _p(p), _p(off),
+            _p(codes), _p(w), C.c_uint64(seed & (2**64 - 1)), C.byref(h)))
+        self._h = h
+
+    def sample(self, shot_lo: int, n_shots: int, want_bits: bool = True, want_tally: bool = False):
+        out, tally = self._out(n_shots, want_bits, want_tally)
+        _check(lib().qec_multi_sampler_sample(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(out), _p(tally)))
+        return out, tally
+
+    def tally_dev(self, shot_lo: int, n_shots: int):
+        """(tally, device ms): tallies only, asynchronous on every device + peer reduce"""
+        _, tally = self._out(0, False, True)
+        ms = C.c_float()
+        _check(lib().qec_multi_sampler_tally_dev(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(tally),
+                                                 C.byref(ms)))
+        return tally, ms.value
+
+
+class MultiEnumerator(_Multi):
+    """``qec_multi_enumerator``: FaultEnumerator path ranges cut across several GPUs."""
+
+    _destroy = "qec_multi_enumerator_destroy"
+
+    def __init__(self, devices, nq, nc, encoded_circ, order, loc_op, pauli_codes_per_loc):
+        self.nc, self.devices = int(nc), [int(d) for d in devices]
+        lib().qec_multi_enumerator_destroy.restype = None
+        lib().qec_multi_enumerator_destroy.argtypes = [C.c_void_p]
+        roff, rdata = rows_to_csr(encoded_circ)
+        loc_op = _i32(loc_op)
+        off = np.zeros(len(loc_op) + 1, dtype=np.int32)
+        for i, codes in enumerate(pauli_codes_per_loc):
+            off[i + 1] = off[i] + len(codes)
+        flat = np.fromiter((c for codes in pauli_codes_per_loc for c in codes), dtype=np.uint8, count=int(off[-1]))
+        devs = _i32(self.devices)
+        h = C.c_void_p()
+        _check(lib().qec_multi_enumerator_create(
+            C.c_int(len(devs)), _p(devs), C.c_int(nq), C.c_int(nc), C.c_int(len(encoded_circ)), _p(roff),
+            _p(rdata), C.c_int(order), C.c_int(len(loc_op)), _p(loc_op), _p(off), _p(flat), C.byref(h)))
+        self._h = h
+
+    def num_paths(self) -> int:
+        n = C.c_int64()
+        _check(lib().qec_multi_enumerator_num_paths(self._h, C.byref(n)))
+        return n.value
+
+    def range(self, lo: int, hi: int, want_bits: bool = True, want_tally: bool = False):
+        out, tally = self._out(hi - lo, want_bits, want_tally)
+        _check(lib().qec_multi_enumerator_range(self._h, C.c_int64(lo), C.c_int64(hi), _p(out), _p(tally)))
+        return out, tally
+
+    def tally_dev(self, lo: int, hi: int):
+        _, tally = self._out(0, False, True)
+        ms = C.c_float()
+        _check(lib().qec_multi_enumerator_tally_dev(self._h, C.c_int64(lo), C.c_int64(hi), _p(tally), C.byref(ms)))
+        return tally, ms.value
 
 
 def outcome_histogram_dev(circuit: Circuit, d_bits: int, n_paths: int, d_keys: int, d_counts: int,

@@ -41,7 +41,10 @@ class FaultEnumerator:
     AVAILABLE_METHODS = {METHOD_STABILIZER, METHOD_PROPAGATOR}
 
     def __init__(self, circ, order: int = 1, method: str = METHOD_PROPAGATOR, model=None,
-                 sim_seed: int = 0):
+                 sim_seed: int = 0, devices=None):
+        """``devices`` (new; the reference is single-device): with more than one GPU index,
+        :meth:`enumerate_packed` cuts its path range across them in one process."""
+        self.devices = [int(d) for d in devices] if devices is not None else None
         if order < 1:
             raise Exception("order < 1")
         self.order = order
@@ -92,4 +95,13 @@ class FaultEnumerator:
     def enumerate_packed(self, lo: int = 0, hi: int = None, want_tally: bool = False):
         """Packed outcomes uint32[nc][ceil((hi-lo)/32)] (+ tallies) of paths [lo, hi)."""
         hi = self.num_paths() if hi is None else hi
+        if self.devices is not None and len(self.devices) > 1:
+            if getattr(self, "_multi", None) is None:
+                from qiskit_qec_b200 import _capi
+                self._multi = _capi.MultiEnumerator(
+                    self.devices, self.circuit.nq, self.circuit.nc, self.circuit.ops, self.order,
+                    self.faulty_ops_indices,
+                    [[_capi.pauli_code(p) for p in pl] for pl in self.faulty_ops_pauli_errors])
+            bits, tally = self._multi.range(lo, hi, True, want_tally)
+            return bits, tally
         return self.faultenum.enumerate_packed(lo, hi, want_tally)

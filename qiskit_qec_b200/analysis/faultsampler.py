@@ -26,8 +26,12 @@ class FaultSampler:
     METHOD_PROPAGATOR: str = "propagator"
     AVAILABLE_METHODS = {METHOD_STABILIZER, METHOD_PROPAGATOR}
 
-    def __init__(self, circ, model, method: str = METHOD_PROPAGATOR, sim_seed: int = 0):
+    def __init__(self, circ, model, method: str = METHOD_PROPAGATOR, sim_seed: int = 0, devices=None):
+        """``devices`` (new; the reference is single-device): GPU indices of this box.  With more
+        than one, the bulk call :meth:`sample_packed` cuts its shots across them (one process,
+        results bit-identical to one GPU); the per-shot calls stay on ``devices[0]``."""
         self.model = model
+        self.devices = [int(d) for d in devices] if devices is not None else None
         if method not in self.AVAILABLE_METHODS:
             raise ValueError(f"method {method} is not supported.")
         if method != self.METHOD_PROPAGATOR:
@@ -71,8 +75,29 @@ class FaultSampler:
 
     # bulk API -----------------------------------------------------------------------------
     def sample_packed(self, n: int, want_bits: bool = True, want_tally: bool = False):
-        """Packed outcomes uint32[nc][ceil(n/32)] and/or tallies of ``n`` fresh shots."""
+        """Packed outcomes uint32[nc][ceil(n/32)] and/or tallies of ``n`` fresh shots (on every
+        device of ``devices`` when several were given)."""
+        if self.devices is not None and len(self.devices) > 1:
+            multi = self._multi_sampler()
+            lo = self.faultsamp.get_cursor()
+            out = multi.sample(lo, int(n), want_bits, want_tally)
+            self.faultsamp.set_cursor(lo + (int(n) + 31) // 32 * 32)
+            return out
         return self.faultsamp.sample_packed(n, want_bits, want_tally)
+
+    def _multi_sampler(self):
+        if getattr(self, "_multi", None) is None:
+            from qiskit_qec_b200 import _capi
+            names = list(dict.fromkeys(self.faulty_ops_labels))
+            cls = {name: i for i, name in enumerate(names)}
+            lw = self.label_to_pauli_weight_tuple
+            self._multi = _capi.MultiSampler(
+                self.devices, self.circuit.nq, self.circuit.nc, self.circuit.ops, self.faulty_ops_indices,
+                [cls[lab] for lab in self.faulty_ops_labels],
+                [self.label_to_error_probability.get(name, 0.0) for name in names],
+                [[_capi.pauli_code(p) for p, _ in lw[name]] for name in names],
+                [[w for _, w in lw[name]] for name in names], self.sim_seed)
+        return self._multi
 
     def sample_events(self, n: int, want_tally: bool = False):
         """Compact form of ``n`` fresh shots: ``(word_cnt, events, tally)`` -- per 32-shot word its

@@ -172,7 +172,11 @@ static int64_t pipe_chunk_words(const qec_circuit *c, int64_t n_words) {
 }
 
 template <class Launch>
-static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, Launch launch) {
+static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, Launch launch,
+                         int64_t host_pitch_words = 0) {
+  // (host_pitch_words: row pitch of the host array when this call fills only a column range of
+  // it -- the multi-GPU entry points; 0 = the array is exactly n_words wide)
+  if (host_pitch_words <= 0) host_pitch_words = n_words;
   const int64_t cw = pipe_chunk_words(c, n_words);
   const size_t buf_bytes = (size_t)c->nc * cw * 4;
   for (int i = 0; i < 2; ++i) {
@@ -193,7 +197,7 @@ static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, L
     int rc = launch(w0, words, d, st);
     if (rc) return rc;
     CU(cudaEventRecord(c->pipe_done[k], st));
-    CU(cudaMemcpy2DAsync(host_bits + w0, (size_t)n_words * 4, d, (size_t)words * 4,
+    CU(cudaMemcpy2DAsync(host_bits + w0, (size_t)host_pitch_words * 4, d, (size_t)words * 4,
                          (size_t)words * 4, (size_t)c->nc, cudaMemcpyDeviceToHost, st));
   }
   CU(cudaStreamSynchronize(c->pipe_stream[0]));
@@ -995,8 +999,14 @@ extern "C" int qec_enumerator_range_dev(qec_enumerator *e, int64_t lo, int64_t h
   return enum_launch(e, lo, hi, d_out_bits, d_tally, (cudaStream_t)stream);
 }
 
+static int enumerator_range_host(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *out_bits,
+                                 int64_t pitch_words, uint64_t *tally);
 extern "C" int qec_enumerator_range(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *out_bits,
                                     uint64_t *tally) {
+  return enumerator_range_host(e, lo, hi, out_bits, 0, tally);
+}
+static int enumerator_range_host(qec_enumerator *e, int64_t lo, int64_t hi, uint32_t *out_bits,
+                                 int64_t pitch_words, uint64_t *tally) {
   ENUM_CHECK(e);
   if (lo < 0 || hi < lo || hi > e->total)
     return fail(QEC_ERR_INVALID, "bad path range [%lld, %lld) of %lld", (long long)lo,
@@ -1021,7 +1031,7 @@ extern "C" int qec_enumerator_range(qec_enumerator *e, int64_t lo, int64_t hi, u
                          const int64_t clo = lo + 32 * w0;
                          return enum_launch(e, clo, std::min<int64_t>(hi, clo + 32 * words), d,
                                             d_tally, st);
-                       });
+                       }, pitch_words);
     if (rc) return rc;
   } else if ((rc = enum_launch(e, lo, hi, nullptr, d_tally, 0))) {
     return rc;
@@ -2060,9 +2070,18 @@ extern "C" int qec_sampler_sample_dev(qec_sampler *s, int64_t shot_lo, int64_t n
   return sample_launch(s, shot_lo, n_shots, d_out_bits, d_tally, X, (cudaStream_t)stream);
 }
 
+static int sampler_sample_host(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint32_t *out_bits,
+                               int64_t pitch_words, uint64_t *tally, uint32_t *fault_cnt,
+                               uint32_t *fault_ev, int fault_cap, int *fault_cap_needed);
 extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
                                   uint32_t *out_bits, uint64_t *tally, uint32_t *fault_cnt,
                                   uint32_t *fault_ev, int fault_cap, int *fault_cap_needed) {
+  return sampler_sample_host(s, shot_lo, n_shots, out_bits, 0, tally, fault_cnt, fault_ev, fault_cap,
+                             fault_cap_needed);
+}
+static int sampler_sample_host(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint32_t *out_bits,
+                               int64_t pitch_words, uint64_t *tally, uint32_t *fault_cnt,
+                               uint32_t *fault_ev, int fault_cap, int *fault_cap_needed) {
   int rc = sample_args(s, shot_lo, n_shots);
   if (rc) return rc;
   qec_circuit *c = s->c;
@@ -2094,7 +2113,7 @@ extern "C" int qec_sampler_sample(qec_sampler *s, int64_t shot_lo, int64_t n_sho
                            return sample_launch(s, shot_lo + 32 * w0,
                                                 std::min<int64_t>(n_shots - 32 * w0, 32 * words), d,
                                                 d_tally, X, st);
-                         });
+                         }, pitch_words);
     } else {
       if (out_bits && (rc = c->out_bits.ensure(std::max<size_t>(out_bytes, 4)))) return rc;
       rc = sample_launch(s, shot_lo, n_shots, out_bits ? (uint32_t *)c->out_bits.p : nullptr,
@@ -2576,4 +2595,317 @@ extern "C" int qec_outcome_counts_noalloc_dev(qec_circuit *c, const uint32_t *d_
   k_noalloc_status<<<1, 1, 0, st>>>((unsigned long long *)d_out_status, max_out);
   CU(cudaGetLastError());
   return 0;
+}
+
+// ---- multi-GPU in one process ---------------------------------------------------
+// The path shards with no data-path collective: every shot and every fault path is independent
+// (the reference re-zeroes the frame per propagate call, errorpropagator.cpp:262-263).  A multi
+// handle owns one circuit + sampler / enumerator per device; a call cuts its shot / path range
+// into contiguous pieces whose boundaries are whole 32-unit lane words (the arithmetic of
+// qiskit_qec_b200/sharding.py), so that the pieces' packed outputs concatenate to the single-GPU
+// output and -- the Philox counters being functions of the GLOBAL shot position -- N GPUs give
+// the bits of one GPU.  Only the tallies are reduced:
+//   * host-buffer calls: one host thread per device runs the single-GPU host path on its piece
+//     (its column range of the caller's [nc][n_words] array), the per-device tallies are summed;
+//   * *_tally_dev calls: all devices launch asynchronously, then device 0 sums the peers'
+//     tallies read over NVLink peer mappings (k_tally_reduce_peers): no collective launch.
+#include <thread>
+
+struct MultiBase {
+  std::vector<int> dev;
+  std::vector<qec_circuit *> circ;
+  std::vector<cudaStream_t> st;
+  std::vector<cudaEvent_t> done;
+  std::vector<uint64_t *> d_tally;       // per device
+  uint64_t *d_sum = nullptr;             // device 0
+  const unsigned long long **d_ptrs = nullptr;  // device 0: the peers' tally pointers
+  cudaEvent_t t0 = nullptr, t1 = nullptr;  // device 0
+  bool peers = false;
+  int nc = 0;
+  size_t tl() const { return QEC_TALLY_LEN(nc); }
+};
+
+// [cut[k], cut[k + 1]) of device k when `total` units starting at a lane-word boundary are cut
+// into n pieces of whole lane words (pieces differ by at most 32 units)
+static std::vector<int64_t> multi_cuts(int64_t total, int n) {
+  const int64_t words = (total + 31) / 32;
+  std::vector<int64_t> cut(n + 1);
+  for (int k = 0; k <= n; ++k) cut[k] = std::min<int64_t>(words * k / n * 32, total);
+  return cut;
+}
+
+static int multi_setup(MultiBase &m, int n_dev, const int *devices, int nq, int nc, int n_ops,
+                       const int32_t *row_off, const int32_t *row_data) {
+  if (n_dev < 1 || n_dev > 64 || !devices) return fail(QEC_ERR_INVALID, "need between 1 and 64 devices");
+  for (int a = 0; a < n_dev; ++a)
+    for (int b = a + 1; b < n_dev; ++b)
+      if (devices[a] == devices[b]) return fail(QEC_ERR_INVALID, "device %d listed twice", devices[a]);
+  m.nc = nc;
+  for (int k = 0; k < n_dev; ++k) {
+    qec_circuit *c = nullptr;
+    const int rc = qec_circuit_create(devices[k], nq, nc, n_ops, row_off, row_data, &c);
+    if (rc) return rc;
+    m.dev.push_back(devices[k]);
+    m.circ.push_back(c);
+    cudaStream_t s;
+    cudaEvent_t e;
+    uint64_t *t = nullptr;
+    CU(cudaSetDevice(devices[k]));
+    CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(qec_dev_alloc((void **)&t, m.tl() * 8));
+    m.st.push_back(s); m.done.push_back(e); m.d_tally.push_back(t);
+  }
+  // device 0 reads its peers' tallies directly when every peer mapping can be enabled
+  CU(cudaSetDevice(m.dev[0]));
+  CU(cudaEventCreate(&m.t0));
+  CU(cudaEventCreate(&m.t1));
+  CU(qec_dev_alloc((void **)&m.d_sum, m.tl() * 8));
+  m.peers = true;
+  for (int k = 1; k < n_dev; ++k) {
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, m.dev[0], m.dev[k]) != cudaSuccess || !can) { m.peers = false; break; }
+    const cudaError_t e = cudaDeviceEnablePeerAccess(m.dev[k], 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { m.peers = false; break; }
+    cudaGetLastError();
+  }
+  if (m.peers) {
+    CU(qec_dev_alloc((void **)&m.d_ptrs, (size_t)n_dev * sizeof(void *)));
+    CU(cudaMemcpy(m.d_ptrs, m.d_tally.data(), (size_t)n_dev * sizeof(void *), cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+static void multi_teardown(MultiBase &m) {
+  for (size_t k = 0; k < m.dev.size(); ++k) {
+    cudaSetDevice(m.dev[k]);
+    cudaDeviceSynchronize();
+    if (k < m.d_tally.size() && m.d_tally[k]) qec_dev_free(m.d_tally[k]);
+    if (k == 0) {
+      if (m.d_sum) qec_dev_free(m.d_sum);
+      if (m.d_ptrs) qec_dev_free((void *)m.d_ptrs);
+      if (m.t0) cudaEventDestroy(m.t0);
+      if (m.t1) cudaEventDestroy(m.t1);
+    }
+    if (k < m.st.size()) cudaStreamDestroy(m.st[k]);
+    if (k < m.done.size()) cudaEventDestroy(m.done[k]);
+  }
+  for (qec_circuit *c : m.circ) qec_circuit_destroy(c);
+}
+
+// Asynchronous tallies-only run on every device + the reduce on device 0.  launch(k, lo, hi, tally,
+// stream) queues device k's piece.  *elapsed_ms: device time from before the first kernel to after
+// the reduce, measured with events on device 0 (every other stream first waits on the start event).
+template <class Launch>
+static int multi_tally_dev(MultiBase &m, const std::vector<int64_t> &cut, uint64_t *tally, float *elapsed_ms,
+                           Launch launch) {
+  const int n = (int)m.dev.size();
+  const size_t tl = m.tl();
+  CU(cudaSetDevice(m.dev[0]));
+  CU(cudaEventRecord(m.t0, m.st[0]));
+  for (int k = 0; k < n; ++k) {
+    CU(cudaSetDevice(m.dev[k]));
+    if (k > 0) CU(cudaStreamWaitEvent(m.st[k], m.t0, 0));
+    CU(cudaMemsetAsync(m.d_tally[k], 0, tl * 8, m.st[k]));
+    if (cut[k + 1] > cut[k]) {
+      const int rc = launch(k, cut[k], cut[k + 1], m.d_tally[k], m.st[k]);
+      if (rc) return rc;
+    }
+    CU(cudaEventRecord(m.done[k], m.st[k]));
+  }
+  CU(cudaSetDevice(m.dev[0]));
+  std::vector<uint64_t> part;
+  if (m.peers) {
+    for (int k = 1; k < n; ++k) CU(cudaStreamWaitEvent(m.st[0], m.done[k], 0));
+    qec_launch_tally_reduce_peers(m.st[0], m.d_ptrs, n, (int)tl, (unsigned long long *)m.d_sum);
+    CU(cudaEventRecord(m.t1, m.st[0]));
+    CU(cudaGetLastError());
+    if (tally) CU(cudaMemcpyAsync(tally, m.d_sum, tl * 8, cudaMemcpyDeviceToHost, m.st[0]));
+    CU(cudaStreamSynchronize(m.st[0]));
+  } else {
+    // no peer mapping (not an NVLink box): the per-device tallies come back over PCIe
+    part.assign((size_t)n * tl, 0);
+    for (int k = 0; k < n; ++k) {
+      CU(cudaSetDevice(m.dev[k]));
+      CU(cudaMemcpyAsync(part.data() + (size_t)k * tl, m.d_tally[k], tl * 8, cudaMemcpyDeviceToHost, m.st[k]));
+    }
+    for (int k = 0; k < n; ++k) { CU(cudaSetDevice(m.dev[k])); CU(cudaStreamSynchronize(m.st[k])); }
+    CU(cudaSetDevice(m.dev[0]));
+    CU(cudaEventRecord(m.t1, m.st[0]));
+    CU(cudaStreamSynchronize(m.st[0]));
+    if (tally) {
+      memset(tally, 0, tl * 8);
+      for (int k = 0; k < n; ++k) for (size_t i = 0; i < tl; ++i) tally[i] += part[(size_t)k * tl + i];
+    }
+  }
+  if (elapsed_ms) CU(cudaEventElapsedTime(elapsed_ms, m.t0, m.t1));
+  return 0;
+}
+
+// Host-buffer run: one host thread per device, each through the single-GPU host path on its
+// column range of the caller's array; per-device tallies summed.  run(k, lo, hi, bits, tally).
+template <class Run>
+static int multi_host(MultiBase &m, const std::vector<int64_t> &cut, uint64_t *tally, Run run) {
+  const int n = (int)m.dev.size();
+  const size_t tl = m.tl();
+  std::vector<uint64_t> part(tally ? (size_t)n * tl : 0, 0);
+  std::vector<int> rcs(n, 0);
+  std::vector<std::string> msgs(n);
+  std::vector<std::thread> th;
+  for (int k = 0; k < n; ++k)
+    th.emplace_back([&, k]() {
+      if (cut[k + 1] <= cut[k]) return;
+      rcs[k] = run(k, cut[k], cut[k + 1], tally ? part.data() + (size_t)k * tl : nullptr);
+      if (rcs[k]) msgs[k] = qec_last_error();   // (the error string is thread local)
+    });
+  for (auto &t : th) t.join();
+  for (int k = 0; k < n; ++k)
+    if (rcs[k]) return fail(rcs[k], "device %d: %s", m.dev[k], msgs[k].c_str());
+  if (tally) {
+    memset(tally, 0, tl * 8);
+    for (int k = 0; k < n; ++k) for (size_t i = 0; i < tl; ++i) tally[i] += part[(size_t)k * tl + i];
+  }
+  return 0;
+}
+
+struct qec_multi_sampler {
+  MultiBase m;
+  std::vector<qec_sampler *> s;
+};
+struct qec_multi_enumerator {
+  MultiBase m;
+  std::vector<qec_enumerator *> e;
+};
+
+extern "C" void qec_multi_sampler_destroy(qec_multi_sampler *ms) {
+  if (!ms) return;
+  for (qec_sampler *s : ms->s) qec_sampler_destroy(s);
+  multi_teardown(ms->m);
+  delete ms;
+}
+
+extern "C" int qec_multi_sampler_create(int n_dev, const int *devices, int nq, int nc, int n_ops,
+                                        const int32_t *row_off, const int32_t *row_data, int L,
+                                        const int32_t *loc_op, const int32_t *loc_class, int n_classes,
+                                        const double *class_p, const int32_t *class_off,
+                                        const uint8_t *class_codes, const double *class_weight,
+                                        uint64_t seed, qec_multi_sampler **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  qec_multi_sampler *ms = new qec_multi_sampler;
+  int rc = multi_setup(ms->m, n_dev, devices, nq, nc, n_ops, row_off, row_data);
+  for (int k = 0; !rc && k < n_dev; ++k) {
+    qec_sampler *s = nullptr;
+    rc = qec_sampler_create(ms->m.circ[k], L, loc_op, loc_class, n_classes, class_p, class_off, class_codes,
+                            class_weight, seed, &s);
+    if (!rc) ms->s.push_back(s);
+  }
+  if (rc) {
+    const std::string keep = g_err;
+    qec_multi_sampler_destroy(ms);
+    g_err = keep;
+    return rc;
+  }
+  *out = ms;
+  return 0;
+}
+
+extern "C" int qec_multi_sampler_sample(qec_multi_sampler *ms, int64_t shot_lo, int64_t n_shots,
+                                        uint32_t *out_bits, uint64_t *tally) {
+  if (!ms) return fail(QEC_ERR_INVALID, "null multi sampler");
+  int rc = sample_args(ms->s[0], shot_lo, n_shots);
+  if (rc) return rc;
+  if (tally) memset(tally, 0, ms->m.tl() * 8);
+  if (n_shots == 0) return 0;
+  const int64_t n_words = (n_shots + 31) / 32;
+  const std::vector<int64_t> cut = multi_cuts(n_shots, (int)ms->m.dev.size());
+  return multi_host(ms->m, cut, tally, [&](int k, int64_t lo, int64_t hi, uint64_t *t) {
+    return sampler_sample_host(ms->s[k], shot_lo + lo, hi - lo, out_bits ? out_bits + lo / 32 : nullptr,
+                               n_words, t, nullptr, nullptr, 0, nullptr);
+  });
+}
+
+extern "C" int qec_multi_sampler_tally_dev(qec_multi_sampler *ms, int64_t shot_lo, int64_t n_shots,
+                                           uint64_t *tally, float *elapsed_ms) {
+  if (!ms) return fail(QEC_ERR_INVALID, "null multi sampler");
+  int rc = sample_args(ms->s[0], shot_lo, n_shots);
+  if (rc) return rc;
+  const std::vector<int64_t> cut = multi_cuts(n_shots, (int)ms->m.dev.size());
+  const QecSampleExport X{nullptr, nullptr, 0};
+  rc = multi_tally_dev(ms->m, cut, tally, elapsed_ms, [&](int k, int64_t lo, int64_t hi, uint64_t *t, cudaStream_t st) {
+    return sample_launch(ms->s[k], shot_lo + lo, hi - lo, nullptr, t, X, st);
+  });
+  if (rc) return rc;
+  for (size_t k = 0; k < ms->s.size(); ++k) {
+    CU(cudaSetDevice(ms->m.dev[k]));
+    if ((rc = sampler_check(ms->s[k]))) return rc;
+  }
+  return 0;
+}
+
+extern "C" void qec_multi_enumerator_destroy(qec_multi_enumerator *me) {
+  if (!me) return;
+  for (qec_enumerator *e : me->e) qec_enumerator_destroy(e);
+  multi_teardown(me->m);
+  delete me;
+}
+
+extern "C" int qec_multi_enumerator_create(int n_dev, const int *devices, int nq, int nc, int n_ops,
+                                           const int32_t *row_off, const int32_t *row_data, int order, int L,
+                                           const int32_t *loc_op, const int32_t *pauli_off,
+                                           const uint8_t *pauli_codes, qec_multi_enumerator **out) {
+  if (!out) return fail(QEC_ERR_INVALID, "null output pointer");
+  *out = nullptr;
+  qec_multi_enumerator *me = new qec_multi_enumerator;
+  int rc = multi_setup(me->m, n_dev, devices, nq, nc, n_ops, row_off, row_data);
+  for (int k = 0; !rc && k < n_dev; ++k) {
+    qec_enumerator *e = nullptr;
+    rc = qec_enumerator_create(me->m.circ[k], order, L, loc_op, pauli_off, pauli_codes, &e);
+    if (!rc) me->e.push_back(e);
+  }
+  if (rc) {
+    const std::string keep = g_err;
+    qec_multi_enumerator_destroy(me);
+    g_err = keep;
+    return rc;
+  }
+  *out = me;
+  return 0;
+}
+
+extern "C" int qec_multi_enumerator_num_paths(const qec_multi_enumerator *me, int64_t *n) {
+  if (!me) return fail(QEC_ERR_INVALID, "null multi enumerator");
+  return qec_enumerator_num_paths(me->e[0], n);
+}
+
+static int multi_enum_args(const qec_multi_enumerator *me, int64_t lo, int64_t hi) {
+  if (!me) return fail(QEC_ERR_INVALID, "null multi enumerator");
+  ENUM_CHECK(me->e[0]);
+  if (lo < 0 || hi < lo || hi > me->e[0]->total)
+    return fail(QEC_ERR_INVALID, "bad path range [%lld, %lld) of %lld", (long long)lo, (long long)hi,
+                (long long)me->e[0]->total);
+  return 0;
+}
+
+extern "C" int qec_multi_enumerator_range(qec_multi_enumerator *me, int64_t lo, int64_t hi,
+                                          uint32_t *out_bits, uint64_t *tally) {
+  int rc = multi_enum_args(me, lo, hi);
+  if (rc) return rc;
+  if (tally) memset(tally, 0, me->m.tl() * 8);
+  if (hi == lo) return 0;
+  const int64_t n_words = (hi - lo + 31) / 32;
+  const std::vector<int64_t> cut = multi_cuts(hi - lo, (int)me->m.dev.size());
+  return multi_host(me->m, cut, tally, [&](int k, int64_t a, int64_t b, uint64_t *t) {
+    return enumerator_range_host(me->e[k], lo + a, lo + b, out_bits ? out_bits + a / 32 : nullptr, n_words, t);
+  });
+}
+
+extern "C" int qec_multi_enumerator_tally_dev(qec_multi_enumerator *me, int64_t lo, int64_t hi,
+                                              uint64_t *tally, float *elapsed_ms) {
+  int rc = multi_enum_args(me, lo, hi);
+  if (rc) return rc;
+  const std::vector<int64_t> cut = multi_cuts(hi - lo, (int)me->m.dev.size());
+  return multi_tally_dev(me->m, cut, tally, elapsed_ms, [&](int k, int64_t a, int64_t b, uint64_t *t, cudaStream_t st) {
+    return enum_launch(me->e[k], lo + a, lo + b, nullptr, t, st);
+  });
 }

@@ -430,6 +430,20 @@ k_ev_compact(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ ev, 
 }
 
 // ------------------------------------------------------------------------------------------
+// Multi-GPU tally reduce without a collective launch: device 0 sums the tallies of its peers,
+// read straight from their memory over NVLink peer mappings (ptrs[k] = tally of device k; the
+// caller's stream has waited on every device's kernels).  ~1.7 KB per device: latency-bound.
+__global__ void __launch_bounds__(256)
+k_tally_reduce_peers(const unsigned long long *const *__restrict__ ptrs, const int n_dev, const int len,
+                     unsigned long long *__restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) {
+    unsigned long long v = 0;
+    for (int k = 0; k < n_dev; ++k) v += ptrs[k][i];
+    out[i] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Integer-pipe roofline denominator: 8 independent LOP3 chains per thread, no memory.  Every
 // chain step is ONE `lop3.b32` written as inline PTX (asm volatile), so that the ops counted by
 // qec_measure_int_peak are the LOP3 instructions the SM executes: ptxas neither merges nor
@@ -540,6 +554,11 @@ void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const ui
   k_ev_block_sums<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, n_words, two_ended, cap, block_sums, overflow);
   k_ev_scan_blocks<<<1, 1024, 0, stream>>>(block_sums, n_blocks, total);
   k_ev_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, ev, n_words, two_ended, cap, block_sums, out_cnt, out_ev, pool_cap);
+}
+
+void qec_launch_tally_reduce_peers(cudaStream_t stream, const unsigned long long *const *ptrs, int n_dev,
+                                   int len, unsigned long long *out) {
+  k_tally_reduce_peers<<<(len + 255) / 256, 256, 0, stream>>>(ptrs, n_dev, len, out);
 }
 
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink) {

@@ -51,6 +51,9 @@ void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const ui
                               int two_ended, int cap, uint32_t *block_sums, uint32_t *overflow,
                               unsigned long long *total, uint16_t *out_cnt, uint32_t *out_ev,
                               unsigned long long pool_cap);
+// multi-GPU: device 0 sums the peers' tallies through peer pointers
+void qec_launch_tally_reduce_peers(cudaStream_t stream, const unsigned long long *const *ptrs, int n_dev,
+                                   int len, unsigned long long *out);
 void qec_launch_int_peak(cudaStream_t stream, int grid, int block, int iters, uint32_t *sink);
 size_t qec_kernel_smem_bytes(int kind, int nq, int nc, int T, uint32_t B, uint32_t K1);
 int qec_kernel_set_smem_attr(int kind, int order, size_t smem);
