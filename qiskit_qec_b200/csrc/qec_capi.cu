@@ -2653,7 +2653,9 @@ static int multi_setup(MultiBase &m, int n_dev, const int *devices, int nq, int 
     CU(cudaSetDevice(devices[k]));
     CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    CU(qec_dev_alloc((void **)&t, m.tl() * 8));
+    // plain cudaMalloc on purpose: device 0 reads these through peer mappings, and memory of the
+    // stream-ordered pool (qec_dev_alloc) is not peer-accessible unless the pool is opened up
+    CU(cudaMalloc((void **)&t, m.tl() * 8));
     m.st.push_back(s); m.done.push_back(e); m.d_tally.push_back(t);
   }
   // device 0 reads its peers' tallies directly when every peer mapping can be enabled
@@ -2680,7 +2682,7 @@ static void multi_teardown(MultiBase &m) {
   for (size_t k = 0; k < m.dev.size(); ++k) {
     cudaSetDevice(m.dev[k]);
     cudaDeviceSynchronize();
-    if (k < m.d_tally.size() && m.d_tally[k]) qec_dev_free(m.d_tally[k]);
+    if (k < m.d_tally.size() && m.d_tally[k]) cudaFree(m.d_tally[k]);
     if (k == 0) {
       if (m.d_sum) qec_dev_free(m.d_sum);
       if (m.d_ptrs) qec_dev_free((void *)m.d_ptrs);

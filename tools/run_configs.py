@@ -50,8 +50,8 @@ def timed(fn, reps, dev, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shots2", type=int, default=100_000_000)
-    ap.add_argument("--shots4", type=int, default=20_000_000, help="global shots of config 4")
-    ap.add_argument("--paths5", type=int, default=200_000_000, help="order-3 paths of config 5 to run")
+    ap.add_argument("--shots4", type=int, default=1_000_000_000, help="global shots of config 4 (BASELINE: 1e9)")
+    ap.add_argument("--paths5", type=int, default=400_000_000, help="order-3 paths of config 5 to run (all 3.4e8 by default)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -122,7 +122,7 @@ def main():
     enum_cfg("cfg1 rep d=3 T=2 order 1", repetition_code_circuit(3, 2), 1)
     samp_cfg("cfg2 surface d=5 T=5 sampler", surface_code_circuit(5, 5), args.shots2)
     enum_cfg("cfg3 surface d=5 T=5 order 2", surface_code_circuit(5, 5), 2)
-    samp_cfg(f"cfg4 surface d=11 T=11 sampler, histogram/tallies only ({args.shots4} of 1e9 shots)",
+    samp_cfg(f"cfg4 surface d=11 T=11 sampler, tallies only ({args.shots4} shots; BASELINE 1e9)",
              surface_code_circuit(11, 11), args.shots4, bits=False)
     links, schedule, color = heavy_hex_27_arc_layout()
     enum_cfg(f"cfg5 heavy-hex ARC T=3 order 3, tallies only (first {args.paths5} paths)",
