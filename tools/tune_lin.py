@@ -55,12 +55,13 @@ def run(mode, warps, n_shots=100_000_000, tally=True, bits=True, reps=5, d=5, T=
 if __name__ == "__main__":
     if len(sys.argv) > 1:
         for spec in sys.argv[1:]:
+            spec, _, opt = spec.partition("!")      # !nt = no tallies, !nb = no packed bits
             m, _, w = spec.partition(":")
             w, _, npx = w.partition("/")
             npx, _, dt = npx.partition("@")     # mode:warps/np@d,T
             dd, tt = (int(x) for x in dt.split(",")) if dt else (5, 5)
             run(m or None, int(w) if w else 0, np_=int(npx) if npx else 0, d=dd, T=tt,
-                n_shots=100_000_000 if dd <= 5 else 20_000_000)
+                n_shots=100_000_000 if dd <= 5 else 20_000_000, tally=opt != "nt", bits=opt != "nb")
     else:
         run("lanes", 0)
         for w in (8, 10, 12, 14, 15, 16):
