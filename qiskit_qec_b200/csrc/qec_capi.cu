@@ -696,6 +696,38 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
   return 0;
 }
 
+// Read-out program of the lane-owned accumulators (lanes_readout, qec_linear.cu): four rows per
+// pass, one per lane group; whole chains of the time-difference basis (c0 -> succ(c0) -> ...) are
+// dealt to the four groups, longest first onto the least loaded, so a group meets the rows of a
+// chain in consecutive passes and undoes the basis with a running XOR in registers.  Entry:
+// row | 1 << 9 valid | 1 << 31 the row continues the chain of the group's previous pass; queues
+// are padded to a whole number of trips (QEC_LANES_UNROLL = 4 passes) with the zero row nc + 1.
+static std::vector<uint32_t> lanes_readout_prog(int nc, const std::vector<int> &pred,
+                                                const std::vector<int> &succ, bool use_diff) {
+  std::vector<std::vector<int>> chains;
+  for (int cb = 0; cb < nc; ++cb) {
+    if (use_diff && pred[cb] >= 0) continue;
+    chains.emplace_back();
+    for (int x = cb; x >= 0; x = use_diff ? succ[x] : -1) chains.back().push_back(x);
+  }
+  std::stable_sort(chains.begin(), chains.end(),
+                   [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
+  std::vector<uint32_t> q[4];
+  for (const auto &ch : chains) {
+    int best = 0;
+    for (int g = 1; g < 4; ++g) if (q[g].size() < q[best].size()) best = g;
+    for (size_t k = 0; k < ch.size(); ++k)
+      q[best].push_back((uint32_t)ch[k] | (1u << 9) | (k ? (1u << 31) : 0u));
+  }
+  size_t n = 0;
+  for (int g = 0; g < 4; ++g) n = std::max(n, q[g].size());
+  n = (n + 3) & ~(size_t)3;
+  std::vector<uint32_t> prog(n * 4, (uint32_t)nc + 1u);
+  for (int g = 0; g < 4; ++g)
+    for (size_t k = 0; k < q[g].size(); ++k) prog[k * 4 + g] = q[g][k];
+  return prog;
+}
+
 // Linear-response enumerator (k_enum_lanes): the signature of every single fault (one frame
 // propagation each, on the GPU, through qec_propagate_batch), as 8-byte records in the
 // time-difference basis when that shortens them, plus the read-out schedule -- the same tables
@@ -786,29 +818,7 @@ static int enum_plan_linear(qec_enumerator *e) {
     for (int k = 0; k < 7; ++k) by[1 + k] = k < (int)lists[f].size() ? (uint8_t)lists[f][k] : (uint8_t)c->nc;
     memcpy(&rec[2 * f], by, 8);
   }
-  // read-out schedule (as in sampler_plan_linear: four rows per pass, 16 per trip, a row never in
-  // one trip with the previous row of its chain)
-  std::vector<uint32_t> prog;
-  {
-    const uint32_t none = (uint32_t)c->nc + 1u;
-    const size_t trip = 16;
-    std::vector<int> cur;
-    auto flush = [&]() {
-      while (!cur.empty() && cur.size() < trip) cur.push_back(-1);
-      for (int x : cur) {
-        if (x < 0) { prog.push_back(none | (none << 8)); continue; }
-        const int pr = use_diff ? pred[x] : -1, sc = use_diff ? succ[x] : -1;
-        prog.push_back((uint32_t)x | ((pr >= 0 ? (uint32_t)pr : none) << 8) | (sc >= 0 ? (1u << 17) : 0u) | (1u << 18));
-      }
-      cur.clear();
-    };
-    for (int cb = 0; cb < c->nc; ++cb) {
-      const int pr = use_diff ? pred[cb] : -1;
-      if (cur.size() == trip || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
-      cur.push_back(cb);
-    }
-    flush();
-  }
+  const std::vector<uint32_t> prog = lanes_readout_prog(c->nc, pred, succ, use_diff);
   const DevInfo &di = *c->info;
   const int e32 = e->total < (1ll << 32) ? 1 : 0;
   const int w_env = env_int("QEC_B200_ENUM_WARPS", 0);
@@ -1354,31 +1364,9 @@ static int sampler_plan_linear(qec_sampler *s) {
     smem = words(lg, info_s, sig_s);
     return true;
   };
-  // read-out passes of the lane-stream variant: four rows per pass, four passes per trip of the
-  // kernel's loop (QEC_LANES_UNROLL), all of a trip's rows loaded before any is stored: a row is
-  // never in one trip with the previous row of its chain.  Entry: row | previous row << 8
-  // (nc + 1 = the zero row: none) | 1 << 17 if a row follows | 1 << 18 valid
+  // read-out passes of the lane-stream variant (lanes_readout_prog)
   std::vector<uint32_t> lanes_prog;
-  if (c->nc <= 254) {
-    const uint32_t none = (uint32_t)c->nc + 1u;
-    const size_t trip = 16;
-    std::vector<int> cur;
-    auto flush = [&]() {
-      while (!cur.empty() && cur.size() < trip) cur.push_back(-1);
-      for (int x : cur) {
-        if (x < 0) { lanes_prog.push_back(none | (none << 8)); continue; }
-        const int pr = use_diff ? pred[x] : -1, sc = use_diff ? succ[x] : -1;
-        lanes_prog.push_back((uint32_t)x | ((pr >= 0 ? (uint32_t)pr : none) << 8) | (sc >= 0 ? (1u << 17) : 0u) | (1u << 18));
-      }
-      cur.clear();
-    };
-    for (int cb = 0; cb < c->nc; ++cb) {
-      const int pr = use_diff ? pred[cb] : -1;
-      if (cur.size() == trip || (pr >= 0 && std::find(cur.begin(), cur.end(), pr) != cur.end())) flush();
-      cur.push_back(cb);
-    }
-    flush();
-  }
+  if (c->nc <= 254) lanes_prog = lanes_readout_prog(c->nc, pred, succ, use_diff);
   bool found = false;
   int warp_mode = 0, threads = T, rec8 = 0, rec_s = 0, fast = 0, lane_mode = 0;
   const char *lmode = std::getenv("QEC_B200_LIN_MODE");

@@ -460,6 +460,9 @@ __device__ __forceinline__ void st_s128z(uint32_t addr) {
 __device__ __forceinline__ void red_xor_if(uint32_t cond, uint32_t addr, uint32_t v) {
   asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.xor.b32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_add_if(bool cond, uint32_t addr, uint32_t v) {
+  asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"((uint32_t)cond), "r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void red_add_if(uint32_t cond, uint32_t addr, uint32_t v) {
   asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
 }
@@ -811,52 +814,58 @@ __device__ __forceinline__ void lanes_apply(const uint32_t p, const bool ok, con
 }
 
 // Read-out of a lane-owned accumulator acc[row][32 word columns] (batch = 32 output words
-// starting at word w0): four rows per pass (8 lanes x 128 bits per row: conflict-free shared
-// loads, one full 128-byte line per row stored), QEC_LANES_UNROLL passes per trip with all
-// shared-memory loads first (the host schedules the passes so that no row of a trip has its
-// previous row inside the same trip); the time-difference basis is undone in place and every row
-// is left zero.  Per-row ones are added to the warp's tally row; returns this lane's share of the
-// batch's non-zero outcomes (lanes 0..7 carry it).
-template <bool TALLY, bool BITS>
-__device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
-                                                  const uint32_t prog_s, const uint32_t n_steps,
-                                                  const long long w0, const bool vec_ok, const int lane) {
+// starting at word w0).  Four rows per pass: lane group g = lane >> 3 takes one row, its eight lanes
+// 128 bits each (conflict-free shared loads, one full 128-byte line per row stored).  The host deals
+// whole chains of the time-difference basis (c0 -> succ(c0) -> ...) to the four groups, so a group
+// meets the rows of a chain in consecutive passes and undoes the basis with a running XOR held in
+// registers: one LDS.128 and one zeroing STS.128 per row, no second load and no write-back.
+// Program entry (qec_capi.cu, lanes_readout_prog): row | 1 << 9 valid | 1 << 31 the row continues
+// the chain of the group's previous pass; pad entries name the always-zero row nc + 1.  Per-row ones
+// go to the warp's tally row by red.shared.add from one lane per group (fire and forget: the
+// load / add / store it replaces serialised the trips); returns this lane's share of the batch's
+// non-zero outcomes (lanes 0..7 carry it).  FAST: the batch's 32 words all exist and the rows are
+// 16-byte aligned.
+template <bool TALLY, bool BITS, bool FAST>
+__device__ __forceinline__ void lanes_readout_loop(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
+                                                   const uint32_t prog_s, const uint32_t n_steps,
+                                                   const long long w0, const int lane, uint4 &anyv) {
   const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
-  const bool whole = w0 >= 0 && w0 + 32 <= O.n_words;  // the batch's 32 words all exist
-  const bool fastst = whole && vec_ok;
-  uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
+  const uint32_t col_s = acc_s + (c4 << 2);
+  const uint32_t pe_s = prog_s + (rsub << 2);
+  // (row * bytes per row in one 32 x 32 -> 64 multiply-add; rows of 2^32 bytes or more take the slow form)
+  const unsigned long long rowbytes = (unsigned long long)O.n_words << 2;
+  const bool row32 = rowbytes < (1ull << 32);
+  char *const colp = reinterpret_cast<char *>(O.bits) + ((w0 + (long long)c4) << 2);
+  const bool head = c4 == 0u;
+  uint4 pv = make_uint4(0u, 0u, 0u, 0u);
   for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
-    // entry: row | previous row of its chain << 8 (nc + 1, the zero row: none) | 1 << 17 if a
-    // row follows in the chain | 1 << 18 if the slot holds a row at all
-    uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL], ap[QEC_LANES_UNROLL];
-    uint4 v[QEC_LANES_UNROLL], pv[QEC_LANES_UNROLL];
+    uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL];
+    uint4 v[QEC_LANES_UNROLL];
 #pragma unroll
-    for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(prog_s + ((((pass + u) << 2) + rsub) << 2));
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(pe_s + ((pass + u) << 4));
 #pragma unroll
     for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-      a[u] = acc_s + ((e[u] & 0xFFu) << 7) + (c4 << 2);
-      ap[u] = acc_s + (((e[u] >> 8) & 0xFFu) << 7) + (c4 << 2);
+      a[u] = col_s + ((e[u] & 0xFFu) << 7);
       v[u] = ld_s128(a[u]);
-      pv[u] = ld_s128(ap[u]);
     }
     uint32_t cpk[QEC_LANES_UNROLL / 2];
 #pragma unroll
     for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-      v[u].x ^= pv[u].x; v[u].y ^= pv[u].y; v[u].z ^= pv[u].z; v[u].w ^= pv[u].w;
-      st_s128z(ap[u]);
-      const uint32_t keep = (e[u] & 0x20000u) ? 0xFFFFFFFFu : 0u;  // the next row of the chain needs this one
-      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(a[u]), "r"(v[u].x & keep), "r"(v[u].y & keep), "r"(v[u].z & keep), "r"(v[u].w & keep) : "memory");
-      const bool rowok = (e[u] & 0x40000u) != 0u;
+      st_s128z(a[u]);
+      const uint32_t m = (uint32_t)((int)e[u] >> 31);  // all ones: XOR the previous row of the chain in
+      v[u].x ^= pv.x & m; v[u].y ^= pv.y & m; v[u].z ^= pv.z & m; v[u].w ^= pv.w & m;
+      pv = v[u];
+      const bool rowok = (e[u] & 0x200u) != 0u;
       if (BITS && rowok) {
-        uint32_t *po = O.bits + ((long long)(e[u] & 0xFFu) * O.n_words + w0 + c4);
-        if (fastst) *reinterpret_cast<uint4 *>(po) = v[u];
-        else if (whole) {  // rows not 16-byte aligned (n_words not a multiple of 4)
-          po[0] = v[u].x; po[1] = v[u].y; po[2] = v[u].z; po[3] = v[u].w;
-        } else {
+        const uint32_t row = e[u] & 0xFFu;
+        char *po = row32 ? colp + (unsigned long long)row * (uint32_t)rowbytes : colp + (unsigned long long)row * rowbytes;
+        if (FAST) *reinterpret_cast<uint4 *>(po) = v[u];
+        else {
+          uint32_t *pw = reinterpret_cast<uint32_t *>(po);
           const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) po[j] = vv[j];
+            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) pw[j] = vv[j];
         }
       }
       if (TALLY) {
@@ -872,16 +881,24 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
         c += __shfl_xor_sync(0xFFFFFFFFu, c, 1);
         c += __shfl_xor_sync(0xFFFFFFFFu, c, 2);
         c += __shfl_xor_sync(0xFFFFFFFFu, c, 4);
-        if (c4 == 0u) {
-          // (invalid slots name the zero row, whose tally entry does not exist: skip them)
-          if (e[2 * h] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c & 0xFFFFu)); }
-          if (e[2 * h + 1] & 0x40000u) { const uint32_t ta = tal_s + ((e[2 * h + 1] & 0xFFu) << 2); st_s(ta, ld_s(ta) + (c >> 16)); }
-        }
+        // (pad entries name the zero row, whose tally entry does not exist: skip them)
+        red_add_if(head && (e[2 * h] & 0x200u), tal_s + ((e[2 * h] & 0xFFu) << 2), c & 0xFFFFu);
+        red_add_if(head && (e[2 * h + 1] & 0x200u), tal_s + ((e[2 * h + 1] & 0xFFu) << 2), c >> 16);
       }
     }
-    // rows kept for the next row of their chain are read by OTHER lanes in a later trip
-    __syncwarp();
   }
+}
+
+template <bool TALLY, bool BITS>
+__device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
+                                                  const uint32_t prog_s, const uint32_t n_steps,
+                                                  const long long w0, const bool vec_ok, const int lane) {
+  const bool whole = w0 >= 0 && w0 + 32 <= O.n_words;  // the batch's 32 words all exist
+  uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
+  if (whole && vec_ok) lanes_readout_loop<TALLY, BITS, true>(O, acc_s, tal_s, prog_s, n_steps, w0, lane, anyv);
+  else lanes_readout_loop<TALLY, BITS, false>(O, acc_s, tal_s, prog_s, n_steps, w0, lane, anyv);
+  // every lane zeroed the rows it read; the next batch's faults may land on any of them
+  __syncwarp();
   uint32_t nz = 0;
   if (TALLY) {
     // non-zero outcomes: OR over the four row groups, then lanes 0..7 hold the batch's 32 words
