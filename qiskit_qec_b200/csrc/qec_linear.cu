@@ -838,15 +838,24 @@ __device__ __forceinline__ void lanes_readout_loop(const QecOutDev &O, const uin
   char *const colp = reinterpret_cast<char *>(O.bits) + ((w0 + (long long)c4) << 2);
   const bool head = c4 == 0u;
   uint4 pv = make_uint4(0u, 0u, 0u, 0u);
+  // software-pipelined: the next trip's program entries and rows are loaded before this trip's
+  // stores, counts and shuffles (n_steps is a multiple of QEC_LANES_UNROLL: lanes_readout_prog)
+  uint32_t en[QEC_LANES_UNROLL];
+  uint4 vn[QEC_LANES_UNROLL];
+#pragma unroll
+  for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(pe_s + ((uint32_t)u << 4));
+#pragma unroll
+  for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(col_s + ((en[u] & 0xFFu) << 7));
   for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
     uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL];
     uint4 v[QEC_LANES_UNROLL];
 #pragma unroll
-    for (int u = 0; u < QEC_LANES_UNROLL; ++u) e[u] = ld_s(pe_s + ((pass + u) << 4));
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; a[u] = col_s + ((e[u] & 0xFFu) << 7); }
+    if (pass + QEC_LANES_UNROLL < n_steps) {
 #pragma unroll
-    for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-      a[u] = col_s + ((e[u] & 0xFFu) << 7);
-      v[u] = ld_s128(a[u]);
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(col_s + ((en[u] & 0xFFu) << 7));
     }
     uint32_t cpk[QEC_LANES_UNROLL / 2];
 #pragma unroll
@@ -916,17 +925,26 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
 struct LanePlanes {
   uint32_t p0, p1, p2, p3, p4, p5;
 };
-__device__ __forceinline__ void planes_add(LanePlanes &P, uint32_t c) {
-  uint32_t t = P.p0 & c; P.p0 ^= c; c = t;
-  t = P.p1 & c; P.p1 ^= c; c = t;
-  if (c) {
-    t = P.p2 & c; P.p2 ^= c; c = t;
-    t = P.p3 & c; P.p3 ^= c; c = t;
-    t = P.p4 & c; P.p4 ^= c; c = t;
-    t = P.p5 & c; P.p5 ^= c; c = t;
-    // 63 + 1: stay at 63 (the last histogram bin is ">= 63")
-    P.p0 |= c; P.p1 |= c; P.p2 |= c; P.p3 |= c; P.p4 |= c; P.p5 |= c;
+__device__ __forceinline__ void planes_carry(LanePlanes &P, uint32_t c) {  // c: carries into plane 2
+  uint32_t t = P.p2 & c; P.p2 ^= c; c = t;
+  t = P.p3 & c; P.p3 ^= c; c = t;
+  t = P.p4 & c; P.p4 ^= c; c = t;
+  t = P.p5 & c; P.p5 ^= c; c = t;
+  // 63 + 1: stay at 63 (the last histogram bin is ">= 63")
+  P.p0 |= c; P.p1 |= c; P.p2 |= c; P.p3 |= c; P.p4 |= c; P.p5 |= c;
+}
+// up to four increments at once: a shot takes at most four, so it carries out of plane 1 at most
+// once and the carries can be collected -- one test per group instead of one per candidate
+__device__ __forceinline__ void planes_add_group(LanePlanes &P, const uint32_t *m, const int n) {  // n <= 4
+  uint32_t cc = 0;
+#pragma unroll
+  for (int j = 0; j < n; ++j) {
+    uint32_t c = m[j];
+    uint32_t t = P.p0 & c; P.p0 ^= c; c = t;
+    t = P.p1 & c; P.p1 ^= c;
+    cc |= t;
   }
+  if (cc) planes_carry(P, cc);
 }
 
 template <bool TALLY, bool BITS, bool EXPORT, int NP>
@@ -1044,8 +1062,11 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
           }
       }
       if (TALLY) {
+        uint32_t mk[2 * NP];
 #pragma unroll
-        for (int j = 0; j < 2 * NP; ++j) planes_add(P, ok[j] ? 1u << (pp[j] & 31u) : 0u);
+        for (int j = 0; j < 2 * NP; ++j) mk[j] = ok[j] ? 1u << (pp[j] & 31u) : 0u;
+#pragma unroll
+        for (int j = 0; j < 2 * NP; j += 4) planes_add_group(P, mk + j, 2 * NP - j < 4 ? 2 * NP - j : 4);
       }
 #pragma unroll
       for (int c = 0; c < NP; ++c) rr[c] = nr[c];
