@@ -1,5 +1,5 @@
 #!/usr/bin/env bash
-# round 2, step 11: planes carries collected per trip, software-pipelined read-out loop
+# round 2, step 11+: read-out tallies in registers (unrolled trips), planes carries per trip
 set -u
 mkdir -p gpurun_out
 O=gpurun_out/r02_step11

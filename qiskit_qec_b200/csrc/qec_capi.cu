@@ -824,7 +824,7 @@ static int enum_plan_linear(qec_enumerator *e) {
   const int w_env = env_int("QEC_B200_ENUM_WARPS", 0);
   int warps = 0;
   size_t smem = 0;
-  for (int wz = (w_env > 0 ? w_env : 16); wz >= (w_env > 0 ? w_env : 4); --wz) {
+  for (int wz = (w_env > 0 ? std::min(w_env, 12) : 12); wz >= (w_env > 0 ? std::min(w_env, 12) : 4); --wz) {  // (k_enum_lanes: 384 threads)
     const size_t need = qec_enum_lanes_smem_words(c->nc, wz, (uint32_t)F, (uint32_t)prog.size(), (uint32_t)e->L,
                                                   e->order, e32) * 4 + 16;
     if (need > di.smem_optin) continue;
@@ -1399,7 +1399,8 @@ static int sampler_plan_linear(qec_sampler *s) {
     const int w_env = env_int("QEC_B200_LIN_WARPS", 0);
     // (the kernel hands out batches dynamically, so the warp count need not be a multiple of the
     // four schedulers: with static dealing 9 warps were slower than 8)
-    for (int wz = (w_env > 0 ? w_env : 16); want && can && wz >= (w_env > 0 ? w_env : 4) && !found; --wz) {
+    // (at most 12 warps: the kernels are built for 384 threads, the register file holding the tally counters)
+    for (int wz = (w_env > 0 ? std::min(w_env, 12) : 12); want && can && wz >= (w_env > 0 ? std::min(w_env, 12) : 4) && !found; --wz) {
       const size_t need = qec_lanes_smem_words(c->nc, wz, (uint32_t)s->L, (uint32_t)F, (uint32_t)lanes_prog.size()) * 4 + 16;
       if (need > di.smem_optin) continue;
       found = true; lane_mode = 1; threads = 32 * wz; ctas = 1; lgb = 10; info_s = 1; sig_s = 0;

@@ -820,92 +820,159 @@ __device__ __forceinline__ void lanes_apply(const uint32_t p, const bool ok, con
 // meets the rows of a chain in consecutive passes and undoes the basis with a running XOR held in
 // registers: one LDS.128 and one zeroing STS.128 per row, no second load and no write-back.
 // Program entry (qec_capi.cu, lanes_readout_prog): row | 1 << 9 valid | 1 << 31 the row continues
-// the chain of the group's previous pass; pad entries name the always-zero row nc + 1.  Per-row ones
-// go to the warp's tally row by red.shared.add from one lane per group (fire and forget: the
-// load / add / store it replaces serialised the trips); returns this lane's share of the batch's
-// non-zero outcomes (lanes 0..7 carry it).  FAST: the batch's 32 words all exist and the rows are
-// 16-byte aligned.
+// the chain of the group's previous pass; pad entries name the always-zero row nc + 1.
+// Per-clbit tallies: the program is the same for every batch, so pass k of group g always meets the
+// same row -- on the fast path (whole, aligned batches) the trips are unrolled and every lane keeps
+// its own partial counts of "its" rows in registers (LaneCounts: two rows per register, 16 bits
+// each), with no shuffle and no shared-memory traffic per batch; they are reduced over the eight
+// lanes of a group and added to the warp's tally row every QEC_LANES_FLUSH batches and at the end
+// (ncu: the per-pass shuffle tree + red.shared.add cost 0.14 of 0.88 ms per 1e8 shots at d=5).
+// Partial batches take the rolled loop with the per-pass reduction.
+// Returns nothing; anyv collects the OR of all rows (non-zero outcomes).
+#define QEC_LANES_MAXTRIPS 16  // 64 passes of four rows >= 254 clbits
+#define QEC_LANES_FLUSH 448u   // batches between flushes: 448 * 128 < 2^16 per lane and row
+
+struct LaneCounts {
+  uint32_t c[2 * QEC_LANES_MAXTRIPS];
+  uint32_t nb;
+};
+
+struct LaneReadCtx {
+  uint32_t col_s, pe_s, c4;
+  char *colp;
+  unsigned long long rowbytes;
+  bool row32;
+  long long w0;
+  long long n_words;
+};
+
+// one trip: QEC_LANES_UNROLL passes whose entries e[] and rows v[] are already loaded
 template <bool TALLY, bool BITS, bool FAST>
-__device__ __forceinline__ void lanes_readout_loop(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
-                                                   const uint32_t prog_s, const uint32_t n_steps,
-                                                   const long long w0, const int lane, uint4 &anyv) {
-  const uint32_t rsub = (uint32_t)lane >> 3, c4 = ((uint32_t)lane & 7u) << 2;
-  const uint32_t col_s = acc_s + (c4 << 2);
-  const uint32_t pe_s = prog_s + (rsub << 2);
-  // (row * bytes per row in one 32 x 32 -> 64 multiply-add; rows of 2^32 bytes or more take the slow form)
-  const unsigned long long rowbytes = (unsigned long long)O.n_words << 2;
-  const bool row32 = rowbytes < (1ull << 32);
-  char *const colp = reinterpret_cast<char *>(O.bits) + ((w0 + (long long)c4) << 2);
-  const bool head = c4 == 0u;
-  uint4 pv = make_uint4(0u, 0u, 0u, 0u);
-  // software-pipelined: the next trip's program entries and rows are loaded before this trip's
-  // stores, counts and shuffles (n_steps is a multiple of QEC_LANES_UNROLL: lanes_readout_prog)
-  uint32_t en[QEC_LANES_UNROLL];
-  uint4 vn[QEC_LANES_UNROLL];
+__device__ __forceinline__ void lanes_trip(const LaneReadCtx &R, const uint32_t (&e)[QEC_LANES_UNROLL],
+                                           uint4 (&v)[QEC_LANES_UNROLL], uint4 &pv, uint4 &anyv,
+                                           uint32_t (&cpk)[QEC_LANES_UNROLL / 2]) {
 #pragma unroll
-  for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(pe_s + ((uint32_t)u << 4));
+  for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
+    st_s128z(R.col_s + ((e[u] & 0xFFu) << 7));
+    const uint32_t m = (uint32_t)((int)e[u] >> 31);  // all ones: XOR the previous row of the chain in
+    v[u].x ^= pv.x & m; v[u].y ^= pv.y & m; v[u].z ^= pv.z & m; v[u].w ^= pv.w & m;
+    pv = v[u];
+    const bool rowok = (e[u] & 0x200u) != 0u;
+    if (BITS && rowok) {
+      const uint32_t row = e[u] & 0xFFu;
+      // (row * bytes per row in one 32 x 32 -> 64 multiply-add; rows of 2^32 bytes or more take the slow form)
+      char *po = R.row32 ? R.colp + (unsigned long long)row * (uint32_t)R.rowbytes : R.colp + (unsigned long long)row * R.rowbytes;
+      if (FAST) *reinterpret_cast<uint4 *>(po) = v[u];
+      else {
+        uint32_t *pw = reinterpret_cast<uint32_t *>(po);
+        const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
-  for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(col_s + ((en[u] & 0xFFu) << 7));
-  for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
-    uint32_t e[QEC_LANES_UNROLL], a[QEC_LANES_UNROLL];
-    uint4 v[QEC_LANES_UNROLL];
-#pragma unroll
-    for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; a[u] = col_s + ((e[u] & 0xFFu) << 7); }
-    if (pass + QEC_LANES_UNROLL < n_steps) {
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(col_s + ((en[u] & 0xFFu) << 7));
-    }
-    uint32_t cpk[QEC_LANES_UNROLL / 2];
-#pragma unroll
-    for (int u = 0; u < QEC_LANES_UNROLL; ++u) {
-      st_s128z(a[u]);
-      const uint32_t m = (uint32_t)((int)e[u] >> 31);  // all ones: XOR the previous row of the chain in
-      v[u].x ^= pv.x & m; v[u].y ^= pv.y & m; v[u].z ^= pv.z & m; v[u].w ^= pv.w & m;
-      pv = v[u];
-      const bool rowok = (e[u] & 0x200u) != 0u;
-      if (BITS && rowok) {
-        const uint32_t row = e[u] & 0xFFu;
-        char *po = row32 ? colp + (unsigned long long)row * (uint32_t)rowbytes : colp + (unsigned long long)row * rowbytes;
-        if (FAST) *reinterpret_cast<uint4 *>(po) = v[u];
-        else {
-          uint32_t *pw = reinterpret_cast<uint32_t *>(po);
-          const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (w0 + c4 + j >= 0 && w0 + c4 + j < O.n_words) pw[j] = vv[j];
-        }
-      }
-      if (TALLY) {
-        anyv.x |= v[u].x; anyv.y |= v[u].y; anyv.z |= v[u].z; anyv.w |= v[u].w;
-        const uint32_t cnt = __popc(v[u].x) + __popc(v[u].y) + __popc(v[u].z) + __popc(v[u].w);
-        if (u & 1) cpk[u >> 1] |= cnt << 16; else cpk[u >> 1] = cnt;  // two rows' counts per register
+        for (int j = 0; j < 4; ++j)
+          if (R.w0 + R.c4 + j >= 0 && R.w0 + R.c4 + j < R.n_words) pw[j] = vv[j];
       }
     }
     if (TALLY) {
-#pragma unroll
-      for (int h = 0; h < QEC_LANES_UNROLL / 2; ++h) {
-        uint32_t c = cpk[h];  // (8-lane sums stay below 2^16: at most 1024 per row)
-        c += __shfl_xor_sync(0xFFFFFFFFu, c, 1);
-        c += __shfl_xor_sync(0xFFFFFFFFu, c, 2);
-        c += __shfl_xor_sync(0xFFFFFFFFu, c, 4);
-        // (pad entries name the zero row, whose tally entry does not exist: skip them)
-        red_add_if(head && (e[2 * h] & 0x200u), tal_s + ((e[2 * h] & 0xFFu) << 2), c & 0xFFFFu);
-        red_add_if(head && (e[2 * h + 1] & 0x200u), tal_s + ((e[2 * h + 1] & 0xFFu) << 2), c >> 16);
-      }
+      anyv.x |= v[u].x; anyv.y |= v[u].y; anyv.z |= v[u].z; anyv.w |= v[u].w;
+      const uint32_t cnt = __popc(v[u].x) + __popc(v[u].y) + __popc(v[u].z) + __popc(v[u].w);
+      if (u & 1) cpk[u >> 1] |= cnt << 16; else cpk[u >> 1] = cnt;  // two rows' counts per register
     }
   }
+}
+
+// 8-lane sums of a packed pair of row counts -> the warp's tally row (head lane of each group)
+__device__ __forceinline__ void lanes_tally_pair(uint32_t lo, uint32_t hi, const uint32_t e0, const uint32_t e1,
+                                                 const uint32_t tal_s, const bool head) {
+  lo += __shfl_xor_sync(0xFFFFFFFFu, lo, 1); hi += __shfl_xor_sync(0xFFFFFFFFu, hi, 1);
+  lo += __shfl_xor_sync(0xFFFFFFFFu, lo, 2); hi += __shfl_xor_sync(0xFFFFFFFFu, hi, 2);
+  lo += __shfl_xor_sync(0xFFFFFFFFu, lo, 4); hi += __shfl_xor_sync(0xFFFFFFFFu, hi, 4);
+  // (pad entries name the zero row, whose tally entry does not exist: skip them)
+  red_add_if(head && (e0 & 0x200u), tal_s + ((e0 & 0xFFu) << 2), lo);
+  red_add_if(head && (e1 & 0x200u), tal_s + ((e1 & 0xFFu) << 2), hi);
+}
+
+__device__ __forceinline__ void lanes_counts_flush(LaneCounts &LC, const uint32_t tal_s, const uint32_t prog_s,
+                                                   const uint32_t n_steps, const int lane) {
+  const uint32_t pe_s = prog_s + (((uint32_t)lane >> 3) << 2);
+  const bool head = ((uint32_t)lane & 7u) == 0u;
+#pragma unroll
+  for (int t = 0; t < QEC_LANES_MAXTRIPS; ++t) {
+    if ((uint32_t)t * QEC_LANES_UNROLL >= n_steps) break;
+#pragma unroll
+    for (int h = 0; h < QEC_LANES_UNROLL / 2; ++h) {
+      const uint32_t c = LC.c[t * (QEC_LANES_UNROLL / 2) + h];
+      LC.c[t * (QEC_LANES_UNROLL / 2) + h] = 0u;
+      const uint32_t e0 = ld_s(pe_s + ((uint32_t)(t * QEC_LANES_UNROLL + 2 * h) << 4));
+      const uint32_t e1 = ld_s(pe_s + ((uint32_t)(t * QEC_LANES_UNROLL + 2 * h + 1) << 4));
+      lanes_tally_pair(c & 0xFFFFu, c >> 16, e0, e1, tal_s, head);
+    }
+  }
+  LC.nb = 0u;
 }
 
 template <bool TALLY, bool BITS>
 __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
                                                   const uint32_t prog_s, const uint32_t n_steps,
-                                                  const long long w0, const bool vec_ok, const int lane) {
+                                                  const long long w0, const bool vec_ok, const int lane,
+                                                  LaneCounts &LC) {
+  static_assert(QEC_LANES_UNROLL == 4, "two packed count registers per trip");
   const bool whole = w0 >= 0 && w0 + 32 <= O.n_words;  // the batch's 32 words all exist
+  LaneReadCtx R;
+  R.c4 = ((uint32_t)lane & 7u) << 2;
+  R.col_s = acc_s + (R.c4 << 2);
+  R.pe_s = prog_s + (((uint32_t)lane >> 3) << 2);
+  R.rowbytes = (unsigned long long)O.n_words << 2;
+  R.row32 = R.rowbytes < (1ull << 32);
+  R.colp = reinterpret_cast<char *>(O.bits) + ((w0 + (long long)R.c4) << 2);
+  R.w0 = w0; R.n_words = O.n_words;
   uint4 anyv = make_uint4(0u, 0u, 0u, 0u);
-  if (whole && vec_ok) lanes_readout_loop<TALLY, BITS, true>(O, acc_s, tal_s, prog_s, n_steps, w0, lane, anyv);
-  else lanes_readout_loop<TALLY, BITS, false>(O, acc_s, tal_s, prog_s, n_steps, w0, lane, anyv);
+  uint4 pv = make_uint4(0u, 0u, 0u, 0u);
+  // software-pipelined: the next trip's program entries and rows are loaded before this trip's
+  // stores and counts (n_steps is a multiple of QEC_LANES_UNROLL: lanes_readout_prog)
+  uint32_t en[QEC_LANES_UNROLL];
+  uint4 vn[QEC_LANES_UNROLL];
+#pragma unroll
+  for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((uint32_t)u << 4));
+#pragma unroll
+  for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
+  if (whole && vec_ok) {
+#pragma unroll
+    for (int t = 0; t < QEC_LANES_MAXTRIPS; ++t) {
+      const uint32_t pass = (uint32_t)t * QEC_LANES_UNROLL;
+      if (pass >= n_steps) break;
+      uint32_t e[QEC_LANES_UNROLL], cpk[QEC_LANES_UNROLL / 2];
+      uint4 v[QEC_LANES_UNROLL];
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; }
+      if (t + 1 < QEC_LANES_MAXTRIPS && pass + QEC_LANES_UNROLL < n_steps) {
+#pragma unroll
+        for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
+#pragma unroll
+        for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
+      }
+      lanes_trip<TALLY, BITS, true>(R, e, v, pv, anyv, cpk);
+      if (TALLY) { LC.c[2 * t] += cpk[0]; LC.c[2 * t + 1] += cpk[1]; }
+    }
+    if (TALLY && ++LC.nb == QEC_LANES_FLUSH) lanes_counts_flush(LC, tal_s, prog_s, n_steps, lane);
+  } else {
+    const bool head = R.c4 == 0u;
+    for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
+      uint32_t e[QEC_LANES_UNROLL], cpk[QEC_LANES_UNROLL / 2];
+      uint4 v[QEC_LANES_UNROLL];
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; }
+      if (pass + QEC_LANES_UNROLL < n_steps) {
+#pragma unroll
+        for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
+#pragma unroll
+        for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
+      }
+      lanes_trip<TALLY, BITS, false>(R, e, v, pv, anyv, cpk);
+      if (TALLY) {
+        lanes_tally_pair(cpk[0] & 0xFFFFu, cpk[0] >> 16, e[0], e[1], tal_s, head);
+        lanes_tally_pair(cpk[1] & 0xFFFFu, cpk[1] >> 16, e[2], e[3], tal_s, head);
+      }
+    }
+  }
   // every lane zeroed the rows it read; the next batch's faults may land on any of them
   __syncwarp();
   uint32_t nz = 0;
@@ -948,7 +1015,7 @@ __device__ __forceinline__ void planes_add_group(LanePlanes &P, const uint32_t *
 }
 
 template <bool TALLY, bool BITS, bool EXPORT, int NP>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(384, 1)
 k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
                const QecSampleExport X) {
   extern __shared__ __align__(16) uint32_t qec_lin_smem[];
@@ -985,6 +1052,10 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   const long long w_lo = shot_lo >> 5;
   const bool vec_ok = ((O.n_words | w_lo) & 3) == 0 && ((size_t)O.bits & 15) == 0;
 
+  LaneCounts LC;
+#pragma unroll
+  for (int i = 0; i < 2 * QEC_LANES_MAXTRIPS; ++i) LC.c[i] = 0u;
+  LC.nb = 0u;
   // batches are handed out dynamically (one atomic per 1024 shots): results depend only on the
   // batch index, and warps that share a scheduler with more neighbours simply take fewer
   for (;;) {
@@ -1078,7 +1149,7 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
 
     // ---- read-out (lanes_readout): four rows per pass, lane = (row of the pass, 4-word piece)
     const long long w0 = (b << 5) - w_lo;  // first output word of the batch (may be < 0 at the range start)
-    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)S.n_steps, w0, vec_ok, lane);
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)S.n_steps, w0, vec_ok, lane, LC);
     if (TALLY) {
       nz_shots += nzb;
       // faults-per-shot histogram from the planes
@@ -1098,6 +1169,7 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
   }
 
   if (TALLY) {
+    lanes_counts_flush(LC, tal_s, prog_s, (uint32_t)S.n_steps, lane);
     unsigned long long t1 = h1, t2 = h2, t3 = h3, tx = hx;
     for (int off = 16; off > 0; off >>= 1) {
       t1 += __shfl_down_sync(0xFFFFFFFFu, t1, off);
@@ -1208,7 +1280,7 @@ __device__ __forceinline__ void lin_enum_unrank(const QecEnumDev &E, const uint3
 }
 
 template <int K, bool TALLY, bool BITS, bool E32>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(384, 1)
 k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, const long long lo, const long long hi) {
   extern __shared__ __align__(16) uint32_t qec_lin_smem[];
   const int T = blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NW = T >> 5;
@@ -1241,6 +1313,10 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
   const long long n_paths = hi - lo;
   const long long n_batches = (n_paths + 1023) >> 10;
   unsigned long long nz_paths = 0;
+  LaneCounts LC;
+#pragma unroll
+  for (int i = 0; i < 2 * QEC_LANES_MAXTRIPS; ++i) LC.c[i] = 0u;
+  LC.nb = 0u;
 
   for (;;) {
     uint32_t kb = 0;
@@ -1276,12 +1352,13 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
       }
     }
     __syncwarp();
-    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)EL.n_steps, b << 5, vec_ok, lane);
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)EL.n_steps, b << 5, vec_ok, lane, LC);
     if (TALLY) nz_paths += nzb;
     __syncwarp();
   }
 
   if (TALLY) {
+    lanes_counts_flush(LC, tal_s, prog_s, (uint32_t)EL.n_steps, lane);
     for (int off = 16; off > 0; off >>= 1) nz_paths += __shfl_down_sync(0xFFFFFFFFu, nz_paths, off);
     if (lane == 0 && nz_paths) atomicAdd(&O.tally[nc], nz_paths);
     __syncthreads();
