@@ -1458,18 +1458,33 @@ static int sampler_plan_linear(qec_sampler *s) {
   // undoes the basis level by level before its read-out
   const bool cta_diff = !warp_mode && !lane_mode && use_diff && env_int("QEC_B200_LIN_CTADIFF", 1) != 0;
   if ((warp_mode || lane_mode || cta_diff) && use_diff) lists.swap(tr);
+  // read-out program of the CTA variant (k_sample_lin): whole chains dealt to the T / BW row
+  // groups of the CTA, longest first onto the least loaded; entry: row | 1 << 30 valid | 1 << 31
+  // the row continues the chain of the group's previous step; layout prog[step * G + group]
   ln.lvl_prog.clear();
   ln.lvl_off.assign(1, 0u);
-  if (cta_diff) {
-    std::vector<int> depth(c->nc, 0);
-    int maxd = 0;
-    for (int cb = 0; cb < c->nc; ++cb)  // (pred[cb] < cb: an earlier measurement)
-      if (pred[cb] >= 0) { depth[cb] = depth[pred[cb]] + 1; maxd = std::max(maxd, depth[cb]); }
-    for (int dlev = 1; dlev <= maxd; ++dlev) {
-      for (int cb = 0; cb < c->nc; ++cb)
-        if (depth[cb] == dlev) ln.lvl_prog.push_back((uint32_t)cb | ((uint32_t)pred[cb] << 16));
-      ln.lvl_off.push_back((uint32_t)ln.lvl_prog.size());
+  int cta_steps = 0;
+  if (!warp_mode && !lane_mode) {
+    const int G = std::max(1, threads >> (lgb - 5));
+    std::vector<std::vector<int>> chains;
+    for (int cb = 0; cb < c->nc; ++cb) {
+      if (cta_diff && pred[cb] >= 0) continue;
+      chains.emplace_back();
+      for (int x = cb; x >= 0; x = cta_diff ? succ[x] : -1) chains.back().push_back(x);
     }
+    std::stable_sort(chains.begin(), chains.end(),
+                     [](const std::vector<int> &a, const std::vector<int> &b) { return a.size() > b.size(); });
+    std::vector<std::vector<uint32_t>> q((size_t)G);
+    for (const auto &ch : chains) {
+      int best = 0;
+      for (int g = 1; g < G; ++g) if (q[g].size() < q[best].size()) best = g;
+      for (size_t k = 0; k < ch.size(); ++k)
+        q[best].push_back((uint32_t)ch[k] | (1u << 30) | (k ? (1u << 31) : 0u));
+    }
+    for (const auto &x : q) cta_steps = std::max(cta_steps, (int)x.size());
+    ln.lvl_prog.assign((size_t)cta_steps * G, 0u);
+    for (int g = 0; g < G; ++g)
+      for (size_t k = 0; k < q[g].size(); ++k) ln.lvl_prog[k * G + g] = q[g][k];
   }
   if (ln.lvl_prog.empty()) ln.lvl_prog.push_back(0u);
   // descriptor + list (CTA variant with tables in shared memory, overflow of long lists) and
@@ -1533,7 +1548,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.lane_mode = lane_mode;
   d.lanes_np = env_int("QEC_B200_LANES_NP", 2);  // (results do not depend on it: the lane's stream is sequential)
   d.lvl_prog = ln.d_lvl_prog; d.lvl_off = ln.d_lvl_off;
-  d.n_lvl = (int)ln.lvl_off.size() - 1;
+  d.n_lvl = cta_steps;  // steps of the CTA variant's read-out program
   d.n_classes = (uint32_t)s->n_classes; d.lgP = s->lgP;
   d.T1 = s->d_T1; d.T2 = s->d_T2; d.info = ln.d_info; d.cls_acc = s->d_cls_acc;
   d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.slloc = s->d_slloc;

@@ -143,9 +143,9 @@ struct QecLinDev {
   int lane_mode;
   int lanes_np;             // Philox calls (two candidates each) per loop trip of the lane-stream kernel: 2, 3 or 4
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
-  // CTA variant with signatures in the time-difference basis: rows with a previous row, grouped by
-  // their depth in the chain (lvl_off[n_lvl + 1] into lvl_prog; entry = row | previous row << 16);
-  // the CTA undoes the basis level by level before the read-out.  n_lvl = 0: raw signatures.
+  // CTA variant: read-out program lvl_prog[step * G + group], G = threads / words per batch row,
+  // n_lvl steps; entry = row | 1 << 30 valid | 1 << 31 the row continues the chain (time-difference
+  // basis) of the group's previous step.  (lvl_off: unused, kept for layout.)
   const uint32_t *lvl_prog, *lvl_off;
   int n_lvl;
 };
@@ -241,7 +241,8 @@ static inline __host__ __device__ size_t qec_lin_smem_words(int nc, int lgb, int
                                                             int sig_in_smem) {
   const size_t BW = (size_t)1 << (lgb - 5);
   size_t w = (size_t)nc * BW + ((size_t)1 << (lgb - 1)) + BW;  // acc, per-shot fault counts, any
-  w += (size_t)(T / 32) * nc + 64;                              // per-warp tallies, histogram
+  w += (size_t)nc + 64;                                         // the CTA's tally row, histogram
+  (void)T;
   w += (size_t)K1 + 2u * B + 1u + 2u * ncls + ((size_t)ncls << lgP); // T1 T2 guide cacc cnp1 cdf
   if (info_in_smem) w += L;
   if (sig_in_smem) w += (size_t)n_faults + (n_sig + 1u) / 2u;

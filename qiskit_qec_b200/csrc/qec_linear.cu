@@ -41,7 +41,7 @@ __device__ __forceinline__ LinSmem lin_carve(uint32_t *sm, const QecLinDev &S, i
   m.cnt = m.acc + (size_t)S.nc * BW;
   m.anyw = m.cnt + ((size_t)1 << (S.lgb - 1));
   m.tally = m.anyw + BW;
-  m.hist = m.tally + (size_t)(T / 32) * S.nc;
+  m.hist = m.tally + (size_t)S.nc;  // one tally row per CTA (red.shared.add from any warp)
   m.T1 = m.hist + 64;
   m.T2 = m.T1 + S.K1;
   m.G = reinterpret_cast<uint16_t *>(m.T2 + S.B + 1u);
@@ -96,38 +96,6 @@ __device__ __forceinline__ uint32_t lin_digit(uint32_t cdf_s, uint32_t r) {
   for (int k = LGP - 1; k >= 0; --k)
     if (ld_s(cdf_s + ((d + (1u << k) - 1u) << 2)) <= r) d += 1u << k;
   return d;
-}
-
-// One thread's share of the accumulator read-out: `n_it` row pieces, `a` / `po` / `tl` walk
-// the accumulator column, the output column and this warp's tally row.  With fewer than 32
-// word columns (FULL = false) a warp spans several rows that may run out at different times:
-// every lane then makes lane 0's number of trips (the most) and idles through the extra ones,
-// so the shuffles always see the whole warp.
-template <bool TALLY, bool BITS, bool FULL>
-__device__ __forceinline__ uint32_t lin_out_rows(int n_it, uint32_t a, const uint32_t a_step,
-                                                 uint32_t *po, const long long po_step, uint32_t tl,
-                                                 const uint32_t tl_step, const bool inr,
-                                                 const bool head, const uint32_t grp) {
-  uint32_t anyv = 0;
-  const int trips = FULL ? n_it : __shfl_sync(0xFFFFFFFFu, n_it, 0);
-#pragma unroll 2
-  for (int it = 0; it < trips; ++it, a += a_step, po += po_step, tl += tl_step) {
-    const bool live = FULL || it < n_it;
-    uint32_t v = 0;
-    if (live) {
-      v = ld_s(a);
-      st_s(a, 0u);
-      if (BITS && inr) *po = v;
-    }
-    if (TALLY) {
-      anyv |= v;
-      int cnt = __popc(v);
-      if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
-      else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
-      if (head && live) st_s(tl, ld_s(tl) + (uint32_t)cnt);
-    }
-  }
-  return anyv;
 }
 
 // Constants of the draw loop that both kernels keep in registers.
@@ -323,7 +291,7 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     m.cdf[i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
   }
   {
-    const size_t nz = (size_t)S.nc * BW + (BATCH >> 1) + BW + (size_t)NW * S.nc + 64;
+    const size_t nz = (size_t)S.nc * BW + (BATCH >> 1) + BW + (size_t)S.nc + 64;
     for (size_t i = tid; i < nz; i += T) m.acc[i] = 0u;  // acc, cnt, anyw, tally, hist are contiguous
   }
   __syncthreads();
@@ -340,7 +308,7 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
   dc.bw4 = 4u << lgw;  // bytes per accumulator row
   dc.P = P;
   dc.lgb = lgb;
-  uint32_t *w_tally = m.tally + (size_t)warp * S.nc;
+  const uint32_t tal_s = (uint32_t)__cvta_generic_to_shared(m.tally);
   unsigned long long nz_shots = 0;
   const long long b0 = shot_lo >> lgb, b1 = (shot_lo + n_shots - 1) >> lgb;
   const long long w_lo = shot_lo >> 5;
@@ -357,38 +325,47 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
       lin_stream<TALLY>(S, m, dc, s, lane, blo, bhi, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
     __syncthreads();
 
-    // ---- signatures in the time-difference basis: row ^= previous row of its chain, one chain
-    // depth at a time (the previous row is final when its own depth is done)
-    for (int lv = 0; lv < S.n_lvl; ++lv) {
-      const uint32_t o0 = __ldg(S.lvl_off + lv) << lgw, o1 = __ldg(S.lvl_off + lv + 1) << lgw;
-      for (uint32_t i = o0 + (uint32_t)tid; i < o1; i += (uint32_t)T) {
-        const uint32_t e = __ldg(S.lvl_prog + (i >> lgw)), wcol = i & (BW - 1u);
-        m.acc[((e & 0xFFFFu) << lgw) + wcol] ^= m.acc[((e >> 16) << lgw) + wcol];
-      }
-      __syncthreads();
-    }
-
-    // ---- stream the accumulator out: thread -> fixed word column wb, clbits c0, c0 + T/BW, ...
+    // ---- read-out: thread = (word column wb, row group g = tid / BW).  The host deals whole chains
+    // of the time-difference basis to the T / BW groups (cta_readout_prog, qec_capi.cu), so a thread
+    // meets the rows of a chain in consecutive steps and undoes the basis with a running XOR in a
+    // register: one LDS, one zeroing STS, one STG per word, no second pass over the accumulator and
+    // no barrier per chain depth.  Entry: row | 1 << 30 valid | 1 << 31 continues the chain of the
+    // group's previous step.  Per-row ones: warp sum (REDUX when a warp spans one row) and one
+    // red.shared.add into the CTA's tally row.
     {
-      const uint32_t wb = (uint32_t)tid & (BW - 1u);
+      const uint32_t wb = (uint32_t)tid & (BW - 1u), G = (uint32_t)T >> lgw;
       const long long w = ((b << lgw) + wb) - w_lo;
       const bool inr = w >= 0 && w < O.n_words;
       const uint32_t grp = BW < 32u ? BW : 32u;  // lanes of a warp that share one clbit
-      uint32_t anyv = 0;
-      // (pointer walks: one LDS / STS / STG, a popcount, a warp sum and lane 0's tally update
-      // per 32-word row piece)
-      const uint32_t rpp = (uint32_t)T >> lgw;  // rows per pass of the CTA
-      uint32_t c = (uint32_t)tid >> lgw;
-      uint32_t a = acc_s + ((uint32_t)tid << 2);
-      const uint32_t a_step = (uint32_t)T << 2;
-      uint32_t *po = O.bits + ((long long)c * O.n_words + (inr ? w : 0));
-      const long long po_step = (long long)rpp * O.n_words;
-      uint32_t tl = (uint32_t)__cvta_generic_to_shared(w_tally) + (c << 2);
-      const uint32_t tl_step = rpp << 2;
       const bool head = (lane & (grp - 1u)) == 0u;
-      const int n_it = c < (uint32_t)S.nc ? (int)(((uint32_t)S.nc - c + rpp - 1u) / rpp) : 0;
-      if (grp == 32u) anyv = lin_out_rows<TALLY, BITS, true>(n_it, a, a_step, po, po_step, tl, tl_step, inr, head, grp);
-      else anyv = lin_out_rows<TALLY, BITS, false>(n_it, a, a_step, po, po_step, tl, tl_step, inr, head, grp);
+      const uint32_t *pp = S.lvl_prog + ((uint32_t)tid >> lgw);
+      const uint32_t col_s = acc_s + (wb << 2);
+      uint32_t *const ocol = O.bits + (inr ? w : 0);
+      uint32_t anyv = 0, pv = 0;
+      uint32_t e_next = __ldg(pp);
+#pragma unroll 4
+      for (int st = 0; st < S.n_lvl; ++st) {
+        const uint32_t e = e_next;
+        if (st + 1 < S.n_lvl) e_next = __ldg(pp + (size_t)(st + 1) * G);
+        const bool valid = (e & 0x40000000u) != 0u;
+        const uint32_t row = e & 0xFFFFu;
+        uint32_t v = 0;
+        if (valid) {
+          const uint32_t a = col_s + (row << (lgw + 2));
+          v = ld_s(a);
+          st_s(a, 0u);
+          v ^= pv & (uint32_t)((int)e >> 31);
+          pv = v;
+          if (BITS && inr) ocol[(long long)row * O.n_words] = v;
+        }
+        if (TALLY) {
+          anyv |= v;
+          int cnt = __popc(v);
+          if (grp == 32u) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+          else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+          if (head && valid && cnt) red_add_s(tal_s + (row << 2), (uint32_t)cnt);
+        }
+      }
       if (TALLY) {
         if (anyv) atomicOr(m.anyw + wb, anyv);
         // faults-per-shot histogram from the 16-bit counters (two shots per word)
@@ -426,11 +403,8 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     __syncthreads();
     for (int off = 16; off > 0; off >>= 1) nz_shots += __shfl_down_sync(0xFFFFFFFFu, nz_shots, off);
     if (lane == 0 && nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
-    for (int c = tid; c < S.nc; c += T) {
-      unsigned long long v = 0;
-      for (int k = 0; k < NW; ++k) v += m.tally[(size_t)k * S.nc + c];
-      if (v) atomicAdd(&O.tally[c], v);
-    }
+    for (int c = tid; c < S.nc; c += T)
+      if (m.tally[c]) atomicAdd(&O.tally[c], (unsigned long long)m.tally[c]);
     for (int c = tid; c < 64; c += T)
       if (m.hist[c]) atomicAdd(&O.tally[S.nc + 2 + c], (unsigned long long)m.hist[c]);
     if (blockIdx.x == 0 && tid == 0) atomicAdd(&O.tally[S.nc + 1], (unsigned long long)n_shots);
