@@ -240,7 +240,7 @@ static inline __host__ __device__ size_t qec_lin_smem_words(int nc, int lgb, int
                                                             uint32_t n_sig, int info_in_smem,
                                                             int sig_in_smem) {
   const size_t BW = (size_t)1 << (lgb - 5);
-  size_t w = (size_t)nc * BW + ((size_t)1 << (lgb - 1)) + BW;  // acc, per-shot fault counts, any
+  size_t w = ((size_t)nc + 1u) * BW + ((size_t)1 << (lgb - 1)) + BW;  // acc (+ a zero row), per-shot fault counts, any
   w += (size_t)nc + 64;                                         // the CTA's tally row, histogram
   (void)T;
   w += (size_t)K1 + 2u * B + 1u + 2u * ncls + ((size_t)ncls << lgP); // T1 T2 guide cacc cnp1 cdf

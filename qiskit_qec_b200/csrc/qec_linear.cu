@@ -38,7 +38,7 @@ __device__ __forceinline__ LinSmem lin_carve(uint32_t *sm, const QecLinDev &S, i
   LinSmem m;
   const size_t BW = (size_t)1 << (S.lgb - 5);
   m.acc = sm;
-  m.cnt = m.acc + (size_t)S.nc * BW;
+  m.cnt = m.acc + ((size_t)S.nc + 1u) * BW;  // (row nc: always zero, the target of the read-out's pad entries)
   m.anyw = m.cnt + ((size_t)1 << (S.lgb - 1));
   m.tally = m.anyw + BW;
   m.hist = m.tally + (size_t)S.nc;  // one tally row per CTA (red.shared.add from any warp)
@@ -69,6 +69,9 @@ __device__ __forceinline__ void red_xor_s(uint32_t addr, uint32_t v) {
 __device__ __forceinline__ void red_add_s(uint32_t addr, uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
+__device__ __forceinline__ void red_add_if(bool cond, uint32_t addr, uint32_t v) {
+  asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"((uint32_t)cond), "r"(addr), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t ld_s(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
@@ -96,6 +99,48 @@ __device__ __forceinline__ uint32_t lin_digit(uint32_t cdf_s, uint32_t r) {
   for (int k = LGP - 1; k >= 0; --k)
     if (ld_s(cdf_s + ((d + (1u << k) - 1u) << 2)) <= r) d += 1u << k;
   return d;
+}
+
+// Read-out steps of one thread of the CTA variant (see k_sample_lin): program entries four steps
+// ahead in registers, branch-free (pad entries name the always-zero row nc and only switch the
+// stores off).  FULL: a warp spans 32 columns of one row (REDUX row sums).
+template <bool TALLY, bool BITS, bool FULL>
+__device__ __forceinline__ uint32_t lin_readout(const uint32_t *pp, const uint32_t G, const int n_steps,
+                                                const uint32_t col_s, const int row_shift, uint32_t *const ocol,
+                                                const long long n_words, const bool inr, const uint32_t tal_s,
+                                                const bool head, const uint32_t grp) {
+  uint32_t anyv = 0, pv = 0;
+  uint32_t en[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) { en[u] = u < n_steps ? __ldg(pp) : 0u; pp += G; }
+  for (int st = 0; st < n_steps; st += 4) {
+    uint32_t e[4], v[4], a[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      e[u] = en[u];
+      a[u] = col_s + ((e[u] & 0xFFFFu) << row_shift);
+      v[u] = ld_s(a[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { en[u] = st + 4 + u < n_steps ? __ldg(pp) : 0u; pp += G; }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (st + u >= n_steps) break;  // (uniform: the program's tail)
+      st_s(a[u], 0u);
+      v[u] ^= pv & (uint32_t)((int)e[u] >> 31);
+      pv = v[u];
+      const bool valid = (e[u] & 0x40000000u) != 0u;
+      if (BITS && inr && valid) ocol[(long long)(e[u] & 0xFFFFu) * n_words] = v[u];
+      if (TALLY) {
+        anyv |= v[u];
+        int cnt = __popc(v[u]);
+        if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+        else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+        red_add_if(head && valid, tal_s + ((e[u] & 0xFFFFu) << 2), (uint32_t)cnt);
+      }
+    }
+  }
+  return anyv;
 }
 
 // Constants of the draw loop that both kernels keep in registers.
@@ -291,7 +336,7 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
     m.cdf[i] = d < n ? S.cdf[o + d] : 0xFFFFFFFFu;
   }
   {
-    const size_t nz = (size_t)S.nc * BW + (BATCH >> 1) + BW + (size_t)S.nc + 64;
+    const size_t nz = ((size_t)S.nc + 1u) * BW + (BATCH >> 1) + BW + (size_t)S.nc + 64;
     for (size_t i = tid; i < nz; i += T) m.acc[i] = 0u;  // acc, cnt, anyw, tally, hist are contiguous
   }
   __syncthreads();
@@ -341,31 +386,9 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
       const uint32_t *pp = S.lvl_prog + ((uint32_t)tid >> lgw);
       const uint32_t col_s = acc_s + (wb << 2);
       uint32_t *const ocol = O.bits + (inr ? w : 0);
-      uint32_t anyv = 0, pv = 0;
-      uint32_t e_next = __ldg(pp);
-#pragma unroll 4
-      for (int st = 0; st < S.n_lvl; ++st) {
-        const uint32_t e = e_next;
-        if (st + 1 < S.n_lvl) e_next = __ldg(pp + (size_t)(st + 1) * G);
-        const bool valid = (e & 0x40000000u) != 0u;
-        const uint32_t row = e & 0xFFFFu;
-        uint32_t v = 0;
-        if (valid) {
-          const uint32_t a = col_s + (row << (lgw + 2));
-          v = ld_s(a);
-          st_s(a, 0u);
-          v ^= pv & (uint32_t)((int)e >> 31);
-          pv = v;
-          if (BITS && inr) ocol[(long long)row * O.n_words] = v;
-        }
-        if (TALLY) {
-          anyv |= v;
-          int cnt = __popc(v);
-          if (grp == 32u) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
-          else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
-          if (head && valid && cnt) red_add_s(tal_s + (row << 2), (uint32_t)cnt);
-        }
-      }
+      uint32_t anyv = 0;
+      if (grp == 32u) anyv = lin_readout<TALLY, BITS, true>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp);
+      else anyv = lin_readout<TALLY, BITS, false>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp);
       if (TALLY) {
         if (anyv) atomicOr(m.anyw + wb, anyv);
         // faults-per-shot histogram from the 16-bit counters (two shots per word)
@@ -433,9 +456,6 @@ __device__ __forceinline__ void st_s128z(uint32_t addr) {
 // predicated shared-memory reductions (no branch: the two candidates of a lane interleave)
 __device__ __forceinline__ void red_xor_if(uint32_t cond, uint32_t addr, uint32_t v) {
   asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.xor.b32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ void red_add_if(bool cond, uint32_t addr, uint32_t v) {
-  asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"((uint32_t)cond), "r"(addr), "r"(v) : "memory");
 }
 __device__ __forceinline__ void red_add_if(uint32_t cond, uint32_t addr, uint32_t v) {
   asm volatile("{ .reg .pred p; setp.ne.u32 p, %0, 0; @p red.shared.add.u32 [%1], %2; }" ::"r"(cond), "r"(addr), "r"(v) : "memory");
