@@ -273,6 +273,22 @@ int qec_outcome_counts_noalloc_dev(qec_circuit *c, const uint32_t *d_bits, int64
                                    int64_t n_words, uint64_t *d_out_counts, uint32_t *d_out_rows,
                                    int64_t max_out, uint64_t *d_out_status, void *stream);
 
+/* ---- minimum distance by brute force ----------------------------------
+ * Replace reference analysis/intern/distance.cpp:17-53 minimum_distance and :172-202
+ * minimum_distance_by_tests (with distance_test :71-159), bound in the reference as
+ * _c_minimum_distance / _c_minimum_distance_by_tests (bindings/analysis_bindings.cpp:56-61).
+ * Matrices are row-major uint8 [rows][2 n] in the reference's [X part | Z part] order.
+ * *distance = the minimum distance, or 0 when it exceeds max_weight (the reference's contract).
+ * Errors: "symplectic vectors must span isotropic space" (QEC_ERR_LOGIC, reference :20-21);
+ * "n-k must be < 63 for this version not to overflow." (QEC_ERR_LOGIC: the reference asserts);
+ * QEC_ERR_LIMIT beyond 256 qubits / 256 syndrome + residual bits / weight 16 (minimum_distance),
+ * beyond 85 qubits or 2^27 syndromes per half (by_tests); QEC_ERR_CUDA without a device. */
+int qec_minimum_distance(int device, int n, int n_stab, const uint8_t *stab, int n_gauge,
+                         const uint8_t *gauge, int max_weight, int *distance);
+int qec_minimum_distance_by_tests(int device, int n, int n_stab, const uint8_t *stab, int n_xl,
+                                  const uint8_t *xl, int n_zl, const uint8_t *zl, int max_weight,
+                                  int *distance);
+
 /* ---- device memory helpers (so a ctypes/cgo caller needs no CUDA binding) ------------- */
 int qec_dev_alloc(int device, size_t bytes, void **out);
 int qec_dev_free(int device, void *p);

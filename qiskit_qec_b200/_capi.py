@@ -36,6 +36,7 @@ SYMBOLS = [
     "qec_multi_sampler_tally_dev", "qec_multi_enumerator_create", "qec_multi_enumerator_destroy",
     "qec_multi_enumerator_num_paths", "qec_multi_enumerator_range", "qec_multi_enumerator_tally_dev",
     "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev", "qec_outcome_counts_noalloc_dev",
+    "qec_minimum_distance", "qec_minimum_distance_by_tests",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
     "qec_last_kernel", "qec_jit_compile_to_file",

@@ -610,105 +610,41 @@ static bool gf2_isotropic(IntMatrix &v) {
   return true;
 }
 
-static bool next_comb(int n, int k, std::vector<int> &s) {
-  if (s.empty()) { for (int j = 0; j < k; ++j) s.push_back(j); return true; }
-  if (s[0] == n - k) return false;
-  int i = k - 1;
-  while (s[i] >= n - k + i) --i;
-  ++s[i];
-  for (int j = i + 1; j < k; ++j) s[j] = s[i] + j - i;
-  return true;
+// The brute-force distance functions run on the GPU (csrc/qec_distance.cu through the C ABI):
+// reference analysis/intern/distance.cpp:17-53 and :172-202.  No host version: without a CUDA
+// device they fail like every other compute entry point.
+static std::vector<uint8_t> flatten(const IntMatrix &m, size_t cols, const char *what) {
+  std::vector<uint8_t> out;
+  out.reserve(m.size() * cols);
+  for (const auto &row : m) {
+    if (row.size() != cols) throw std::invalid_argument(std::string(what) + ": rows of unequal length");
+    for (int v : row) out.push_back((uint8_t)(v & 1));
+  }
+  return out;
 }
 
 static int min_distance(IntMatrix &stab, IntMatrix &gauge, int max_weight) {
-  if (!gf2_isotropic(stab)) throw std::logic_error("symplectic vectors must span isotropic space");
-  const int n = (int)stab[0].size() / 2;
-  const int rk = gf2_rank(stab);
-  BitRows V(gauge);
-  std::vector<size_t> piv;
-  const int rk2 = echelon(V, &piv);
-  const int k = n - (rk + rk2) / 2;
-  for (int weight = 1; weight <= std::min(max_weight, n); ++weight) {
-    std::vector<int> where;
-    while (next_comb(n, weight, where)) {
-      std::vector<int> dig(weight, 0);
-      for (;;) {
-        std::vector<int> err(2 * (size_t)n, 0);
-        for (int i = 0; i < weight; ++i) {
-          if (dig[i] == 0 || dig[i] == 2) err[where[i]] = 1;
-          if (dig[i] == 1 || dig[i] == 2) err[where[i] + n] = 1;
-        }
-        bool commutes = true;
-        for (const auto &srow : stab) if (sip(srow, err)) { commutes = false; break; }
-        if (commutes) {
-          std::vector<uint64_t> e = V.pack(err);  // membership in span(gauge): reduce by the basis
-          for (int b = 0; b < rk2; ++b)
-            if ((e[piv[b] >> 6] >> (piv[b] & 63)) & 1)
-              for (size_t w = 0; w < V.words; ++w) e[w] ^= V.r[b][w];
-          bool inV = true;
-          for (uint64_t w : e) if (w) { inV = false; break; }
-          if ((k > 0 && !inV) || (k == 0 && inV)) return weight;
-        }
-        int j = weight - 1;
-        for (; j >= 0; --j) { if (++dig[j] < 3) break; dig[j] = 0; }
-        if (j < 0) break;
-      }
-    }
-  }
-  return 0;
-}
-
-// exists a Pauli built from `weight` single-qubit terms that commutes with every stabilizer
-// row and anticommutes with `logical` (meet in the middle over syndromes)
-static bool distance_test(const IntMatrix &stab, const std::vector<int> &logical, int weight) {
-  const int n = (int)stab[0].size() / 2, m = (int)stab.size();
-  if (m >= 63) throw std::logic_error("n-k must be < 63 for this version not to overflow.");
-  std::vector<uint64_t> sq;
-  for (int q = 0; q < n; ++q) {
-    uint64_t sx = 0, sz = 0;
-    for (int i = 0; i < m; ++i) {
-      if (stab[i][n + q] == 1) sx |= 1ull << i;
-      if (stab[i][q] == 1) sz |= 1ull << i;
-    }
-    if (logical[n + q] == 1) sx |= 1ull << m;
-    if (logical[q] == 1) sz |= 1ull << m;
-    sq.push_back(sx); sq.push_back(sz); sq.push_back(sx ^ sz);
-  }
-  const int w1 = (weight + 1) / 2, w2 = weight / 2;
-  const uint64_t top = 1ull << m;
-  auto collect = [&](int w, std::vector<uint64_t> &comm, std::vector<uint64_t> &anti) {
-    if (w <= 0) return;
-    if (w > (int)sq.size()) throw std::invalid_argument("0 <= k <= n");
-    std::vector<int> s;
-    while (next_comb((int)sq.size(), w, s)) {
-      uint64_t synd = 0;
-      for (int i = 0; i < w; ++i) synd ^= sq[s[i]];
-      if (synd & top) anti.push_back(synd ^ top); else comm.push_back(synd);
-    }
-    std::sort(comm.begin(), comm.end());
-    std::sort(anti.begin(), anti.end());
-  };
-  std::vector<uint64_t> c1, a1, c2, a2;
-  collect(w1, c1, a1);
-  if (w1 != w2) collect(w2, c2, a2); else { c2 = c1; a2 = a1; }
-  auto meets = [](const std::vector<uint64_t> &x, const std::vector<uint64_t> &y) {
-    size_t i = 0, j = 0;
-    while (i < x.size() && j < y.size()) {
-      if (x[i] == y[j]) return true;
-      if (x[i] < y[j]) ++i; else ++j;
-    }
-    return false;
-  };
-  return meets(c1, a2) || meets(a1, c2);
+  if (stab.empty() || gauge.empty() || stab[0].empty() || (stab[0].size() & 1))
+    throw std::invalid_argument("minimum_distance: empty or odd-length symplectic vectors");
+  const size_t cols = stab[0].size();
+  const std::vector<uint8_t> s = flatten(stab, cols, "symplectic_vectors"), g = flatten(gauge, cols, "symplectic_gauge_vectors");
+  int d = 0;
+  check(qec_minimum_distance(default_device(), (int)(cols / 2), (int)stab.size(), s.data(), (int)gauge.size(),
+                             g.data(), max_weight, &d));
+  return d;
 }
 
 static int min_distance_by_tests(IntMatrix &stab, IntMatrix &xl, IntMatrix &zl, int max_weight) {
-  int best = max_weight + 1;
-  for (const IntMatrix *ops : {&xl, &zl})
-    for (const auto &row : *ops)
-      for (int w = 1; w <= max_weight; ++w)
-        if (distance_test(stab, row, w)) { best = std::min(best, w); break; }
-  return best <= max_weight ? best : 0;
+  if (stab.empty() || stab[0].empty() || (stab[0].size() & 1))
+    throw std::invalid_argument("minimum_distance_by_tests: empty or odd-length symplectic vectors");
+  const size_t cols = stab[0].size();
+  const std::vector<uint8_t> s = flatten(stab, cols, "symplectic_vectors"), x = flatten(xl, cols, "symplectic_xl"),
+                             z = flatten(zl, cols, "symplectic_zl");
+  int d = 0;
+  check(qec_minimum_distance_by_tests(default_device(), (int)(cols / 2), (int)stab.size(), s.data(), (int)xl.size(),
+                                      x.empty() ? nullptr : x.data(), (int)zl.size(), z.empty() ? nullptr : z.data(),
+                                      max_weight, &d));
+  return d;
 }
 
 }  // namespace qecb200

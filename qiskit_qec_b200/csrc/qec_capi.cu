@@ -18,6 +18,7 @@
 #include "../../include/qec_b200.h"
 #include "qec_kernels.cuh"
 #include "qec_jit.h"
+#include "qec_distance.h"
 
 // ---- error plumbing --------------------------------------------------------------------------
 static thread_local std::string g_err;
@@ -2432,6 +2433,27 @@ extern "C" int qec_measure_int_peak(int device, double ms, double *lane_ops_per_
   if (lane_ops_per_s) *lane_ops_per_s = best;
   if (sm_clock_mhz) *sm_clock_mhz = khz / 1000.0;
   return 0;
+}
+
+// ---- minimum distance (qec_distance.cu) --------------------------------------------------------
+extern "C" int qec_minimum_distance(int device, int n, int n_stab, const uint8_t *stab, int n_gauge,
+                                    const uint8_t *gauge, int max_weight, int *distance) {
+  DevInfo *d;
+  if (int rc = dev_info(device, &d)) return rc;
+  char msg[256] = "";
+  const int rc = qd_minimum_distance(device, d->sms, n, n_stab, stab, n_gauge, gauge, max_weight, distance, msg, sizeof msg);
+  return rc ? fail(rc, "%s", msg) : 0;
+}
+
+extern "C" int qec_minimum_distance_by_tests(int device, int n, int n_stab, const uint8_t *stab, int n_xl,
+                                             const uint8_t *xl, int n_zl, const uint8_t *zl, int max_weight,
+                                             int *distance) {
+  DevInfo *d;
+  if (int rc = dev_info(device, &d)) return rc;
+  char msg[256] = "";
+  const int rc = qd_minimum_distance_by_tests(device, d->sms, n, n_stab, stab, n_xl, xl, n_zl, zl, max_weight,
+                                              distance, msg, sizeof msg);
+  return rc ? fail(rc, "%s", msg) : 0;
 }
 
 #define DEV_ENTER(device) { DevInfo *d__; int rc__ = dev_info(device, &d__); if (rc__) return rc__; CU(cudaSetDevice(device)); }

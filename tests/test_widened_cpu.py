@@ -1,10 +1,9 @@
 """CPU tests of the pieces around the hot path that need no GPU:
 
-  * the four free functions the reference module exports next to the three classes
-    (``_c_minimum_distance``, ``_c_minimum_distance_by_tests``, ``_c_rank``, ``_c_isotropic``;
-    reference ``analysis/bindings/analysis_bindings.cpp:56-61``): the host versions in
-    ``csrc/bindings.cpp`` against the compiled reference (``oracle/_ref``) on the reference's own
-    code tables (``test/distance/test_minimum_distance_extension.py``) and on random inputs;
+  * ``_c_rank`` / ``_c_isotropic`` (reference ``analysis/bindings/analysis_bindings.cpp:56-61``,
+    host linear algebra as in the reference) against the compiled reference (``oracle/_ref``) on
+    the reference's own code tables and on random inputs; the two distance functions of the same
+    block run on the GPU and are tested in ``tests/test_gpu_distance.py``;
   * ``lower()`` fed by a qiskit-shaped circuit -- a stub ``qiskit.converters``
     with duck-typed DAG nodes (``.name .qargs .cargs .op._label``), since qiskit itself is not
     installed here: op order, qubit / clbit flattening, labels, the unknown-op exception and the
@@ -47,52 +46,33 @@ def ours():
 
 
 @pytest.mark.parametrize("name", sorted(CODES))
-def test_minimum_distance_reference_kats(ours, ref, name):
-    paulis, d = CODES[name]
+def test_rank_and_isotropic_on_reference_tables(ours, ref, name):
+    paulis, _ = CODES[name]
     stab = [_strarray(p) for p in paulis]
-    assert ours._c_minimum_distance(stab, stab) == d == ref._c_minimum_distance(stab, stab)
-    assert ours._c_minimum_distance(stab, stab, 2) == ref._c_minimum_distance(stab, stab, 2)
     assert ours._c_isotropic(stab) is True and ref._c_isotropic(stab) is True
     assert ours._c_rank(stab) == ref._c_rank(stab)
 
 
-def test_minimum_distance_by_tests_matches_reference(ours, ref):
-    # Steane code with its transversal logicals; five-qubit code
-    stab = [_strarray(p) for p in CODES["steane"][0]]
-    xl, zl = [_strarray("xxxxxxx")], [_strarray("zzzzzzz")]
-    assert ours._c_minimum_distance_by_tests(stab, xl, zl) == 3 == ref._c_minimum_distance_by_tests(stab, xl, zl)
-    assert ours._c_minimum_distance_by_tests(stab, xl, zl, 2) == ref._c_minimum_distance_by_tests(stab, xl, zl, 2) == 0
-    stab = [_strarray(p) for p in CODES["five"][0]]
-    xl, zl = [_strarray("xxxxx")], [_strarray("zzzzz")]
-    assert ours._c_minimum_distance_by_tests(stab, xl, zl) == ref._c_minimum_distance_by_tests(stab, xl, zl) == 3
-
-
-def test_rank_isotropic_and_distance_random_differential(ours, ref):
+def test_rank_isotropic_random_differential(ours, ref):
     rng = np.random.default_rng(2)
     for trial in range(200):
         rows, cols = int(rng.integers(1, 9)), 2 * int(rng.integers(1, 40))
         m = rng.integers(0, 2, size=(rows, cols)).astype(int).tolist()
         assert ours._c_rank(m) == ref._c_rank(m), trial
         assert ours._c_isotropic(m) == ref._c_isotropic(m), trial
-    # random small stabilizer groups (commuting sets built by rejection) with gauge = stabilizer
-    done = 0
-    while done < 25:
-        n = int(rng.integers(3, 7))
-        gens = []
-        for _ in range(int(rng.integers(1, n))):
-            for _try in range(50):
-                v = rng.integers(0, 2, size=2 * n).astype(int).tolist()
-                if any(v) and ours._c_isotropic(gens + [v]):
-                    gens.append(v)
-                    break
-        if not gens:
-            continue
-        assert ours._c_minimum_distance(gens, gens, 4) == ref._c_minimum_distance(gens, gens, 4), gens
-        done += 1
-    with pytest.raises(RuntimeError):
-        ours._c_minimum_distance([_strarray("xi"), _strarray("zi")], [_strarray("xi")])
-    with pytest.raises(RuntimeError):
-        ref._c_minimum_distance([_strarray("xi"), _strarray("zi")], [_strarray("xi")])
+
+
+def test_minimum_distance_needs_the_gpu(ours):
+    """The brute-force distance functions run on the GPU (csrc/qec_distance.cu; parity tests in
+    tests/test_gpu_distance.py): without a device they fail loudly, there is no host version."""
+    from qiskit_qec_b200 import _capi
+    if _capi.device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    stab = [_strarray(p) for p in CODES["four"][0]]
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        ours._c_minimum_distance(stab, stab)
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        ours._c_minimum_distance_by_tests(stab, [_strarray("xxii")], [_strarray("zzii")])
 
 
 # ------------------------------------------------------------------------- 8(f1): lower()
