@@ -20,6 +20,11 @@
 #include "qec_jit.h"
 #include "qec_distance.h"
 
+// revision tag of the linear-response kernels in the variant strings: bumped with every change of
+// k_sample_lanes / k_sample_lin, so that a committed ncu capture (profiles/rNN/ncu_dominant_kernel.json,
+// "variant_key") can only be attributed to the code it was taken from
+#define QEC_LIN_REV "r2d"
+
 // ---- error plumbing --------------------------------------------------------------------------
 static thread_local std::string g_err;
 
@@ -1920,7 +1925,7 @@ extern "C" const char *qec_sampler_variant(const qec_sampler *s) {
   qec_sampler *m = const_cast<qec_sampler *>(s);
   if (s->lin.eligible) {
     const QecLinDev &d = s->lin.dev;
-    m->variant = std::string("linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
+    m->variant = std::string("linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams/" QEC_LIN_REV : d.warp_mode ? "warp-batches" : "cta-batches/" QEC_LIN_REV) +
                  " batch=" + std::to_string(1 << d.lgb) + " streams=" + std::to_string(d.n_streams) +
                  " draw=" + std::to_string(d.draw);
   } else if (s->jit.eligible) {
@@ -1991,7 +1996,7 @@ static int sample_launch(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint3
     time_end(s->c, stream);
     CU(cudaGetLastError());
     s->last_cap = 0;
-    g_last_kernel = std::string("sample:linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams" : d.warp_mode ? "warp-batches" : "cta-batches") +
+    g_last_kernel = std::string("sample:linear ") + (s->lin.l16 ? "lane16-streams" : d.lane_mode ? "lane-streams/" QEC_LIN_REV : d.warp_mode ? "warp-batches" : "cta-batches/" QEC_LIN_REV) +
                     " batch=" + std::to_string(1 << d.lgb) + " streams=" +
                     std::to_string(d.n_streams) + " T=" + std::to_string(cfg.block) + " ctas/sm=" +
                     std::to_string(s->lin.ctas) + " smem=" + std::to_string(cfg.smem) +

@@ -1008,6 +1008,95 @@ __device__ __forceinline__ void planes_add_group(LanePlanes &P, const uint32_t *
   if (cc) planes_carry(P, cc);
 }
 
+// The lane's fault stream of one batch.  NP Philox calls (2 NP candidates) per trip,
+// software-pipelined: the next trip's Philox and gaps do not depend on the position, so they are
+// computed while this trip's candidates wait on shared memory.  The position saturates at `end`
+// (a finished lane's candidates all land beyond it).  FAST: every shot of the batch is inside the
+// requested range and no 32-bit draw reaches the gap clamp.
+template <bool TALLY, bool EXPORT, int NP, bool FAST>
+__device__ __forceinline__ void lanes_stream(const QecLinDev &S, const QecSampleExport &X, const uint32_t blo,
+                                             const uint32_t bhi, const int lane, const uint32_t end, const float C,
+                                             const uint32_t lane_sh, const uint32_t nsh, const uint32_t info2_s,
+                                             const uint32_t rec_s, const uint32_t lane_acc, LanePlanes &P,
+                                             uint32_t *xrow, uint32_t &xk) {
+  uint32_t pos = 0xFFFFFFFFu;  // -1
+  QecPhilox rr[NP];
+  uint32_t gg[2 * NP];
+#pragma unroll
+  for (int c = 0; c < NP; ++c) {
+    rr[c] = qec_philox_rk(blo, bhi, (uint32_t)c * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+    gg[2 * c] = qec_gap_len(rr[c].c[0], C);
+    gg[2 * c + 1] = qec_gap_len(rr[c].c[2], C);
+  }
+  // (pos + 1 <= end: the lane is still inside its stream; positions stay below 2^27 + end)
+  for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); it += NP) {
+    QecPhilox nr[NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c)
+      nr[c] = qec_philox_rk(blo, bhi, (it + NP + (uint32_t)c) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
+    uint32_t pp[2 * NP], sl[2 * NP], dd[2 * NP];
+    bool ok[2 * NP];
+    uint2 qq[2 * NP];
+    uint32_t run = pos;
+    if (FAST) {
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) {
+        run += gg[j] + 1u;
+        pp[j] = run;
+        ok[j] = run < end;
+        sl[j] = ok[j] ? run >> 5 : 0u;
+      }
+      pos = min(run, end);
+    } else {
+      const bool live = pos + 1u <= end;
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) {
+        const bool has = gg[j] < QEC_GAP_CAP;
+        run += gg[j] + (has ? 1u : 0u);
+        pp[j] = run;
+        ok[j] = live && has && run < end && (lane_sh + (run & 31u)) < nsh;
+        sl[j] = ok[j] ? run >> 5 : 0u;
+      }
+      pos = live ? min(run, end) : end;
+    }
+#pragma unroll
+    for (int j = 0; j < 2 * NP; ++j) {
+      const uint32_t inf = ld_s(info2_s + (sl[j] << 2));
+      dd[j] = __umulhi(rr[j >> 1].c[(j & 1) * 2 + 1], inf >> 21);
+      qq[j] = ld_s64(rec_s + (((inf & 0x1FFFFFu) + dd[j]) << 3));
+    }
+    uint32_t ng[2 * NP];
+#pragma unroll
+    for (int c = 0; c < NP; ++c) {
+      ng[2 * c] = qec_gap_len(nr[c].c[0], C);
+      ng[2 * c + 1] = qec_gap_len(nr[c].c[2], C);
+    }
+#pragma unroll
+    for (int j = 0; j < 2 * NP; ++j) lanes_apply(pp[j], ok[j], qq[j], lane_acc);
+    if (EXPORT) {
+      // the lane owns its 32-shot word: events go to the word's row in stream order, the count
+      // stays in a register (no atomics)
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j)
+        if (ok[j]) {
+          if (xk < (uint32_t)X.cap) xrow[xk] = (S.slloc[sl[j]] << 14) | ((pp[j] & 31u) << 9) | dd[j];
+          ++xk;
+        }
+    }
+    if (TALLY) {
+      uint32_t mk[2 * NP];
+#pragma unroll
+      for (int j = 0; j < 2 * NP; ++j) mk[j] = ok[j] ? 1u << (pp[j] & 31u) : 0u;
+#pragma unroll
+      for (int j = 0; j < 2 * NP; j += 4) planes_add_group(P, mk + j, 2 * NP - j < 4 ? 2 * NP - j : 4);
+    }
+#pragma unroll
+    for (int c = 0; c < NP; ++c) rr[c] = nr[c];
+#pragma unroll
+    for (int j = 0; j < 2 * NP; ++j) gg[j] = ng[j];
+  }
+}
+
 template <bool TALLY, bool BITS, bool EXPORT, int NP>
 __global__ void __launch_bounds__(384, 1)
 k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, const long long n_shots,
@@ -1066,78 +1155,16 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
 
     // ---- the lane's fault stream
     LanePlanes P = {0u, 0u, 0u, 0u, 0u, 0u};
-    uint32_t pos = 0xFFFFFFFFu;  // -1; saturates at `end`
     uint32_t xk = 0;
     const long long xw = (b << 5) + lane - w_lo;  // the lane's word in the export arrays
     const bool xin = EXPORT && xw >= 0 && xw < O.n_words;
     uint32_t *xrow = EXPORT ? X.ev + (xin ? xw : 0) * X.cap : nullptr;
-    // NP Philox calls (2 NP candidates) per trip, software-pipelined: the next trip's Philox and
-    // gaps do not depend on the position, so they are computed while this trip's candidates wait
-    // on shared memory (2 NP independent dependency chains per warp).
-    QecPhilox rr[NP];
-    uint32_t gg[2 * NP];
-#pragma unroll
-    for (int c = 0; c < NP; ++c) {
-      rr[c] = qec_philox_rk(blo, bhi, (uint32_t)c * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      gg[2 * c] = qec_gap_len(rr[c].c[0], C);
-      gg[2 * c + 1] = qec_gap_len(rr[c].c[2], C);
-    }
-    for (uint32_t it = 0; __any_sync(0xFFFFFFFFu, pos + 1u <= end); it += NP) {
-      QecPhilox nr[NP];
-#pragma unroll
-      for (int c = 0; c < NP; ++c)
-        nr[c] = qec_philox_rk(blo, bhi, (it + NP + (uint32_t)c) * 32u + (uint32_t)lane, 0x4D000000u, S.rk);
-      // (pos + 1 <= end: the lane is still inside its stream; positions stay below 2^27 + end)
-      const bool live = pos + 1u <= end;
-      uint32_t pp[2 * NP], sl[2 * NP], dd[2 * NP];
-      bool ok[2 * NP];
-      uint2 qq[2 * NP];
-      uint32_t run = pos;
-#pragma unroll
-      for (int j = 0; j < 2 * NP; ++j) {
-        const bool has = g_noclamp || gg[j] < QEC_GAP_CAP;
-        run += gg[j] + (has ? 1u : 0u);
-        pp[j] = run;
-        ok[j] = live && has && run < end && (full || (lane_sh + (run & 31u)) < nsh);
-        sl[j] = ok[j] ? run >> 5 : 0u;
-      }
-      pos = live ? min(run, end) : end;
-#pragma unroll
-      for (int j = 0; j < 2 * NP; ++j) {
-        const uint32_t inf = ld_s(info2_s + (sl[j] << 2));
-        dd[j] = __umulhi(rr[j >> 1].c[(j & 1) * 2 + 1], inf >> 21);
-        qq[j] = ld_s64(rec_s + (((inf & 0x1FFFFFu) + dd[j]) << 3));
-      }
-      uint32_t ng[2 * NP];
-#pragma unroll
-      for (int c = 0; c < NP; ++c) {
-        ng[2 * c] = qec_gap_len(nr[c].c[0], C);
-        ng[2 * c + 1] = qec_gap_len(nr[c].c[2], C);
-      }
-#pragma unroll
-      for (int j = 0; j < 2 * NP; ++j) lanes_apply(pp[j], ok[j], qq[j], lane_acc);
-      if (EXPORT) {
-        // the lane owns its 32-shot word: events go to the word's row in stream order, the count
-        // stays in a register (no atomics)
-#pragma unroll
-        for (int j = 0; j < 2 * NP; ++j)
-          if (ok[j]) {
-            if (xk < (uint32_t)X.cap) xrow[xk] = (S.slloc[sl[j]] << 14) | ((pp[j] & 31u) << 9) | dd[j];
-            ++xk;
-          }
-      }
-      if (TALLY) {
-        uint32_t mk[2 * NP];
-#pragma unroll
-        for (int j = 0; j < 2 * NP; ++j) mk[j] = ok[j] ? 1u << (pp[j] & 31u) : 0u;
-#pragma unroll
-        for (int j = 0; j < 2 * NP; j += 4) planes_add_group(P, mk + j, 2 * NP - j < 4 ? 2 * NP - j : 4);
-      }
-#pragma unroll
-      for (int c = 0; c < NP; ++c) rr[c] = nr[c];
-#pragma unroll
-      for (int j = 0; j < 2 * NP; ++j) gg[j] = ng[j];
-    }
+    // (FAST: every shot of the batch is inside the requested range and no 32-bit draw reaches the
+    // gap clamp -- the common case: no range test, no clamp test per candidate)
+    if (full && g_noclamp)
+      lanes_stream<TALLY, EXPORT, NP, true>(S, X, blo, bhi, lane, end, C, lane_sh, nsh, info2_s, rec_s, lane_acc, P, xrow, xk);
+    else
+      lanes_stream<TALLY, EXPORT, NP, false>(S, X, blo, bhi, lane, end, C, lane_sh, nsh, info2_s, rec_s, lane_acc, P, xrow, xk);
     if (EXPORT && xin) X.cnt[xw] = xk;
     __syncwarp();
 

@@ -33,6 +33,7 @@ def main():
         "kernel": d.get("Kernel Name", "") + " -- " + (sys.argv[3] if len(sys.argv) > 3 else ""),
         "capture": "ncu --set full --clock-control none --import-source on -k regex:k_sample_l -s 3 -c 1 python "
                    "bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-enum (profiles/profile_cmd.sh)",
+        "variant_key": sys.argv[4] if len(sys.argv) > 4 else "",
         "shots_per_launch": shots,
         "gpu__time_duration_ms": t_ms,
         "dram__bytes_write.sum": nbytes("dram__bytes_write.sum"),
