@@ -23,7 +23,7 @@
 // revision tag of the linear-response kernels in the variant strings: bumped with every change of
 // k_sample_lanes / k_sample_lin, so that a committed ncu capture (profiles/rNN/ncu_dominant_kernel.json,
 // "variant_key") can only be attributed to the code it was taken from
-#define QEC_LIN_REV "r2d"
+#define QEC_LIN_REV "r2e"
 
 // ---- error plumbing --------------------------------------------------------------------------
 static thread_local std::string g_err;

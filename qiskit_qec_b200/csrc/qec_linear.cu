@@ -840,8 +840,11 @@ struct LaneReadCtx {
   long long n_words;
 };
 
-// one trip: QEC_LANES_UNROLL passes whose entries e[] and rows v[] are already loaded
-template <bool TALLY, bool BITS, bool FAST>
+// one trip: QEC_LANES_UNROLL passes whose entries e[] and rows v[] are already loaded.  ST: how a
+// lane stores its four words of a row -- 2: one 128-bit store (rows 16-byte aligned), 1: four
+// 32-bit stores (the batch's words all exist, rows not aligned: n_words not a multiple of 4),
+// 0: each word checked against the range
+template <bool TALLY, bool BITS, int ST>
 __device__ __forceinline__ void lanes_trip(const LaneReadCtx &R, const uint32_t (&e)[QEC_LANES_UNROLL],
                                            uint4 (&v)[QEC_LANES_UNROLL], uint4 &pv, uint4 &anyv,
                                            uint32_t (&cpk)[QEC_LANES_UNROLL / 2]) {
@@ -856,8 +859,11 @@ __device__ __forceinline__ void lanes_trip(const LaneReadCtx &R, const uint32_t 
       const uint32_t row = e[u] & 0xFFu;
       // (row * bytes per row in one 32 x 32 -> 64 multiply-add; rows of 2^32 bytes or more take the slow form)
       char *po = R.row32 ? R.colp + (unsigned long long)row * (uint32_t)R.rowbytes : R.colp + (unsigned long long)row * R.rowbytes;
-      if (FAST) *reinterpret_cast<uint4 *>(po) = v[u];
-      else {
+      if (ST == 2) *reinterpret_cast<uint4 *>(po) = v[u];
+      else if (ST == 1) {
+        uint32_t *pw = reinterpret_cast<uint32_t *>(po);
+        pw[0] = v[u].x; pw[1] = v[u].y; pw[2] = v[u].z; pw[3] = v[u].w;
+      } else {
         uint32_t *pw = reinterpret_cast<uint32_t *>(po);
         const uint32_t vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
@@ -903,6 +909,29 @@ __device__ __forceinline__ void lanes_counts_flush(LaneCounts &LC, const uint32_
   LC.nb = 0u;
 }
 
+template <bool TALLY, bool BITS, int ST>
+__device__ __forceinline__ void lanes_readout_unrolled(const LaneReadCtx &R, const uint32_t n_steps,
+                                                       uint32_t (&en)[QEC_LANES_UNROLL], uint4 (&vn)[QEC_LANES_UNROLL],
+                                                       uint4 &pv, uint4 &anyv, LaneCounts &LC) {
+#pragma unroll
+  for (int t = 0; t < QEC_LANES_MAXTRIPS; ++t) {
+    const uint32_t pass = (uint32_t)t * QEC_LANES_UNROLL;
+    if (pass >= n_steps) break;
+    uint32_t e[QEC_LANES_UNROLL], cpk[QEC_LANES_UNROLL / 2];
+    uint4 v[QEC_LANES_UNROLL];
+#pragma unroll
+    for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; }
+    if (t + 1 < QEC_LANES_MAXTRIPS && pass + QEC_LANES_UNROLL < n_steps) {
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
+#pragma unroll
+      for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
+    }
+    lanes_trip<TALLY, BITS, ST>(R, e, v, pv, anyv, cpk);
+    if (TALLY) { LC.c[2 * t] += cpk[0]; LC.c[2 * t + 1] += cpk[1]; }
+  }
+}
+
 template <bool TALLY, bool BITS>
 __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
                                                   const uint32_t prog_s, const uint32_t n_steps,
@@ -928,24 +957,11 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
   for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((uint32_t)u << 4));
 #pragma unroll
   for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
-  if (whole && vec_ok) {
-#pragma unroll
-    for (int t = 0; t < QEC_LANES_MAXTRIPS; ++t) {
-      const uint32_t pass = (uint32_t)t * QEC_LANES_UNROLL;
-      if (pass >= n_steps) break;
-      uint32_t e[QEC_LANES_UNROLL], cpk[QEC_LANES_UNROLL / 2];
-      uint4 v[QEC_LANES_UNROLL];
-#pragma unroll
-      for (int u = 0; u < QEC_LANES_UNROLL; ++u) { e[u] = en[u]; v[u] = vn[u]; }
-      if (t + 1 < QEC_LANES_MAXTRIPS && pass + QEC_LANES_UNROLL < n_steps) {
-#pragma unroll
-        for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((pass + QEC_LANES_UNROLL + u) << 4));
-#pragma unroll
-        for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
-      }
-      lanes_trip<TALLY, BITS, true>(R, e, v, pv, anyv, cpk);
-      if (TALLY) { LC.c[2 * t] += cpk[0]; LC.c[2 * t + 1] += cpk[1]; }
-    }
+  if (whole) {
+    // the trips unrolled: per-clbit counts in registers (LaneCounts).  One straight-line copy per
+    // store mode (the kernel is sensitive to instruction fetch: the two must not interleave).
+    if (vec_ok) lanes_readout_unrolled<TALLY, BITS, 2>(R, n_steps, en, vn, pv, anyv, LC);
+    else lanes_readout_unrolled<TALLY, BITS, 1>(R, n_steps, en, vn, pv, anyv, LC);
     if (TALLY && ++LC.nb == QEC_LANES_FLUSH) lanes_counts_flush(LC, tal_s, prog_s, n_steps, lane);
   } else {
     const bool head = R.c4 == 0u;
@@ -960,7 +976,7 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
 #pragma unroll
         for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
       }
-      lanes_trip<TALLY, BITS, false>(R, e, v, pv, anyv, cpk);
+      lanes_trip<TALLY, BITS, 0>(R, e, v, pv, anyv, cpk);
       if (TALLY) {
         lanes_tally_pair(cpk[0] & 0xFFFFu, cpk[0] >> 16, e[0], e[1], tal_s, head);
         lanes_tally_pair(cpk[1] & 0xFFFFu, cpk[1] >> 16, e[2], e[3], tal_s, head);
