@@ -850,6 +850,8 @@ static int enum_plan_linear(qec_enumerator *e) {
   ln.dev.n_faults = (uint32_t)F;
   ln.dev.batch_ctr = ln.d_ctr;
   ln.dev.e32 = e32;
+  // (QEC_B200_LANES_FLUSH: a test hook -- small values exercise the mid-launch flush of the counters)
+  ln.dev.flush_every = (uint32_t)std::min(448, std::max(1, env_int("QEC_B200_LANES_FLUSH", 448)));
   ln.cfg.block = 32 * warps; ln.cfg.grid = di.sms; ln.cfg.smem = smem;
   ln.eligible = true;
   return 0;
@@ -1559,6 +1561,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   d.info2 = reinterpret_cast<const uint2 *>(ln.d_info2);
   d.fast = fast;
   d.lane_mode = lane_mode;
+  d.flush_every = (uint32_t)std::min(448, std::max(1, env_int("QEC_B200_LANES_FLUSH", 448)));  // (test hook, see enum_plan_linear)
   d.lanes_np = env_int("QEC_B200_LANES_NP", 2);  // (results do not depend on it: the lane's stream is sequential)
   d.lvl_prog = ln.d_lvl_prog; d.lvl_off = ln.d_lvl_off;
   d.n_lvl = cta_steps;  // steps of the CTA variant's read-out program

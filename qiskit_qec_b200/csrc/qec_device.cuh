@@ -141,6 +141,7 @@ struct QecLinDev {
   // lane-stream variant (k_sample_lanes): lgb = 10, lane = word column, no shared-memory atomics;
   // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
   int lane_mode;
+  uint32_t flush_every;     // lane-stream kernel: batches between flushes of the register tally counters (at most 448)
   int lanes_np;             // Philox calls (two candidates each) per loop trip of the lane-stream kernel: 2, 3 or 4
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
   // CTA variant: read-out program lvl_prog[step * G + group], G = threads / words per batch row,
@@ -161,6 +162,7 @@ struct QecEnumLinDev {
   uint32_t n_faults;
   uint32_t *batch_ctr;      // batches handed out so far in this launch (zeroed per launch)
   int e32;                  // fewer than 2^32 paths: suffix-sum tables as 32-bit words in shared memory
+  uint32_t flush_every;     // batches between flushes of the register tally counters (at most 448)
 };
 static inline __host__ __device__ size_t qec_enum_lanes_smem_words(int nc, int warps, uint32_t n_faults,
                                                                    uint32_t prog_words, uint32_t L, int order,

@@ -824,7 +824,7 @@ __device__ __forceinline__ void lanes_apply(const uint32_t p, const bool ok, con
 // Partial batches take the rolled loop with the per-pass reduction.
 // Returns nothing; anyv collects the OR of all rows (non-zero outcomes).
 #define QEC_LANES_MAXTRIPS 16  // 64 passes of four rows >= 254 clbits
-#define QEC_LANES_FLUSH 448u   // batches between flushes: 448 * 128 < 2^16 per lane and row
+#define QEC_LANES_FLUSH 448u   // most batches between flushes (QecLinDev::flush_every): 448 * 128 < 2^16 per lane and row
 
 struct LaneCounts {
   uint32_t c[2 * QEC_LANES_MAXTRIPS];
@@ -936,7 +936,7 @@ template <bool TALLY, bool BITS>
 __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint32_t acc_s, const uint32_t tal_s,
                                                   const uint32_t prog_s, const uint32_t n_steps,
                                                   const long long w0, const bool vec_ok, const int lane,
-                                                  LaneCounts &LC) {
+                                                  LaneCounts &LC, const uint32_t flush_every) {
   static_assert(QEC_LANES_UNROLL == 4, "two packed count registers per trip");
   const bool whole = w0 >= 0 && w0 + 32 <= O.n_words;  // the batch's 32 words all exist
   LaneReadCtx R;
@@ -962,7 +962,7 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
     // store mode (the kernel is sensitive to instruction fetch: the two must not interleave).
     if (vec_ok) lanes_readout_unrolled<TALLY, BITS, 2>(R, n_steps, en, vn, pv, anyv, LC);
     else lanes_readout_unrolled<TALLY, BITS, 1>(R, n_steps, en, vn, pv, anyv, LC);
-    if (TALLY && ++LC.nb == QEC_LANES_FLUSH) lanes_counts_flush(LC, tal_s, prog_s, n_steps, lane);
+    if (TALLY && ++LC.nb >= flush_every) lanes_counts_flush(LC, tal_s, prog_s, n_steps, lane);
   } else {
     const bool head = R.c4 == 0u;
     for (uint32_t pass = 0; pass < n_steps; pass += QEC_LANES_UNROLL) {
@@ -1186,7 +1186,7 @@ k_sample_lanes(const QecOutDev O, const QecLinDev S, const long long shot_lo, co
 
     // ---- read-out (lanes_readout): four rows per pass, lane = (row of the pass, 4-word piece)
     const long long w0 = (b << 5) - w_lo;  // first output word of the batch (may be < 0 at the range start)
-    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)S.n_steps, w0, vec_ok, lane, LC);
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)S.n_steps, w0, vec_ok, lane, LC, S.flush_every);
     if (TALLY) {
       nz_shots += nzb;
       // faults-per-shot histogram from the planes
@@ -1365,12 +1365,18 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
     if (nv > 0) {
       LinEnumState<K> st;
       lin_enum_unrank<K, E32>(E, es_s, linfo_s, (unsigned long long)(lo + first), st);
+      // (software-pipelined: the next path's records are loaded before this path's flips)
+      uint2 qn[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) qn[j] = ld_s64(rec_s + ((st.pb[j] + st.dig[j]) << 3));
       for (int i = 0; i < nv; ++i) {
         const uint32_t msk = 1u << i;
         uint2 q[K];
 #pragma unroll
-        for (int j = 0; j < K; ++j) q[j] = ld_s64(rec_s + ((st.pb[j] + st.dig[j]) << 3));
+        for (int j = 0; j < K; ++j) q[j] = qn[j];
         lin_enum_next<K>(linfo_s, L, st);
+#pragma unroll
+        for (int j = 0; j < K; ++j) qn[j] = ld_s64(rec_s + ((st.pb[j] + st.dig[j]) << 3));
 #pragma unroll
         for (int j = 0; j < K; ++j) {
           // (two faults of a path may flip the same row: one record at a time, loads first)
@@ -1389,7 +1395,7 @@ k_enum_lanes(const QecOutDev O, const QecEnumDev E, const QecEnumLinDev EL, cons
       }
     }
     __syncwarp();
-    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)EL.n_steps, b << 5, vec_ok, lane, LC);
+    const uint32_t nzb = lanes_readout<TALLY, BITS>(O, acc_s, tal_s, prog_s, (uint32_t)EL.n_steps, b << 5, vec_ok, lane, LC, EL.flush_every);
     if (TALLY) nz_paths += nzb;
     __syncwarp();
   }

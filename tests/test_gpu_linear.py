@@ -308,3 +308,40 @@ def test_linear_kernels_on_random_circuits_with_clbits_out_of_time_order(capi, p
             assert np.array_equal(capi.unpack_bits(bits, n_shots), want), f"trial {trial} mode {mode}"
             assert np.array_equal(tally[:circ.nc], want.sum(axis=0).astype(np.uint64))
         monkeypatch.delenv("QEC_B200_LIN_MODE")
+
+
+@pytest.mark.parametrize("flush", [1, 3])
+def test_register_tally_counters_flush_mid_launch(capi, monkeypatch, flush):
+    """The lane kernels keep the per-clbit counts of whole batches in registers and add them to
+    the tally row every N batches (N = 448 by default: more batches per warp than any test
+    launch has).  With N = 1 and 3 (QEC_B200_LANES_FLUSH) the mid-launch flush runs many times per
+    warp: tallies must equal those of the default and the column sums of the bits, for the
+    sampler (aligned and unaligned windows) and the enumerator (rows not 16-byte aligned)."""
+    circ = _circuit("surf5")
+    model = standard_depolarizing_model(2e-3)
+    idx, labels, lw, lp = sampler_inputs(circ, model)
+    _, _, paulis = noise_inputs(circ, model)
+    n = 148 * 9 * 1024 * 5 + 32 * 7          # several batches per warp, a ragged end
+    n_en, lo_en = 2_000_000 + 17, 1_000_003   # n_words of the window is not a multiple of 4
+
+    def run():
+        g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=11)
+        bits, tally, _, _ = sm.sample(0, n, want_tally=True)
+        assert "lane-streams" in capi.last_kernel()
+        bits_u, tally_u, _, _ = sm.sample(4096 + 32, n, want_tally=True)   # rows off the 16-byte grid
+        en = make_enumerator(capi, g, 2, idx, paulis)
+        be, te = en.range(lo_en, lo_en + n_en, want_tally=True)
+        assert "enumerate:linear" in capi.last_kernel()
+        return bits, tally, bits_u, tally_u, be, te
+
+    ref_out = run()
+    monkeypatch.setenv("QEC_B200_LANES_FLUSH", str(flush))
+    out = run()
+    for a, b in zip(ref_out, out):
+        assert np.array_equal(a, b)
+    nc = circ.nc
+    for bits, tally, count in ((out[0], out[1], n), (out[2], out[3], n), (out[4], out[5], n_en)):
+        ones = np.array([int(np.unpackbits(bits[c].view(np.uint8)).sum()) for c in range(nc)], dtype=np.uint64)
+        assert np.array_equal(tally[:nc], ones)
+        assert int(tally[nc + 1]) == count
