@@ -234,6 +234,59 @@ __device__ __forceinline__ void lin_apply(const QecLinDev &S, const LinSmem &m, 
   }
 }
 
+// The two candidates of a lane in one go, for the common configuration of the CTA variant (draw
+// scheme 2, no class thinning, equal Pauli weights, 16-byte records in device memory): both
+// records are requested before either is applied, so a step exposes one L2 latency, not two
+// (ncu on d=11: the wait for the record was the largest single stall of the draw phase).
+template <bool TALLY>
+__device__ __forceinline__ void lin_apply_pair16(const QecLinDev &S, const LinSmem &m, const LinDraw &dc,
+                                                 const int p0, const int p1, const bool has0, const bool has1,
+                                                 const uint32_t rd0, const uint32_t rd1, const int end,
+                                                 const uint32_t slo, const uint32_t shi, const long long base_shot,
+                                                 const long long w_lo, const uint32_t acc_s, const uint32_t cnt_s,
+                                                 const QecSampleExport &X) {
+  const int lgb = dc.lgb;
+  const uint32_t BATCH = 1u << lgb, bw4 = dc.bw4;
+  const int pp[2] = {p0, p1};
+  const bool hh[2] = {has0, has1};
+  const uint32_t rr[2] = {rd0, rd1};
+  uint32_t sl[2], shot[2], d[2];
+  bool ok[2];
+  uint4 q[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    sl[j] = (uint32_t)pp[j] >> lgb;
+    shot[j] = (uint32_t)pp[j] & (BATCH - 1u);
+    ok[j] = hh[j] && pp[j] < end && shot[j] >= slo && shot[j] < shi;
+    const uint32_t inf = ok[j] ? m.info[sl[j]] : 0u;
+    const uint32_t np1 = m.cnp1[(inf >> 21) & 1023u];
+    d[j] = min(__umulhi(rr[j], np1 + 1u), np1);  // == the cdf count (host: ceil thresholds)
+    q[j] = make_uint4(0u, 0u, 0u, 0u);           // (length 0: nothing to apply)
+    if (ok[j]) q[j] = __ldg(S.sigrec + ((inf & 0x1FFFFFu) + d[j]));
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const uint32_t colb = acc_s + ((shot[j] >> 5) << 2);
+    const uint32_t msk = 1u << (shot[j] & 31u);
+    const uint32_t len = q[j].x & 0xFFFFu;
+#define QEC_RED(K, E) if (len > (K)) red_xor_s(colb + (E) * bw4, msk)
+    QEC_RED(0u, q[j].x >> 16);
+    QEC_RED(1u, q[j].y & 0xFFFFu); QEC_RED(2u, q[j].y >> 16);
+    QEC_RED(3u, q[j].z & 0xFFFFu); QEC_RED(4u, q[j].z >> 16);
+    QEC_RED(5u, q[j].w & 0xFFFFu); QEC_RED(6u, q[j].w >> 16);
+#undef QEC_RED
+    if (ok[j]) {
+      if (TALLY) red_add_s(cnt_s + ((shot[j] >> 1) << 2), 1u << ((shot[j] & 1u) << 4));
+      if (X.cnt) {
+        const long long wr = ((base_shot + shot[j]) >> 5) - w_lo;
+        const uint32_t k = atomicAdd(X.cnt + wr, 1u);
+        if (k < (uint32_t)X.cap)
+          X.ev[wr * X.cap + k] = (S.slloc[sl[j]] << 14) | ((shot[j] & 31u) << 9) | d[j];
+      }
+    }
+  }
+}
+
 // One fault stream of one batch, walked by one warp: 32 Philox calls per step (lane = call),
 // each giving one candidate fault (draw schemes 0 and 1) or two (scheme 2); a warp prefix sum
 // of the gaps places them, then every lane resolves its candidates (lin_apply).
@@ -249,6 +302,8 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
   const int start = (int)((uint32_t)s * S.slen);
   const int end = (int)min((uint32_t)start + S.slen, S.n_slots);
   const int draw = S.draw;
+  // (uniform_digits implies no thinning only together with all-always classes: draw == 2)
+  const bool pair16 = draw == 2 && S.uniform_digits && !S.sig_in_smem && !S.rec8 && !S.rec2;
   int pos = start - 1;
   for (uint32_t it = 0; pos < end; ++it) {
     const QecPhilox r = qec_philox_rk(blo, bhi, it * 32u + (uint32_t)lane, 0x4C000000u | (uint32_t)s,
@@ -290,9 +345,13 @@ __device__ __forceinline__ void lin_stream(const QecLinDev &S, const LinSmem &m,
     const int p1 = pos + (int)incl, p0 = p1 - (int)len1;
     pos = __shfl_sync(0xFFFFFFFFu, p1, 31);
     // (nested ifs, no `continue`: the warp reconverges before the next step's shuffles)
-    lin_apply<TALLY>(S, m, dc, p0, has0, rd0, r.c[2], end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
-    if (draw == 2)
-      lin_apply<TALLY>(S, m, dc, p1, has1, rd1, 0u, end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    if (pair16) {
+      lin_apply_pair16<TALLY>(S, m, dc, p0, p1, has0, has1, rd0, rd1, end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    } else {
+      lin_apply<TALLY>(S, m, dc, p0, has0, rd0, r.c[2], end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+      if (draw == 2)
+        lin_apply<TALLY>(S, m, dc, p1, has1, rd1, 0u, end, slo, shi, base_shot, w_lo, acc_s, cnt_s, X);
+    }
   }
 }
 
