@@ -142,7 +142,7 @@ struct QecLinDev {
   // rowprog is then [n_steps passes][4 rows]: row | previous row of its chain << 8 | flags (qec_linear.cu)
   int lane_mode;
   uint32_t flush_every;     // lane-stream kernel: batches between flushes of the register tally counters (at most 448)
-  int lanes_np;             // Philox calls (two candidates each) per loop trip of the lane-stream kernel: 2, 3 or 4
+  int lanes_np;             // Philox calls (two candidates each) per loop trip of the lane-stream kernel: 1 or 2
   uint32_t *batch_ctr;      // lane-stream kernel: batches handed out so far in this launch (zeroed per launch)
   // CTA variant: read-out program lvl_prog[step * G + group], G = threads / words per batch row,
   // n_lvl steps; entry = row | 1 << 30 valid | 1 << 31 the row continues the chain (time-difference

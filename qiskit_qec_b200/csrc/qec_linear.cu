@@ -1488,7 +1488,7 @@ int qec_lin_set_smem_attr(size_t smem) {
   QEC_SET((k_sample_lanes<false, true, false, NP>)) QEC_SET((k_sample_lanes<false, false, false, NP>)) \
   QEC_SET((k_sample_lanes<true, true, true, NP>)) QEC_SET((k_sample_lanes<true, false, true, NP>)) \
   QEC_SET((k_sample_lanes<false, true, true, NP>)) QEC_SET((k_sample_lanes<false, false, true, NP>))
-  QEC_SETL(2) QEC_SETL(3) QEC_SETL(4)
+  QEC_SETL(1) QEC_SETL(2)
 #undef QEC_SETL
   QEC_SET((k_sample_linw<true, true, true>)) QEC_SET((k_sample_linw<true, false, true>))
   QEC_SET((k_sample_linw<false, true, true>)) QEC_SET((k_sample_linw<false, false, true>))
@@ -1515,7 +1515,8 @@ void qec_launch_sample_lin(const QecLaunchCfg &cfg, cudaStream_t stream, const Q
     else if (b) QEC_GO((k_sample_lanes<false, true, false, NP>));            \
     else QEC_GO((k_sample_lanes<false, false, false, NP>));                  \
   }
-    if (S.lanes_np == 3) { QEC_GOL(3) } else if (S.lanes_np == 4) { QEC_GOL(4) } else { QEC_GOL(2) }
+    // (three and four calls per trip measured slower: the loop body outgrows the instruction cache)
+    if (S.lanes_np == 1) { QEC_GOL(1) } else { QEC_GOL(2) }
 #undef QEC_GOL
   } else if (S.warp_mode && S.fast) {
     if (t && b) QEC_GO((k_sample_linw<true, true, true>));
