@@ -19,6 +19,17 @@
 #include "qec_kernels.cuh"
 #include "qec_jit.h"
 #include "qec_distance.h"
+#include <memory_resource>
+
+// per-fault clbit lists of the planners: thousands of short vectors, allocated from one monotonic
+// arena (a create call spent 1.6 of its 2.4 ms in malloc / free of these)
+using SigList = std::pmr::vector<uint16_t>;
+using SigLists = std::pmr::vector<SigList>;
+// (the outer vectors live in the arena too and are abandoned with it: no destructor per list)
+static SigLists &arena_lists(std::pmr::monotonic_buffer_resource &arena, size_t n) {
+  void *mem = arena.allocate(sizeof(SigLists), alignof(SigLists));
+  return *new (mem) SigLists(n, SigList(&arena), &arena);
+}
 
 // revision tag of the linear-response kernels in the variant strings: bumped with every change of
 // k_sample_lanes / k_sample_lin, so that a committed ncu capture (profiles/rNN/ncu_dominant_kernel.json,
@@ -60,6 +71,17 @@ extern "C" int qec_device_count(void) {
     return 0;
   }
   return n;
+}
+
+// QEC_B200_TRACE=1: wall-clock stamps of the creation steps on stderr (where does a create call go?)
+#include <chrono>
+static bool trace_on() { static int v = -1; if (v < 0) { const char *e = std::getenv("QEC_B200_TRACE"); v = e && *e && *e != '0'; } return v; }
+static void trace(const char *what) {
+  if (!trace_on()) return;
+  static thread_local std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+  const auto now = std::chrono::steady_clock::now();
+  fprintf(stderr, "[qec trace] %-34s +%8.1f us\n", what, std::chrono::duration<double, std::micro>(now - last).count());
+  last = now;
 }
 
 // ---- per-device state --------------------------------------------------------------------------
@@ -702,6 +724,26 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
   return 0;
 }
 
+// Per-fault clbit lists from the bit-sliced single-fault outcomes bits[nc][FW]: 32 faults (one word
+// column) at a time through small local buffers, so that every list is written in one go (the
+// clbit-major scan wrote each entry into a different list: a cache miss per entry).
+static void lists_from_bits(const std::vector<uint32_t> &bits, int nc, int64_t FW, int64_t F, SigLists &lists) {
+  std::vector<uint16_t> buf((size_t)32 * (size_t)nc);
+  uint32_t cnt[32];
+  for (int64_t fw = 0; fw < FW; ++fw) {
+    for (int b = 0; b < 32; ++b) cnt[b] = 0;
+    for (int cb = 0; cb < nc; ++cb)
+      for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u) {
+        const int b = __builtin_ctz(v);
+        buf[(size_t)b * nc + cnt[b]++] = (uint16_t)cb;
+      }
+    for (int b = 0; b < 32; ++b) {
+      const int64_t f = 32 * fw + b;
+      if (f < F && cnt[b]) lists[(size_t)f].assign(buf.begin() + (size_t)b * nc, buf.begin() + (size_t)b * nc + cnt[b]);
+    }
+  }
+}
+
 // Read-out program of the lane-owned accumulators (lanes_readout, qec_linear.cu): four rows per
 // pass, one per lane group; whole chains of the time-difference basis (c0 -> succ(c0) -> ...) are
 // dealt to the four groups, longest first onto the least loaded, so a group meets the rows of a
@@ -778,11 +820,9 @@ static int enum_plan_linear(qec_enumerator *e) {
   std::vector<uint32_t> bits((size_t)c->nc * FW);
   int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), e->pcode.data(), bits.data(), nullptr);
   if (rc) return rc;
-  std::vector<std::vector<uint16_t>> lists((size_t)F), tr((size_t)F);
-  for (int cb = 0; cb < c->nc; ++cb)
-    for (int64_t fw = 0; fw < FW; ++fw)
-      for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u)
-        lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
+  std::pmr::monotonic_buffer_resource arena(1 << 20);
+  SigLists &lists = arena_lists(arena, (size_t)F), &tr = arena_lists(arena, (size_t)F);
+  lists_from_bits(bits, c->nc, FW, F, lists);
   // time-difference basis: clbit c -> c ^ pred(c), pred = the previous final measurement of the
   // same qubit (see sampler_plan_linear)
   std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
@@ -796,14 +836,23 @@ static int enum_plan_linear(qec_enumerator *e) {
   size_t raw_total = 0, tr_total = 0;
   {
     std::vector<uint8_t> mark(c->nc, 0);
+    std::vector<uint16_t> tmp;
+    tmp.reserve(64);
     for (int64_t f = 0; f < F; ++f) {
       for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
+      tmp.clear();  // (one allocation per list: collected and sorted in a scratch vector)
       for (uint16_t cb : lists[f]) {
-        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
+        if (mark[cb]) { tmp.push_back(cb); mark[cb] = 0; }
         const int sc = succ[cb];
-        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
+        if (sc >= 0 && mark[sc]) { tmp.push_back((uint16_t)sc); mark[sc] = 0; }
       }
-      std::sort(tr[f].begin(), tr[f].end());
+      for (size_t i = 1; i < tmp.size(); ++i) {  // (a few entries: insertion sort)
+        const uint16_t x = tmp[i];
+        size_t j = i;
+        for (; j > 0 && tmp[j - 1] > x; --j) tmp[j] = tmp[j - 1];
+        tmp[j] = x;
+      }
+      tr[f].assign(tmp.begin(), tmp.end());
       raw_total += lists[f].size();
       tr_total += tr[f].size();
     }
@@ -1123,7 +1172,7 @@ struct qec_sampler {
   } lin;
 };
 
-static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<uint16_t>> &lists,
+static int sampler_plan_lanes16(qec_sampler *s, const SigLists &lists,
                                 const std::vector<int> &pred, const std::vector<int> &succ,
                                 bool use_diff, bool forced);
 
@@ -1271,13 +1320,14 @@ static int sampler_plan_linear(qec_sampler *s) {
   for (int64_t f = 0; f <= F; ++f) path_off[f] = f;
   const int64_t FW = (F + 31) / 32;
   std::vector<uint32_t> bits((size_t)c->nc * FW);
+  trace("plan_linear: fault table");
   int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), fpauli.data(), bits.data(), nullptr);
   if (rc) return rc;
-  std::vector<std::vector<uint16_t>> lists((size_t)F);
-  for (int cb = 0; cb < c->nc; ++cb)
-    for (int64_t fw = 0; fw < FW; ++fw)
-      for (uint32_t v = bits[(size_t)cb * FW + fw]; v; v &= v - 1u)
-        lists[(size_t)(32 * fw + (__builtin_ffs((int)v) - 1))].push_back((uint16_t)cb);
+  trace("plan_linear: propagate_batch");
+  std::pmr::monotonic_buffer_resource arena(1 << 20);
+  SigLists &lists = arena_lists(arena, (size_t)F);
+  lists_from_bits(bits, c->nc, FW, F, lists);
+  trace("plan_linear: lists");
   uint32_t n_sig = 0;  // (clbit-list entries before any change of basis: sizes the CTA variant's tables)
   for (int64_t f = 0; f < F; ++f) n_sig += (uint32_t)lists[f].size();
   ln.loc2sl.assign(s->L, 0);
@@ -1292,7 +1342,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   int n_steps = 0;
   bool use_diff = false;
   size_t maxlen_w = 0;  // longest list the warp variant would see
-  std::vector<std::vector<uint16_t>> tr((size_t)F);
+  SigLists &tr = arena_lists(arena, (size_t)F);
   std::vector<int> pred(c->nc, -1), succ(c->nc, -1);
   {
     std::vector<int> last(c->nq, -1);
@@ -1305,14 +1355,23 @@ static int sampler_plan_linear(qec_sampler *s) {
     }
     size_t raw_total = 0, tr_total = 0;
     std::vector<uint8_t> mark(c->nc, 0);
+    std::vector<uint16_t> tmp;
+    tmp.reserve(64);
     for (int64_t f = 0; f < F; ++f) {
       for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
+      tmp.clear();  // (one allocation per list: collected and sorted in a scratch vector)
       for (uint16_t cb : lists[f]) {
-        if (mark[cb]) { tr[f].push_back(cb); mark[cb] = 0; }
+        if (mark[cb]) { tmp.push_back(cb); mark[cb] = 0; }
         const int sc = succ[cb];
-        if (sc >= 0 && mark[sc]) { tr[f].push_back((uint16_t)sc); mark[sc] = 0; }
+        if (sc >= 0 && mark[sc]) { tmp.push_back((uint16_t)sc); mark[sc] = 0; }
       }
-      std::sort(tr[f].begin(), tr[f].end());
+      for (size_t i = 1; i < tmp.size(); ++i) {  // (a few entries: insertion sort)
+        const uint16_t x = tmp[i];
+        size_t j = i;
+        for (; j > 0 && tmp[j - 1] > x; --j) tmp[j] = tmp[j - 1];
+        tmp[j] = x;
+      }
+      tr[f].assign(tmp.begin(), tmp.end());
       raw_total += lists[f].size();
       tr_total += tr[f].size();
     }
@@ -1344,6 +1403,7 @@ static int sampler_plan_linear(qec_sampler *s) {
     for (int l = 0; l < 32; ++l)
       for (size_t k = 0; k < lanes[l].size(); ++k) ln.rowprog[k * 32 + l] = lanes[l][k];
   }
+  trace("plan_linear: time-difference basis + chains");
   // geometry: the largest batch whose accumulator fits, two CTAs per SM when they fit with
   // 4096-shot batches (one streams its accumulator out while the other draws)
   const DevInfo &di = *c->info;
@@ -1469,6 +1529,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   ns = env_int("QEC_B200_LIN_STREAMS", ns);
   if (ns < 1 || ns > 1024) return fail(QEC_ERR_INVALID, "QEC_B200_LIN_STREAMS out of range");
 
+  trace("plan_linear: geometry");
   // the CTA variant takes the shorter lists too (fewer shared-memory atomics per fault) and
   // undoes the basis level by level before its read-out
   const bool cta_diff = !warp_mode && !lane_mode && use_diff && env_int("QEC_B200_LIN_CTADIFF", 1) != 0;
@@ -1536,16 +1597,19 @@ static int sampler_plan_linear(qec_sampler *s) {
     n_steps = (int)(lanes_prog.size() / 4);
   }
   if (ln.rowprog.empty()) ln.rowprog.push_back(0u);
+  trace("plan_linear: basis, geometry, records");
   if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
   if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
       (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)) ||
       (rc = upload(ln.info2, &ln.d_info2)) || (rc = upload(ln.lvl_prog, &ln.d_lvl_prog)) ||
       (rc = upload(ln.lvl_off, &ln.d_lvl_off)))
     return rc;
+  trace("plan_linear: uploads");
   {
     const int e = qec_lin_set_smem_attr(smem);
     if (e) return fail(QEC_ERR_CUDA, "cudaFuncSetAttribute failed: %s", cudaGetErrorString((cudaError_t)e));
   }
+  trace("plan_linear: set_smem_attr");
   QecLinDev &d = ln.dev;
   d.nc = c->nc; d.L = s->L; d.lgb = lgb; d.n_streams = ns;
   d.n_slots = (uint32_t)s->L << lgb;
@@ -1597,12 +1661,13 @@ static int sampler_plan_linear(qec_sampler *s) {
     ln.l16dev.batch_ctr = d.batch_ctr;
   }
   ln.eligible = true;
+  trace("plan_linear: device block");
   return 0;
 }
 
 // Tables of the half-word lane-stream kernel (QecLanes16Dev): chains of the time-difference basis
 // paired into word-rows, deduplicated 16-byte offset records, the read-out program.
-static int sampler_plan_lanes16(qec_sampler *s, const std::vector<std::vector<uint16_t>> &lists,
+static int sampler_plan_lanes16(qec_sampler *s, const SigLists &lists,
                                 const std::vector<int> &pred, const std::vector<int> &succ,
                                 bool use_diff, bool forced) {
   qec_sampler::Lin &ln = s->lin;
@@ -1871,6 +1936,7 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
       s->T2[j] = (num == 0) ? 0u : fix32(num / den);
     }
   }
+  trace("sampler_create: host tables");
   CU(cudaSetDevice(c->device));
   int rc = 0;
   if ((rc = upload(s->T1, &s->d_T1)) || (rc = upload(s->T2, &s->d_T2)) ||
@@ -1887,19 +1953,25 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
     qec_sampler_destroy(s);
     return fail(QEC_ERR_CUDA, "cudaMalloc failed");
   }
+  trace("sampler_create: uploads + pick_cfg");
   const double mu = s->mean_events;
   s->cap = (int)(std::ceil(mu + 10.0 * std::sqrt(mu) + 32.0) + 7) / 8 * 8;
   if ((rc = s->scratch.ensure((size_t)s->cfg.grid * s->cfg.block * s->cap * 4))) {
     qec_sampler_destroy(s);
     return rc;
   }
+  trace("sampler_create: scratch");
   QecSamplerDev &d = s->dev;
   d.L = L; d.B = s->B; d.K1 = s->K1; d.T1 = s->d_T1; d.T2 = s->d_T2; d.slop = s->d_slop;
   d.slinf = s->d_slinf; d.n_classes = n_classes; d.lgP = s->lgP; d.n_seg = 1; d.seg_end = nullptr;
   d.slloc = s->d_slloc; d.slcls = s->d_slcls; d.cls_acc = s->d_cls_acc;
   d.cls_always = s->d_cls_always; d.cls_off = s->d_cls_off; d.cdf = s->d_cdf; d.codes = s->d_codes;
   d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32);
-  if ((rc = sampler_plan_jit(s)) || (rc = sampler_plan_linear(s))) {
+  rc = sampler_plan_jit(s);
+  trace("sampler_create: plan_jit");
+  if (!rc) rc = sampler_plan_linear(s);
+  trace("sampler_create: plan_linear (total)");
+  if (rc) {
     qec_sampler_destroy(s);
     return rc;
   }
