@@ -169,6 +169,12 @@ int qec_sampler_sample_dev(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
 int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
                               uint32_t *events, int64_t events_cap, int64_t *n_events,
                               uint64_t *tally);
+/* The same with three bytes per event (little endian): location << 9 | shot_bit << 4 | digit --
+ * 2.4 bytes per shot on the d=5 circuit.  events24 host uint8[3 * events_cap].  QEC_ERR_LIMIT for
+ * more than 32768 locations or more than 16 Paulis on a location. */
+int qec_sampler_sample_events24(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
+                                uint8_t *events24, int64_t events_cap, int64_t *n_events,
+                                uint64_t *tally);
 /* asynchronous sample_dev calls cannot report an event-buffer overflow (probability < 1e-20
  * per word with the default sizing); this checks for one: QEC_ERR_OVERFLOW means the last
  * batch of sample_dev results is invalid and must be re-run (the buffer has been grown). */

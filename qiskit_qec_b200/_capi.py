@@ -36,7 +36,7 @@ SYMBOLS = [
     "qec_multi_sampler_tally_dev", "qec_multi_enumerator_create", "qec_multi_enumerator_destroy",
     "qec_multi_enumerator_num_paths", "qec_multi_enumerator_range", "qec_multi_enumerator_tally_dev",
     "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev", "qec_outcome_counts_noalloc_dev",
-    "qec_minimum_distance", "qec_minimum_distance_by_tests",
+    "qec_minimum_distance", "qec_minimum_distance_by_tests", "qec_sampler_sample_events24",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
     "qec_last_kernel", "qec_jit_compile_to_file",
@@ -307,27 +307,37 @@ class Sampler:
     def check(self):
         _check(lib().qec_sampler_check(self._h))
 
-    def sample_events(self, shot_lo: int, n_shots: int, want_tally: bool = False, pinned=None):
+    def sample_events(self, shot_lo: int, n_shots: int, want_tally: bool = False, pinned=None,
+                      packed24: bool = False):
         """Compact form: (word_cnt uint16[ceil(n/32)], events uint32[n_events], tally).  ``pinned``
-        may hold preallocated (word_cnt, events) arrays (e.g. pinned host memory) to fill."""
+        may hold preallocated (word_cnt, events) arrays (e.g. pinned host memory) to fill.
+        ``packed24``: three bytes per event on the wire (events uint8[n_events, 3], see
+        ``unpack_events24``); ``pinned`` then holds (word_cnt, uint8 buffer of 3 * capacity)."""
         nw = (max(n_shots, 0) + 31) // 32
         tally = np.zeros(tally_len(self.circuit.nc), dtype=np.uint64) if want_tally else None
+        eb = 3 if packed24 else 4
         if pinned is not None:
             cnt, ev = pinned
         else:
             cnt = np.zeros(nw, dtype=np.uint16)
-            ev = np.zeros(max(1024, int(1.2 * n_shots) + 4096), dtype=np.uint32)
+            ev = np.zeros(max(1024, int(1.2 * n_shots) + 4096) * (3 if packed24 else 1),
+                          dtype=np.uint8 if packed24 else np.uint32)
+        fn = lib().qec_sampler_sample_events24 if packed24 else lib().qec_sampler_sample_events
         n_ev = C.c_int64()
         for _ in range(6):
-            rc = lib().qec_sampler_sample_events(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(cnt),
-                                                 _p(ev), C.c_int64(len(ev)), C.byref(n_ev), _p(tally))
+            cap = len(ev) // 3 if packed24 else len(ev)
+            rc = fn(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(cnt), _p(ev), C.c_int64(cap),
+                    C.byref(n_ev), _p(tally))
             if rc == QEC_ERR_OVERFLOW:
                 continue                       # deterministic RNG: re-run with the raised capacity
-            if rc == QEC_ERR_LIMIT and pinned is None and n_ev.value > len(ev):
-                ev = np.zeros(int(n_ev.value * max(1.0, nw * 32 / max(1, n_shots)) * 2) + 4096, dtype=np.uint32)
+            if rc == QEC_ERR_LIMIT and pinned is None and n_ev.value > cap:
+                grow = int(n_ev.value * max(1.0, nw * 32 / max(1, n_shots)) * 2) + 4096
+                ev = np.zeros(grow * (3 if packed24 else 1), dtype=ev.dtype)
                 continue
             break
         _check(rc)
+        if packed24:
+            return cnt[:nw], ev[:3 * n_ev.value].reshape(-1, 3), tally
         return cnt[:nw], ev[:n_ev.value], tally
 
     def variant(self) -> str:
@@ -504,6 +514,13 @@ def pack_rows(packed: np.ndarray, n: int) -> np.ndarray:
     pad = np.zeros((n, rw * 32), dtype=np.uint8)
     pad[:, :nc] = b
     return np.packbits(pad, axis=1, bitorder="little").view(np.uint32).reshape(n, rw)
+
+
+def unpack_events24(ev24: np.ndarray) -> np.ndarray:
+    """uint8[n, 3] events (location << 9 | shot bit << 4 | digit, little endian) -> the uint32 form
+    location << 14 | shot bit << 9 | digit of ``sample_events``."""
+    e = ev24[:, 0].astype(np.uint32) | (ev24[:, 1].astype(np.uint32) << 8) | (ev24[:, 2].astype(np.uint32) << 16)
+    return ((e >> 9) << 14) | (((e >> 4) & 31) << 9) | (e & 15)
 
 
 def unpack_bits(packed: np.ndarray, n: int) -> np.ndarray:

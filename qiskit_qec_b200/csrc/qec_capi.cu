@@ -2264,12 +2264,20 @@ static int sampler_sample_host(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
 // point moves only that across PCIe: per 32-shot word a 16-bit count, and one dense pool of
 // events (location << 14 | shot bit << 9 | digit; a word's events are contiguous, words in
 // order), compacted on the device from the kernels' fixed-capacity export rows, plus the tallies.
-extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
-                                         uint16_t *word_cnt, uint32_t *events, int64_t events_cap,
-                                         int64_t *n_events, uint64_t *tally) {
+// ev_bytes: 4 (event = location << 14 | shot bit << 9 | digit) or 3 (location << 9 | shot bit << 4 | digit)
+static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
+                              void *events, int64_t events_cap, int64_t *n_events, uint64_t *tally,
+                              const int ev_bytes) {
   int rc = sample_args(s, shot_lo, n_shots);
   if (rc) return rc;
   if (!word_cnt || !events || !n_events) return fail(QEC_ERR_INVALID, "null pointer");
+  if (ev_bytes == 3) {
+    uint32_t max_np = 0, max_loc = 0;
+    for (size_t k = 0; k + 1 < s->cls_off.size(); ++k) max_np = std::max(max_np, s->cls_off[k + 1] - s->cls_off[k]);
+    for (uint32_t l : s->slloc) max_loc = std::max(max_loc, l);
+    if (max_np > 16 || max_loc >= (1u << 15))
+      return fail(QEC_ERR_LIMIT, "24-bit events hold 32768 locations and 16 Paulis per location");
+  }
   qec_circuit *c = s->c;
   const size_t tl = QEC_TALLY_LEN(c->nc);
   *n_events = 0;
@@ -2287,8 +2295,11 @@ extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_
   struct Buf { DevBuf cnt, ev, sums, ocnt, oev, misc; } buf[2];
   cudaStream_t st[2];
   cudaEvent_t kdone[2], tdone[2];
-  unsigned long long *h_total = nullptr;
-  if (cudaMallocHost((void **)&h_total, 4 * 8) != cudaSuccess) return fail(QEC_ERR_CUDA, "cudaMallocHost failed");
+  // (a small pinned scratch per device, allocated once: cudaMallocHost costs 0.1-0.3 ms a call)
+  static unsigned long long *g_h_total[64] = {nullptr};
+  if (!g_h_total[c->device] && cudaMallocHost((void **)&g_h_total[c->device], 4 * 8) != cudaSuccess)
+    return fail(QEC_ERR_CUDA, "cudaMallocHost failed");
+  unsigned long long *h_total = g_h_total[c->device];
   auto cleanup = [&]() {
     cudaDeviceSynchronize();
     for (int i = 0; i < 2; ++i) {
@@ -2296,7 +2307,6 @@ extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_
       buf[i].oev.release(); buf[i].misc.release();
       cudaEventDestroy(kdone[i]); cudaEventDestroy(tdone[i]);
     }
-    cudaFreeHost(h_total);
   };
   for (int i = 0; i < 2; ++i) {
     if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
@@ -2335,7 +2345,7 @@ extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_
     qec_launch_event_compact(st[i], (const uint32_t *)buf[i].cnt.p, (const uint32_t *)buf[i].ev.p, words,
                              two_ended ? 1 : 0, cap, (uint32_t *)buf[i].sums.p, (uint32_t *)buf[i].misc.p + 2,
                              (unsigned long long *)buf[i].misc.p, (uint16_t *)buf[i].ocnt.p, (uint32_t *)buf[i].oev.p,
-                             (unsigned long long)pool);
+                             (unsigned long long)pool, ev_bytes == 3 ? 1 : 0);
     cudaEventRecord(kdone[i], st[i]);
     cudaMemcpyAsync(h_total + 2 * i, buf[i].misc.p, 16, cudaMemcpyDeviceToHost, st[i]);
     cudaEventRecord(tdone[i], st[i]);
@@ -2357,7 +2367,8 @@ extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_
       break;
     }
     if (run + total > events_cap) { *n_events = run + total; err = QEC_ERR_LIMIT; break; }
-    cudaMemcpyAsync(events + run, buf[i].oev.p, (size_t)total * 4, cudaMemcpyDeviceToHost, st[i]);
+    cudaMemcpyAsync(reinterpret_cast<uint8_t *>(events) + (size_t)run * ev_bytes, buf[i].oev.p, (size_t)total * ev_bytes,
+                    cudaMemcpyDeviceToHost, st[i]);
     cudaMemcpyAsync(word_cnt + w0, buf[i].ocnt.p, (size_t)words * 2, cudaMemcpyDeviceToHost, st[i]);
     run += total;
   }
@@ -2371,6 +2382,18 @@ extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_
   if ((rc = sampler_check(s))) return rc;
   *n_events = run;
   return 0;
+}
+
+extern "C" int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                         uint16_t *word_cnt, uint32_t *events, int64_t events_cap,
+                                         int64_t *n_events, uint64_t *tally) {
+  return sample_events_impl(s, shot_lo, n_shots, word_cnt, events, events_cap, n_events, tally, 4);
+}
+
+extern "C" int qec_sampler_sample_events24(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                           uint16_t *word_cnt, uint8_t *events24, int64_t events_cap,
+                                           int64_t *n_events, uint64_t *tally) {
+  return sample_events_impl(s, shot_lo, n_shots, word_cnt, events24, events_cap, n_events, tally, 3);
 }
 
 // ---- K4 + helpers --------------------------------------------------------------------------------

@@ -388,7 +388,8 @@ k_ev_scan_blocks(uint32_t *__restrict__ block_sums, const int n_blocks, unsigned
 __global__ void __launch_bounds__(QEC_EVC_T)
 k_ev_compact(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ ev, const long long n_words,
              const int two_ended, const int cap, const uint32_t *__restrict__ block_off,
-             uint16_t *__restrict__ out_cnt, uint32_t *__restrict__ out_ev, const unsigned long long pool_cap) {
+             uint16_t *__restrict__ out_cnt, uint32_t *__restrict__ out_ev, const unsigned long long pool_cap,
+             const int ev24) {
   __shared__ uint32_t warp_tot[QEC_EVC_T / 32];
   const long long w0 = (long long)blockIdx.x * QEC_EVC_WPB;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -418,12 +419,18 @@ k_ev_compact(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ ev, 
     out_cnt[w] = (uint16_t)tot[j];
     if ((unsigned long long)o + tot[j] > pool_cap) break;  // (the host sees total > pool and re-runs)
     const uint32_t *row = ev + w * cap;
-    if (two_ended) {
-      const uint32_t lo = min(c[j] & 0xFFFFu, tot[j]), hi = tot[j] - lo;
-      for (uint32_t k = 0; k < lo; ++k) out_ev[o + k] = row[k];
-      for (uint32_t k = 0; k < hi; ++k) out_ev[o + lo + k] = row[cap - 1 - k];
+    const uint32_t lo = two_ended ? min(c[j] & 0xFFFFu, tot[j]) : tot[j];
+    if (ev24) {
+      // three bytes per event: location << 9 | shot bit << 4 | digit (the host checked the ranges)
+      uint8_t *o8 = reinterpret_cast<uint8_t *>(out_ev) + 3ull * o;
+      for (uint32_t k = 0; k < tot[j]; ++k) {
+        const uint32_t e = k < lo ? row[k] : row[cap - 1 - (k - lo)];
+        const uint32_t e24 = ((e >> 14) << 9) | (((e >> 9) & 31u) << 4) | (e & 15u);
+        o8[3 * k] = (uint8_t)e24; o8[3 * k + 1] = (uint8_t)(e24 >> 8); o8[3 * k + 2] = (uint8_t)(e24 >> 16);
+      }
     } else {
-      for (uint32_t k = 0; k < tot[j]; ++k) out_ev[o + k] = row[k];
+      for (uint32_t k = 0; k < lo; ++k) out_ev[o + k] = row[k];
+      for (uint32_t k = lo; k < tot[j]; ++k) out_ev[o + k] = row[cap - 1 - (k - lo)];
     }
     o += tot[j];
   }
@@ -548,12 +555,12 @@ void qec_launch_hist_compact(cudaStream_t stream, const unsigned long long *keys
 void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const uint32_t *ev, long long n_words,
                               int two_ended, int cap, uint32_t *block_sums, uint32_t *overflow,
                               unsigned long long *total, uint16_t *out_cnt, uint32_t *out_ev,
-                              unsigned long long pool_cap) {
+                              unsigned long long pool_cap, int ev24) {
   const int n_blocks = (int)((n_words + QEC_EVC_WPB - 1) / QEC_EVC_WPB);
   if (n_blocks < 1) return;
   k_ev_block_sums<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, n_words, two_ended, cap, block_sums, overflow);
   k_ev_scan_blocks<<<1, 1024, 0, stream>>>(block_sums, n_blocks, total);
-  k_ev_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, ev, n_words, two_ended, cap, block_sums, out_cnt, out_ev, pool_cap);
+  k_ev_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, ev, n_words, two_ended, cap, block_sums, out_cnt, out_ev, pool_cap, ev24);
 }
 
 void qec_launch_tally_reduce_peers(cudaStream_t stream, const unsigned long long *const *ptrs, int n_dev,

@@ -359,3 +359,21 @@ def test_hhc_labelled_idles_order1_stream_vs_reference(capi, ref, kw):
             locs, digs = en.unrank(r)
             assert want[r][0] == r and want[r][1] == [labels[l] for l in locs]
             assert want[r][2] == [paulis[l][dd] for l, dd in zip(locs, digs)]
+
+
+def test_events24_equal_the_32_bit_events(capi):
+    """qec_sampler_sample_events24 (three bytes per fault on the wire) decodes to exactly the events
+    of qec_sampler_sample_events, counts and tallies included; circuits it cannot encode are refused."""
+    from qiskit_qec_b200.circuits import surface_code_circuit
+    from qiskit_qec_b200.noise import standard_depolarizing_model
+    from helpers import make_sampler, sampler_inputs
+    for d, T, n, lo in ((5, 5, 300_000 + 17, 64), (3, 2, 10_000, 0), (7, 3, 100_000 + 5, 4096)):
+        circ = surface_code_circuit(d, T)
+        idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(2e-3))
+        g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=21)
+        wc, ev, tl = sm.sample_events(lo, n, want_tally=True)
+        wc3, ev3, tl3 = sm.sample_events(lo, n, want_tally=True, packed24=True)
+        assert ev3.dtype == np.uint8 and ev3.shape == (len(ev), 3)
+        assert np.array_equal(wc, wc3) and np.array_equal(tl, tl3)
+        assert np.array_equal(capi.unpack_events24(ev3), ev)
