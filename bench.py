@@ -286,9 +286,14 @@ def run_ours(args):
         and two equally slow passes must not end the warm-up"""
         seen = []
         for _ in range(max_iter):
+            if world > 1:
+                dist.barrier()  # (all ranks pass together, as in the timed steps: they share the host's memory system)
             ts = time.perf_counter()
             fn(0)
-            seen.append(time.perf_counter() - ts)
+            el = torch.tensor([time.perf_counter() - ts], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(el, op=dist.ReduceOp.MAX)  # one decision for all ranks
+            seen.append(float(el.item()))
             last = seen[-3:]
             if len(seen) >= 3 and max(last) <= 1.05 * min(last) and max(last) <= 1.5 * min(seen):
                 break
