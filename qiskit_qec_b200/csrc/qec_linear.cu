@@ -1016,7 +1016,9 @@ __device__ __forceinline__ uint32_t lanes_readout(const QecOutDev &O, const uint
   for (int u = 0; u < QEC_LANES_UNROLL; ++u) en[u] = ld_s(R.pe_s + ((uint32_t)u << 4));
 #pragma unroll
   for (int u = 0; u < QEC_LANES_UNROLL; ++u) vn[u] = ld_s128(R.col_s + ((en[u] & 0xFFu) << 7));
-  if (whole) {
+  // (a long chain dealt to one lane group can push the program past the unrolled trips -- e.g. a
+  // repetition code with a hundred rounds: such programs take the rolled loop for every batch)
+  if (whole && n_steps <= (uint32_t)(QEC_LANES_MAXTRIPS * QEC_LANES_UNROLL)) {
     // the trips unrolled: per-clbit counts in registers (LaneCounts).  One straight-line copy per
     // store mode (the kernel is sensitive to instruction fetch: the two must not interleave).
     if (vec_ok) lanes_readout_unrolled<TALLY, BITS, 2>(R, n_steps, en, vn, pv, anyv, LC);

@@ -35,6 +35,8 @@ def _circuit(name):
         return surface_code_circuit(3, 2, basis="x")
     if name == "surf7":
         return surface_code_circuit(7, 3)
+    if name == "rep100":  # two chains of 100 rows: the lane read-out program outgrows its unrolled trips
+        return repetition_code_circuit(3, 100, resets=True)
     links, sched, color = heavy_hex_27_arc_layout()
     return arc_circuit(links, 3, "zx", sched, color)
 
@@ -230,7 +232,8 @@ def test_frame_mode_switch(capi, monkeypatch):
 
 
 @pytest.mark.parametrize("name,order", [("rep", 1), ("rep", 2), ("rep", 3), ("surf3", 1), ("surf3", 2),
-                                        ("surf3x", 2), ("arc", 2), ("arc", 3), ("surf5", 1), ("surf5", 2)])
+                                        ("surf3x", 2), ("arc", 2), ("arc", 3), ("surf5", 1), ("surf5", 2),
+                                        ("rep100", 1), ("rep100", 2)])
 def test_linear_enumerator_equals_frame_enumerator(capi, monkeypatch, name, order):
     """k_enum_lanes (outcome = XOR of the faults' signatures) against the frame-propagation
     enumerators, bit for bit: whole enumerations when small, else windows cut anywhere (unaligned
@@ -345,3 +348,10 @@ def test_register_tally_counters_flush_mid_launch(capi, monkeypatch, flush):
         ones = np.array([int(np.unpackbits(bits[c].view(np.uint8)).sum()) for c in range(nc)], dtype=np.uint64)
         assert np.array_equal(tally[:nc], ones)
         assert int(tally[nc + 1]) == count
+
+
+def test_lane_sampler_with_a_long_chain_program(capi, port):
+    """Repetition code, 100 rounds: 203 clbits in two chains of 100 rows, so one lane group's
+    read-out queue (100 passes) is longer than the unrolled trips of the fast path hold."""
+    _check_sampler_against_port_and_oracle(capi, port, "rep100", 0.004, 6_000, 2048 + 64)
+    assert "lane-streams" in capi.last_kernel()
