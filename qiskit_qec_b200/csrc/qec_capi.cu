@@ -2296,7 +2296,7 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
   cudaStream_t st[2];
   cudaEvent_t kdone[2], tdone[2];
   // (a small pinned scratch per device, allocated once: cudaMallocHost costs 0.1-0.3 ms a call)
-  static unsigned long long *g_h_total[64] = {nullptr};
+  static thread_local unsigned long long *g_h_total[64] = {nullptr};  // (per host thread: calls may run concurrently)
   if (!g_h_total[c->device] && cudaMallocHost((void **)&g_h_total[c->device], 4 * 8) != cudaSuccess)
     return fail(QEC_ERR_CUDA, "cudaMallocHost failed");
   unsigned long long *h_total = g_h_total[c->device];
