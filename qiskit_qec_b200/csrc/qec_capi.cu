@@ -34,7 +34,7 @@ static SigLists &arena_lists(std::pmr::monotonic_buffer_resource &arena, size_t 
 // revision tag of the linear-response kernels in the variant strings: bumped with every change of
 // k_sample_lanes / k_sample_lin, so that a committed ncu capture (profiles/rNN/ncu_dominant_kernel.json,
 // "variant_key") can only be attributed to the code it was taken from
-#define QEC_LIN_REV "r2e"
+#define QEC_LIN_REV "r2f"
 
 // ---- error plumbing --------------------------------------------------------------------------
 static thread_local std::string g_err;
@@ -1558,7 +1558,8 @@ static int sampler_plan_linear(qec_sampler *s) {
         q[best].push_back((uint32_t)ch[k] | (1u << 30) | (k ? (1u << 31) : 0u));
     }
     for (const auto &x : q) cta_steps = std::max(cta_steps, (int)x.size());
-    ln.lvl_prog.assign((size_t)cta_steps * G, (uint32_t)c->nc);  // pad: the zero row nc, stores off
+    cta_steps = (cta_steps + 3) & ~3;  // whole trips of four steps, then four pad steps for the prefetch
+    ln.lvl_prog.assign((size_t)(cta_steps + 4) * G, (uint32_t)c->nc);  // pad: the zero row nc, stores off
     for (int g = 0; g < G; ++g)
       for (size_t k = 0; k < q[g].size(); ++k) ln.lvl_prog[k * G + g] = q[g][k];
   }

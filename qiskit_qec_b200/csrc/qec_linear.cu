@@ -104,39 +104,51 @@ __device__ __forceinline__ uint32_t lin_digit(uint32_t cdf_s, uint32_t r) {
 // Read-out steps of one thread of the CTA variant (see k_sample_lin): program entries four steps
 // ahead in registers, branch-free (pad entries name the always-zero row nc and only switch the
 // stores off).  FULL: a warp spans 32 columns of one row (REDUX row sums).
-template <bool TALLY, bool BITS, bool FULL>
-__device__ __forceinline__ uint32_t lin_readout(const uint32_t *pp, const uint32_t G, const int n_steps,
+#define QEC_CTA_REGCNT 4  // register tally counters of the CTA read-out: programs of up to 32 * 4 steps
+template <bool TALLY, bool BITS, bool FULL, bool REGCNT>
+__device__ __forceinline__ uint32_t lin_readout(const uint32_t *prog, const uint32_t G, const int n_steps,
                                                 const uint32_t col_s, const int row_shift, uint32_t *const ocol,
                                                 const long long n_words, const bool inr, const uint32_t tal_s,
-                                                const bool head, const uint32_t grp) {
+                                                const bool head, const uint32_t grp, const int lane,
+                                                uint32_t (&rc)[QEC_CTA_REGCNT]) {
+  // (the program is padded to a multiple of four steps and followed by four pad steps: the
+  // prefetch needs no bound check; n_steps counts the padded steps)
   uint32_t anyv = 0, pv = 0;
   uint32_t en[4];
+  uint32_t off = 0;
 #pragma unroll
-  for (int u = 0; u < 4; ++u) { en[u] = u < n_steps ? __ldg(pp) : 0u; pp += G; }
-  for (int st = 0; st < n_steps; st += 4) {
-    uint32_t e[4], v[4], a[4];
+  for (int u = 0; u < 4; ++u) { en[u] = __ldg(prog + off); off += G; }
+  // REGCNT: the row sums (REDUX: every lane has them) stay in registers -- lane l keeps the count
+  // of step 32 k + l in rc[k], the same row in every batch -- and reach the tally row once, at the
+  // end of the kernel; the outer loop is unrolled so that k is static
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      e[u] = en[u];
-      a[u] = col_s + ((e[u] & 0xFFFFu) << row_shift);
-      v[u] = ld_s(a[u]);
-    }
+  for (int k = 0; k < (REGCNT ? QEC_CTA_REGCNT : 1); ++k) {
+    const int st_end = REGCNT ? min(n_steps, 32 * (k + 1)) : n_steps;
+    for (int st = REGCNT ? 32 * k : 0; st < st_end; st += 4) {
+      uint32_t e[4], v[4], a[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) { en[u] = st + 4 + u < n_steps ? __ldg(pp) : 0u; pp += G; }
+      for (int u = 0; u < 4; ++u) {
+        e[u] = en[u];
+        a[u] = col_s + ((e[u] & 0xFFFFu) << row_shift);
+        v[u] = ld_s(a[u]);
+      }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      if (st + u >= n_steps) break;  // (uniform: the program's tail)
-      st_s(a[u], 0u);
-      v[u] ^= pv & (uint32_t)((int)e[u] >> 31);
-      pv = v[u];
-      const bool valid = (e[u] & 0x40000000u) != 0u;
-      if (BITS && inr && valid) ocol[(long long)(e[u] & 0xFFFFu) * n_words] = v[u];
-      if (TALLY) {
-        anyv |= v[u];
-        int cnt = __popc(v[u]);
-        if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
-        else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
-        red_add_if(head && valid, tal_s + ((e[u] & 0xFFFFu) << 2), (uint32_t)cnt);
+      for (int u = 0; u < 4; ++u) { en[u] = __ldg(prog + off); off += G; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        st_s(a[u], 0u);
+        v[u] ^= pv & (uint32_t)((int)e[u] >> 31);
+        pv = v[u];
+        const bool valid = (e[u] & 0x40000000u) != 0u;
+        if (BITS && inr && valid) ocol[(long long)(e[u] & 0xFFFFu) * n_words] = v[u];
+        if (TALLY) {
+          anyv |= v[u];
+          int cnt = __popc(v[u]);
+          if (FULL) cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+          else for (uint32_t o = grp >> 1; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+          if (REGCNT) rc[k] += (lane == st + u - 32 * k) ? (uint32_t)cnt : 0u;  // (pad rows count nothing: they are zero)
+          else red_add_if(head && valid, tal_s + ((e[u] & 0xFFFFu) << 2), (uint32_t)cnt);
+        }
       }
     }
   }
@@ -413,6 +425,12 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
   dc.P = P;
   dc.lgb = lgb;
   const uint32_t tal_s = (uint32_t)__cvta_generic_to_shared(m.tally);
+  // register tally counters of the read-out (lin_readout): a warp spans 32 columns of one row and the
+  // program fits 32 * QEC_CTA_REGCNT steps
+  const bool regcnt = TALLY && BW >= 32u && S.n_lvl <= 32 * QEC_CTA_REGCNT;
+  uint32_t rc[QEC_CTA_REGCNT];
+#pragma unroll
+  for (int k = 0; k < QEC_CTA_REGCNT; ++k) rc[k] = 0u;
   unsigned long long nz_shots = 0;
   const long long b0 = shot_lo >> lgb, b1 = (shot_lo + n_shots - 1) >> lgb;
   const long long w_lo = shot_lo >> 5;
@@ -446,8 +464,9 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
       const uint32_t col_s = acc_s + (wb << 2);
       uint32_t *const ocol = O.bits + (inr ? w : 0);
       uint32_t anyv = 0;
-      if (grp == 32u) anyv = lin_readout<TALLY, BITS, true>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp);
-      else anyv = lin_readout<TALLY, BITS, false>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp);
+      if (regcnt) anyv = lin_readout<TALLY, BITS, true, true>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp, lane, rc);
+      else if (grp == 32u) anyv = lin_readout<TALLY, BITS, true, false>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp, lane, rc);
+      else anyv = lin_readout<TALLY, BITS, false, false>(pp, G, S.n_lvl, col_s, lgw + 2, ocol, O.n_words, inr, tal_s, head, grp, lane, rc);
       if (TALLY) {
         if (anyv) atomicOr(m.anyw + wb, anyv);
         // faults-per-shot histogram from the 16-bit counters (two shots per word)
@@ -482,6 +501,18 @@ k_sample_lin(const QecOutDev O, const QecLinDev S, const long long shot_lo, cons
 
   // ---- tallies: per-warp rows -> global (layout: QEC_TALLY_LEN in qec_b200.h)
   if (TALLY) {
+    if (regcnt) {
+      // lane l of a warp kept the count of step 32 k + l of the warp's row group
+      const uint32_t G = (uint32_t)T >> lgw;
+#pragma unroll
+      for (int k = 0; k < QEC_CTA_REGCNT; ++k) {
+        const int st = 32 * k + lane;
+        if (st < S.n_lvl) {
+          const uint32_t e = __ldg(S.lvl_prog + (size_t)st * G + ((uint32_t)tid >> lgw));
+          if ((e & 0x40000000u) && rc[k]) red_add_s(tal_s + ((e & 0xFFFFu) << 2), rc[k]);
+        }
+      }
+    }
     __syncthreads();
     for (int off = 16; off > 0; off >>= 1) nz_shots += __shfl_down_sync(0xFFFFFFFFu, nz_shots, off);
     if (lane == 0 && nz_shots) atomicAdd(&O.tally[S.nc], nz_shots);
