@@ -421,6 +421,44 @@ def run_ours(args):
                 "hbm_frac": (total * nc / 8.0 / (ems * 1e-3) / 1e9 / peaks_hbm()) if world == 1 else None}
         en.close()
         del ebits
+        # the same circuit at order 3 (4.8e10 paths; the first 4e9, tallies only): the strong-scaling
+        # point that is not launch-bound (order 2 is 0.03 ms of kernel per rank at 8 GPUs)
+        en3 = _capi.Enumerator(g, 3, idx, [[_capi.pauli_code(p) for p in pl] for pl in paulis])
+        total3 = min(en3.num_paths(), 4_000_000_000)
+        lo3, hi3 = shard_range(total3, rank, world)
+        t3 = [torch.zeros(_capi.tally_len(nc), dtype=torch.int64, device=dev) for _ in range(4)]
+
+        def estep3(i):
+            en3.range_dev(lo3, hi3, 0, t3[i].data_ptr(), stream)
+            if side is not None:
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    allreduce_tally(t3[i])
+
+        estep3(0)
+        if side is not None:
+            main.wait_stream(side)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(3):
+            estep3(1 + i)
+        if side is not None:
+            main.wait_stream(side)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ems3 = float(t.item()) / 3
+        assert int(t3[-1][nc + 1].item()) == total3
+        enum["order3"] = {"metric": "FaultEnumerator order-3 faults/s (tallies only)", "value": total3 / (ems3 * 1e-3),
+                          "unit": "faults/s", "paths": total3, "ms": ems3, "scaling": "strong",
+                          "workload": "order=3, first 4e9 of 4.76e10 paths, SurfaceCodeCircuit d=5 T=5",
+                          "kernel": _capi.last_kernel()}
+        en3.close()
 
     # the gate-stream (frame-propagation) kernels the north star names: the same workloads under
     # QEC_B200_SAMPLER=frame / QEC_B200_ENUM=frame.  These EXECUTE the W_bit/32 lane-ops per shot,
