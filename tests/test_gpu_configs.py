@@ -377,3 +377,18 @@ def test_events24_equal_the_32_bit_events(capi):
         assert ev3.dtype == np.uint8 and ev3.shape == (len(ev), 3)
         assert np.array_equal(wc, wc3) and np.array_equal(tl, tl3)
         assert np.array_equal(capi.unpack_events24(ev3), ev)
+
+
+def test_events24_refuses_what_it_cannot_encode(capi):
+    """More than 16 Paulis on a location do not fit the 4-bit digit of the 24-bit event."""
+    circ = EncodedCircuit(nq=2, nc=2, name="wide")
+    circ.cx(0, 1)
+    circ.measure(0, 0)
+    circ.measure(1, 1)
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    two = ["ix", "iy", "iz", "xi", "xx", "xy", "xz", "yi", "yx", "yy", "yz", "zi", "zx", "zy", "zz", "xx", "zz"]
+    sm = capi.Sampler(g, [0], [0], [0.2], [[capi.pauli_code(p) for p in two]], [[1.0] * len(two)], 3)
+    wc, ev, _ = sm.sample_events(0, 4096)
+    assert int(wc.sum()) == len(ev) > 0
+    with pytest.raises(RuntimeError, match="24-bit events"):
+        sm.sample_events(0, 4096, packed24=True)

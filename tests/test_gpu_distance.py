@@ -157,3 +157,26 @@ def test_larger_code_through_the_c_abi(capi):
     rc = lib.qec_minimum_distance(C.c_int(0), C.c_int(n), C.c_int(len(stabs)), p, C.c_int(len(stabs)), p,
                                   C.c_int(4), C.byref(dist))
     assert rc == 0 and dist.value == 0
+
+
+def test_distance_limits_and_argument_errors(ours, capi):
+    """What the C ABI refuses: empty input, ragged rows (binding), weights above 16, more stabilizer
+    generators than the 64-bit syndromes of distance_test hold."""
+    lib = capi.lib()
+    d = C.c_int(0)
+    z = np.zeros((1, 4), dtype=np.uint8)
+    p = z.ctypes.data_as(C.c_void_p)
+    assert lib.qec_minimum_distance(C.c_int(0), C.c_int(0), C.c_int(1), p, C.c_int(1), p, C.c_int(3), C.byref(d)) == -2
+    with pytest.raises(ValueError):
+        ours._c_minimum_distance([[1, 0, 0, 0], [0, 1, 0]], [[1, 0, 0, 0]])
+    with pytest.raises(ValueError):
+        ours._c_minimum_distance([], [])
+    # 70 commuting generators (Z on one qubit each, 70 qubits): distance_test needs m < 63
+    n = 70
+    stab = np.zeros((n, 2 * n), dtype=int)
+    for i in range(n):
+        stab[i, n + i] = 1
+    with pytest.raises(RuntimeError, match="n-k must be < 63"):
+        ours._c_minimum_distance_by_tests(stab.tolist(), [[1] * n + [0] * n], [], 2)
+    # minimum_distance on the same stabilizer state (k = 0): the lightest element of V has weight 1
+    assert ours._c_minimum_distance(stab.tolist(), stab.tolist(), 2) == 1
