@@ -314,3 +314,32 @@ def test_drivers_fed_by_a_quantum_circuit_shaped_object(ext, monkeypatch):
     for j, pj in enumerate([0.8 * 0.81, 0.2 * 0.81 + 0.8 * 0.18, 0.8 * 0.01 + 0.2 * 0.18, 0.2 * 0.01]):
         assert abs(k[j] - pj) < 5 * np.sqrt(pj * (1 - pj) / n), j
     assert fs.sample_one()[3][2] == " "
+
+
+def test_sample_tuples_equal_the_c_abi_export(ext, capi):
+    """`_CFaultSampler.sample(N)` (the literal drop-in call) returns, shot by shot, exactly what the
+    C ABI exports for the same seed: labels and errors of the shot's faults in location order, and
+    the outcome list of the packed bits -- across 16-word gather blocks, a ragged last word and a
+    second call that continues the shot stream."""
+    from qiskit_qec_b200.circuits import surface_code_circuit
+    from qiskit_qec_b200.noise import standard_depolarizing_model
+    from helpers import make_sampler, sampler_inputs
+    circ = surface_code_circuit(3, 3)
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.02))
+    fs = ext._CFaultSampler(circ.nq, circ.nc, circ.ops, idx, labels, lw, lp, 17)
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, names = make_sampler(capi, g, idx, labels, lw, lp, seed=17)
+    lo = 0
+    for n in (32 * 37 + 11, 5):
+        block = fs.sample(n)
+        bits, _, cnt, ev = sm.sample(lo, n, fault_cap=64)
+        want_bits = capi.unpack_bits(bits, n)
+        assert len(block) == n
+        for i, (minus, labs, errs, outcome) in enumerate(block):
+            w, b = divmod(i, 32)
+            mine = [int(e) for e in ev[w, :cnt[w]] if ((int(e) >> 9) & 31) == b]
+            assert minus == -1
+            assert labs == [labels[e >> 14] for e in mine]
+            assert errs == [lw[labels[e >> 14]][e & 511][0] for e in mine]
+            assert outcome == want_bits[i].tolist()
+        lo = fs.get_cursor()
