@@ -1531,7 +1531,7 @@ static int sampler_plan_linear(qec_sampler *s) {
 
   trace("plan_linear: geometry");
   // the CTA variant takes the shorter lists too (fewer shared-memory atomics per fault) and
-  // undoes the basis level by level before its read-out
+  // undoes the basis in its read-out (running XOR along each chain, lin_readout)
   const bool cta_diff = !warp_mode && !lane_mode && use_diff && env_int("QEC_B200_LIN_CTADIFF", 1) != 0;
   if ((warp_mode || lane_mode || cta_diff) && use_diff) lists.swap(tr);
   // read-out program of the CTA variant (k_sample_lin): whole chains dealt to the T / BW row

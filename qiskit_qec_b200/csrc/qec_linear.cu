@@ -16,8 +16,9 @@
 //                   variants below at ~2 cycles per lane)
 //   k_sample_linw   warp variant: one warp per 256-shot batch, one stream, warp prefix sum of
 //                   the gaps, red.shared.xor into the warp's accumulator
-//   k_sample_lin    CTA variant for circuits with many clbits (d=11): one CTA per batch of 2^lgb
-//                   shots, streams dealt to its warps, CTA barrier, column-wise read-out
+//   k_sample_lin    CTA variant for circuits with many clbits (d=7, d=11): one CTA of 1024 threads per
+//                   batch of 2^lgb shots, one stream per warp, CTA barrier, chain-walk read-out
+//                   (lin_readout: running XOR in a register, row sums in registers)
 //   k_enum_lanes    the same idea for FaultEnumerator: outcome(path) = XOR of the signatures of
 //                   its faults; lane l owns the 32 paths of output word l
 // Draw schemes (QecLinDev::draw): computed 32-bit geometric gaps (qec_gap_len), two candidates
