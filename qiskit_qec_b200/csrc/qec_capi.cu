@@ -2332,10 +2332,14 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
   }
   cudaStreamSynchronize(0);
   uint64_t *d_tally = tally ? (uint64_t *)c->tally.p : nullptr;
-  const int64_t n_chunks = (n_words + cw - 1) / cw;
+  // (a short first chunk: nothing crosses PCIe before the first kernel + compaction are done)
+  const int64_t c0 = std::min(n_words, std::max<int64_t>(cw / 4 / 1024 * 1024, 1024));
+  const int64_t n_chunks = 1 + (n_words - c0 + cw - 1) / cw;
+  auto chunk_start = [&](int64_t k) { return k == 0 ? (int64_t)0 : c0 + (k - 1) * cw; };
+  auto chunk_words = [&](int64_t k) { return k == 0 ? c0 : std::min(cw, n_words - chunk_start(k)); };
   auto launch = [&](int64_t k) -> int {
     const int i = (int)(k & 1);
-    const int64_t w0 = k * cw, words = std::min(cw, n_words - w0);
+    const int64_t w0 = chunk_start(k), words = chunk_words(k);
     const int64_t shots = std::min<int64_t>(n_shots - 32 * w0, 32 * words);
     if (k > 0) cudaStreamWaitEvent(st[i], kdone[i ^ 1], 0);  // kernels of successive chunks share scratch
     cudaMemsetAsync(buf[i].cnt.p, 0, (size_t)words * 4, st[i]);
@@ -2361,7 +2365,7 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
     if (cudaEventSynchronize(tdone[i]) != cudaSuccess) { err = QEC_ERR_CUDA; break; }
     const int64_t total = (int64_t)h_total[2 * i];
     const uint32_t worst = (uint32_t)(h_total[2 * i + 1] & 0xFFFFFFFFu);
-    const int64_t w0 = k * cw, words = std::min(cw, n_words - w0);
+    const int64_t w0 = chunk_start(k), words = chunk_words(k);
     if (worst > (uint32_t)cap || (size_t)total > pool) {  // (astronomically rare with the sizing above)
       s->ev_cap_hint = std::max<int>(2 * cap, (int)worst + 8);
       err = QEC_ERR_OVERFLOW;
