@@ -392,3 +392,23 @@ def test_events24_refuses_what_it_cannot_encode(capi):
     assert int(wc.sum()) == len(ev) > 0
     with pytest.raises(RuntimeError, match="24-bit events"):
         sm.sample_events(0, 4096, packed24=True)
+
+
+def test_events_do_not_depend_on_the_chunking(capi):
+    """qec_sampler_sample_events streams its output in chunks (a short first one, then equal ones);
+    a call that spans several chunks returns exactly the concatenation of smaller calls."""
+    from qiskit_qec_b200.circuits import surface_code_circuit
+    from qiskit_qec_b200.noise import standard_depolarizing_model
+    from helpers import make_sampler, sampler_inputs
+    circ = surface_code_circuit(3, 2)
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.01))
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=4)
+    n, cut = 6_000_000 + 32 * 5 + 9, 2_000_000 + 1024 * 3 + 64
+    for packed in (False, True):
+        wc, ev, tl = sm.sample_events(0, n, want_tally=True, packed24=packed)
+        wa, ea, ta = sm.sample_events(0, cut, want_tally=True, packed24=packed)
+        wb, eb, tb = sm.sample_events(cut, n - cut, want_tally=True, packed24=packed)
+        assert np.array_equal(wc, np.concatenate([wa, wb]))
+        assert np.array_equal(ev, np.concatenate([ea, eb]))
+        assert np.array_equal(tl, ta + tb)
