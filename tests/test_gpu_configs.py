@@ -298,6 +298,12 @@ def test_compact_events_equal_the_fault_export(capi, monkeypatch, d, T, p, n_sho
     wc, events, tally_c = sm.sample_events(lo, n_small, want_tally=True)
     assert np.array_equal(tally_c, tally)
     assert np.array_equal(wc.astype(np.uint32), cnt)
+    wc3, ev3, _ = sm.sample_events(lo, n_small, packed24=True)   # the 24-bit form, whichever kernel exports
+    e3 = capi.unpack_events24(ev3)
+    assert np.array_equal(wc3, wc) and len(e3) == len(events)
+    word_of = np.repeat(np.arange(len(wc)), wc.astype(np.int64))  # (the CTA variant appends with atomics:
+    key = lambda e: np.lexsort((e, word_of))                      #  a word's events come in any order)
+    assert np.array_equal(e3[key(e3)], events[key(events)])
     off = np.concatenate([[0], np.cumsum(wc.astype(np.int64))])
     assert off[-1] == len(events)
     first = np.cumsum([0] + [len(pl) for pl in paulis])
@@ -376,7 +382,10 @@ def test_events24_equal_the_32_bit_events(capi):
         wc3, ev3, tl3 = sm.sample_events(lo, n, want_tally=True, packed24=True)
         assert ev3.dtype == np.uint8 and ev3.shape == (len(ev), 3)
         assert np.array_equal(wc, wc3) and np.array_equal(tl, tl3)
-        assert np.array_equal(capi.unpack_events24(ev3), ev)
+        # (inside a word the order is the kernel's; the CTA variant appends with atomics)
+        word_of = np.repeat(np.arange(len(wc)), wc.astype(np.int64))
+        e3 = capi.unpack_events24(ev3)
+        assert np.array_equal(e3[np.lexsort((e3, word_of))], ev[np.lexsort((ev, word_of))])
 
 
 def test_events24_refuses_what_it_cannot_encode(capi):
