@@ -336,18 +336,20 @@ def run_ours(args):
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     # (1) compact call -- the headline: the sampled faults of every shot + tallies.  Lossless:
     # labels and errors ARE the list, the outcome is the XOR of the faults' signatures; about
-    # 2.4 B/shot cross PCIe instead of 18.1
-    # (three bytes per fault on the wire: location << 9 | shot bit << 4 | Pauli digit)
-    ev_pin = torch.empty(3 * (int(n_shots * max(1.2 * len(idx) * P_NOISE, 0.05)) + 65536),
-                         dtype=torch.uint8, pin_memory=True)
+    # 1.6 B/shot cross PCIe instead of 18.1
+    # (two bytes per fault on the wire where the lane-stream kernel serves the sampler: delta-coded
+    # entries in slot order, qec_sampler_sample_events16; else three: qec_sampler_sample_events24)
+    ev16 = "lane-streams" in sampler_kernel
+    ev_cap = int(n_shots * max(1.2 * len(idx) * P_NOISE, 0.05)) * (5 if ev16 else 4) // 4 + 65536
+    ev_pin = torch.empty(ev_cap * (2 if ev16 else 3), dtype=torch.uint8, pin_memory=True)
     wc_pin = torch.empty(n_words, dtype=torch.int16, pin_memory=True)
-    pinned = (wc_pin.numpy().view(np.uint16), ev_pin.numpy())
+    pinned = (wc_pin.numpy().view(np.uint16), ev_pin.numpy().view(np.uint16) if ev16 else ev_pin.numpy())
     ev_bytes = [0]
 
     def e2e_compact(i):
         g2, s2 = new_sampler()
         wc, ev, tl = s2.sample_events(((rank * 1_000_003 + 500_000 + i) * n_words) * 32, n_shots,
-                                      want_tally=True, pinned=pinned, packed24=True)
+                                      want_tally=True, pinned=pinned, packed24=not ev16, packed16=ev16)
         ev_bytes[0] = int(ev.nbytes + wc.nbytes + tl.nbytes)
         assert int(tl[nc + 1]) == n_shots
         s2.close()
@@ -591,9 +593,12 @@ def run_ours(args):
                     "d2h_bytes_per_step": ev_bytes[0], "steps": e2e_steps,
                     "ms_per_step": [round(x * 1e3, 2) for x in e2e_times],
                     "warmup_ms": [round(x * 1e3, 1) for x in e2e_warm],
-                    "call": "qec_circuit_create + qec_sampler_create + qec_sampler_sample_events24 "
-                            "(pinned host buffers: per-word counts + the sampled faults of every shot, "
-                            "three bytes each, + tallies) + destroy; lossless compact form of the shots",
+                    "call": "qec_circuit_create + qec_sampler_create + " +
+                            ("qec_sampler_sample_events16 (pinned host buffers: per-word counts + the sampled "
+                             "faults of every shot, delta-coded in two bytes each" if ev16 else
+                             "qec_sampler_sample_events24 (pinned host buffers: per-word counts + the sampled "
+                             "faults of every shot, three bytes each") +
+                            ", + tallies) + destroy; lossless compact form of the shots",
                     "kernel": compact_kernel},
             "e2e_dense": {"value": dense_value, "unit": "shots/s", "h2d_bytes_per_step": tab_bytes,
                           "d2h_bytes_per_step": dense_bytes,

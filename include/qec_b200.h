@@ -175,6 +175,15 @@ int qec_sampler_sample_events(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
 int qec_sampler_sample_events24(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
                                 uint8_t *events24, int64_t events_cap, int64_t *n_events,
                                 uint64_t *tally);
+/* The same, delta-coded in two bytes per entry: 1.6 bytes per shot on the d=5 circuit.  A word's
+ * events come in SLOT order (slot = sorted location * 32 + shot_bit; qec_sampler_tables carries the
+ * sorted -> original location map); entry = delta << 4 | digit with delta = slot - previous slot
+ * - 1 (previous = -1 at the start of each word), and 0xFFF0 = "4095 slots without an event".
+ * word_cnt counts ENTRIES (events + skips).  Served by the lane-stream kernel only (its lanes
+ * export in slot order): QEC_ERR_LIMIT otherwise, and for more than 16 Paulis on a location. */
+int qec_sampler_sample_events16(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
+                                uint16_t *entries16, int64_t entries_cap, int64_t *n_entries,
+                                uint64_t *tally);
 /* asynchronous sample_dev calls cannot report an event-buffer overflow (probability < 1e-20
  * per word with the default sizing); this checks for one: QEC_ERR_OVERFLOW means the last
  * batch of sample_dev results is invalid and must be re-run (the buffer has been grown). */

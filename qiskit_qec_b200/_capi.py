@@ -36,7 +36,7 @@ SYMBOLS = [
     "qec_multi_sampler_tally_dev", "qec_multi_enumerator_create", "qec_multi_enumerator_destroy",
     "qec_multi_enumerator_num_paths", "qec_multi_enumerator_range", "qec_multi_enumerator_tally_dev",
     "qec_outcome_histogram_dev", "qec_outcome_histogram_rows_dev", "qec_outcome_counts_noalloc_dev",
-    "qec_minimum_distance", "qec_minimum_distance_by_tests", "qec_sampler_sample_events24",
+    "qec_minimum_distance", "qec_minimum_distance_by_tests", "qec_sampler_sample_events24", "qec_sampler_sample_events16",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
     "qec_last_kernel", "qec_jit_compile_to_file",
@@ -308,31 +308,34 @@ class Sampler:
         _check(lib().qec_sampler_check(self._h))
 
     def sample_events(self, shot_lo: int, n_shots: int, want_tally: bool = False, pinned=None,
-                      packed24: bool = False):
+                      packed24: bool = False, packed16: bool = False):
         """Compact form: (word_cnt uint16[ceil(n/32)], events uint32[n_events], tally).  ``pinned``
         may hold preallocated (word_cnt, events) arrays (e.g. pinned host memory) to fill.
         ``packed24``: three bytes per event on the wire (events uint8[n_events, 3], see
-        ``unpack_events24``); ``pinned`` then holds (word_cnt, uint8 buffer of 3 * capacity)."""
+        ``unpack_events24``); ``pinned`` then holds (word_cnt, uint8 buffer of 3 * capacity).
+        ``packed16``: delta-coded 16-bit entries in slot order (``unpack_events16``; word_cnt then
+        counts entries); ``pinned`` holds (word_cnt, uint16 buffer)."""
         nw = (max(n_shots, 0) + 31) // 32
         tally = np.zeros(tally_len(self.circuit.nc), dtype=np.uint64) if want_tally else None
-        eb = 3 if packed24 else 4
+        per = 3 if packed24 else 1                      # array elements per event / entry
+        dt = np.uint8 if packed24 else np.uint16 if packed16 else np.uint32
         if pinned is not None:
             cnt, ev = pinned
         else:
             cnt = np.zeros(nw, dtype=np.uint16)
-            ev = np.zeros(max(1024, int(1.2 * n_shots) + 4096) * (3 if packed24 else 1),
-                          dtype=np.uint8 if packed24 else np.uint32)
-        fn = lib().qec_sampler_sample_events24 if packed24 else lib().qec_sampler_sample_events
+            ev = np.zeros(max(1024, int(1.2 * n_shots) + 4096) * per, dtype=dt)
+        fn = (lib().qec_sampler_sample_events24 if packed24 else lib().qec_sampler_sample_events16 if packed16
+              else lib().qec_sampler_sample_events)
         n_ev = C.c_int64()
         for _ in range(6):
-            cap = len(ev) // 3 if packed24 else len(ev)
+            cap = len(ev) // per
             rc = fn(self._h, C.c_int64(shot_lo), C.c_int64(n_shots), _p(cnt), _p(ev), C.c_int64(cap),
                     C.byref(n_ev), _p(tally))
             if rc == QEC_ERR_OVERFLOW:
                 continue                       # deterministic RNG: re-run with the raised capacity
             if rc == QEC_ERR_LIMIT and pinned is None and n_ev.value > cap:
                 grow = int(n_ev.value * max(1.0, nw * 32 / max(1, n_shots)) * 2) + 4096
-                ev = np.zeros(grow * (3 if packed24 else 1), dtype=ev.dtype)
+                ev = np.zeros(grow * per, dtype=dt)
                 continue
             break
         _check(rc)
@@ -521,6 +524,28 @@ def unpack_events24(ev24: np.ndarray) -> np.ndarray:
     location << 14 | shot bit << 9 | digit of ``sample_events``."""
     e = ev24[:, 0].astype(np.uint32) | (ev24[:, 1].astype(np.uint32) << 8) | (ev24[:, 2].astype(np.uint32) << 16)
     return ((e >> 9) << 14) | (((e >> 4) & 31) << 9) | (e & 15)
+
+
+def unpack_events16(word_cnt: np.ndarray, entries: np.ndarray, tables: np.ndarray):
+    """Delta-coded entries of ``sample_events(packed16=True)`` -> (event counts per word uint16,
+    events uint32 in the form location << 14 | shot bit << 9 | digit, in slot order per word).
+    ``tables`` = ``Sampler.tables()`` (carries the sorted -> original location map)."""
+    B, K1, L = int(tables[0]), int(tables[1]), int(tables[3])
+    slloc = tables[8 + K1 + B + L: 8 + K1 + B + 2 * L].astype(np.uint32)
+    wc = word_cnt.astype(np.int64)
+    e = entries.astype(np.int64)
+    esc = (e >> 4) == 4095
+    step = np.where(esc, 4095, (e >> 4) + 1)
+    word_of = np.repeat(np.arange(len(wc)), wc)
+    run = np.cumsum(step)
+    first = np.concatenate([[0], np.cumsum(wc)])[:-1]           # index of each word's first entry
+    base = np.where(wc > 0, run[np.minimum(first, len(run) - 1)] - step[np.minimum(first, len(run) - 1)], 0) if len(run) else first
+    slot = run - base[word_of] - 1                               # slot of the entry inside its word
+    keep = ~esc
+    sl, bit = (slot[keep] >> 5), (slot[keep] & 31)
+    events = (slloc[sl].astype(np.uint32) << 14) | (bit.astype(np.uint32) << 9) | (e[keep] & 15).astype(np.uint32)
+    counts = np.bincount(word_of[keep], minlength=len(wc)).astype(np.uint16)
+    return counts, events
 
 
 def unpack_bits(packed: np.ndarray, n: int) -> np.ndarray:

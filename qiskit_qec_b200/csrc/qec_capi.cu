@@ -2265,7 +2265,8 @@ static int sampler_sample_host(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
 // point moves only that across PCIe: per 32-shot word a 16-bit count, and one dense pool of
 // events (location << 14 | shot bit << 9 | digit; a word's events are contiguous, words in
 // order), compacted on the device from the kernels' fixed-capacity export rows, plus the tallies.
-// ev_bytes: 4 (event = location << 14 | shot bit << 9 | digit) or 3 (location << 9 | shot bit << 4 | digit)
+// ev_bytes: 4 (event = location << 14 | shot bit << 9 | digit), 3 (location << 9 | shot bit << 4 | digit) or
+// 2 (delta-coded entries in slot order, written by the lane-stream kernel itself: QecSampleExport::fmt16)
 static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, uint16_t *word_cnt,
                               void *events, int64_t events_cap, int64_t *n_events, uint64_t *tally,
                               const int ev_bytes) {
@@ -2280,6 +2281,12 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
       return fail(QEC_ERR_LIMIT, "24-bit events hold 32768 locations and 16 Paulis per location");
   }
   qec_circuit *c = s->c;
+  if (ev_bytes == 2) {
+    uint32_t max_np = 0;
+    for (size_t k = 0; k + 1 < s->cls_off.size(); ++k) max_np = std::max(max_np, s->cls_off[k + 1] - s->cls_off[k]);
+    if (!(s->lin.eligible && s->lin.dev.lane_mode && !s->lin.l16) || max_np > 16)
+      return fail(QEC_ERR_LIMIT, "16-bit events need the lane-stream kernel (events in slot order) and at most 16 Paulis per location");
+  }
   const size_t tl = QEC_TALLY_LEN(c->nc);
   *n_events = 0;
   if (tally) memset(tally, 0, tl * 8);
@@ -2317,8 +2324,10 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
   }
   // event pool of a chunk: mean + 6 sigma of its total (checked below)
   const double chunk_mu = mu * (double)cw;
-  const size_t pool = (size_t)(chunk_mu + 6.0 * std::sqrt(chunk_mu) + 4096.0);
+  size_t pool = (size_t)(chunk_mu + 6.0 * std::sqrt(chunk_mu) + 4096.0);
+  if (ev_bytes == 2) pool = pool + pool / 4 + (size_t)cw * (size_t)(((int64_t)s->L * 32) / 4095 + 1);  // (+ escape entries)
   for (int i = 0; i < 2; ++i) {
+
     if ((rc = buf[i].cnt.ensure((size_t)cw * 4)) || (rc = buf[i].ev.ensure((size_t)cw * cap * 4)) ||
         (rc = buf[i].sums.ensure((size_t)(cw / 1024 + 1) * 4)) || (rc = buf[i].ocnt.ensure((size_t)cw * 2)) ||
         (rc = buf[i].oev.ensure(pool * 4)) || (rc = buf[i].misc.ensure(16))) {
@@ -2344,9 +2353,15 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
     if (k > 0) cudaStreamWaitEvent(st[i], kdone[i ^ 1], 0);  // kernels of successive chunks share scratch
     cudaMemsetAsync(buf[i].cnt.p, 0, (size_t)words * 4, st[i]);
     cudaMemsetAsync(buf[i].misc.p, 0, 16, st[i]);
-    QecSampleExport X{(uint32_t *)buf[i].cnt.p, (uint32_t *)buf[i].ev.p, cap};
+    QecSampleExport X{(uint32_t *)buf[i].cnt.p, (uint32_t *)buf[i].ev.p, cap, ev_bytes == 2 ? 1 : 0};
     const int r = sample_launch(s, shot_lo + 32 * w0, shots, nullptr, d_tally, X, st[i]);
     if (r) return r;
+    if (ev_bytes == 2)
+      qec_launch_event_compact16(st[i], (const uint32_t *)buf[i].cnt.p, (const uint16_t *)buf[i].ev.p, words, cap,
+                                 (uint32_t *)buf[i].sums.p, (uint32_t *)buf[i].misc.p + 2,
+                                 (unsigned long long *)buf[i].misc.p, (uint16_t *)buf[i].ocnt.p,
+                                 (uint16_t *)buf[i].oev.p, (unsigned long long)pool);
+    else
     qec_launch_event_compact(st[i], (const uint32_t *)buf[i].cnt.p, (const uint32_t *)buf[i].ev.p, words,
                              two_ended ? 1 : 0, cap, (uint32_t *)buf[i].sums.p, (uint32_t *)buf[i].misc.p + 2,
                              (unsigned long long *)buf[i].misc.p, (uint16_t *)buf[i].ocnt.p, (uint32_t *)buf[i].oev.p,
@@ -2366,7 +2381,7 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
     const int64_t total = (int64_t)h_total[2 * i];
     const uint32_t worst = (uint32_t)(h_total[2 * i + 1] & 0xFFFFFFFFu);
     const int64_t w0 = chunk_start(k), words = chunk_words(k);
-    if (worst > (uint32_t)cap || (size_t)total > pool) {  // (astronomically rare with the sizing above)
+    if (worst > (uint32_t)(ev_bytes == 2 ? 2 * cap : cap) || (size_t)total > pool) {  // (astronomically rare with the sizing above)
       s->ev_cap_hint = std::max<int>(2 * cap, (int)worst + 8);
       err = QEC_ERR_OVERFLOW;
       break;
@@ -2399,6 +2414,12 @@ extern "C" int qec_sampler_sample_events24(qec_sampler *s, int64_t shot_lo, int6
                                            uint16_t *word_cnt, uint8_t *events24, int64_t events_cap,
                                            int64_t *n_events, uint64_t *tally) {
   return sample_events_impl(s, shot_lo, n_shots, word_cnt, events24, events_cap, n_events, tally, 3);
+}
+
+extern "C" int qec_sampler_sample_events16(qec_sampler *s, int64_t shot_lo, int64_t n_shots,
+                                           uint16_t *word_cnt, uint16_t *entries16, int64_t entries_cap,
+                                           int64_t *n_entries, uint64_t *tally) {
+  return sample_events_impl(s, shot_lo, n_shots, word_cnt, entries16, entries_cap, n_entries, tally, 2);
 }
 
 // ---- K4 + helpers --------------------------------------------------------------------------------

@@ -255,6 +255,7 @@ struct QecSampleExport {
   uint32_t *cnt;  // [n_words] or nullptr
   uint32_t *ev;   // [n_words][cap]
   int cap;
+  int fmt16;      // lane-stream kernel only: rows hold 2 * cap delta-coded 16-bit entries (qec_kernels.cu)
 };
 
 // words of shared memory the specialised sampler keeps its small tables in:

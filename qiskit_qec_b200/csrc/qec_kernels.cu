@@ -444,6 +444,49 @@ k_ev_compact(const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ ev, 
   }
 }
 
+// ---- 16-bit delta-coded events (qec_sampler_sample_events16) --------------------------------------
+// A word's events arrive in slot order (slot = sorted location * 32 + shot bit: the lane-stream
+// kernel appends them as its stream meets them).  Entry = (delta << 4) | digit, delta = slot -
+// previous slot - 1 (previous = -1 at the start of a word), delta < 4095; 0xFFF0 = "4095 slots
+// without an event".  The lane-stream kernel writes the entries itself (QecSampleExport::fmt16:
+// rows of 2 * cap entries, cnt[w] = their number); the block sums / scan above place them and
+// k_ev16_compact copies them out.
+__global__ void __launch_bounds__(QEC_EVC_T)
+k_ev16_compact(const uint32_t *__restrict__ cnt16, const uint16_t *__restrict__ rows16, const long long n_words,
+               const int cap, const uint32_t *__restrict__ block_off, uint16_t *__restrict__ out_cnt,
+               uint16_t *__restrict__ out_ev, const unsigned long long pool_cap) {
+  __shared__ uint32_t warp_tot[QEC_EVC_T / 32];
+  const long long w0 = (long long)blockIdx.x * QEC_EVC_WPB;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t run = block_off[blockIdx.x];
+  uint32_t tot[4], mine = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const long long w = w0 + 4 * (long long)threadIdx.x + j;
+    tot[j] = w < n_words ? min(cnt16[w], 2u * (uint32_t)cap) : 0u;
+    mine += tot[j];
+  }
+  uint32_t incl = mine;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+    if ((int)lane >= o) incl += t;
+  }
+  if (lane == 31u) warp_tot[warp] = incl;
+  __syncthreads();
+  for (unsigned k = 0; k < warp; ++k) run += warp_tot[k];
+  uint32_t o = run + incl - mine;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const long long w = w0 + 4 * (long long)threadIdx.x + j;
+    if (w >= n_words) break;
+    out_cnt[w] = (uint16_t)tot[j];
+    if ((unsigned long long)o + tot[j] > pool_cap) break;  // (the host sees total > pool and re-runs)
+    const uint16_t *row = rows16 + w * (2 * (long long)cap);
+    for (uint32_t k = 0; k < tot[j]; ++k) out_ev[o + k] = row[k];
+    o += tot[j];
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // Multi-GPU tally reduce without a collective launch: device 0 sums the tallies of its peers,
 // read straight from their memory over NVLink peer mappings (ptrs[k] = tally of device k; the
@@ -569,6 +612,17 @@ void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const ui
   k_ev_block_sums<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, n_words, two_ended, cap, block_sums, overflow);
   k_ev_scan_blocks<<<1, 1024, 0, stream>>>(block_sums, n_blocks, total);
   k_ev_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, ev, n_words, two_ended, cap, block_sums, out_cnt, out_ev, pool_cap, ev24);
+}
+
+void qec_launch_event_compact16(cudaStream_t stream, const uint32_t *cnt, const uint16_t *rows16, long long n_words,
+                                int cap, uint32_t *block_sums, uint32_t *overflow, unsigned long long *total,
+                                uint16_t *out_cnt, uint16_t *out_ev, unsigned long long pool_cap) {
+  const int n_blocks = (int)((n_words + QEC_EVC_WPB - 1) / QEC_EVC_WPB);
+  if (n_blocks < 1) return;
+  // (a row holds 2 * cap entries: longer words are reported through `overflow` and the host re-runs)
+  k_ev_block_sums<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, n_words, 0, 2 * cap, block_sums, overflow);
+  k_ev_scan_blocks<<<1, 1024, 0, stream>>>(block_sums, n_blocks, total);
+  k_ev16_compact<<<n_blocks, QEC_EVC_T, 0, stream>>>(cnt, rows16, n_words, cap, block_sums, out_cnt, out_ev, pool_cap);
 }
 
 void qec_launch_tally_reduce_peers(cudaStream_t stream, const unsigned long long *const *ptrs, int n_dev,

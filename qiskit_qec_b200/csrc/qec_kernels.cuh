@@ -51,6 +51,10 @@ void qec_launch_event_compact(cudaStream_t stream, const uint32_t *cnt, const ui
                               int two_ended, int cap, uint32_t *block_sums, uint32_t *overflow,
                               unsigned long long *total, uint16_t *out_cnt, uint32_t *out_ev,
                               unsigned long long pool_cap, int ev24 = 0);
+// 16-bit delta-coded form of the same (events in slot order per word; qec_kernels.cu)
+void qec_launch_event_compact16(cudaStream_t stream, const uint32_t *cnt, const uint16_t *rows16, long long n_words,
+                                int cap, uint32_t *block_sums, uint32_t *overflow, unsigned long long *total,
+                                uint16_t *out_cnt, uint16_t *out_ev, unsigned long long pool_cap);
 // multi-GPU: device 0 sums the peers' tallies through peer pointers
 void qec_launch_tally_reduce_peers(cudaStream_t stream, const unsigned long long *const *ptrs, int n_dev,
                                    int len, unsigned long long *out);

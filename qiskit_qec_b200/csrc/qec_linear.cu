@@ -1129,6 +1129,7 @@ __device__ __forceinline__ void lanes_stream(const QecLinDev &S, const QecSample
                                              const uint32_t rec_s, const uint32_t lane_acc, LanePlanes &P,
                                              uint32_t *xrow, uint32_t &xk) {
   uint32_t pos = 0xFFFFFFFFu;  // -1
+  uint32_t xprev = 0xFFFFFFFFu;  // (16-bit export: slot of the lane's previous fault)
   QecPhilox rr[NP];
   uint32_t gg[2 * NP];
 #pragma unroll
@@ -1185,12 +1186,27 @@ __device__ __forceinline__ void lanes_stream(const QecLinDev &S, const QecSample
     if (EXPORT) {
       // the lane owns its 32-shot word: events go to the word's row in stream order, the count
       // stays in a register (no atomics)
+      if (X.fmt16) {
+        // delta-coded 16-bit entries (qec_sampler_sample_events16): the position IS the slot
+        uint16_t *xrow16 = reinterpret_cast<uint16_t *>(xrow);
+        const uint32_t cap16 = 2u * (uint32_t)X.cap;
 #pragma unroll
-      for (int j = 0; j < 2 * NP; ++j)
-        if (ok[j]) {
-          if (xk < (uint32_t)X.cap) xrow[xk] = (S.slloc[sl[j]] << 14) | ((pp[j] & 31u) << 9) | dd[j];
-          ++xk;
-        }
+        for (int j = 0; j < 2 * NP; ++j)
+          if (ok[j]) {
+            uint32_t delta = pp[j] - xprev - 1u;  // (xprev starts at -1)
+            for (; delta >= 4095u; delta -= 4095u) { if (xk < cap16) xrow16[xk] = 0xFFF0u; ++xk; }
+            if (xk < cap16) xrow16[xk] = (uint16_t)((delta << 4) | dd[j]);
+            ++xk;
+            xprev = pp[j];
+          }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 2 * NP; ++j)
+          if (ok[j]) {
+            if (xk < (uint32_t)X.cap) xrow[xk] = (S.slloc[sl[j]] << 14) | ((pp[j] & 31u) << 9) | dd[j];
+            ++xk;
+          }
+      }
     }
     if (TALLY) {
       uint32_t mk[2 * NP];

@@ -421,3 +421,32 @@ def test_events_do_not_depend_on_the_chunking(capi):
         assert np.array_equal(wc, np.concatenate([wa, wb]))
         assert np.array_equal(ev, np.concatenate([ea, eb]))
         assert np.array_equal(tl, ta + tb)
+
+
+def test_events16_delta_coded_form(capi, monkeypatch):
+    """qec_sampler_sample_events16 (two bytes per entry, delta-coded in slot order) decodes to the
+    events of the 32-bit form, word by word; served by the lane-stream kernel only."""
+    from qiskit_qec_b200.circuits import surface_code_circuit
+    from qiskit_qec_b200.noise import standard_depolarizing_model
+    from helpers import make_sampler, sampler_inputs
+    for d, T, p, n, lo in ((5, 5, 1e-3, 400_000 + 21, 4096 + 64), (3, 2, 0.02, 20_000, 0), (5, 5, 2e-5, 300_000, 32)):
+        circ = surface_code_circuit(d, T)
+        idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(p))
+        g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+        sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=23)
+        wc, ev, tl = sm.sample_events(lo, n, want_tally=True)
+        assert "lane-streams" in capi.last_kernel()
+        wc2, ent, tl2 = sm.sample_events(lo, n, want_tally=True, packed16=True)
+        assert ent.dtype == np.uint16 and np.array_equal(tl, tl2) and int(wc2.sum()) == len(ent)
+        cnt, dec = capi.unpack_events16(wc2, ent, sm.tables())
+        assert np.array_equal(cnt, wc)
+        word_of = np.repeat(np.arange(len(wc)), wc.astype(np.int64))
+        assert np.array_equal(dec[np.lexsort((dec, word_of))], ev[np.lexsort((ev, word_of))])
+    # the CTA variant appends a word's events with atomics, in no order: refused
+    monkeypatch.setenv("QEC_B200_LIN_MODE", "cta")
+    circ = surface_code_circuit(3, 2)
+    idx, labels, lw, lp = sampler_inputs(circ, standard_depolarizing_model(0.01))
+    g = capi.Circuit(circ.nq, circ.nc, circ.ops)
+    sm, _ = make_sampler(capi, g, idx, labels, lw, lp, seed=23)
+    with pytest.raises(RuntimeError, match="16-bit events"):
+        sm.sample_events(0, 4096, packed16=True)

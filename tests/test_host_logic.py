@@ -104,3 +104,33 @@ def test_counts_from_packed_matches_qiskit_format():
     assert sum(counts_from_packed(packed, n, [nc]).values()) == n
     with pytest.raises(ValueError):
         counts_from_packed(packed, n, [3, 3])
+
+
+def test_unpack_events16_decodes_a_synthetic_stream():
+    """The host decoder of the delta-coded 16-bit event form (include/qec_b200.h,
+    qec_sampler_sample_events16): entries (delta << 4 | digit) and 0xFFF0 skips per word -> events
+    location << 14 | shot bit << 9 | digit through the sorted -> original location map."""
+    import numpy as np
+    from qiskit_qec_b200 import _capi
+    L = 300
+    tables = np.zeros(8 + 1 + 32 + 5 * L + 50, dtype=np.uint32)
+    tables[0], tables[1], tables[3] = 32, 1, L
+    tables[8 + 1 + 32 + L: 8 + 1 + 32 + 2 * L] = np.arange(L)[::-1]
+    rng = np.random.default_rng(0)
+    wc, ent, want, wantc = [], [], [], []
+    for w in range(80):
+        slots = np.sort(rng.choice(L * 32, size=int(rng.integers(0, 6)), replace=False))
+        prev, n = -1, 0
+        for sl in slots:
+            d = int(sl) - prev - 1
+            while d >= 4095:
+                ent.append(0xFFF0); d -= 4095; n += 1
+            dig = int(rng.integers(0, 15))
+            ent.append((d << 4) | dig); n += 1; prev = int(sl)
+            want.append(((L - 1 - (int(sl) >> 5)) << 14) | ((int(sl) & 31) << 9) | dig)
+        wc.append(n); wantc.append(len(slots))
+    assert 0xFFF0 in ent  # (skips are exercised)
+    c, e = _capi.unpack_events16(np.array(wc, dtype=np.uint16), np.array(ent, dtype=np.uint16), tables)
+    assert np.array_equal(c, np.array(wantc)) and np.array_equal(e, np.array(want, dtype=np.uint32))
+    c, e = _capi.unpack_events16(np.zeros(3, dtype=np.uint16), np.zeros(0, dtype=np.uint16), tables)
+    assert len(e) == 0 and np.array_equal(c, [0, 0, 0])
