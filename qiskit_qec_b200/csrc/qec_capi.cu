@@ -524,9 +524,9 @@ extern "C" int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_
                       mask_code(c, op, fault_pauli[j]));
       }
     }
-    std::stable_sort(tmp.begin(), tmp.end(), [](uint32_t a, uint32_t b) {
-      return (a >> QEC_EV_OP_SHIFT) < (b >> QEC_EV_OP_SHIFT);
-    });
+    const auto by_op = [](uint32_t a, uint32_t b) { return (a >> QEC_EV_OP_SHIFT) < (b >> QEC_EV_OP_SHIFT); };
+    // (the planners' single-fault paths arrive in op order already: no sort, no temporary buffer)
+    if (!std::is_sorted(tmp.begin(), tmp.end(), by_op)) std::stable_sort(tmp.begin(), tmp.end(), by_op);
     ev.insert(ev.end(), tmp.begin(), tmp.end());
     off[w + 1] = (long long)ev.size();
   }
