@@ -10,6 +10,7 @@ SURVEY.md 8(b) "Error conventions").
 from __future__ import annotations
 
 import ctypes as C
+import itertools
 import os
 from typing import Optional, Sequence, Tuple
 
@@ -128,10 +129,13 @@ def jit_compile_to_file(nq: int, nc: int, encoded_circ, loc_op, kind: int, order
 
 
 def rows_to_csr(encoded_circ: Sequence[Sequence[int]]) -> Tuple[np.ndarray, np.ndarray]:
-    off = np.zeros(len(encoded_circ) + 1, dtype=np.int32)
-    for i, row in enumerate(encoded_circ):
-        off[i + 1] = off[i] + len(row)
-    data = np.fromiter((v for row in encoded_circ for v in row), dtype=np.int32, count=int(off[-1]))
+    """The reference's ``encoded_circ`` (one list per op) as the C ABI takes it: int32 row offsets
+    and the rows' entries back to back (``qec_circuit_create``)."""
+    n = len(encoded_circ)
+    off = np.zeros(n + 1, dtype=np.int32)
+    if n:
+        np.cumsum(np.fromiter(map(len, encoded_circ), dtype=np.int32, count=n), out=off[1:])
+    data = np.fromiter(itertools.chain.from_iterable(encoded_circ), dtype=np.int32, count=int(off[-1]))
     return off, data
 
 
@@ -153,8 +157,16 @@ class Circuit:
     """``qec_circuit``: the compiled circuit IR resident on one GPU."""
 
     def __init__(self, nq: int, nc: int, encoded_circ: Sequence[Sequence[int]], device: int = 0):
-        self.nq, self.nc, self.n_ops, self.device = int(nq), int(nc), len(encoded_circ), int(device)
-        off, data = rows_to_csr(encoded_circ)
+        # encoded_circ: the reference's list of rows, or the (row_off, row_data) int32 arrays of
+        # rows_to_csr -- the host buffers qec_circuit_create reads (a caller that creates many
+        # objects of one circuit flattens the Python lists once)
+        if isinstance(encoded_circ, tuple) and len(encoded_circ) == 2 and isinstance(encoded_circ[0], np.ndarray):
+            off, data = _i32(encoded_circ[0]), _i32(encoded_circ[1])
+            if len(off) < 1 or int(off[0]) != 0 or int(off[-1]) != len(data) or bool((off[1:] < off[:-1]).any()):
+                raise ValueError("row offsets do not match the row data")
+        else:
+            off, data = rows_to_csr(encoded_circ)
+        self.nq, self.nc, self.n_ops, self.device = int(nq), int(nc), len(off) - 1, int(device)
         h = C.c_void_p()
         _check(lib().qec_circuit_create(C.c_int(device), C.c_int(nq), C.c_int(nc),
                                         C.c_int(self.n_ops), _p(off), _p(data), C.byref(h)))

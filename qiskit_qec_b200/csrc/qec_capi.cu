@@ -19,17 +19,40 @@
 #include "qec_kernels.cuh"
 #include "qec_jit.h"
 #include "qec_distance.h"
-#include <memory_resource>
+#include <memory>
+#include <mutex>
 
-// per-fault clbit lists of the planners: thousands of short vectors, allocated from one monotonic
-// arena (a create call spent 1.6 of its 2.4 ms in malloc / free of these)
-using SigList = std::pmr::vector<uint16_t>;
-using SigLists = std::pmr::vector<SigList>;
-// (the outer vectors live in the arena too and are abandoned with it: no destructor per list)
-static SigLists &arena_lists(std::pmr::monotonic_buffer_resource &arena, size_t n) {
-  void *mem = arena.allocate(sizeof(SigLists), alignof(SigLists));
-  return *new (mem) SigLists(n, SigList(&arena), &arena);
-}
+// per-fault clbit lists of the planners: thousands of short lists, kept as (pointer, length) views
+// into one bump arena that is dropped as a whole (a create call once spent 1.6 of its 2.4 ms in
+// malloc / free of one std::vector per list; polymorphic-allocator vectors still cost an
+// allocator round trip and 32 bytes of header per list)
+struct SigList {
+  const uint16_t *p = nullptr;
+  uint32_t n = 0;
+  size_t size() const { return n; }
+  const uint16_t *begin() const { return p; }
+  const uint16_t *end() const { return p + n; }
+  uint16_t operator[](size_t k) const { return p[k]; }
+};
+using SigLists = std::vector<SigList>;
+struct SigArena {
+  std::vector<std::unique_ptr<uint16_t[]>> blocks;  // (never moved: the views stay valid)
+  uint16_t *cur = nullptr;
+  size_t left = 0;
+  void put(SigList &l, const uint16_t *src, size_t n) {
+    if (n > left) {
+      const size_t sz = std::max<size_t>(n, (size_t)1 << 17);
+      blocks.emplace_back(new uint16_t[sz]);
+      cur = blocks.back().get();
+      left = sz;
+    }
+    if (n) memcpy(cur, src, n * sizeof(uint16_t));
+    l.p = cur;
+    l.n = (uint32_t)n;
+    cur += n;
+    left -= n;
+  }
+};
 
 // revision tag of the linear-response kernels in the variant strings: bumped with every change of
 // k_sample_lanes / k_sample_lin, so that a committed ncu capture (profiles/rNN/ncu_dominant_kernel.json,
@@ -91,8 +114,29 @@ struct DevInfo {
   size_t smem_optin = 0, smem_sm = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
+  // idle non-blocking streams, handed back by destroyed circuits (a circuit per call is the
+  // end-to-end pattern: cudaStreamCreate + cudaStreamDestroy cost ~25 us a pair)
+  std::mutex mu;
+  std::vector<cudaStream_t> idle_streams;
 };
 static DevInfo g_dev[64];
+
+static cudaError_t stream_take(DevInfo *d, cudaStream_t *out) {
+  {
+    std::lock_guard<std::mutex> lock(d->mu);
+    if (!d->idle_streams.empty()) {
+      *out = d->idle_streams.back();
+      d->idle_streams.pop_back();
+      return cudaSuccess;
+    }
+  }
+  return cudaStreamCreateWithFlags(out, cudaStreamNonBlocking);
+}
+static void stream_give(DevInfo *d, cudaStream_t st) {  // (the stream must be idle)
+  std::lock_guard<std::mutex> lock(d->mu);
+  if (d->idle_streams.size() < 16) d->idle_streams.push_back(st);
+  else cudaStreamDestroy(st);
+}
 
 static int dev_info(int device, DevInfo **out) {
   if (device < 0 || device >= 64) return fail(QEC_ERR_CUDA, "bad device index %d", device);
@@ -168,6 +212,42 @@ static int upload(const std::vector<T> &v, T **out) {
   return 0;
 }
 
+// Several host tables -> ONE device allocation and ONE copy: a sampler is made of twenty small
+// tables, and a cudaMallocAsync + pageable cudaMemcpy pair costs ~11 us (0.22 ms of a 1.3 ms
+// create call).  Tables keep 256-byte alignment inside the pack; an empty table still gets a
+// valid address, as upload() gives it.  The owner frees the pack, never the tables.
+struct UploadPack {
+  struct Item { const void *src; size_t bytes; void **out; };
+  std::vector<Item> items;
+  template <class T>
+  void add(const std::vector<T> &v, T **out) {
+    *out = nullptr;
+    items.push_back({v.data(), v.size() * sizeof(T), (void **)out});
+  }
+  static size_t slot(size_t bytes) { return (std::max<size_t>(bytes, 1) + 255) & ~(size_t)255; }
+  int commit(void **base) {
+    *base = nullptr;
+    size_t total = 0;
+    for (const Item &it : items) total += slot(it.bytes);
+    static thread_local std::vector<uint8_t> stage;
+    if (stage.size() < total) stage.resize(total);
+    size_t off = 0;
+    for (const Item &it : items) {
+      if (it.bytes) memcpy(stage.data() + off, it.src, it.bytes);
+      off += slot(it.bytes);
+    }
+    CU(qec_dev_alloc(base, std::max<size_t>(total, 1)));
+    if (total) CU(cudaMemcpy(*base, stage.data(), total, cudaMemcpyHostToDevice));
+    off = 0;
+    for (const Item &it : items) {
+      *it.out = (uint8_t *)*base + off;
+      off += slot(it.bytes);
+    }
+    items.clear();
+    return 0;
+  }
+};
+
 // ---- circuit IR --------------------------------------------------------------------------------
 // reference opcodes (errorpropagator.h:9-42)
 enum { R_H = 0, R_S, R_X, R_Y, R_Z, R_CX, R_ID, R_RESET, R_MEASURE, R_BARRIER };
@@ -208,7 +288,7 @@ static int pipelined_out(qec_circuit *c, int64_t n_words, uint32_t *host_bits, L
   const int64_t cw = pipe_chunk_words(c, n_words);
   const size_t buf_bytes = (size_t)c->nc * cw * 4;
   for (int i = 0; i < 2; ++i) {
-    if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    if (!c->pipe_stream[i]) CU(stream_take(c->info, &c->pipe_stream[i]));
     if (!c->pipe_done[i]) CU(cudaEventCreateWithFlags(&c->pipe_done[i], cudaEventDisableTiming));
     int rc = c->pipe_buf[i].ensure(std::max<size_t>(buf_bytes, 4));
     if (rc) return rc;
@@ -342,7 +422,7 @@ extern "C" void qec_circuit_destroy(qec_circuit *c) {
   c->ev_off.release(); c->ev.release();
   for (int i = 0; i < 2; ++i) {
     c->pipe_buf[i].release();
-    if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
+    if (c->pipe_stream[i]) stream_give(c->info, c->pipe_stream[i]);  // (idle: the device was synchronised above)
     if (c->pipe_done[i]) cudaEventDestroy(c->pipe_done[i]);
   }
   delete c;
@@ -510,26 +590,29 @@ extern "C" int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_
   // duplicated op index inside one path keeps the reference's "last one wins" order
   std::vector<long long> off(n_words + 1, 0);
   std::vector<uint32_t> ev;
-  ev.reserve((size_t)(path_off[n_paths] - path_off[0]));
-  std::vector<uint32_t> tmp;
+  ev.reserve((size_t)std::max<int64_t>(path_off[n_paths] - path_off[0], 0));
+  const auto by_op = [](uint32_t a, uint32_t b) { return (a >> QEC_EV_OP_SHIFT) < (b >> QEC_EV_OP_SHIFT); };
   for (int64_t w = 0; w < n_words; ++w) {
-    tmp.clear();
+    const size_t w0 = ev.size();
     const int64_t p1 = std::min<int64_t>(n_paths, 32 * w + 32);
+    bool sorted = true;
+    int prev = -1;
     for (int64_t p = 32 * w; p < p1; ++p) {
       for (int64_t j = path_off[p]; j < path_off[p + 1]; ++j) {
         const int op = fault_op[j];
         if (op < 0 || op >= c->n_ops)
           return fail(QEC_ERR_LOGIC, "fault op index %d out of range [0, %d)", op, c->n_ops);
-        tmp.push_back(((uint32_t)op << QEC_EV_OP_SHIFT) | ((uint32_t)(p & 31) << 4) |
-                      mask_code(c, op, fault_pauli[j]));
+        ev.push_back(((uint32_t)op << QEC_EV_OP_SHIFT) | ((uint32_t)(p & 31) << 4) |
+                     mask_code(c, op, fault_pauli[j]));
+        sorted = sorted && op >= prev;
+        prev = op;
       }
     }
-    const auto by_op = [](uint32_t a, uint32_t b) { return (a >> QEC_EV_OP_SHIFT) < (b >> QEC_EV_OP_SHIFT); };
-    // (the planners' single-fault paths arrive in op order already: no sort, no temporary buffer)
-    if (!std::is_sorted(tmp.begin(), tmp.end(), by_op)) std::stable_sort(tmp.begin(), tmp.end(), by_op);
-    ev.insert(ev.end(), tmp.begin(), tmp.end());
+    // (the planners' single-fault paths arrive in op order already: written in place, no sort)
+    if (!sorted) std::stable_sort(ev.begin() + (ptrdiff_t)w0, ev.end(), by_op);
     off[w + 1] = (long long)ev.size();
   }
+  trace("propagate_batch: marshal");
   CU(cudaSetDevice(c->device));
   QecLaunchCfg cfg;
   int rc = pick_cfg(c, 0, 0, 0, 0, &cfg);
@@ -546,12 +629,15 @@ extern "C" int qec_propagate_batch(qec_circuit *c, int64_t n_paths, const int64_
   O.frame = out_frame ? (uint32_t *)c->out_frame.p : nullptr;
   O.tally = nullptr;
   O.n_words = n_words;
+  trace("propagate_batch: buffers + uploads");
   time_begin(c, 0);
   qec_launch_batch(cfg, 0, c->dev, O, (const long long *)c->ev_off.p, (const uint32_t *)c->ev.p);
   time_end(c, 0);
   CU(cudaGetLastError());
+  if (trace_on()) { cudaDeviceSynchronize(); trace("propagate_batch: kernel"); }
   CU(cudaMemcpy(out_bits, c->out_bits.p, out_bytes, cudaMemcpyDeviceToHost));
   if (out_frame) CU(cudaMemcpy(out_frame, c->out_frame.p, fr_bytes, cudaMemcpyDeviceToHost));
+  trace("propagate_batch: read-back");
   return 0;
 }
 
@@ -727,7 +813,8 @@ extern "C" int qec_enumerator_create(qec_circuit *c, int order, int L, const int
 // Per-fault clbit lists from the bit-sliced single-fault outcomes bits[nc][FW]: 32 faults (one word
 // column) at a time through small local buffers, so that every list is written in one go (the
 // clbit-major scan wrote each entry into a different list: a cache miss per entry).
-static void lists_from_bits(const std::vector<uint32_t> &bits, int nc, int64_t FW, int64_t F, SigLists &lists) {
+static void lists_from_bits(const std::vector<uint32_t> &bits, int nc, int64_t FW, int64_t F, SigArena &arena,
+                            SigLists &lists) {
   std::vector<uint16_t> buf((size_t)32 * (size_t)nc);
   uint32_t cnt[32];
   for (int64_t fw = 0; fw < FW; ++fw) {
@@ -739,9 +826,48 @@ static void lists_from_bits(const std::vector<uint32_t> &bits, int nc, int64_t F
       }
     for (int b = 0; b < 32; ++b) {
       const int64_t f = 32 * fw + b;
-      if (f < F && cnt[b]) lists[(size_t)f].assign(buf.begin() + (size_t)b * nc, buf.begin() + (size_t)b * nc + cnt[b]);
+      if (f < F && cnt[b]) arena.put(lists[(size_t)f], buf.data() + (size_t)b * nc, cnt[b]);
     }
   }
+}
+
+// Chains of final measurements: pred(c) = the previous final measurement of the same qubit.
+static void measure_chains(const qec_circuit *c, std::vector<int> &pred, std::vector<int> &succ) {
+  pred.assign(c->nc, -1);
+  succ.assign(c->nc, -1);
+  std::vector<int> last(c->nq, -1);
+  for (size_t i = 0; i < c->packed.size(); ++i) {
+    const uint32_t g = c->packed[i];
+    if ((g & 15u) != QOP_MEASF) continue;
+    const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
+    if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
+    last[q] = cb;
+  }
+}
+
+// Time-difference basis on the bit-sliced signatures themselves: row c ^= row pred(c), every row
+// from the ORIGINAL rows -- 32 faults per XOR, and only the lists of the basis that is kept are
+// ever extracted (the per-list version, a mark array and a small sort per fault, was the longest
+// step of a create call: 0.25 ms at d=5 on top of 0.19 ms for the raw lists).
+static std::vector<uint32_t> diff_bits(const std::vector<uint32_t> &bits, int nc, int64_t FW,
+                                       const std::vector<int> &pred) {
+  std::vector<uint32_t> d(bits.size());
+  for (int cb = 0; cb < nc; ++cb) {
+    const uint32_t *a = &bits[(size_t)cb * FW];
+    uint32_t *o = &d[(size_t)cb * FW];
+    if (pred[cb] < 0) {
+      memcpy(o, a, (size_t)FW * 4);
+    } else {
+      const uint32_t *b = &bits[(size_t)pred[cb] * FW];
+      for (int64_t w = 0; w < FW; ++w) o[w] = a[w] ^ b[w];
+    }
+  }
+  return d;
+}
+static size_t count_bits(const std::vector<uint32_t> &v) {
+  size_t n = 0;
+  for (uint32_t x : v) n += (size_t)__builtin_popcount(x);
+  return n;
 }
 
 // Read-out program of the lane-owned accumulators (lanes_readout, qec_linear.cu): four rows per
@@ -820,49 +946,20 @@ static int enum_plan_linear(qec_enumerator *e) {
   std::vector<uint32_t> bits((size_t)c->nc * FW);
   int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), e->pcode.data(), bits.data(), nullptr);
   if (rc) return rc;
-  std::pmr::monotonic_buffer_resource arena(1 << 20);
-  SigLists &lists = arena_lists(arena, (size_t)F), &tr = arena_lists(arena, (size_t)F);
-  lists_from_bits(bits, c->nc, FW, F, lists);
   // time-difference basis: clbit c -> c ^ pred(c), pred = the previous final measurement of the
-  // same qubit (see sampler_plan_linear)
-  std::vector<int> pred(c->nc, -1), succ(c->nc, -1), last(c->nq, -1);
-  for (size_t i = 0; i < c->packed.size(); ++i) {
-    const uint32_t g = c->packed[i];
-    if ((g & 15u) != QOP_MEASF) continue;
-    const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
-    if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
-    last[q] = cb;
-  }
-  size_t raw_total = 0, tr_total = 0;
-  {
-    std::vector<uint8_t> mark(c->nc, 0);
-    std::vector<uint16_t> tmp;
-    tmp.reserve(64);
-    for (int64_t f = 0; f < F; ++f) {
-      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
-      tmp.clear();  // (one allocation per list: collected and sorted in a scratch vector)
-      for (uint16_t cb : lists[f]) {
-        if (mark[cb]) { tmp.push_back(cb); mark[cb] = 0; }
-        const int sc = succ[cb];
-        if (sc >= 0 && mark[sc]) { tmp.push_back((uint16_t)sc); mark[sc] = 0; }
-      }
-      for (size_t i = 1; i < tmp.size(); ++i) {  // (a few entries: insertion sort)
-        const uint16_t x = tmp[i];
-        size_t j = i;
-        for (; j > 0 && tmp[j - 1] > x; --j) tmp[j] = tmp[j - 1];
-        tmp[j] = x;
-      }
-      tr[f].assign(tmp.begin(), tmp.end());
-      raw_total += lists[f].size();
-      tr_total += tr[f].size();
-    }
-  }
+  // same qubit (see sampler_plan_linear); kept when it shortens the lists
+  std::vector<int> pred, succ;
+  measure_chains(c, pred, succ);
   // (the read-out schedule walks the rows in clbit order: a previous row must have the smaller
   // index, which holds whenever clbits are allocated in time order)
   bool ordered = true;
   for (int cb = 0; cb < c->nc; ++cb) ordered = ordered && pred[cb] < cb;
+  const std::vector<uint32_t> dbits = diff_bits(bits, c->nc, FW, pred);
+  const size_t raw_total = count_bits(bits), tr_total = count_bits(dbits);
   const bool use_diff = ordered && tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
-  if (use_diff) lists.swap(tr);
+  SigArena arena;
+  SigLists lists((size_t)F);
+  lists_from_bits(use_diff ? dbits : bits, c->nc, FW, F, arena, lists);
   size_t maxlen = 0;
   for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
   if (maxlen > 7) { ln.why = "a fault flips more than 7 entries"; return 0; }
@@ -1128,6 +1225,7 @@ struct qec_sampler {
   uint16_t *d_slcls = nullptr;
   uint8_t *d_cls_always = nullptr, *d_codes = nullptr;
   uint32_t *d_flag = nullptr;
+  void *d_pack = nullptr;  // owns d_T1 ... d_codes, d_slinf, d_flag (UploadPack)
   DevBuf scratch, xcnt, xev;
   int cap = 0;
   QecLaunchCfg cfg{};
@@ -1159,6 +1257,7 @@ struct qec_sampler {
     std::vector<uint32_t> rowprog;
     uint32_t *d_rowprog = nullptr;
     uint32_t *d_batch_ctr = nullptr;  // lane-stream kernel: next batch of the launch (dynamic assignment)
+    void *d_pack = nullptr;  // owns d_rowprog, d_info, d_sigdesc, d_siglist, d_sigrec, d_info2, d_lvl_* (UploadPack)
     std::vector<uint32_t> lvl_prog, lvl_off;  // CTA variant: undo of the time-difference basis
     uint32_t *d_lvl_prog = nullptr, *d_lvl_off = nullptr;
     bool cls_uniform_all = true;
@@ -1324,12 +1423,6 @@ static int sampler_plan_linear(qec_sampler *s) {
   int rc = qec_propagate_batch(c, F, path_off.data(), fop.data(), fpauli.data(), bits.data(), nullptr);
   if (rc) return rc;
   trace("plan_linear: propagate_batch");
-  std::pmr::monotonic_buffer_resource arena(1 << 20);
-  SigLists &lists = arena_lists(arena, (size_t)F);
-  lists_from_bits(bits, c->nc, FW, F, lists);
-  trace("plan_linear: lists");
-  uint32_t n_sig = 0;  // (clbit-list entries before any change of basis: sizes the CTA variant's tables)
-  for (int64_t f = 0; f < F; ++f) n_sig += (uint32_t)lists[f].size();
   ln.loc2sl.assign(s->L, 0);
   for (int sl = 0; sl < s->L; ++sl) ln.loc2sl[s->slloc[sl]] = (uint32_t)sl;
 
@@ -1338,49 +1431,40 @@ static int sampler_plan_linear(qec_sampler *s) {
   // c ^ pred(c) (pred = the previous final measurement of the same qubit) the same fault touches
   // one or two entries.  The read-out undoes it: each lane walks whole chains
   // c0 -> succ(c0) -> ... with a running XOR (rowprog).  Kept only when it shortens the lists.
+  // The change of basis is done on the bit-sliced rows (diff_bits); per-fault lists are extracted
+  // for the basis in use only (the raw ones on demand, need_raw).
   ln.rowprog.clear();
   int n_steps = 0;
   bool use_diff = false;
   size_t maxlen_w = 0;  // longest list the warp variant would see
-  SigLists &tr = arena_lists(arena, (size_t)F);
-  std::vector<int> pred(c->nc, -1), succ(c->nc, -1);
+  SigArena arena;
+  SigLists lists, tr;  // raw lists / time-difference lists
+  const auto need_raw = [&]() {
+    if (!lists.empty()) return;
+    lists.resize((size_t)F);
+    lists_from_bits(bits, c->nc, FW, F, arena, lists);
+  };
+  std::vector<int> pred, succ;
+  measure_chains(c, pred, succ);
+  // (clbit-list entries before any change of basis: sizes the CTA variant's tables)
+  const size_t raw_total = count_bits(bits);
+  const uint32_t n_sig = (uint32_t)raw_total;
   {
-    std::vector<int> last(c->nq, -1);
-    for (size_t i = 0; i < c->packed.size(); ++i) {
-      const uint32_t g = c->packed[i];
-      if ((g & 15u) != QOP_MEASF) continue;
-      const int q = (int)((g >> 4) & 0x3FFFu), cb = (int)(g >> 18);
-      if (last[q] >= 0) { pred[cb] = last[q]; succ[last[q]] = cb; }
-      last[q] = cb;
-    }
-    size_t raw_total = 0, tr_total = 0;
-    std::vector<uint8_t> mark(c->nc, 0);
-    std::vector<uint16_t> tmp;
-    tmp.reserve(64);
-    for (int64_t f = 0; f < F; ++f) {
-      for (uint16_t cb : lists[f]) { mark[cb] ^= 1; if (succ[cb] >= 0) mark[succ[cb]] ^= 1; }
-      tmp.clear();  // (one allocation per list: collected and sorted in a scratch vector)
-      for (uint16_t cb : lists[f]) {
-        if (mark[cb]) { tmp.push_back(cb); mark[cb] = 0; }
-        const int sc = succ[cb];
-        if (sc >= 0 && mark[sc]) { tmp.push_back((uint16_t)sc); mark[sc] = 0; }
-      }
-      for (size_t i = 1; i < tmp.size(); ++i) {  // (a few entries: insertion sort)
-        const uint16_t x = tmp[i];
-        size_t j = i;
-        for (; j > 0 && tmp[j - 1] > x; --j) tmp[j] = tmp[j - 1];
-        tmp[j] = x;
-      }
-      tr[f].assign(tmp.begin(), tmp.end());
-      raw_total += lists[f].size();
-      tr_total += tr[f].size();
-    }
+    const std::vector<uint32_t> dbits = diff_bits(bits, c->nc, FW, pred);
+    const size_t tr_total = count_bits(dbits);
     // (the lane-stream and CTA read-outs walk the rows in clbit order: a previous row must have
     // the smaller index, which holds whenever clbits are allocated in time order)
     bool ordered = true;
     for (int cb = 0; cb < c->nc; ++cb) ordered = ordered && pred[cb] < cb;
     use_diff = ordered && tr_total < raw_total && env_int("QEC_B200_LIN_DIFF", 1) != 0;
     const bool use = use_diff;
+    if (use) {
+      tr.resize((size_t)F);
+      lists_from_bits(dbits, c->nc, FW, F, arena, tr);
+    } else {
+      need_raw();
+    }
+    trace("plan_linear: lists");
     for (int64_t f = 0; f < F; ++f) maxlen_w = std::max(maxlen_w, use ? tr[f].size() : lists[f].size());
     // chains -> 32 lanes, longest first onto the least loaded lane
     std::vector<std::vector<int>> chains;
@@ -1534,6 +1618,7 @@ static int sampler_plan_linear(qec_sampler *s) {
   // undoes the basis in its read-out (running XOR along each chain, lin_readout)
   const bool cta_diff = !warp_mode && !lane_mode && use_diff && env_int("QEC_B200_LIN_CTADIFF", 1) != 0;
   if ((warp_mode || lane_mode || cta_diff) && use_diff) lists.swap(tr);
+  else need_raw();
   // read-out program of the CTA variant (k_sample_lin): whole chains dealt to the T / BW row
   // groups of the CTA, longest first onto the least loaded; entry: row | 1 << 30 valid | 1 << 31
   // the row continues the chain of the group's previous step; layout prog[step * G + group]
@@ -1569,28 +1654,36 @@ static int sampler_plan_linear(qec_sampler *s) {
   ln.sigdesc.clear();
   ln.siglist.clear();
   ln.sigrec.clear();
-  size_t maxlen = 0;
-  for (int64_t f = 0; f < F; ++f) maxlen = std::max(maxlen, lists[f].size());
+  size_t maxlen = 0, n_entries = 0;
+  for (int64_t f = 0; f < F; ++f) { maxlen = std::max(maxlen, lists[f].size()); n_entries += lists[f].size(); }
   const int rec2 = maxlen > 7 ? 1 : 0;
   if (rec8 && (maxlen > 7 || !(warp_mode || lane_mode))) return fail(QEC_ERR_LOGIC, "linear sampler: record plan out of step");
+  // (tables sized once and written by index: this loop runs once per fault of every create call)
+  const size_t per = rec8 ? 4u : rec2 ? 16u : 8u;  // uint16 units per record
+  ln.sigdesc.resize((size_t)F);
+  ln.sigrec.assign((size_t)F * per, (uint16_t)0);
+  ln.siglist.resize(n_entries);
+  size_t pos = 0;
   for (int64_t f = 0; f < F; ++f) {
     const size_t len = lists[f].size();
-    if (len > 1023 || ln.siglist.size() + len >= (1u << 22)) {
+    if (len > 1023 || pos + len >= (1u << 22)) {
       ln.why = "fault signatures too long for the packed descriptor";
       return 0;
     }
-    ln.sigdesc.push_back((uint32_t)ln.siglist.size() | ((uint32_t)len << 22));
+    ln.sigdesc[(size_t)f] = (uint32_t)pos | ((uint32_t)len << 22);
+    uint16_t *r = &ln.sigrec[(size_t)f * per];
     if (rec8) {  // bytes: validity mask of the entries (2^len - 1), 7 clbits
       // (lane-stream variant: absent entries name the dummy row nc)
       const uint8_t pad = lane_mode ? (uint8_t)c->nc : (uint8_t)0;
       uint8_t by[8] = {(uint8_t)((1u << len) - 1u), pad, pad, pad, pad, pad, pad, pad};
       for (size_t k = 0; k < len; ++k) by[1 + k] = (uint8_t)lists[f][k];
-      for (int k = 0; k < 4; ++k) ln.sigrec.push_back((uint16_t)(by[2 * k] | (by[2 * k + 1] << 8)));
+      for (int k = 0; k < 4; ++k) r[k] = (uint16_t)(by[2 * k] | (by[2 * k + 1] << 8));
     } else {
-      ln.sigrec.push_back((uint16_t)len);
-      for (size_t k = 0; k < (rec2 ? 15u : 7u); ++k) ln.sigrec.push_back(k < len ? lists[f][k] : (uint16_t)0);
+      r[0] = (uint16_t)len;
+      for (size_t k = 0; k < std::min<size_t>(len, rec2 ? 15u : 7u); ++k) r[1 + k] = lists[f][k];
     }
-    ln.siglist.insert(ln.siglist.end(), lists[f].begin(), lists[f].end());
+    if (len) memcpy(&ln.siglist[pos], lists[f].begin(), len * sizeof(uint16_t));
+    pos += len;
   }
   ln.siglist.resize((ln.siglist.size() + 2u) & ~(size_t)1u, 0);  // whole 32-bit words, never empty
   if (lane_mode) {
@@ -1599,11 +1692,14 @@ static int sampler_plan_linear(qec_sampler *s) {
   }
   if (ln.rowprog.empty()) ln.rowprog.push_back(0u);
   trace("plan_linear: basis, geometry, records");
-  if ((rc = upload(ln.rowprog, &ln.d_rowprog))) return rc;
-  if ((rc = upload(ln.info, &ln.d_info)) || (rc = upload(ln.sigdesc, &ln.d_sigdesc)) ||
-      (rc = upload(ln.siglist, &ln.d_siglist)) || (rc = upload(ln.sigrec, &ln.d_sigrec)) ||
-      (rc = upload(ln.info2, &ln.d_info2)) || (rc = upload(ln.lvl_prog, &ln.d_lvl_prog)) ||
-      (rc = upload(ln.lvl_off, &ln.d_lvl_off)))
+  {
+    UploadPack up;
+    up.add(ln.rowprog, &ln.d_rowprog); up.add(ln.info, &ln.d_info); up.add(ln.sigdesc, &ln.d_sigdesc);
+    up.add(ln.siglist, &ln.d_siglist); up.add(ln.sigrec, &ln.d_sigrec); up.add(ln.info2, &ln.d_info2);
+    up.add(ln.lvl_prog, &ln.d_lvl_prog); up.add(ln.lvl_off, &ln.d_lvl_off);
+    rc = up.commit(&ln.d_pack);
+  }
+  if (rc)
     return rc;
   trace("plan_linear: uploads");
   {
@@ -1940,19 +2036,19 @@ extern "C" int qec_sampler_create(qec_circuit *c, int L, const int32_t *loc_op,
   trace("sampler_create: host tables");
   CU(cudaSetDevice(c->device));
   int rc = 0;
-  if ((rc = upload(s->T1, &s->d_T1)) || (rc = upload(s->T2, &s->d_T2)) ||
-      (rc = upload(s->slop, &s->d_slop)) || (rc = upload(s->slloc, &s->d_slloc)) ||
-      (rc = upload(s->slinf, &s->d_slinf)) ||
-      (rc = upload(s->slcls, &s->d_slcls)) || (rc = upload(s->cls_acc, &s->d_cls_acc)) ||
-      (rc = upload(s->cls_always, &s->d_cls_always)) || (rc = upload(s->cls_off, &s->d_cls_off)) ||
-      (rc = upload(s->cdf, &s->d_cdf)) || (rc = upload(s->codes, &s->d_codes)) ||
-      (rc = pick_cfg(c, 2, 0, s->B, s->K1, &s->cfg))) {
+  {
+    UploadPack up;
+    up.add(s->T1, &s->d_T1); up.add(s->T2, &s->d_T2); up.add(s->slop, &s->d_slop);
+    up.add(s->slloc, &s->d_slloc); up.add(s->slinf, &s->d_slinf); up.add(s->slcls, &s->d_slcls);
+    up.add(s->cls_acc, &s->d_cls_acc); up.add(s->cls_always, &s->d_cls_always);
+    up.add(s->cls_off, &s->d_cls_off); up.add(s->cdf, &s->d_cdf); up.add(s->codes, &s->d_codes);
+    const std::vector<uint32_t> flag0(1, 0u);  // the overflow flag starts cleared
+    up.add(flag0, &s->d_flag);
+    rc = up.commit(&s->d_pack);
+  }
+  if (rc || (rc = pick_cfg(c, 2, 0, s->B, s->K1, &s->cfg))) {
     qec_sampler_destroy(s);
     return rc;
-  }
-  if (qec_dev_alloc((void **)&s->d_flag, 4) != cudaSuccess || cudaMemset(s->d_flag, 0, 4) != cudaSuccess) {
-    qec_sampler_destroy(s);
-    return fail(QEC_ERR_CUDA, "cudaMalloc failed");
   }
   trace("sampler_create: uploads + pick_cfg");
   const double mu = s->mean_events;
@@ -1984,12 +2080,9 @@ extern "C" void qec_sampler_destroy(qec_sampler *s) {
   if (!s) return;
   cudaSetDevice(s->c->device);
   cudaDeviceSynchronize();  // (see qec_dev_alloc: frees are stream-ordered)
-  void *ptrs[] = {s->d_T1, s->d_T2, s->d_slop, s->d_slloc, s->d_slcls, s->d_cls_acc,
-                  s->d_cls_always, s->d_cls_off, s->d_cdf, s->d_codes, s->d_flag, s->d_slinf,
-                  s->d_seg_end, s->lin.d_info, s->lin.d_sigdesc, s->lin.d_siglist,
-                  s->lin.d_sigrec, s->lin.d_rowprog, s->lin.d_info2, s->lin.d_batch_ctr,
-                  s->lin.d_lvl_prog, s->lin.d_lvl_off, s->lin.d16_info, s->lin.d16_prog,
-                  s->lin.d16_recidx, s->lin.d16_rec};
+  // (the tables of the two upload packs are freed with their packs)
+  void *ptrs[] = {s->d_pack, s->d_seg_end, s->lin.d_pack, s->lin.d_batch_ctr,
+                  s->lin.d16_info, s->lin.d16_prog, s->lin.d16_recidx, s->lin.d16_rec};
   for (void *p : ptrs) if (p) qec_dev_free(p);
   s->scratch.release(); s->xcnt.release(); s->xev.release();
   s->jit.release();
@@ -2317,7 +2410,7 @@ static int sample_events_impl(qec_sampler *s, int64_t shot_lo, int64_t n_shots, 
     }
   };
   for (int i = 0; i < 2; ++i) {
-    if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    if (!c->pipe_stream[i]) CU(stream_take(c->info, &c->pipe_stream[i]));
     st[i] = c->pipe_stream[i];
     cudaEventCreateWithFlags(&kdone[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&tdone[i], cudaEventDisableTiming);

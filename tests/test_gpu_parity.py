@@ -48,6 +48,10 @@ def test_k1_surface_d5(capi, ref):
     g = capi.Circuit(circ.nq, circ.nc, circ.ops)
     bits = g.propagate_batch(*fault_lists_to_csr(paths))
     np.testing.assert_array_equal(capi.unpack_bits(bits, len(paths)), want)
+    # the same circuit handed over as the C ABI's own host buffers (row offsets + row data)
+    g2 = capi.Circuit(circ.nq, circ.nc, capi.rows_to_csr(circ.ops))
+    assert g2.n_ops == len(circ.ops)
+    np.testing.assert_array_equal(g2.propagate_batch(*fault_lists_to_csr(paths)), bits)
 
 
 def _ref_enum_all(ref, circ, order, idx, labels, paulis, blocksize=10000, max_paths=None):

@@ -134,3 +134,25 @@ def test_unpack_events16_decodes_a_synthetic_stream():
     assert np.array_equal(c, np.array(wantc)) and np.array_equal(e, np.array(want, dtype=np.uint32))
     c, e = _capi.unpack_events16(np.zeros(3, dtype=np.uint16), np.zeros(0, dtype=np.uint16), tables)
     assert len(e) == 0 and np.array_equal(c, [0, 0, 0])
+
+
+def test_rows_to_csr_and_the_csr_form_of_a_circuit():
+    """`rows_to_csr` lays the reference's list of rows out as qec_circuit_create reads it; a
+    Circuit also takes that pair directly and refuses offsets that do not describe the data."""
+    from qiskit_qec_b200 import _capi
+    rows = [[5, 0, 1], [0, 2], [9], [8, 1, 0]]
+    off, data = _capi.rows_to_csr(rows)
+    assert off.dtype == np.int32 and data.dtype == np.int32
+    assert off.tolist() == [0, 3, 5, 6, 9]
+    assert data.tolist() == [5, 0, 1, 0, 2, 9, 8, 1, 0]
+    off0, data0 = _capi.rows_to_csr([])
+    assert off0.tolist() == [0] and len(data0) == 0
+    circ = surface_code_circuit(3, 2)
+    off, data = _capi.rows_to_csr(circ.ops)
+    assert len(off) == len(circ.ops) + 1 and int(off[-1]) == sum(len(r) for r in circ.ops)
+    assert [data[off[i]:off[i + 1]].tolist() for i in range(len(circ.ops))] == [list(r) for r in circ.ops]
+    for bad in ((np.array([1, 3], np.int32), np.zeros(3, np.int32)),        # does not start at 0
+                (np.array([0, 2], np.int32), np.zeros(3, np.int32)),        # does not cover the data
+                (np.array([0, 3, 2, 3], np.int32), np.zeros(3, np.int32))):  # decreasing
+        with pytest.raises(ValueError):
+            _capi.Circuit(2, 2, bad)
