@@ -649,7 +649,9 @@ def main():
     ap.add_argument("--shots", type=int, default=100_000_000, help="shots per GPU per step")
     ap.add_argument("--ref-shots", type=int, default=40_000,
                     help="reference shots per host process per step (bounded CPU sample)")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=8,
+                    help="timed steps of each end-to-end leg (at most --steps): a single slow step -- on an "
+                         "8-GPU box the ranks share one host memory system -- weighs 1/8, not 1/3")
     ap.add_argument("--plugin-shots", type=int, default=1_000_000,
                     help="shots of the literal _CFaultSampler.sample(N) call (0: skip)")
     ap.add_argument("--frame-shots", type=int, default=50_000_000,
