@@ -331,6 +331,20 @@ int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t *row_off,
                             int order, int tally, int bits, int threads, int min_blocks,
                             int group, const char *cubin_path, const char *source_path);
 
+/* The host step of the linear-response planners on caller-given single-fault signatures, for
+ * tests and inspection; needs no device.  bits[nc][ceil(n_faults / 32)]: bit f of row c = fault f
+ * flips clbit c (what qec_propagate_batch returns for single-fault paths).  pred[nc] (or NULL):
+ * the previous final measurement of the same qubit, -1 for none; diff_basis != 0 lists the rows
+ * c ^ pred(c) (the time-difference basis the kernels accumulate in) instead of the raw ones.
+ * Writes list_off[n_faults + 1] and the clbits of every fault back to back (ascending inside a
+ * list) into entries[entries_cap]; raw_total / diff_total (may be NULL) receive the entry counts
+ * of the two bases, whose comparison decides which one a sampler uses.  expect_short selects the
+ * one-pass extraction the planners use for the time-difference lists (same result). */
+int qec_planner_signature_lists(const uint32_t *bits, int nc, int64_t n_faults,
+                                const int32_t *pred, int diff_basis, int expect_short,
+                                int64_t *list_off, uint16_t *entries, int64_t entries_cap,
+                                int64_t *raw_total, int64_t *diff_total);
+
 #ifdef __cplusplus
 }
 #endif

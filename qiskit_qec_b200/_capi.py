@@ -40,7 +40,7 @@ SYMBOLS = [
     "qec_minimum_distance", "qec_minimum_distance_by_tests", "qec_sampler_sample_events24", "qec_sampler_sample_events16",
     "qec_dev_alloc", "qec_dev_free", "qec_dev_memset", "qec_dev_to_host", "qec_host_to_dev",
     "qec_host_alloc_pinned", "qec_host_free_pinned", "qec_stream_sync", "qec_last_kernel_ms",
-    "qec_last_kernel", "qec_jit_compile_to_file",
+    "qec_last_kernel", "qec_jit_compile_to_file", "qec_planner_signature_lists",
 ]
 
 _lib = None
@@ -126,6 +126,24 @@ def jit_compile_to_file(nq: int, nc: int, encoded_circ, loc_op, kind: int, order
         _p(loc), C.c_int(kind), C.c_int(order), C.c_int(int(tally)), C.c_int(int(bits)),
         C.c_int(threads), C.c_int(min_blocks), C.c_int(group), cubin_path.encode(),
         source_path.encode()))
+
+
+def planner_signature_lists(bits: np.ndarray, n_faults: int, pred=None, diff_basis: bool = False,
+                            expect_short: bool = False):
+    """The planners' host step on single-fault signatures ``bits[nc][ceil(n_faults / 32)]`` (no GPU
+    needed): (list_off int64[n_faults + 1], entries uint16[...], raw_total, diff_total)."""
+    bits = np.ascontiguousarray(bits, dtype=np.uint32)
+    nc = bits.shape[0]
+    assert bits.shape[1] == (n_faults + 31) // 32
+    pr = None if pred is None else _i32(pred)
+    off = np.zeros(n_faults + 1, dtype=np.int64)
+    cap = max(1, int(nc) * int(n_faults))
+    ent = np.zeros(cap, dtype=np.uint16)
+    raw, dif = C.c_int64(), C.c_int64()
+    _check(lib().qec_planner_signature_lists(_p(bits), C.c_int(nc), C.c_int64(n_faults), _p(pr),
+                                             C.c_int(int(diff_basis)), C.c_int(int(expect_short)),
+                                             _p(off), _p(ent), C.c_int64(cap), C.byref(raw), C.byref(dif)))
+    return off, ent[:off[-1]], raw.value, dif.value
 
 
 def rows_to_csr(encoded_circ: Sequence[Sequence[int]]) -> Tuple[np.ndarray, np.ndarray]:

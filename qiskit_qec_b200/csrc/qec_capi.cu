@@ -2755,6 +2755,42 @@ extern "C" int qec_stream_sync(int device, void *stream) {
   return 0;
 }
 
+// ---- diagnostics: the planners' host step on caller-given signatures (no device) -------------------
+// What enum_plan_linear / sampler_plan_linear do between the single-fault propagation and the
+// record tables: count the raw entries, change to the time-difference basis on the bit-sliced
+// rows, extract the per-fault lists of one basis.  The CPU tests pin it against numpy.
+extern "C" int qec_planner_signature_lists(const uint32_t *bits, int nc, int64_t n_faults,
+                                           const int32_t *pred, int diff_basis, int expect_short,
+                                           int64_t *list_off, uint16_t *entries, int64_t entries_cap,
+                                           int64_t *raw_total, int64_t *diff_total) {
+  if (nc < 1 || nc > 65535 || n_faults < 1) return fail(QEC_ERR_INVALID, "bad sizes");
+  if (!bits || !list_off || (!entries && entries_cap > 0)) return fail(QEC_ERR_INVALID, "null pointer");
+  const int64_t FW = (n_faults + 31) / 32;
+  std::vector<uint32_t> rows(bits, bits + (size_t)nc * FW);
+  if (n_faults & 31)  // (bits past the last fault do not belong to any list)
+    for (int cb = 0; cb < nc; ++cb) rows[(size_t)cb * FW + FW - 1] &= (1u << (n_faults & 31)) - 1u;
+  std::vector<int> pr(nc, -1);
+  if (pred)
+    for (int cb = 0; cb < nc; ++cb) {
+      if (pred[cb] >= nc) return fail(QEC_ERR_INVALID, "pred[%d] out of range", cb);
+      pr[cb] = pred[cb] < 0 ? -1 : pred[cb];
+    }
+  const std::vector<uint32_t> drows = diff_bits(rows, nc, FW, pr);
+  if (raw_total) *raw_total = (int64_t)count_bits(rows);
+  if (diff_total) *diff_total = (int64_t)count_bits(drows);
+  SigArena arena;
+  SigLists lists((size_t)n_faults);
+  lists_from_bits(diff_basis ? drows : rows, nc, FW, n_faults, arena, lists, expect_short != 0);
+  int64_t o = 0;
+  for (int64_t f = 0; f < n_faults; ++f) {
+    list_off[f] = o;
+    if (o + (int64_t)lists[(size_t)f].size() > entries_cap) return fail(QEC_ERR_LIMIT, "entry buffer too small");
+    for (uint16_t cb : lists[(size_t)f]) entries[o++] = cb;
+  }
+  list_off[n_faults] = o;
+  return 0;
+}
+
 // ---- diagnostics: the specialised kernel of a circuit, compiled without a device -----------------
 extern "C" int qec_jit_compile_to_file(int nq, int nc, int n_ops, const int32_t *row_off,
                                        const int32_t *row_data, int L, const int32_t *loc_op,

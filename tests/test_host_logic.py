@@ -156,3 +156,60 @@ def test_rows_to_csr_and_the_csr_form_of_a_circuit():
                 (np.array([0, 3, 2, 3], np.int32), np.zeros(3, np.int32))):  # decreasing
         with pytest.raises(ValueError):
             _capi.Circuit(2, 2, bad)
+
+
+def _pack_columns(m):
+    """bool [nc][F] -> uint32 [nc][ceil(F / 32)], fault f in bit f % 32 of word f // 32"""
+    nc, F = m.shape
+    fw = (F + 31) // 32
+    pad = np.zeros((nc, fw * 32), dtype=np.uint32)
+    pad[:, :F] = m
+    return (pad.reshape(nc, fw, 32) << np.arange(32, dtype=np.uint32)).sum(axis=2, dtype=np.uint64).astype(np.uint32)
+
+
+@pytest.mark.parametrize("seed,nc,F,density", [(1, 1, 1, 0.5), (2, 7, 127, 0.3), (3, 145, 6601, 0.04),
+                                               (4, 200, 1000, 0.5), (5, 33, 32, 0.1), (6, 64, 4097, 0.01)])
+def test_planner_signature_lists_match_numpy(seed, nc, F, density):
+    """The host step of the linear-response planners (time-difference basis on the bit-sliced
+    rows, list extraction in one or two passes) against a direct numpy statement of it."""
+    from qiskit_qec_b200 import _capi
+    rng = np.random.default_rng(seed)
+    m = rng.random((nc, F)) < density
+    # chains of "the same qubit measured again": every clbit has at most one successor
+    pred = np.full(nc, -1, dtype=np.int32)
+    step = max(1, nc // 6)
+    for c in range(step, nc):
+        if rng.random() < 0.8:
+            pred[c] = c - step
+    bits = _pack_columns(m)
+    # stray bits past the last fault must not reach any list
+    if F % 32:
+        bits[:, -1] |= np.uint32((0xFFFFFFFF << (F % 32)) & 0xFFFFFFFF)
+    d = m.copy()
+    has = pred >= 0
+    d[has] ^= m[pred[has]]
+    for diff, want in ((False, m), (True, d)):
+        for short in (False, True):
+            off, ent, raw, dif = _capi.planner_signature_lists(bits, F, pred, diff, short)
+            assert raw == int(m.sum()) and dif == int(d.sum())
+            assert off[0] == 0 and off[-1] == int(want.sum()) == len(ent)
+            cols = [np.nonzero(want[:, f])[0] for f in range(F)]
+            np.testing.assert_array_equal(np.diff(off), [len(c) for c in cols])
+            np.testing.assert_array_equal(ent, np.concatenate(cols) if len(ent) else np.zeros(0, np.uint16))
+
+
+def test_planner_time_difference_basis_shortens_repeated_stabiliser_flips():
+    """A fault that flips a stabiliser flips every later measurement of it: raw lists grow with
+    the rounds, the time-difference lists stay at one entry."""
+    from qiskit_qec_b200 import _capi
+    rounds, stabs = 5, 4
+    nc = rounds * stabs
+    pred = np.array([c - stabs if c >= stabs else -1 for c in range(nc)], dtype=np.int32)
+    m = np.zeros((nc, rounds * stabs), dtype=bool)       # fault f = (round r, stabiliser s)
+    for r in range(rounds):
+        for s_ in range(stabs):
+            m[[q * stabs + s_ for q in range(r, rounds)], r * stabs + s_] = True
+    off, ent, raw, dif = _capi.planner_signature_lists(_pack_columns(m), m.shape[1], pred, True, True)
+    assert raw == stabs * sum(range(1, rounds + 1)) and dif == rounds * stabs
+    np.testing.assert_array_equal(np.diff(off), np.ones(rounds * stabs, dtype=np.int64))
+    np.testing.assert_array_equal(ent, np.arange(nc))
