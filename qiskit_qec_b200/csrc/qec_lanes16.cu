@@ -54,9 +54,6 @@ __device__ __forceinline__ uint32_t l16_ldh(uint32_t addr) {
   asm volatile("{ .reg .u16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(addr) : "memory");
   return v;
 }
-__device__ __forceinline__ void l16_sth(uint32_t addr, uint32_t v) {
-  asm volatile("{ .reg .u16 t; cvt.u16.u32 t, %1; st.shared.u16 [%0], t; }" ::"r"(addr), "r"(v) : "memory");
-}
 __device__ __forceinline__ void l16_red_add(uint32_t addr, uint32_t v) {
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
