@@ -177,6 +177,7 @@ class ClockSampler:
 # ---------------------------------------------------------------------------- our arm
 def run_ours(args):
     import torch
+    import gc
     import torch.distributed as dist
     import numpy as np
 
@@ -327,6 +328,11 @@ def run_ours(args):
 
     def timed_e2e(fn, steps):
         warm = settle(fn)
+        # host-timed steps: keep the cyclic collector out of them, as timeit does (a generation-2
+        # pass of a process with torch loaded takes tens of ms -- several 4 ms steps)
+        gc.collect()
+        gc_was = gc.isenabled()
+        gc.disable()
         if world > 1:
             dist.barrier()
         t0 = time.perf_counter()
@@ -335,7 +341,10 @@ def run_ours(args):
             ts = time.perf_counter()
             fn(1 + i)
             times.append(time.perf_counter() - ts)
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        elapsed = time.perf_counter() - t0
+        if gc_was:
+            gc.enable()
+        t = torch.tensor([elapsed], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return world * n_shots * steps / float(t.item()), times, warm
